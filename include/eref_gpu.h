@@ -1,0 +1,106 @@
+/*
+ * eref_gpu.h — C ABI of liberef_gpu.so: the B200 (sm_100a) implementation of PALACE's `eref`
+ * k-mer reference-identification step.
+ *
+ * The reference has no library/FFI boundary for this path: `eref` is a process
+ * (bin/extract_ref.cpp:1210-1334, called by palace:475-477).  The drop-in is therefore the `eref`
+ * executable built from palace_b200/csrc/eref_main.cpp, and THIS header is the one thin layer
+ * between that host code (or any other host: ctypes, cgo, JNI ...) and the CUDA kernels.
+ * Each entry point names the reference code it replaces.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * error code (message via eref_last_error()); no C++ types or exceptions cross the boundary; the
+ * caller owns host buffers, the context owns device memory; one context = one GPU; calls on one
+ * context come from one thread at a time.  There is NO CPU fallback: without a CUDA device every
+ * compute entry point fails with EREF_ERR_CUDA.
+ */
+#ifndef EREF_GPU_H
+#define EREF_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EREF_K 32                      /* bin/extract_ref.cpp:24 */
+#define EREF_OK 0
+#define EREF_ERR_ARG   (-1)
+#define EREF_ERR_CUDA  (-2)
+#define EREF_ERR_STATE (-3)
+#define EREF_ERR_LIMIT (-4)            /* input beyond an implementation limit (e.g. FASTA shard >= 4 GiB) */
+#define EREF_ERR_UNSUPPORTED (-5)      /* reference behaviour not implemented yet: fails loudly */
+
+/* eref_create flags */
+#define EREF_FLAG_NO_PRUNE 1u          /* probe all three streams at every position (no candidate filter) */
+
+typedef struct eref_ctx eref_ctx;
+
+/* One record per kept reference (len > 32), ordinal order — the numbers of the stdout line at :617 */
+typedef struct {
+    uint32_t ordinal;                  /* 1-based, only records with len > 32 count (:887, :1175) */
+    uint32_t frag;                     /* frag_index (:509) */
+    uint32_t el;                       /* covered length (:611-614) */
+    uint32_t ref_len;                  /* record length (:694) */
+} eref_result;
+
+/* CUDA-event times of the last call of each phase, in milliseconds, and launch counts */
+typedef struct {
+    float query_h2d_ms, query_pack_ms, query_count_ms;      /* last eref_query_add* */
+    float ref_h2d_ms, ref_frame_ms, ref_pack_ms;            /* last eref_ref_set*   */
+    float scan_sample_ms, scan_cand_ms, scan_probe_ms, scan_window_ms, scan_interval_ms, scan_d2h_ms;
+    uint64_t kernel_launches;                               /* since eref_create */
+    uint64_t ref_bases, ref_words, ref_need_words;          /* last scan */
+    uint64_t query_seq_bytes;                               /* last eref_query_add* (cal_sam_ratio's sum) */
+} eref_phase_times;
+
+const char* eref_last_error(void);
+int  eref_device_count(void);
+
+/* replaces generate_coder/generate_base/generate_complement + saved_random_coder state
+ * (:1216-1218, :1258) and the argv ratios (:1228-1229).  coder = 96 entries in {0,1,2}:
+ * coder[z*3+i] is the 1-bit alphabet used at window position z by code stream i (:972). */
+int  eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_ratio,
+                 float perfect_hit_ratio, unsigned flags);
+void eref_destroy(eref_ctx* ctx);
+/* run all work of this context on an existing CUDA stream (cudaStream_t); NULL = context's own */
+int  eref_set_stream(eref_ctx* ctx, void* cuda_stream);
+
+/* memset(kmer_count_table) at :1257 */
+int  eref_query_reset(eref_ctx* ctx);
+/* read_fastq at one thread (:905-1008) over one whole FASTQ file: frames lines (index%4==1),
+ * forms the three canonical codes of every valid 32-mer and counts them, saturating at 3. */
+int  eref_query_add(eref_ctx* ctx, const char* fastq_host, size_t n);
+int  eref_query_add_device(eref_ctx* ctx, const void* fastq_dev, size_t n);
+/* cal_sam_ratio's sum (:1133-1142) for the file of the last eref_query_add* call */
+int  eref_query_seq_bytes(eref_ctx* ctx, uint64_t* out);
+
+/* read_ref's framing (:686-805) over one FASTA text (whole DB or one shard starting at a '>' line):
+ * records, lengths, drop len <= 32, ordinals; packs the kept records into HBM. */
+int  eref_ref_set(eref_ctx* ctx, const char* fasta_host, size_t n);
+int  eref_ref_set_device(eref_ctx* ctx, const void* fasta_dev, size_t n);
+int  eref_ref_count(eref_ctx* ctx, size_t* n_kept, size_t* n_records, uint64_t* kept_bases);
+
+/* read_index + slide_window (:813-903, :504-624) for every kept record of the current reference
+ * against the current table.  Writes min(cap, n_kept) records; *n_out = n_kept. */
+int  eref_scan(eref_ctx* ctx, eref_result* out, size_t cap, size_t* n_out);
+/* same, results left on the device as n_kept x 4 uint32 (for an NCCL allgather by the caller) */
+int  eref_scan_device(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out);
+
+/* the per-record body of <db>.k32.index.dat (:711-738): (len-31)*3 codes, 0 = invalid window.
+ * ordinal is 1-based within the current reference text.  Test hook and index writer (f2). */
+int  eref_get_codes(eref_ctx* ctx, uint32_t ordinal, uint32_t* codes_host, size_t cap, size_t* n_out);
+/* name offset/length of a kept record's header line inside the text given to eref_ref_set* */
+int  eref_ref_record(eref_ctx* ctx, uint32_t ordinal, uint64_t* hdr_off, uint32_t* hdr_len, uint32_t* len);
+
+/* table inspection (tests): number of codes with count >= level (1..3) */
+int  eref_query_popcount(eref_ctx* ctx, int level, uint64_t* out);
+
+int  eref_timings(eref_ctx* ctx, eref_phase_times* out);
+
+/* the stdout line of :615-617; returns bytes written, 0 if the record is not selected */
+int  eref_format_line(const eref_result* r, char* buf, size_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,555 @@
+// api.cu — the C ABI of liberef_gpu.so (include/eref_gpu.h): context, workspaces, phase ordering.
+// Prefix sums over tile/line/record tables use cub::DeviceScan (CUDA toolkit); every kernel that
+// touches sequence data is hand-written in frame.cu / table.cu / scan.cu.
+#include "eref_internal.cuh"
+#include <cub/device/device_scan.cuh>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include <new>
+
+namespace {
+thread_local char g_err[512] = "";
+}
+
+int eref_fail(int code, const char* fmt, ...)
+{
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int eref_fail_cuda(cudaError_t e, const char* what, const char* file, int line)
+{
+    snprintf(g_err, sizeof g_err, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    return EREF_ERR_CUDA;
+}
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, EV_COUNT };
+
+} // namespace
+
+struct eref_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    CoderMasks masks{};
+    float hit_ratio = 0, perfect_hit_ratio = 0;
+    int one_min = 0, three_min = 0;
+    unsigned flags = 0;
+    cudaEvent_t ev[EV_COUNT]{};
+    // query table: level L bitmap = "code seen >= L times"
+    uint32_t* bm[3] = {nullptr, nullptr, nullptr};
+    // shared scratch
+    DevBuf tile_counts, tile_prefix, cub_tmp, counters;      // counters: 4 x u64
+    // query side
+    DevBuf q_text, q_hi, q_lo, q_ok;
+    // reference side
+    DevBuf r_text, nl_pos, line_val, line_cum, rec_hdr_line, rec_first, rec_len, rec_kept, rec_words,
+        rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
+        sample_hits, cand, need, single, trio, good, results, codes_tmp;
+    const uint8_t* ref_text_dev = nullptr;    // where the current reference text lives
+    uint64_t ref_text_n = 0;
+    bool have_ref = false;
+    uint32_t n_nl = 0, n_lines = 0, n_recs = 0, n_genomes = 0;
+    uint64_t ref_words = 0, ref_bases = 0;
+    std::vector<uint32_t> h_g_len, h_g_word, h_g_rec, h_rec_hdr_line;
+    std::vector<uint32_t> h_nl_hdr;           // unused placeholder for future name lookups
+    eref_phase_times t{};
+    uint64_t launches = 0;
+};
+
+namespace {
+
+#define LAUNCH(ctx, expr)                                                                  \
+    do {                                                                                   \
+        (ctx)->launches++;                                                                 \
+        CUDA_TRY(expr);                                                                    \
+    } while (0)
+
+template <class T>
+int exclusive_scan(eref_ctx* c, const T* in, T* out, size_t n)
+{
+    size_t bytes = 0;
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, (int)n, c->stream));
+    CUDA_TRY(c->cub_tmp.ensure(bytes));
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, bytes, in, out, (int)n, c->stream));
+    return 0;
+}
+
+float ev_ms(eref_ctx* c, int a, int b)
+{
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]);
+    return ms;
+}
+
+// newline census of a text: tile_prefix[t] = newlines before tile t, tile_prefix[ntiles] = total
+int newline_census(eref_ctx* c, const uint8_t* text, uint64_t n, uint64_t* ntiles_out)
+{
+    uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
+    if (ntiles >= (1ull << 31)) return eref_fail(EREF_ERR_LIMIT, "text of %llu bytes has too many tiles", (unsigned long long)n);
+    CUDA_TRY(c->tile_counts.ensure((ntiles + 1) * 4));
+    CUDA_TRY(c->tile_prefix.ensure((ntiles + 1) * 4));
+    CUDA_TRY(cudaMemsetAsync(c->tile_counts.as<uint32_t>() + ntiles, 0, 4, c->stream));
+    LAUNCH(c, launch_count_newlines(text, n, c->tile_counts.as<uint32_t>(), ntiles, c->stream));
+    int rc = exclusive_scan<uint32_t>(c, c->tile_counts.as<uint32_t>(), c->tile_prefix.as<uint32_t>(), ntiles + 1);
+    if (rc) return rc;
+    *ntiles_out = ntiles;
+    return 0;
+}
+
+int check_text_ptr(const void* p, size_t n)
+{
+    if (n && !p) return eref_fail(EREF_ERR_ARG, "null text pointer with n=%zu", n);
+    if (((uintptr_t)p & 15) != 0) return eref_fail(EREF_ERR_ARG, "device text must be 16-byte aligned");
+    return 0;
+}
+
+int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
+{
+    cudaStream_t st = c->stream;
+    CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+    uint64_t ntiles = 0;
+    int rc = newline_census(c, text, n, &ntiles);
+    if (rc) return rc;
+    Planes pl;
+    pl.nwords = (n + 31) / 32;
+    CUDA_TRY(c->q_hi.ensure((pl.nwords + 1) * 4));
+    CUDA_TRY(c->q_lo.ensure((pl.nwords + 1) * 4));
+    CUDA_TRY(c->q_ok.ensure((pl.nwords + 1) * 4));
+    pl.hi = c->q_hi.as<uint32_t>(); pl.lo = c->q_lo.as<uint32_t>(); pl.ok = c->q_ok.as<uint32_t>();
+    CUDA_TRY(cudaMemsetAsync(pl.hi + pl.nwords, 0, 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.lo + pl.nwords, 0, 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.ok + pl.nwords, 0, 4, st));
+    unsigned long long* seq_bytes = c->counters.as<unsigned long long>();
+    CUDA_TRY(cudaMemsetAsync(seq_bytes, 0, 8, st));
+    LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), pl, seq_bytes, st));
+    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+    LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
+    CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+    unsigned long long h = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    c->t.query_seq_bytes = h;
+    c->t.query_h2d_ms = ev_ms(c, E0, E1);
+    c->t.query_pack_ms = ev_ms(c, E1, E2);
+    c->t.query_count_ms = ev_ms(c, E2, E3);
+    return 0;
+}
+
+int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
+{
+    cudaStream_t st = c->stream;
+    c->have_ref = false;
+    if (n >= 0xFFFFFF00ull)
+        return eref_fail(EREF_ERR_LIMIT, "reference text of %llu bytes: one shard must stay below 4 GiB",
+                         (unsigned long long)n);
+    CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+    // 1. newline positions
+    uint64_t ntiles = 0;
+    int rc = newline_census(c, text, n, &ntiles);
+    if (rc) return rc;
+    uint32_t n_nl = 0;
+    CUDA_TRY(cudaMemcpyAsync(&n_nl, c->tile_prefix.as<uint32_t>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const uint32_t n_lines = n_nl + 1;             // the last line may be empty: it then adds nothing
+    CUDA_TRY(c->nl_pos.ensure(((size_t)n_nl + 1) * 4));
+    CUDA_TRY(c->line_val.ensure(((size_t)n_lines + 1) * 8));
+    CUDA_TRY(c->line_cum.ensure(((size_t)n_lines + 1) * 8));
+    LAUNCH(c, launch_write_newlines(text, n, c->tile_prefix.as<uint32_t>(), c->nl_pos.as<uint32_t>(), ntiles, st));
+    // 2. per-line (header flag, sequence bytes) and their running sums
+    LAUNCH(c, launch_line_info(text, n, c->nl_pos.as<uint32_t>(), n_nl, n_lines, c->line_val.as<uint64_t>(), st));
+    rc = exclusive_scan<uint64_t>(c, c->line_val.as<uint64_t>(), c->line_cum.as<uint64_t>(), (size_t)n_lines + 1);
+    if (rc) return rc;
+    uint64_t totals = 0;
+    CUDA_TRY(cudaMemcpyAsync(&totals, c->line_cum.as<uint64_t>() + n_lines, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const uint32_t n_recs = (uint32_t)(totals >> 40) + 1;
+    const uint64_t total_seq = totals & ((1ull << 40) - 1);
+    // 3. records: first sequence byte, length, keep flag, packed size
+    const size_t rn = (size_t)n_recs + 1;
+    CUDA_TRY(c->rec_hdr_line.ensure(rn * 4)); CUDA_TRY(c->rec_first.ensure(rn * 4));
+    CUDA_TRY(c->rec_len.ensure(rn * 4)); CUDA_TRY(c->rec_kept.ensure(rn * 4));
+    CUDA_TRY(c->rec_words.ensure(rn * 4)); CUDA_TRY(c->rec_kept_ex.ensure(rn * 4));
+    CUDA_TRY(c->rec_words_ex.ensure(rn * 4));
+    LAUNCH(c, launch_record_starts(c->line_val.as<uint64_t>(), c->line_cum.as<uint64_t>(), n_lines,
+                                   c->rec_hdr_line.as<uint32_t>(), c->rec_first.as<uint32_t>(), st));
+    LAUNCH(c, launch_record_info(c->rec_first.as<uint32_t>(), n_recs, total_seq, c->rec_len.as<uint32_t>(),
+                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(), st));
+    rc = exclusive_scan<uint32_t>(c, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(), rn);
+    if (rc) return rc;
+    rc = exclusive_scan<uint32_t>(c, c->rec_words.as<uint32_t>(), c->rec_words_ex.as<uint32_t>(), rn);
+    if (rc) return rc;
+    uint32_t n_genomes = 0, n_words = 0;
+    CUDA_TRY(cudaMemcpyAsync(&n_genomes, c->rec_kept_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(&n_words, c->rec_words_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+    // 4. genome table + packed planes
+    const size_t gn = (size_t)n_genomes + 1;
+    CUDA_TRY(c->g_rec.ensure(gn * 4)); CUDA_TRY(c->g_len.ensure(gn * 4));
+    CUDA_TRY(c->g_word.ensure(gn * 4)); CUDA_TRY(c->g_first.ensure(gn * 4));
+    LAUNCH(c, launch_genome_table(c->rec_len.as<uint32_t>(), c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(),
+                                  c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(),
+                                  c->rec_hdr_line.as<uint32_t>(), n_recs, c->g_rec.as<uint32_t>(),
+                                  c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_first.as<uint32_t>(), st));
+    Planes pl;
+    pl.nwords = n_words;
+    CUDA_TRY(c->r_hi.ensure(((size_t)n_words + 1) * 4));
+    CUDA_TRY(c->r_lo.ensure(((size_t)n_words + 1) * 4));
+    CUDA_TRY(c->r_ok.ensure(((size_t)n_words + 1) * 4));
+    CUDA_TRY(c->word_genome.ensure(((size_t)n_words + 1) * 4));
+    pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
+    CUDA_TRY(cudaMemsetAsync(pl.hi + n_words, 0, 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.lo + n_words, 0, 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.ok + n_words, 0, 4, st));
+    if (n_genomes)
+        LAUNCH(c, launch_pack_fasta(text, n, c->nl_pos.as<uint32_t>(), n_nl, c->line_cum.as<uint64_t>(), n_lines,
+                                    c->rec_hdr_line.as<uint32_t>(), n_recs, c->g_rec.as<uint32_t>(),
+                                    c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_first.as<uint32_t>(),
+                                    n_genomes, pl, c->word_genome.as<uint32_t>(), st));
+    CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+    // host copies of the small tables (ordinal -> length / packed offset / header line)
+    c->h_g_len.assign(gn, 0); c->h_g_word.assign(gn, 0); c->h_g_rec.assign(gn, 0);
+    c->h_rec_hdr_line.assign(rn, 0);
+    if (n_genomes) {
+        CUDA_TRY(cudaMemcpyAsync(c->h_g_len.data(), c->g_len.p, (size_t)n_genomes * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_g_word.data(), c->g_word.p, gn * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_g_rec.data(), c->g_rec.p, (size_t)n_genomes * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->h_rec_hdr_line.data(), c->rec_hdr_line.p, (size_t)n_recs * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    uint64_t bases = 0;
+    for (uint32_t g = 0; g < n_genomes; g++) bases += c->h_g_len[g];
+    c->ref_text_dev = text; c->ref_text_n = n;
+    c->n_nl = n_nl; c->n_lines = n_lines; c->n_recs = n_recs; c->n_genomes = n_genomes;
+    c->ref_words = n_words; c->ref_bases = bases;
+    c->have_ref = true;
+    c->t.ref_h2d_ms = ev_ms(c, E0, E1);
+    c->t.ref_frame_ms = ev_ms(c, E1, E2);
+    c->t.ref_pack_ms = ev_ms(c, E2, E3);
+    c->t.ref_bases = bases; c->t.ref_words = n_words;
+    return 0;
+}
+
+int scan_impl(eref_ctx* c)
+{
+    if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "eref_scan before eref_ref_set");
+    cudaStream_t st = c->stream;
+    const uint64_t nw = c->ref_words;
+    const uint32_t G = c->n_genomes;
+    Planes pl;
+    pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
+    pl.nwords = nw;
+    CUDA_TRY(c->single.ensure((nw + 1) * 4)); CUDA_TRY(c->trio.ensure((nw + 1) * 4));
+    CUDA_TRY(c->good.ensure((nw + 1) * 4));
+    CUDA_TRY(c->results.ensure(((size_t)G + 1) * 16));
+    const int min_sample_hits = c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE);
+    const bool prune = !(c->flags & EREF_FLAG_NO_PRUNE) && min_sample_hits > 0;
+    const uint8_t* need = nullptr;
+    unsigned long long* need_count = c->counters.as<unsigned long long>() + 1;
+    CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+    if (prune) {
+        CUDA_TRY(c->sample_hits.ensure(nw + 1)); CUDA_TRY(c->cand.ensure(nw + 1)); CUDA_TRY(c->need.ensure(nw + 1));
+        CUDA_TRY(cudaMemsetAsync(need_count, 0, 8, st));
+        LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->sample_hits.as<uint8_t>(), st));
+        CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+        LAUNCH(c, launch_candidates(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(),
+                                    c->g_word.as<uint32_t>(), nw, min_sample_hits, c->cand.as<uint8_t>(), st));
+        LAUNCH(c, launch_need(c->cand.as<uint8_t>(), c->word_genome.as<uint32_t>(), nw, c->need.as<uint8_t>(),
+                              need_count, st));
+        need = c->need.as<uint8_t>();
+    } else {
+        CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+    LAUNCH(c, launch_probe_full(pl, c->masks, c->bm[2], need, c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
+    CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+    LAUNCH(c, launch_window(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), need, c->word_genome.as<uint32_t>(),
+                            c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), nw, c->one_min, c->three_min,
+                            c->good.as<uint32_t>(), st));
+    CUDA_TRY(cudaEventRecord(c->ev[E4], st));
+    LAUNCH(c, launch_intervals(c->good.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), G,
+                               c->results.as<uint32_t>(), st));
+    CUDA_TRY(cudaEventRecord(c->ev[E5], st));
+    return 0;
+}
+
+void scan_times(eref_ctx* c, bool with_d2h)
+{
+    c->t.scan_sample_ms = ev_ms(c, E0, E1);
+    c->t.scan_cand_ms = ev_ms(c, E1, E2);
+    c->t.scan_probe_ms = ev_ms(c, E2, E3);
+    c->t.scan_window_ms = ev_ms(c, E3, E4);
+    c->t.scan_interval_ms = ev_ms(c, E4, E5);
+    c->t.scan_d2h_ms = with_d2h ? ev_ms(c, E5, E6) : 0.f;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* eref_last_error(void) { return g_err; }
+
+int eref_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_ratio, float perfect_hit_ratio,
+                unsigned flags)
+{
+    if (!out || !coder) return eref_fail(EREF_ERR_ARG, "eref_create: null argument");
+    *out = nullptr;
+    CoderMasks m{};
+    for (int z = 0; z < EREF_K; z++)
+        for (int i = 0; i < 3; i++) {
+            int a = coder[z * 3 + i];
+            if (a < 0 || a > 2)
+                return eref_fail(EREF_ERR_ARG, "coder[%d] = %d is not one of the three 1-bit alphabets", z * 3 + i, a);
+            if (a == 0) m.sel0[i] |= 1u << (EREF_K - 1 - z);
+            if (a == 2) m.sel2[i] |= 1u << (EREF_K - 1 - z);
+        }
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return eref_fail(EREF_ERR_ARG, "device %d of %d", device, ndev);
+    CUDA_TRY(cudaSetDevice(device));
+    eref_ctx* c = new (std::nothrow) eref_ctx();
+    if (!c) return eref_fail(EREF_ERR_ARG, "out of host memory");
+    c->device = device; c->masks = m; c->flags = flags;
+    c->hit_ratio = hit_ratio; c->perfect_hit_ratio = perfect_hit_ratio;
+    c->one_min = (int)(WINDOW * hit_ratio);              // :513 — int * float, truncated
+    c->three_min = (int)(WINDOW * perfect_hit_ratio);    // :514
+    cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
+    for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
+    if (e == cudaSuccess) e = c->counters.ensure(64);
+    if (e != cudaSuccess) { eref_destroy(c); return eref_fail_cuda(e, "context allocation", __FILE__, __LINE__); }
+    c->stream = c->own_stream;
+    *out = c;
+    int rc = eref_query_reset(c);
+    if (rc) { eref_destroy(c); *out = nullptr; }
+    return rc;
+}
+
+void eref_destroy(eref_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->q_text, &c->q_hi, &c->q_lo,
+                      &c->q_ok, &c->r_text, &c->nl_pos, &c->line_val, &c->line_cum, &c->rec_hdr_line, &c->rec_first,
+                      &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
+                      &c->g_len, &c->g_word, &c->g_first, &c->r_hi, &c->r_lo, &c->r_ok, &c->word_genome,
+                      &c->sample_hits, &c->cand, &c->need, &c->single, &c->trio, &c->good, &c->results,
+                      &c->codes_tmp};
+    for (DevBuf* b : bufs) b->release();
+    for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
+    for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+int eref_set_stream(eref_ctx* c, void* cuda_stream)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return 0;
+}
+
+int eref_query_reset(eref_ctx* c)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    CUDA_TRY(cudaSetDevice(c->device));
+    for (int l = 0; l < 3; l++) CUDA_TRY(cudaMemsetAsync(c->bm[l], 0, (size_t)TABLE_WORDS * 4, c->stream));
+    return 0;
+}
+
+int eref_query_add(eref_ctx* c, const char* fastq_host, size_t n)
+{
+    if (!c || (n && !fastq_host)) return eref_fail(EREF_ERR_ARG, "eref_query_add: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(c->q_text.ensure(n + 64));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
+    if (n) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fastq_host, n, cudaMemcpyHostToDevice, c->stream));
+    return query_add_impl(c, c->q_text.as<uint8_t>(), n);
+}
+
+int eref_query_add_device(eref_ctx* c, const void* fastq_dev, size_t n)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    int rc = check_text_ptr(fastq_dev, n);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
+    return query_add_impl(c, static_cast<const uint8_t*>(fastq_dev), n);
+}
+
+int eref_query_seq_bytes(eref_ctx* c, uint64_t* out)
+{
+    if (!c || !out) return eref_fail(EREF_ERR_ARG, "null argument");
+    *out = c->t.query_seq_bytes;
+    return 0;
+}
+
+int eref_ref_set(eref_ctx* c, const char* fasta_host, size_t n)
+{
+    if (!c || (n && !fasta_host)) return eref_fail(EREF_ERR_ARG, "eref_ref_set: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(c->r_text.ensure(n + 64));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
+    if (n) CUDA_TRY(cudaMemcpyAsync(c->r_text.p, fasta_host, n, cudaMemcpyHostToDevice, c->stream));
+    return ref_set_impl(c, c->r_text.as<uint8_t>(), n);
+}
+
+int eref_ref_set_device(eref_ctx* c, const void* fasta_dev, size_t n)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    int rc = check_text_ptr(fasta_dev, n);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
+    return ref_set_impl(c, static_cast<const uint8_t*>(fasta_dev), n);
+}
+
+int eref_ref_count(eref_ctx* c, size_t* n_kept, size_t* n_records, uint64_t* kept_bases)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
+    if (n_kept) *n_kept = c->n_genomes;
+    if (n_records) *n_records = c->n_recs;
+    if (kept_bases) *kept_bases = c->ref_bases;
+    return 0;
+}
+
+int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
+{
+    if (!c || (cap && !out)) return eref_fail(EREF_ERR_ARG, "eref_scan: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = scan_impl(c);
+    if (rc) return rc;
+    size_t n = c->n_genomes < cap ? c->n_genomes : cap;
+    if (n) CUDA_TRY(cudaMemcpyAsync(out, c->results.p, n * sizeof(eref_result), cudaMemcpyDeviceToHost, c->stream));
+    unsigned long long need_words = 0;
+    CUDA_TRY(cudaMemcpyAsync(&need_words, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaEventRecord(c->ev[E6], c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    scan_times(c, true);
+    const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE) > 0;
+    c->t.ref_need_words = pruned ? need_words : c->ref_words;
+    if (n_out) *n_out = c->n_genomes;
+    return 0;
+}
+
+int eref_scan_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
+{
+    if (!c || !results_dev) return eref_fail(EREF_ERR_ARG, "eref_scan_device: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = scan_impl(c);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    scan_times(c, false);
+    *results_dev = c->results.as<uint32_t>();
+    if (n_out) *n_out = c->n_genomes;
+    return 0;
+}
+
+int eref_get_codes(eref_ctx* c, uint32_t ordinal, uint32_t* codes_host, size_t cap, size_t* n_out)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
+    if (ordinal < 1 || ordinal > c->n_genomes) return eref_fail(EREF_ERR_ARG, "ordinal %u of %u", ordinal, c->n_genomes);
+    CUDA_TRY(cudaSetDevice(c->device));
+    const uint32_t len = c->h_g_len[ordinal - 1];
+    const size_t n = (size_t)(len - EREF_K + 1) * 3;
+    if (n_out) *n_out = n;
+    if (!codes_host || cap < n) return 0;
+    CUDA_TRY(c->codes_tmp.ensure(n * 4));
+    Planes pl;
+    pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
+    pl.nwords = c->ref_words;
+    LAUNCH(c, launch_record_codes(pl, c->masks, c->h_g_word[ordinal - 1], len, c->codes_tmp.as<uint32_t>(), c->stream));
+    CUDA_TRY(cudaMemcpyAsync(codes_host, c->codes_tmp.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int eref_ref_record(eref_ctx* c, uint32_t ordinal, uint64_t* hdr_off, uint32_t* hdr_len, uint32_t* len)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
+    if (ordinal < 1 || ordinal > c->n_genomes) return eref_fail(EREF_ERR_ARG, "ordinal %u of %u", ordinal, c->n_genomes);
+    CUDA_TRY(cudaSetDevice(c->device));
+    const uint32_t r = c->h_g_rec[ordinal - 1];
+    if (len) *len = c->h_g_len[ordinal - 1];
+    uint64_t off = 0; uint32_t hl = 0;
+    if (r > 0) {                                      // record 0 has no header line
+        const uint32_t line = c->h_rec_hdr_line[r];
+        uint32_t se[2] = {0, 0};
+        if (line > 0) CUDA_TRY(cudaMemcpy(&se[0], c->nl_pos.as<uint32_t>() + (line - 1), 4, cudaMemcpyDeviceToHost));
+        if (line < c->n_nl) CUDA_TRY(cudaMemcpy(&se[1], c->nl_pos.as<uint32_t>() + line, 4, cudaMemcpyDeviceToHost));
+        else se[1] = (uint32_t)c->ref_text_n;
+        off = line > 0 ? (uint64_t)se[0] + 1 : 0;
+        hl = (uint32_t)(se[1] - off);
+    }
+    if (hdr_off) *hdr_off = off;
+    if (hdr_len) *hdr_len = hl;
+    return 0;
+}
+
+int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
+{
+    if (!c || !out || level < 1 || level > 3) return eref_fail(EREF_ERR_ARG, "eref_query_popcount: bad argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    unsigned long long* ctr = c->counters.as<unsigned long long>() + 2;
+    CUDA_TRY(cudaMemsetAsync(ctr, 0, 8, c->stream));
+    LAUNCH(c, launch_popcount(c->bm[level - 1], TABLE_WORDS, ctr, c->stream));
+    unsigned long long h = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h, ctr, 8, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    *out = h;
+    return 0;
+}
+
+int eref_timings(eref_ctx* c, eref_phase_times* out)
+{
+    if (!c || !out) return eref_fail(EREF_ERR_ARG, "null argument");
+    *out = c->t;
+    out->kernel_launches = c->launches;
+    return 0;
+}
+
+int eref_format_line(const eref_result* r, char* buf, size_t cap)
+{
+    if (!r || !buf) return 0;
+    float ratio = (float)r->el / (float)r->ref_len;           // :615
+    if (!(r->el > 0 && ratio > 0.75)) return 0;               // :616
+    // :617 — ostream << float at default precision is printf %g
+    return snprintf(buf, cap, "ref_index\t%u\t%u\t%u\t%u\t%g\n", r->ordinal, r->frag, r->el, r->ref_len, (double)ratio);
+}
+
+} // extern "C"

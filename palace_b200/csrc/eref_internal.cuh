@@ -1,0 +1,144 @@
+// eref_internal.cuh — shared declarations of liberef_gpu.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/eref_gpu.h"
+
+// ---- layout constants ---------------------------------------------------------------------------
+// Text tiles: one CTA of 256 threads frames 8 KiB of text, 32 bytes per thread, so one thread owns
+// exactly one 32-position word of the bit-planes.
+constexpr int      TILE_THREADS = 256;
+constexpr int      TILE_BYTES   = TILE_THREADS * 32;
+constexpr uint32_t TABLE_WORDS  = 1u << 27;          // 2^32 one-bit slots per level (bin/extract_ref.cpp:25)
+constexpr int      WINDOW       = 500;               // :510
+constexpr int      WIN_WORDS    = 16;                // a 500-position window reaches back 16 words
+constexpr int      SAMPLE_STRIDE = 4;                // candidate filter probes every 4th position
+
+// Per-stream select masks of the coder assignment: bit (31-z) of sel0[i] (sel2[i]) is set iff code
+// stream i uses 1-bit alphabet 0 (2) at window position z; alphabet 1 everywhere else (:972).
+struct CoderMasks {
+    uint32_t sel0[3];
+    uint32_t sel2[3];
+};
+
+// Three bit-planes over a position space, MSB-first: position p lives in word p>>5, bit 31-(p&31).
+//   hi/lo : 2-bit base code A=00 C=01 G=10 T=11;  ok : 1 iff the byte is one of ACGTacgt (and, for
+//   FASTQ, lies on a sequence line).  One zero pad word follows the last word.
+struct Planes {
+    uint32_t* hi;
+    uint32_t* lo;
+    uint32_t* ok;
+    uint64_t  nwords;        // without the pad word
+};
+
+__device__ __forceinline__ uint32_t bitsel(uint32_t mask, uint32_t a, uint32_t b)
+{
+    return (a & mask) | (b & ~mask);                 // one LOP3
+}
+
+// Valid-window mask for the 32 window starts of one word: bit 31-s set iff ok bits s..s+31 of the
+// 64-bit string (ok0:ok1) are all ones, i.e. the 32-mer starting s positions into the word has no
+// invalid base (:978-982).
+__device__ __forceinline__ uint32_t valid_windows(uint32_t ok0, uint32_t ok1)
+{
+    uint64_t t = ((uint64_t)ok0 << 32) | ok1;
+    t &= t << 1; t &= t << 2; t &= t << 4; t &= t << 8; t &= t << 16;
+    return (uint32_t)(t >> 32);
+}
+
+// 32-position window starting s positions into (w0:w1), first position in the MSB.
+__device__ __forceinline__ uint32_t window32(uint32_t w0, uint32_t w1, int s)
+{
+    return __funnelshift_l(w1, w0, s);
+}
+
+// The canonical code of stream i for the window (hi, lo) — restates the z-loop of
+// bin/extract_ref.cpp:971-994 through bit-planes:
+//   alphabet0 = ~(hi^lo) (A,T->1), alphabet1 = ~hi (A,C->1), alphabet2 = ~lo (A,G->1);
+//   complementing a base keeps alphabet0 and flips alphabets 1 and 2, so the reverse-complement
+//   code is the same select over bit-reversed planes rh = brev(hi), rl = brev(lo):
+//   alphabet0' = ~(rh^rl), alphabet1' = rh, alphabet2' = rl.
+struct WindowBits {
+    uint32_t a0, a1, a2;     // forward alphabets
+    uint32_t r0, r1, r2;     // reverse-complement alphabets
+};
+
+__device__ __forceinline__ WindowBits window_bits(uint32_t hi, uint32_t lo)
+{
+    WindowBits b;
+    b.a0 = ~(hi ^ lo); b.a1 = ~hi; b.a2 = ~lo;
+    uint32_t rh = __brev(hi), rl = __brev(lo);
+    b.r0 = ~(rh ^ rl); b.r1 = rh; b.r2 = rl;
+    return b;
+}
+
+__device__ __forceinline__ uint32_t stream_code(const CoderMasks& m, const WindowBits& b, int i)
+{
+    uint32_t fwd = bitsel(m.sel2[i], b.a2, bitsel(m.sel0[i], b.a0, b.a1));
+    uint32_t rc  = bitsel(m.sel2[i], b.r2, bitsel(m.sel0[i], b.r0, b.r1));
+    return min(fwd, rc);                             // :989-994, unsigned compare
+}
+
+// byte -> (2-bit code, validity).  A=0x41 C=0x43 G=0x47 T=0x54 (and +0x20): bits 2..1 give
+// A=00 C=01 G=11 T=10; hi = bit2, lo = bit1 ^ bit2.
+__device__ __forceinline__ bool is_acgt(uint32_t c)
+{
+    uint32_t u = c & 0xDFu;
+    return u == 0x41u || u == 0x43u || u == 0x47u || u == 0x54u;
+}
+
+#define CUDA_TRY(expr)                                                                     \
+    do {                                                                                   \
+        cudaError_t e_ = (expr);                                                           \
+        if (e_ != cudaSuccess) return eref_fail_cuda(e_, #expr, __FILE__, __LINE__);       \
+    } while (0)
+
+int eref_fail_cuda(cudaError_t e, const char* what, const char* file, int line);
+int eref_fail(int code, const char* fmt, ...);
+
+// ---- kernel launchers (each returns a cudaError_t from the launch) ------------------------------
+// frame.cu
+cudaError_t launch_count_newlines(const uint8_t* text, uint64_t n, uint32_t* tile_counts,
+                                  uint64_t ntiles, cudaStream_t st);
+cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
+                              Planes pl, unsigned long long* seq_bytes, cudaStream_t st);
+cudaError_t launch_write_newlines(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
+                                  uint32_t* nl_pos, uint64_t ntiles, cudaStream_t st);
+cudaError_t launch_line_info(const uint8_t* text, uint64_t n, const uint32_t* nl_pos, uint32_t n_nl,
+                             uint32_t n_lines, uint64_t* line_val, cudaStream_t st);
+cudaError_t launch_record_starts(const uint64_t* line_val, const uint64_t* line_cum, uint32_t n_lines,
+                                 uint32_t* rec_hdr_line, uint32_t* rec_first, cudaStream_t st);
+cudaError_t launch_record_info(const uint32_t* rec_first, uint32_t n_recs, uint64_t total_seq,
+                               uint32_t* rec_len, uint32_t* rec_kept, uint32_t* rec_words, cudaStream_t st);
+cudaError_t launch_genome_table(const uint32_t* rec_len, const uint32_t* rec_kept,
+                                const uint32_t* rec_kept_ex, const uint32_t* rec_words_ex,
+                                const uint32_t* rec_first, const uint32_t* rec_hdr_line, uint32_t n_recs,
+                                uint32_t* g_rec, uint32_t* g_len, uint32_t* g_word, uint32_t* g_first,
+                                cudaStream_t st);
+cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const uint32_t* nl_pos, uint32_t n_nl,
+                              const uint64_t* line_cum, uint32_t n_lines, const uint32_t* rec_hdr_line,
+                              uint32_t n_recs, const uint32_t* g_rec, const uint32_t* g_len,
+                              const uint32_t* g_word, const uint32_t* g_first, uint32_t n_genomes,
+                              Planes pl, uint32_t* word_genome, cudaStream_t st);
+// table.cu
+cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
+                               cudaStream_t st);
+cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);
+// scan.cu
+cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, uint8_t* sample_hits,
+                                 cudaStream_t st);
+cudaError_t launch_candidates(const uint8_t* sample_hits, const uint32_t* word_genome,
+                              const uint32_t* g_word, uint64_t nwords, int min_sample_hits,
+                              uint8_t* cand, cudaStream_t st);
+cudaError_t launch_need(const uint8_t* cand, const uint32_t* word_genome, uint64_t nwords,
+                        uint8_t* need, unsigned long long* need_count, cudaStream_t st);
+cudaError_t launch_probe_full(Planes pl, CoderMasks m, const uint32_t* bm3, const uint8_t* need,
+                              uint32_t* single, uint32_t* trio, cudaStream_t st);
+cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint8_t* need,
+                          const uint32_t* word_genome, const uint32_t* g_word, const uint32_t* g_len,
+                          uint64_t nwords, int one_min, int three_min, uint32_t* good, cudaStream_t st);
+cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const uint32_t* g_len,
+                             uint32_t n_genomes, uint32_t* results, cudaStream_t st);
+cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,
+                                uint32_t* codes, cudaStream_t st);

@@ -1,0 +1,311 @@
+// eref_main.cpp — the drop-in `eref` executable for the PALACE pipeline (palace:475-477):
+//
+//   eref <fq1> <fq2> <phagedb.fasta> <interval_out> <hit_ratio> <perfect_hit_ratio> <threads>  > ref_names.txt
+//
+// Same seven positional arguments, same stdout lines and side-effect files as
+// bin/extract_ref.cpp:1210-1334; all sequence work runs on B200s through the C ABI of
+// liberef_gpu.so (include/eref_gpu.h).  There is no CPU path: without a GPU it exits non-zero.
+//
+// Environment (the palace call line stays unchanged):
+//   EREF_GPUS=N|all     GPUs to shard the database over (default: one per 128 MiB of FASTA, <= visible)
+//   EREF_CODER_SEED=S   seed of the coder draw when <db>.k32.index.dat does not exist (default time(0), :1088)
+//   EREF_NO_PRUNE=1     probe all three streams everywhere (disables the exact candidate filter)
+//   EREF_TIMING=1       per-phase CUDA-event times on stderr
+#include "eref_gpu.h"
+#include <cuda_runtime.h>
+#include <nccl.h>
+#include <algorithm>
+#include <atomic>
+#include <cerrno>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <ctime>
+#include <fstream>
+#include <iostream>
+#include <string>
+#include <thread>
+#include <vector>
+#include <condition_variable>
+#include <mutex>
+
+namespace {
+
+struct HostFile {                       // whole file in pinned host memory
+    char* p = nullptr;
+    size_t n = 0;
+    bool pinned = false;
+    ~HostFile() { if (p) { if (pinned) cudaFreeHost(p); else free(p); } }
+};
+
+bool read_file(const std::string& path, HostFile& f, std::string& err)
+{
+    FILE* fp = fopen(path.c_str(), "rb");
+    if (!fp) { err = "cannot open " + path + ": " + strerror(errno); return false; }
+    fseek(fp, 0, SEEK_END);
+    long sz = ftell(fp);
+    fseek(fp, 0, SEEK_SET);
+    if (sz < 0) { fclose(fp); err = "cannot size " + path; return false; }
+    f.n = (size_t)sz;
+    void* q = nullptr;
+    if (cudaHostAlloc(&q, f.n + 64, cudaHostAllocDefault) == cudaSuccess) { f.pinned = true; }
+    else { cudaGetLastError(); q = malloc(f.n + 64); }
+    if (!q) { fclose(fp); err = "out of memory reading " + path; return false; }
+    f.p = (char*)q;
+    size_t got = 0;
+    while (got < f.n) {
+        size_t r = fread(f.p + got, 1, f.n - got, fp);
+        if (!r) break;
+        got += r;
+    }
+    fclose(fp);
+    if (got != f.n) { err = "short read on " + path; return false; }
+    return true;
+}
+
+// random_coder (:1082-1102): srand(seed); 32 draws of rand()%6 pick one ordering of {0,1,2} each
+void draw_coder(unsigned seed, int16_t coder[96])
+{
+    static const int16_t orderings[6][3] = {{0, 1, 2}, {0, 2, 1}, {1, 2, 0}, {1, 0, 2}, {2, 0, 1}, {2, 1, 0}};
+    srand(seed);
+    for (int z = 0; z < EREF_K; z++) {
+        int r = rand() % 6;
+        for (int i = 0; i < 3; i++) coder[z * 3 + i] = orderings[r][i];
+    }
+}
+
+// saved_random_coder (:1104-1122): low 16 bits of the first 96 words of an existing index
+bool read_index_header(const std::string& index, int16_t coder[96])
+{
+    FILE* fp = fopen(index.c_str(), "rb");
+    if (!fp) return false;
+    uint32_t w[96];
+    size_t got = fread(w, 4, 96, fp);
+    fclose(fp);
+    if (got != 96) return false;
+    for (int j = 0; j < 96; j++) coder[j] = (int16_t)(w[j] & 0xffffu);
+    return true;
+}
+
+bool read_sidecar(const std::string& path, int16_t coder[96])
+{
+    std::ifstream in(path);
+    if (!in) return false;
+    for (int j = 0; j < 96; j++) { int v; if (!(in >> v)) return false; coder[j] = (int16_t)v; }
+    return true;
+}
+
+// shard boundaries: byte offsets that start a header line ('>' right after a newline)
+std::vector<size_t> shard_offsets(const char* fa, size_t n, int shards)
+{
+    std::vector<size_t> cut(1, 0);
+    for (int s = 1; s < shards; s++) {
+        size_t pos = std::max(cut.back(), n / shards * s);
+        size_t found = n;
+        while (pos < n) {
+            const char* nl = (const char*)memchr(fa + pos, '\n', n - pos);
+            if (!nl) break;
+            size_t q = (size_t)(nl - fa) + 1;
+            if (q < n && fa[q] == '>') { found = q; break; }
+            pos = q;
+        }
+        cut.push_back(found);
+    }
+    cut.push_back(n);
+    return cut;
+}
+
+struct Barrier {
+    std::mutex m; std::condition_variable cv; int count, waiting = 0, gen = 0;
+    explicit Barrier(int n) : count(n) {}
+    void wait()
+    {
+        std::unique_lock<std::mutex> lk(m);
+        int g = gen;
+        if (++waiting == count) { gen++; waiting = 0; cv.notify_all(); }
+        else cv.wait(lk, [&] { return g != gen; });
+    }
+};
+
+} // namespace
+
+int main(int argc, char** argv)
+{
+    if (argc < 8) {
+        fprintf(stderr, "usage: eref <fq1> <fq2> <phagedb.fasta> <interval_out> <hit_ratio> <perfect_hit_ratio> <threads>\n");
+        return 2;
+    }
+    const std::string fq1 = argv[1], fq2 = argv[2], fasta = argv[3], interval_name = argv[4];
+    float hit_ratio, perfect_hit_ratio;
+    try {
+        hit_ratio = (float)std::stod(argv[5]);               // :1228
+        perfect_hit_ratio = (float)std::stod(argv[6]);       // :1229
+        (void)std::stod(argv[7]);                            // :1231 threads: a hint, unused on the GPU
+    } catch (const std::exception& e) {
+        fprintf(stderr, "eref: bad numeric argument: %s\n", e.what());
+        return 2;
+    }
+    const bool timing = getenv("EREF_TIMING") != nullptr;
+    auto t_start = std::chrono::steady_clock::now();
+
+    int ndev = eref_device_count();
+    if (ndev <= 0) { fprintf(stderr, "eref: no CUDA device visible (this build has no CPU path)\n"); return 3; }
+
+    { std::ofstream trunc(interval_name, std::ios::out | std::ios::trunc); }   // :825 created, left empty
+
+    // ---- coder assignment (:1245-1258) ----
+    int16_t coder[96];
+    const std::string index_name = fasta + ".k" + std::to_string(EREF_K) + ".index.dat";
+    const std::string sidecar = fasta + ".k" + std::to_string(EREF_K) + ".coder";
+    if (!read_index_header(index_name, coder) && !read_sidecar(sidecar, coder)) {
+        const char* s = getenv("EREF_CODER_SEED");
+        draw_coder(s ? (unsigned)strtoul(s, nullptr, 10) : (unsigned)time(nullptr), coder);
+        std::ofstream out(sidecar);
+        for (int j = 0; j < 96; j++) out << coder[j] << (j % 3 == 2 ? '\n' : ' ');
+        if (!out) fprintf(stderr, "eref: warning: could not persist the coder assignment to %s\n", sidecar.c_str());
+    }
+
+    // ---- inputs ----
+    HostFile f1, f2, fa;
+    std::string err;
+    if (!read_file(fq1, f1, err) || !read_file(fq2, f2, err) || !read_file(fasta, fa, err)) {
+        fprintf(stderr, "eref: %s\n", err.c_str());
+        return 3;
+    }
+    auto t_read = std::chrono::steady_clock::now();
+
+    int shards = (int)std::min<size_t>((size_t)ndev, std::max<size_t>(1, fa.n >> 27));
+    if (const char* g = getenv("EREF_GPUS")) {
+        shards = strcmp(g, "all") == 0 ? ndev : atoi(g);
+        if (shards < 1 || shards > ndev) { fprintf(stderr, "eref: EREF_GPUS=%s but %d device(s) visible\n", g, ndev); return 3; }
+    }
+    std::vector<size_t> cut = shard_offsets(fa.p, fa.n, shards);
+    const unsigned flags = getenv("EREF_NO_PRUNE") ? EREF_FLAG_NO_PRUNE : 0u;
+
+    std::vector<ncclComm_t> comms(shards);
+    if (shards > 1) {
+        std::vector<int> devs(shards);
+        for (int i = 0; i < shards; i++) devs[i] = i;
+        ncclResult_t r = ncclCommInitAll(comms.data(), shards, devs.data());
+        if (r != ncclSuccess) { fprintf(stderr, "eref: ncclCommInitAll: %s\n", ncclGetErrorString(r)); return 3; }
+    }
+
+    std::vector<size_t> kept(shards, 0);
+    std::vector<std::string> errors(shards);
+    std::vector<eref_phase_times> times(shards);
+    std::vector<eref_result> merged;                 // filled by shard 0
+    std::atomic<int> failed{0};
+    Barrier bar(shards);
+    size_t max_kept = 0;
+    bool go = false;
+
+    auto worker = [&](int i) {
+        eref_ctx* ctx = nullptr;
+        auto fail = [&](const char* what) {
+            errors[i] = std::string(what) + ": " + eref_last_error();
+            failed.store(1);
+        };
+        bool ok = true;
+        if (eref_create(&ctx, i, coder, hit_ratio, perfect_hit_ratio, flags)) { fail("eref_create"); ok = false; }
+        if (ok && eref_query_add(ctx, f1.p, f1.n)) { fail("eref_query_add(fq1)"); ok = false; }
+        if (ok) {
+            // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1), integer division
+            uint64_t seq = 0;
+            eref_query_seq_bytes(ctx, &seq);
+            if (seq == 0) { errors[i] = "fq1 holds no sequence lines (the reference divides by zero here, :1145)"; failed.store(1); ok = false; }
+            else {
+                long ratio = 100L * 2000000000L / (long)(2 * seq);
+                if (ratio < 100) {
+                    errors[i] = "fq1 holds more than 1 Gbase: the reference's rand()-driven down-sampling (:955-960) "
+                                "is not implemented; refusing to diverge silently";
+                    failed.store(1); ok = false;
+                }
+            }
+        }
+        if (ok && eref_query_add(ctx, f2.p, f2.n)) { fail("eref_query_add(fq2)"); ok = false; }
+        if (ok && eref_ref_set(ctx, fa.p + cut[i], cut[i + 1] - cut[i])) { fail("eref_ref_set"); ok = false; }
+        if (ok) eref_ref_count(ctx, &kept[i], nullptr, nullptr);
+        bar.wait();                                   // every shard's record count is known
+        if (i == 0) { max_kept = *std::max_element(kept.begin(), kept.end()); go = failed.load() == 0; }
+        bar.wait();
+        const bool all_ok = go;                       // one decision for every shard: all enter the collective or none
+        if (all_ok && shards == 1) {
+            merged.resize(kept[0]);
+            size_t n = 0;
+            if (eref_scan(ctx, merged.data(), merged.size(), &n)) fail("eref_scan");
+        } else if (all_ok) {
+            // one collective: allgather of fixed-size records, shards padded to max_kept
+            const uint32_t* dres = nullptr;
+            size_t n = 0;
+            void *send = nullptr, *recv = nullptr;
+            cudaStream_t st = nullptr;
+            const size_t slot = std::max<size_t>(max_kept, 1) * sizeof(eref_result);
+            bool good = eref_scan_device(ctx, &dres, &n) == 0;
+            if (!good) fail("eref_scan_device");
+            good = good && cudaSetDevice(i) == cudaSuccess && cudaStreamCreate(&st) == cudaSuccess &&
+                   cudaMalloc(&send, slot) == cudaSuccess && cudaMalloc(&recv, slot * shards) == cudaSuccess &&
+                   cudaMemsetAsync(send, 0, slot, st) == cudaSuccess &&
+                   (n == 0 || cudaMemcpyAsync(send, dres, n * sizeof(eref_result), cudaMemcpyDeviceToDevice, st) == cudaSuccess);
+            if (!good && errors[i].empty()) { errors[i] = "allgather staging failed"; failed.store(1); }
+            // every rank must enter the collective, even after a local failure, or the others hang
+            ncclResult_t r = ncclAllGather(send, recv, slot, ncclChar, comms[i], st);
+            if (r != ncclSuccess) { errors[i] = std::string("ncclAllGather: ") + ncclGetErrorString(r); failed.store(1); }
+            cudaStreamSynchronize(st);
+            if (i == 0 && failed.load() == 0) {
+                std::vector<eref_result> all(std::max<size_t>(max_kept, 1) * shards);
+                cudaMemcpy(all.data(), recv, slot * shards, cudaMemcpyDeviceToHost);
+                uint32_t base = 0;
+                for (int s = 0; s < shards; s++) {
+                    for (size_t k = 0; k < kept[s]; k++) {
+                        eref_result rr = all[(size_t)s * std::max<size_t>(max_kept, 1) + k];
+                        rr.ordinal += base;           // ordinals continue across shards (file order)
+                        merged.push_back(rr);
+                    }
+                    base += (uint32_t)kept[s];
+                }
+            }
+            if (send) cudaFree(send);
+            if (recv) cudaFree(recv);
+            if (st) cudaStreamDestroy(st);
+        }
+        if (ctx) { eref_timings(ctx, &times[i]); eref_destroy(ctx); }
+    };
+
+    std::vector<std::thread> pool;
+    for (int i = 0; i < shards; i++) pool.emplace_back(worker, i);
+    for (auto& t : pool) t.join();
+    if (shards > 1) for (auto& c : comms) ncclCommDestroy(c);
+
+    if (failed.load()) {
+        for (int i = 0; i < shards; i++)
+            if (!errors[i].empty()) fprintf(stderr, "eref: gpu %d: %s\n", i, errors[i].c_str());
+        return 3;                                     // nothing was written to stdout
+    }
+
+    std::string out;
+    char line[256];
+    for (const eref_result& r : merged) {
+        int k = eref_format_line(&r, line, sizeof line);    // :615-617
+        if (k > 0) out.append(line, (size_t)k);
+    }
+    fwrite(out.data(), 1, out.size(), stdout);
+    fflush(stdout);
+
+    if (timing) {
+        auto t_end = std::chrono::steady_clock::now();
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "eref timing: read %.1f ms, gpu+merge %.1f ms, shards %d\n", ms(t_start, t_read), ms(t_read, t_end), shards);
+        for (int i = 0; i < shards; i++) {
+            const eref_phase_times& t = times[i];
+            fprintf(stderr,
+                    "  gpu %d: fq2 h2d %.3f pack %.3f count %.3f | ref h2d %.3f frame %.3f pack %.3f | scan sample %.3f cand %.3f "
+                    "probe %.3f window %.3f intervals %.3f d2h %.3f ms | bases %llu need_words %llu/%llu launches %llu\n",
+                    i, t.query_h2d_ms, t.query_pack_ms, t.query_count_ms, t.ref_h2d_ms, t.ref_frame_ms, t.ref_pack_ms,
+                    t.scan_sample_ms, t.scan_cand_ms, t.scan_probe_ms, t.scan_window_ms, t.scan_interval_ms, t.scan_d2h_ms,
+                    (unsigned long long)t.ref_bases, (unsigned long long)t.ref_need_words, (unsigned long long)t.ref_words,
+                    (unsigned long long)t.kernel_launches);
+        }
+    }
+    return 0;
+}

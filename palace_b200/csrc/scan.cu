@@ -1,0 +1,304 @@
+// scan.cu — the streaming reference scan (north_star part 4): probe the query table at every
+// reference position, apply the 500-position window rule, and reduce each record to
+// {ordinal, frag, el, ref_len}.  Replaces read_index (:813-903) + slide_window (:504-624).
+//
+// Exact candidate filter.  A window is "good" only if at least three_min of its 500 positions are
+// hit by ALL three code streams (:561), hence by stream 0.  Probing stream 0 at every 4th position
+// bounds that count from above: trio(window) <= sampled_hits(window) + 375.  Words whose bound stays
+// below three_min can never be good, so the full three-stream probe runs only on the words that can
+// influence a window that still might be.  The selected records and their numbers are unchanged;
+// random-sector probes drop from 3 per base to ~0.25 per base plus 3 per base on candidate regions.
+#include "eref_internal.cuh"
+
+namespace {
+
+__device__ __forceinline__ uint32_t probe(const uint32_t* __restrict__ bm3, uint32_t code)
+{
+    // code 0 is the index's "no k-mer" sentinel (:733-735, :861-866): never a hit
+    return code ? (__ldg(bm3 + (code >> 5)) >> (code & 31)) & 1u : 0u;
+}
+
+// ---- P1: stream 0 at positions 0,4,...,28 of every word ------------------------------------------
+__global__ void __launch_bounds__(256)
+k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, uint8_t* __restrict__ sample_hits)
+{
+    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= pl.nwords) return;
+    const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
+    uint32_t out = 0;
+    if (vm & 0x88888888u) {
+        const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
+        uint32_t code[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int s = q * SAMPLE_STRIDE;
+            WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+            code[q] = ((vm >> (31 - s)) & 1u) ? stream_code(m, b, 0) : 0u;
+        }
+#pragma unroll
+        for (int q = 0; q < 8; q++) out |= probe(bm3, code[q]) << (7 - q);
+    }
+    sample_hits[w] = (uint8_t)out;
+}
+
+// ---- P2: candidate words and the words they depend on --------------------------------------------
+// cand[w]: the sampled hits in words w-16..w (a superset of every window ending in word w) reach
+// min_sample_hits = three_min - (500 - 125).
+__global__ void k_candidates(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ word_genome,
+                             const uint32_t* __restrict__ g_word, uint64_t nwords, int min_sample_hits,
+                             uint8_t* __restrict__ cand)
+{
+    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= nwords) return;
+    const uint64_t gs = g_word[word_genome[w]];
+    int c = 0;
+#pragma unroll
+    for (int k = 0; k <= WIN_WORDS; k++)
+        if (w >= gs + k) c += __popc((uint32_t)sample_hits[w - k]);
+    cand[w] = c >= min_sample_hits;
+}
+
+// need[w]: some word in w..w+16 of the same record is a candidate, i.e. a position of word w lies
+// inside a window that may be good.
+__global__ void k_need(const uint8_t* __restrict__ cand, const uint32_t* __restrict__ word_genome,
+                       uint64_t nwords, uint8_t* __restrict__ need, unsigned long long* __restrict__ need_count)
+{
+    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t v = 0;
+    if (w < nwords) {
+        const uint32_t g = word_genome[w];
+#pragma unroll
+        for (int k = 0; k <= WIN_WORDS; k++)
+            if (w + k < nwords && word_genome[w + k] == g) v |= cand[w + k];
+        need[w] = (uint8_t)v;
+    }
+    uint32_t b = __ballot_sync(0xffffffffu, v != 0);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(need_count, (unsigned long long)__popc(b));
+}
+
+// ---- P3: all three streams at every position of the needed words ----------------------------------
+// single bit = at least one stream hit, trio bit = all three hit (:528-546).
+__global__ void __launch_bounds__(256)
+k_probe_full(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const uint8_t* __restrict__ need,
+             uint32_t* __restrict__ single, uint32_t* __restrict__ trio)
+{
+    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= pl.nwords) return;
+    uint32_t one = 0, three = 0;
+    if (!need || need[w]) {
+        const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
+        if (vm) {
+            const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
+#pragma unroll
+            for (int s0 = 0; s0 < 32; s0 += 8) {
+                uint32_t code[24];
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int s = s0 + q;
+                    WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                    const bool v = (vm >> (31 - s)) & 1u;
+#pragma unroll
+                    for (int i = 0; i < 3; i++) code[q * 3 + i] = v ? stream_code(m, b, i) : 0u;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    uint32_t h0 = probe(bm3, code[q * 3]), h1 = probe(bm3, code[q * 3 + 1]),
+                             h2 = probe(bm3, code[q * 3 + 2]);
+                    one |= (h0 | h1 | h2) << (31 - s0 - q);
+                    three |= (h0 & h1 & h2) << (31 - s0 - q);
+                }
+            }
+        }
+    }
+    single[w] = one; trio[w] = three;
+}
+
+// ---- P4: window counts -> good bit per position (:548-566) -----------------------------------------
+// Position p of a record looks back over [max(0,p-499), p].  For the first position of word w that is
+// bit 31 of word w, words w-1..w-15 and the low 19 bits of word w-16; each further position adds the
+// next bit of word w and drops the next bit of the string (word w-16 : word w-15) from index 13 on.
+__device__ __forceinline__ void window_load(const uint32_t* __restrict__ plane, uint64_t w, uint64_t gs,
+                                            uint32_t& cur, uint32_t& body, uint64_t& leave)
+{
+    cur = plane[w];
+    body = 0;
+#pragma unroll
+    for (int k = 1; k < WIN_WORDS; k++)
+        if (w >= gs + k) body += __popc(plane[w - k]);
+    uint32_t w16 = w >= gs + WIN_WORDS ? plane[w - WIN_WORDS] : 0u;
+    uint32_t w15 = w >= gs + WIN_WORDS - 1 ? plane[w - (WIN_WORDS - 1)] : 0u;
+    body += __popc(w16 & 0x7FFFFu);
+    leave = ((uint64_t)w16 << 32) | w15;
+}
+
+__global__ void __launch_bounds__(256)
+k_window(const uint32_t* __restrict__ single, const uint32_t* __restrict__ trio, const uint8_t* __restrict__ need,
+         const uint32_t* __restrict__ word_genome, const uint32_t* __restrict__ g_word,
+         const uint32_t* __restrict__ g_len, uint64_t nwords, int one_min, int three_min,
+         uint32_t* __restrict__ good)
+{
+    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= nwords) return;
+    uint32_t out = 0;
+    if (!need || need[w]) {
+        const uint32_t g = word_genome[w];
+        const uint64_t gs = g_word[g];
+        const uint32_t len = g_len[g];
+        const uint32_t p0 = (uint32_t)(w - gs) << 5;
+        uint32_t s_cur, s_body, t_cur, t_body;
+        uint64_t s_leave, t_leave;
+        window_load(single, w, gs, s_cur, s_body, s_leave);
+        window_load(trio, w, gs, t_cur, t_body, t_leave);
+        int c1 = (int)s_body + (int)(s_cur >> 31);
+        int c3 = (int)t_body + (int)(t_cur >> 31);
+#pragma unroll
+        for (int s = 0; s < 32; s++) {
+            if (c1 >= one_min && c3 >= three_min && p0 + s < len) out |= 0x80000000u >> s;
+            if (s < 31) {
+                c1 += (int)((s_cur >> (30 - s)) & 1u) - (int)((s_leave >> (50 - s)) & 1ull);
+                c3 += (int)((t_cur >> (30 - s)) & 1u) - (int)((t_leave >> (50 - s)) & 1ull);
+            }
+        }
+    }
+    good[w] = out;
+}
+
+// ---- P5: good runs -> padded, merged intervals -> {ordinal, frag, el, ref_len} (:568-617) ------------
+// One warp per record walks its good words in order; the (rare) rising/falling edges are replayed by
+// every lane in lock step, so the state machine stays warp-uniform.
+__global__ void __launch_bounds__(128)
+k_intervals(const uint32_t* __restrict__ good, const uint32_t* __restrict__ g_word,
+            const uint32_t* __restrict__ g_len, uint32_t n_genomes, uint32_t* __restrict__ results)
+{
+    const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= n_genomes) return;
+    const uint64_t gs = g_word[g];
+    const int len = (int)g_len[g];
+    const uint32_t nw = ((uint32_t)len + 31u) >> 5;
+    int start = 0, last_end = 0, frag = 0, el = 0;
+    bool open = false;
+    uint32_t carry = 0;                               // good bit of the previous position
+    for (uint32_t base = 0; base < nw; base += 32) {
+        const uint32_t idx = base + lane;
+        uint32_t x = idx < nw ? good[gs + idx] : 0u;
+        uint32_t vmask = 0;
+        if (idx < nw) {
+            uint32_t rem = (uint32_t)len - (idx << 5);
+            vmask = rem >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> rem);
+        }
+        x &= vmask;
+        uint32_t pb = __shfl_up_sync(0xffffffffu, x & 1u, 1);
+        if (lane == 0) pb = carry;
+        const uint32_t prev = (x >> 1) | (pb << 31);
+        const uint32_t rise = x & ~prev & vmask, fall = ~x & prev & vmask;
+        uint32_t pending = __ballot_sync(0xffffffffu, (rise | fall) != 0);
+        while (pending) {
+            const int l = __ffs(pending) - 1;
+            pending &= pending - 1;
+            const uint32_t r = __shfl_sync(0xffffffffu, rise, l), f = __shfl_sync(0xffffffffu, fall, l);
+            uint32_t e = r | f;
+            while (e) {
+                const int s = __clz(e);
+                const uint32_t bit = 0x80000000u >> s;
+                e &= ~bit;
+                const int j = (int)((base + l) << 5) + s;
+                if (r & bit) {                        // :568-574
+                    start = j - 2 * WINDOW; if (start < 1) start = 1;
+                    open = true;
+                } else {                              // :575-589
+                    int end = j + 2 * WINDOW; if (end > len) end = len;
+                    if (frag > 0 && start - last_end < WINDOW) el += end - last_end;
+                    else { frag++; el += end - start; }
+                    last_end = end; open = false;
+                }
+            }
+        }
+        carry = __shfl_sync(0xffffffffu, x & 1u, 31);
+    }
+    if (open) {                                       // :599-609
+        if (frag > 0 && start - last_end < WINDOW) el += len - last_end;
+        else { frag++; el += len - start; }
+    }
+    if (lane == 0) {
+        uint4 rec = make_uint4(g + 1, (uint32_t)frag, (uint32_t)el, (uint32_t)len);
+        reinterpret_cast<uint4*>(results)[g] = rec;
+    }
+}
+
+// ---- index body of one record (:711-738): 3 codes per window start, 0 = invalid --------------------
+__global__ void k_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,
+                               uint32_t* __restrict__ codes)
+{
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j + EREF_K > len) return;
+    const uint64_t w = first_word + (j >> 5);
+    const int s = j & 31;
+    const bool v = window32(pl.ok[w], pl.ok[w + 1], s) == 0xFFFFFFFFu;
+    WindowBits b = window_bits(window32(pl.hi[w], pl.hi[w + 1], s), window32(pl.lo[w], pl.lo[w + 1], s));
+#pragma unroll
+    for (int i = 0; i < 3; i++) codes[(size_t)j * 3 + i] = v ? stream_code(m, b, i) : 0u;
+}
+
+} // namespace
+
+static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, uint8_t* sample_hits,
+                                 cudaStream_t st)
+{
+    if (!pl.nwords) return cudaSuccess;
+    k_probe_sampled<<<grid_for(pl.nwords, 256), 256, 0, st>>>(pl, m, bm3, sample_hits);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_candidates(const uint8_t* sample_hits, const uint32_t* word_genome, const uint32_t* g_word,
+                              uint64_t nwords, int min_sample_hits, uint8_t* cand, cudaStream_t st)
+{
+    if (!nwords) return cudaSuccess;
+    k_candidates<<<grid_for(nwords, 256), 256, 0, st>>>(sample_hits, word_genome, g_word, nwords,
+                                                        min_sample_hits, cand);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_need(const uint8_t* cand, const uint32_t* word_genome, uint64_t nwords, uint8_t* need,
+                        unsigned long long* need_count, cudaStream_t st)
+{
+    if (!nwords) return cudaSuccess;
+    k_need<<<grid_for(nwords, 256), 256, 0, st>>>(cand, word_genome, nwords, need, need_count);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_probe_full(Planes pl, CoderMasks m, const uint32_t* bm3, const uint8_t* need,
+                              uint32_t* single, uint32_t* trio, cudaStream_t st)
+{
+    if (!pl.nwords) return cudaSuccess;
+    k_probe_full<<<grid_for(pl.nwords, 256), 256, 0, st>>>(pl, m, bm3, need, single, trio);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint8_t* need,
+                          const uint32_t* word_genome, const uint32_t* g_word, const uint32_t* g_len,
+                          uint64_t nwords, int one_min, int three_min, uint32_t* good, cudaStream_t st)
+{
+    if (!nwords) return cudaSuccess;
+    k_window<<<grid_for(nwords, 256), 256, 0, st>>>(single, trio, need, word_genome, g_word, g_len, nwords,
+                                                    one_min, three_min, good);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const uint32_t* g_len,
+                             uint32_t n_genomes, uint32_t* results, cudaStream_t st)
+{
+    if (!n_genomes) return cudaSuccess;
+    k_intervals<<<grid_for((uint64_t)n_genomes * 32, 128), 128, 0, st>>>(good, g_word, g_len, n_genomes, results);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len, uint32_t* codes,
+                                cudaStream_t st)
+{
+    if (len < (uint32_t)EREF_K) return cudaSuccess;
+    k_record_codes<<<grid_for(len - EREF_K + 1, 256), 256, 0, st>>>(pl, m, first_word, len, codes);
+    return cudaGetLastError();
+}

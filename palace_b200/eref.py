@@ -1,0 +1,291 @@
+"""Host-side mirror of PALACE's `eref` over the C ABI of liberef_gpu.so (include/eref_gpu.h).
+
+The reference has no library interface for this path — it is the process
+`eref fq1 fq2 phagedb.fasta interval_out hit_ratio perfect_hit_ratio threads`
+(bin/extract_ref.cpp:1221-1231, palace:475-477).  `run_eref()` takes the same seven arguments and
+returns what that process writes to stdout; `ErefGPU` exposes the phases underneath it
+(query table, reference framing, scan) for tests and for bench.py.
+
+There is no CPU path here: if liberef_gpu.so is missing or no CUDA device is visible, every entry
+point raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import (POINTER, Structure, byref, c_char_p, c_float, c_int, c_int16, c_size_t, c_uint,
+                    c_uint32, c_uint64, c_void_p)
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liberef_gpu.so")
+EREF_BIN = os.path.join(_HERE, "bin", "eref")
+
+K = 32
+FLAG_NO_PRUNE = 1
+
+RESULT_DTYPE = np.dtype([("ordinal", "<u4"), ("frag", "<u4"), ("el", "<u4"), ("ref_len", "<u4")])
+
+# every symbol include/eref_gpu.h declares
+ABI_SYMBOLS = (
+    "eref_last_error", "eref_device_count", "eref_create", "eref_destroy", "eref_set_stream",
+    "eref_query_reset", "eref_query_add", "eref_query_add_device", "eref_query_seq_bytes",
+    "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device",
+    "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
+)
+
+
+class PhaseTimes(Structure):
+    _fields_ = [(n, c_float) for n in (
+        "query_h2d_ms", "query_pack_ms", "query_count_ms", "ref_h2d_ms", "ref_frame_ms", "ref_pack_ms",
+        "scan_sample_ms", "scan_cand_ms", "scan_probe_ms", "scan_window_ms", "scan_interval_ms",
+        "scan_d2h_ms")] + [(n, c_uint64) for n in (
+        "kernel_launches", "ref_bases", "ref_words", "ref_need_words", "query_seq_bytes")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class ErefError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library() -> ctypes.CDLL:
+    """dlopen liberef_gpu.so and bind the ABI.  Fails loudly when the extension was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ErefError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(make -C palace_b200/csrc). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.eref_last_error.restype = c_char_p
+    lib.eref_device_count.restype = c_int
+    lib.eref_create.argtypes = [POINTER(c_void_p), c_int, POINTER(c_int16), c_float, c_float, c_uint]
+    lib.eref_destroy.argtypes = [c_void_p]
+    lib.eref_destroy.restype = None
+    lib.eref_set_stream.argtypes = [c_void_p, c_void_p]
+    lib.eref_query_reset.argtypes = [c_void_p]
+    lib.eref_query_add.argtypes = [c_void_p, c_void_p, c_size_t]
+    lib.eref_query_add_device.argtypes = [c_void_p, c_void_p, c_size_t]
+    lib.eref_query_seq_bytes.argtypes = [c_void_p, POINTER(c_uint64)]
+    lib.eref_ref_set.argtypes = [c_void_p, c_void_p, c_size_t]
+    lib.eref_ref_set_device.argtypes = [c_void_p, c_void_p, c_size_t]
+    lib.eref_ref_count.argtypes = [c_void_p, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_uint64)]
+    lib.eref_scan.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_size_t)]
+    lib.eref_scan_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
+    lib.eref_get_codes.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]
+    lib.eref_ref_record.argtypes = [c_void_p, c_uint32, POINTER(c_uint64), POINTER(c_uint32), POINTER(c_uint32)]
+    lib.eref_query_popcount.argtypes = [c_void_p, c_int, POINTER(c_uint64)]
+    lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
+    lib.eref_format_line.argtypes = [c_void_p, ctypes.c_char_p, c_size_t]
+    _lib = lib
+    return lib
+
+
+def _check(lib, rc, what):
+    if rc != 0:
+        raise ErefError(f"{what} failed ({rc}): {lib.eref_last_error().decode(errors='replace')}")
+
+
+# ---- coder assignment (bin/extract_ref.cpp:1082-1122) -------------------------------------------
+
+_ORDERINGS = ((0, 1, 2), (0, 2, 1), (1, 2, 0), (1, 0, 2), (2, 0, 1), (2, 1, 0))   # permu[18], :1084
+
+
+def random_coder(seed: int) -> np.ndarray:
+    """random_coder (:1082-1102): glibc srand(seed), then 32 draws of rand() % 6."""
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(c_uint(seed))
+    out = np.zeros(96, np.int16)
+    for z in range(K):
+        out[z * 3: z * 3 + 3] = _ORDERINGS[libc.rand() % 6]
+    return out
+
+
+def read_coder(index_path: str) -> np.ndarray:
+    """saved_random_coder (:1104-1122): low 16 bits of the first 96 u32 words of <db>.k32.index.dat."""
+    w = np.fromfile(index_path, dtype="<u4", count=96)
+    if w.size != 96:
+        raise ErefError(f"{index_path}: truncated index header")
+    return (w & 0xFFFF).astype(np.int16)
+
+
+def _as_bytes_array(buf) -> np.ndarray:
+    if isinstance(buf, np.ndarray):
+        a = buf if buf.dtype == np.uint8 else buf.view(np.uint8)
+        return np.ascontiguousarray(a)
+    return np.frombuffer(bytes(buf) if not isinstance(buf, (bytes, bytearray, memoryview)) else buf, dtype=np.uint8)
+
+
+class ErefGPU:
+    """One context = one GPU: the query table, one reference text (whole DB or one shard), the scan."""
+
+    def __init__(self, coder, hit_ratio: float = 0.9, perfect_hit_ratio: float = 0.85, device: int = 0,
+                 prune: bool = True):
+        self.lib = load_library()
+        if self.lib.eref_device_count() <= 0:
+            raise ErefError("no CUDA device visible; liberef_gpu.so has no CPU fallback")
+        c = np.ascontiguousarray(np.asarray(coder, dtype=np.int16))
+        if c.size != 96:
+            raise ErefError("coder must have 96 entries")
+        self._h = c_void_p()
+        rc = self.lib.eref_create(byref(self._h), device, c.ctypes.data_as(POINTER(c_int16)),
+                                  c_float(hit_ratio), c_float(perfect_hit_ratio), 0 if prune else FLAG_NO_PRUNE)
+        _check(self.lib, rc, "eref_create")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.eref_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_stream(self, cuda_stream: int):
+        _check(self.lib, self.lib.eref_set_stream(self._h, c_void_p(cuda_stream)), "eref_set_stream")
+
+    def query_reset(self):
+        _check(self.lib, self.lib.eref_query_reset(self._h), "eref_query_reset")
+
+    def query_add(self, fastq) -> int:
+        """Count one FASTQ file held in HOST memory; returns its sequence-line byte sum (:1138-1140)."""
+        a = _as_bytes_array(fastq)
+        _check(self.lib, self.lib.eref_query_add(self._h, c_void_p(a.ctypes.data), a.size), "eref_query_add")
+        return self.query_seq_bytes()
+
+    def query_add_device(self, ptr: int, n: int) -> int:
+        _check(self.lib, self.lib.eref_query_add_device(self._h, c_void_p(ptr), n), "eref_query_add_device")
+        return self.query_seq_bytes()
+
+    def query_seq_bytes(self) -> int:
+        v = c_uint64()
+        _check(self.lib, self.lib.eref_query_seq_bytes(self._h, byref(v)), "eref_query_seq_bytes")
+        return v.value
+
+    def ref_set(self, fasta):
+        a = _as_bytes_array(fasta)
+        _check(self.lib, self.lib.eref_ref_set(self._h, c_void_p(a.ctypes.data), a.size), "eref_ref_set")
+
+    def ref_set_device(self, ptr: int, n: int):
+        _check(self.lib, self.lib.eref_ref_set_device(self._h, c_void_p(ptr), n), "eref_ref_set_device")
+
+    def ref_count(self):
+        k, r, b = c_size_t(), c_size_t(), c_uint64()
+        _check(self.lib, self.lib.eref_ref_count(self._h, byref(k), byref(r), byref(b)), "eref_ref_count")
+        return k.value, r.value, b.value
+
+    def scan(self) -> np.ndarray:
+        kept, _, _ = self.ref_count()
+        out = np.zeros(max(kept, 1), RESULT_DTYPE)
+        n = c_size_t()
+        _check(self.lib, self.lib.eref_scan(self._h, c_void_p(out.ctypes.data), kept, byref(n)), "eref_scan")
+        return out[:n.value]
+
+    def scan_device(self):
+        """Results stay in HBM: (device pointer to n x 4 uint32, n)."""
+        p, n = c_void_p(), c_size_t()
+        _check(self.lib, self.lib.eref_scan_device(self._h, byref(p), byref(n)), "eref_scan_device")
+        return p.value, n.value
+
+    def get_codes(self, ordinal: int) -> np.ndarray:
+        n = c_size_t()
+        _check(self.lib, self.lib.eref_get_codes(self._h, ordinal, None, 0, byref(n)), "eref_get_codes")
+        out = np.zeros(n.value, "<u4")
+        _check(self.lib, self.lib.eref_get_codes(self._h, ordinal, c_void_p(out.ctypes.data), out.size, byref(n)),
+               "eref_get_codes")
+        return out
+
+    def ref_record(self, ordinal: int):
+        off, hl, ln = c_uint64(), c_uint32(), c_uint32()
+        _check(self.lib, self.lib.eref_ref_record(self._h, ordinal, byref(off), byref(hl), byref(ln)), "eref_ref_record")
+        return off.value, hl.value, ln.value
+
+    def query_popcount(self, level: int) -> int:
+        v = c_uint64()
+        _check(self.lib, self.lib.eref_query_popcount(self._h, level, byref(v)), "eref_query_popcount")
+        return v.value
+
+    def timings(self) -> dict:
+        t = PhaseTimes()
+        _check(self.lib, self.lib.eref_timings(self._h, byref(t)), "eref_timings")
+        return t.as_dict()
+
+
+def format_results(results: np.ndarray, ordinal_base: int = 0) -> str:
+    """The stdout of eref (:615-617) for an array of result records."""
+    lib = load_library()
+    buf = ctypes.create_string_buffer(256)
+    out = []
+    rec = np.zeros(1, RESULT_DTYPE)
+    for r in results:
+        rec[0] = r
+        rec[0]["ordinal"] += ordinal_base
+        k = lib.eref_format_line(c_void_p(rec.ctypes.data), buf, 256)
+        if k > 0:
+            out.append(buf.raw[:k].decode())
+    return "".join(out)
+
+
+def shard_offsets(fasta: np.ndarray, shards: int):
+    """Byte offsets that split a FASTA text into `shards` ranges, each starting at a header line."""
+    n = fasta.size
+    cuts = [0]
+    raw = fasta.tobytes() if shards > 1 else b""
+    for s in range(1, shards):
+        pos = max(cuts[-1], n // shards * s)
+        q = raw.find(b"\n>", pos)
+        cuts.append(n if q < 0 else q + 1)
+    cuts.append(n)
+    return cuts
+
+
+def check_sample_ratio(seq_bytes_fq1: int):
+    """cal_sam_ratio (:1124-1148).  Below 100 the reference down-samples with rand(): not implemented."""
+    if seq_bytes_fq1 == 0:
+        raise ErefError("fq1 holds no sequence lines (the reference divides by zero here, :1145)")
+    ratio = 100 * 2_000_000_000 // (2 * seq_bytes_fq1)
+    if ratio < 100:
+        raise ErefError("fq1 holds more than 1 Gbase: the reference's rand()-driven down-sampling (:955-960) is not "
+                        "implemented; refusing to diverge silently")
+    return ratio
+
+
+def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
+             perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
+             return_results: bool = False):
+    """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
+
+    `devices`: GPUs to shard the database over (one context each, run one after the other here —
+    the concurrent multi-GPU drivers are palace_b200/bin/eref and bench.py under torchrun).
+    """
+    del threads                                            # a hint in the reference, unused here
+    if interval_out:
+        open(interval_out, "w").close()                   # :825
+    if coder is None:
+        raise ErefError("run_eref needs the coder assignment (read_coder(index) or random_coder(seed))")
+    fq1, fq2, fasta = _as_bytes_array(fq1), _as_bytes_array(fq2), _as_bytes_array(fasta)
+    cuts = shard_offsets(fasta, len(devices))
+    parts = []
+    for i, dev in enumerate(devices):
+        with ErefGPU(coder, hit_ratio, perfect_hit_ratio, dev, prune) as g:
+            check_sample_ratio(g.query_add(fq1))
+            g.query_add(fq2)
+            g.ref_set(fasta[cuts[i]:cuts[i + 1]])
+            parts.append(g.scan().copy())
+    base = 0
+    for p in parts:
+        p["ordinal"] += base
+        base += p.size
+    res = np.concatenate(parts) if parts else np.zeros(0, RESULT_DTYPE)
+    text = format_results(res)
+    return (text, res) if return_results else text
