@@ -1,0 +1,60 @@
+import gzip
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+def _have_gpu():
+    try:
+        from palace_b200 import eref
+        return eref.load_library().eref_device_count() > 0
+    except Exception:
+        return False
+
+
+def pytest_collection_modifyitems(config, items):
+    if _have_gpu():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    """ctypes view of oracle/liberef_oracle.so (the CPU restatement) — the checker, test-only."""
+    from tests import oracle_util
+    return oracle_util.load()
+
+
+def load_golden(name):
+    with open(os.path.join(GOLDEN, name + ".json")) as f:
+        meta = json.load(f)
+
+    def rd(ext):
+        with gzip.open(os.path.join(GOLDEN, f"{name}.{ext}.gz"), "rb") as g:
+            return np.frombuffer(g.read(), np.uint8)
+
+    return meta, rd("fa"), rd("r1.fq"), rd("r2.fq")
+
+
+GOLDEN_CASES = ("basic", "short_reads", "edge")
+
+
+@pytest.fixture(scope="session", params=GOLDEN_CASES)
+def golden(request):
+    return (request.param,) + load_golden(request.param)
