@@ -1,0 +1,59 @@
+"""Multi-GPU plumbing of the `eref` path: one process per GPU, the reference database sharded by
+record, and ONE collective — an allgather of fixed-size per-record results.
+
+Records are {ordinal, frag, el, ref_len} as 4 x 32-bit words (bin/extract_ref.cpp:617 prints them).
+Shards hold different numbers of records, so each rank pads its block to the largest shard; ordinals
+are local to a shard and are offset by the record counts of the shards before it, which restores
+the file-order numbering of read_index (:887, :1175).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .eref import RESULT_DTYPE
+
+
+def pad_records(rec: np.ndarray, slot: int) -> np.ndarray:
+    out = np.zeros(slot, RESULT_DTYPE)
+    out[: rec.size] = rec
+    return out
+
+
+def merge_gathered(flat: np.ndarray, counts, slot: int) -> np.ndarray:
+    """flat: world*slot records as gathered; counts[r]: real records of rank r."""
+    parts, base = [], 0
+    for r, n in enumerate(counts):
+        p = flat[r * slot: r * slot + n].copy()
+        p["ordinal"] += base
+        base += n
+        parts.append(p)
+    return np.concatenate(parts) if parts else np.zeros(0, RESULT_DTYPE)
+
+
+def allgather_records(local, n_local: int):
+    """local: (n_local, 4) int32 tensor on this rank's device (cuda under NCCL, cpu under gloo).
+    Returns the merged (sum n, 4) int64 tensor on every rank, ordinals offset into file order.
+    The count of each shard travels in the same collective: one extra header row per block."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    # the slot size must be agreed before the gather; it is data-independent host knowledge when the
+    # caller shards by record count, otherwise one tiny all_reduce(MAX) of a scalar precedes it
+    slot_t = torch.tensor([n_local], dtype=torch.int64, device=local.device)
+    dist.all_reduce(slot_t, op=dist.ReduceOp.MAX)
+    slot = int(slot_t.item())
+    block = torch.zeros((slot + 1, 4), dtype=torch.int32, device=local.device)
+    block[0, 0] = n_local
+    if n_local:
+        block[1: n_local + 1] = local[:n_local]
+    out = torch.empty((world * (slot + 1), 4), dtype=torch.int32, device=local.device)
+    dist.all_gather_into_tensor(out, block)
+    out = out.view(world, slot + 1, 4).to(torch.int64)
+    parts, base = [], 0
+    for r in range(world):
+        n = int(out[r, 0, 0].item())
+        p = out[r, 1: n + 1].clone()
+        p[:, 0] += base
+        base += n
+        parts.append(p)
+    return torch.cat(parts) if parts else out.new_zeros((0, 4))

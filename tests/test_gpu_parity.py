@@ -1,0 +1,194 @@
+"""GPU suite (-m gpu): the CUDA path through the C ABI against (a) the golden fixtures produced by the
+unmodified reference, (b) the CPU oracle on seeded inputs, (c) size-independent properties."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from palace_b200 import eref, synth
+from tests.conftest import GOLDEN_CASES, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+# ---- (a) golden fixtures: bit-exact stdout of the real reference ---------------------------------
+
+@pytest.mark.parametrize("prune", [True, False])
+def test_golden_stdout(golden, prune):
+    name, meta, fa, f1, f2 = golden
+    for key, expect in meta["stdout"].items():
+        hr, phr = (float(x) for x in key.split(","))
+        got = eref.run_eref(f1, f2, fa, None, hr, phr, 1, coder=meta["coder"], prune=prune)
+        assert got == expect, f"{name} {key} prune={prune}"
+
+
+def test_golden_codes_match_reference_index(golden, oracle):
+    """eref_get_codes == the body of the reference's <db>.k32.index.dat (via the pinned oracle), every record"""
+    import hashlib
+    name, meta, fa, f1, f2 = golden
+    seqs, _ = oracle.parse_fasta(fa)
+    h = hashlib.sha256()
+    with eref.ErefGPU(meta["coder"]) as g:
+        g.ref_set(fa)
+        kept, recs, bases = g.ref_count()
+        assert kept == len(seqs)
+        assert bases == sum(len(s) for s in seqs)
+        for i, s in enumerate(seqs):
+            got = g.get_codes(i + 1)
+            assert (got == oracle.record_codes(meta["coder"], s)).all(), f"{name} record {i + 1}"
+            h.update(np.uint32(len(s)).tobytes()); h.update(got.tobytes())
+    assert h.hexdigest() == meta["index_body_sha256"]
+
+
+def test_golden_all_records_match_oracle(golden, oracle):
+    """not only the selected lines: {ordinal, frag, el, ref_len} of EVERY kept record"""
+    name, meta, fa, f1, f2 = golden
+    want = oracle.run(f1, f2, fa, meta["coder"], 0.9, 0.85)
+    _, got = eref.run_eref(f1, f2, fa, None, 0.9, 0.85, 1, coder=meta["coder"], return_results=True)
+    assert got.size == want.size
+    assert (got == want).all()
+
+
+# ---- (b) seeded inputs against the oracle ----------------------------------------------------------
+
+def _case(seed, n_genomes=80, db_bp=2_000_000, q_bp=500_000, **kw):
+    db = synth.make_db(n_genomes, db_bp, seed, **kw.pop("db_kw", {}))
+    f1, f2, present = synth.make_reads(db, q_bp, seed + 1, **kw)
+    return db, f1, f2, present
+
+
+@pytest.mark.parametrize("seed,ratios", [(11, (0.9, 0.85)), (12, (0.8, 0.5)), (13, (0.3, 0.2)), (14, (0.99, 0.97))])
+def test_seeded_parity_all_records(oracle, seed, ratios):
+    db, f1, f2, _ = _case(seed, cov_lo=1.0, cov_hi=5.0)
+    coder = eref.random_coder(seed)
+    want = oracle.run(f1, f2, db.text, coder, *ratios, threads=4)
+    for prune in (True, False):
+        text, got = eref.run_eref(f1, f2, db.text, None, *ratios, 1, coder=coder, prune=prune, return_results=True)
+        assert (got == want).all(), f"seed {seed} prune={prune}"
+        assert text == oracle.format(want)
+    assert (want["el"] > 0).any()
+
+
+def test_table_levels_match_oracle_counts(oracle):
+    """level-L bitmap popcounts == number of codes the byte table holds at >= L (bin/extract_ref.cpp:995-997)"""
+    db, f1, f2, _ = _case(21, n_genomes=20, db_bp=300_000, q_bp=200_000)
+    coder = eref.random_coder(5)
+    # independent count on the CPU from the oracle's codes: concatenate reads as pseudo records
+    import collections
+    cnt = collections.Counter()
+    for fq in (f1, f2):
+        lines = fq.tobytes().split(b"\n")
+        for s in lines[1::4]:
+            if len(s) >= 32:
+                c = oracle.record_codes(coder, s).reshape(-1, 3)
+                ok = c.any(axis=1)                  # the oracle writes 0,0,0 for a window with an invalid base
+                cnt.update(c[ok].ravel().tolist())
+    with eref.ErefGPU(coder) as g:
+        g.query_add(f1); g.query_add(f2)
+        for level in (1, 2, 3):
+            assert g.query_popcount(level) == sum(1 for v in cnt.values() if v >= level)
+
+
+def test_seq_bytes_matches_cal_sam_ratio_sum(oracle, golden):
+    name, meta, fa, f1, f2 = golden
+    with eref.ErefGPU(meta["coder"]) as g:
+        assert g.query_add(f1) == oracle.fastq_seq_bytes(f1)
+        assert g.query_add(f2) == oracle.fastq_seq_bytes(f2)
+
+
+def test_edge_inputs(oracle):
+    coder = eref.random_coder(3)
+    fq = np.frombuffer(b"@r\n" + b"ACGT" * 10 + b"\n+\n" + b"I" * 40 + b"\n", np.uint8)
+    cases = {
+        "no records": b"",
+        "only short": b">a\nACGT\n>b\n" + b"A" * 32 + b"\n",
+        "no trailing newline": b">a\n" + b"ACGT" * 20,
+        "blank lines": b"\n\n>a\n\n" + b"ACGT" * 10 + b"\n\n" + b"TTGCA" * 10 + b"\n\n",
+        "exactly 33": b">a\n" + b"ACGTA" * 6 + b"CGT\n",
+    }
+    for name, fa in cases.items():
+        fa = np.frombuffer(fa, np.uint8)
+        want = oracle.run(fq, fq, fa, coder)
+        _, got = eref.run_eref(fq, fq, fa, None, 0.9, 0.85, 1, coder=coder, return_results=True)
+        assert got.size == want.size and (got == want).all(), name
+    # empty fq1: the reference divides by zero (:1145); the product refuses loudly
+    with pytest.raises(eref.ErefError):
+        eref.run_eref(np.zeros(0, np.uint8), fq, np.frombuffer(cases["exactly 33"], np.uint8), coder=coder)
+    # a coder entry outside {0,1,2} is rejected
+    bad = coder.copy(); bad[5] = 7
+    with pytest.raises(eref.ErefError):
+        eref.ErefGPU(bad)
+
+
+# ---- (c) properties that hold at any size ----------------------------------------------------------
+
+def test_shard_invariance_and_idempotence(oracle):
+    """splitting the DB at record boundaries and merging ordinals gives the same records; a second scan too"""
+    db, f1, f2, _ = _case(31, n_genomes=120, db_bp=3_000_000, q_bp=600_000)
+    coder = eref.random_coder(31)
+    _, whole = eref.run_eref(f1, f2, db.text, coder=coder, return_results=True)
+    _, three = eref.run_eref(f1, f2, db.text, coder=coder, devices=(0, 0, 0), return_results=True)
+    assert (whole == three).all()
+    with eref.ErefGPU(coder) as g:
+        g.query_add(f1); g.query_add(f2); g.ref_set(db.text)
+        a = g.scan().copy(); b = g.scan().copy()
+        assert (a == b).all() and (a == whole).all()
+        # counting the same reads again cannot remove hits: every el stays or grows
+        g.query_add(f1); g.query_add(f2)
+        c = g.scan()
+        assert (c["el"] >= a["el"]).all()
+
+
+def test_strand_and_order_invariance():
+    """reverse-complementing every read, or swapping fq1/fq2, leaves the table and the result unchanged"""
+    db, f1, f2, _ = _case(41, n_genomes=40, db_bp=1_000_000, q_bp=300_000)
+    coder = eref.random_coder(41)
+    comp = bytes.maketrans(b"ACGTN", b"TGCAN")
+
+    def rc_fastq(fq):
+        lines = fq.tobytes().split(b"\n")
+        for i in range(1, len(lines), 4):
+            lines[i] = lines[i].translate(comp)[::-1]
+        return np.frombuffer(b"\n".join(lines), np.uint8)
+
+    _, a = eref.run_eref(f1, f2, db.text, coder=coder, return_results=True)
+    _, b = eref.run_eref(rc_fastq(f1), rc_fastq(f2), db.text, coder=coder, return_results=True)
+    _, c = eref.run_eref(f2, f1, db.text, coder=coder, return_results=True)
+    assert (a == b).all() and (a == c).all()
+    assert (a["el"] > 0).any()
+
+
+def test_present_genomes_are_selected_at_depth():
+    """a genome tiled at 8x by error-free reads is reported with el_ratio ~ 1; absent genomes are not"""
+    db = synth.make_db(50, 1_000_000, 51, frac_mutated=0.0, frac_n=0.0, frac_lower=0.0, n_short=0)
+    present = np.array([3, 17, 30])
+    f1, f2, _ = synth.make_reads(db, 0, 52, cov_lo=8, cov_hi=8, sub_rate=0.0, n_rate=0.0, present=present)
+    coder = eref.random_coder(51)
+    text, res = eref.run_eref(f1, f2, db.text, coder=coder, return_results=True)
+    sel = {int(l.split("\t")[1]) for l in text.splitlines()}
+    assert sel == {int(p) + 1 for p in present}
+    absent = np.setdiff1d(np.arange(50), present)
+    assert (res["el"][absent] == 0).all()
+
+
+def test_eref_binary_end_to_end(golden, tmp_path):
+    """the drop-in executable: same argv, stdout and side-effect files as the reference"""
+    name, meta, fa, f1, f2 = golden
+    if not os.path.exists(eref.EREF_BIN):
+        pytest.fail("palace_b200/bin/eref not built")
+    fa.tofile(tmp_path / "db.fa"); f1.tofile(tmp_path / "r1.fq"); f2.tofile(tmp_path / "r2.fq")
+    # a reference-format index header next to the DB carries the coder (what a shared DB directory holds)
+    hdr = np.zeros(100, "<u4"); hdr[:96] = np.asarray(meta["coder"], np.uint32)
+    hdr.tofile(tmp_path / "db.fa.k32.index.dat")
+    for key, expect in meta["stdout"].items():
+        hr, phr = key.split(",")
+        for gpus in ("1", "2"):
+            env = dict(os.environ, EREF_GPUS=gpus)
+            if gpus == "2" and eref.load_library().eref_device_count() < 2:
+                continue
+            r = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "4"], cwd=tmp_path,
+                               capture_output=True, env=env)
+            assert r.returncode == 0, r.stderr.decode()
+            assert r.stdout.decode() == expect, f"{name} {key} gpus={gpus}"
+            assert (tmp_path / "tmp_out.txt").exists() and (tmp_path / "tmp_out.txt").stat().st_size == 0

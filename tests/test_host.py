@@ -1,0 +1,89 @@
+"""CPU suite, part 3: host-side logic — sharding at record boundaries, the down-sampling guard, and
+the N>1 merge (allgather of padded fixed-size records, ordinal offsets) over gloo with world_size 2."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from palace_b200 import eref, synth
+from palace_b200.dist import merge_gathered, pad_records
+
+
+def test_shard_offsets_start_at_headers():
+    db = synth.make_db(30, 200_000, 3, min_len=2000, max_len=20000)
+    for shards in (1, 2, 3, 8):
+        cuts = eref.shard_offsets(db.text, shards)
+        assert cuts[0] == 0 and cuts[-1] == db.text.size and len(cuts) == shards + 1
+        assert all(a <= b for a, b in zip(cuts, cuts[1:]))
+        for c in cuts[1:-1]:
+            assert c == db.text.size or (db.text[c] == ord(">") and db.text[c - 1] == ord("\n"))
+
+
+def test_shards_cover_all_records(oracle):
+    db = synth.make_db(30, 200_000, 4, min_len=2000, max_len=20000, n_short=4)
+    whole, _ = oracle.parse_fasta(db.text)
+    for shards in (2, 5):
+        cuts = eref.shard_offsets(db.text, shards)
+        parts = []
+        for i in range(shards):
+            parts += oracle.parse_fasta(db.text[cuts[i]:cuts[i + 1]])[0]
+        assert parts == whole
+
+
+def test_sample_ratio_guard():
+    assert eref.check_sample_ratio(50_000_000) >= 100
+    assert eref.check_sample_ratio(1_000_000_000) == 100
+    with pytest.raises(eref.ErefError):
+        eref.check_sample_ratio(1_000_000_001 + 10_000_000)       # ratio 99: the reference would down-sample
+    with pytest.raises(eref.ErefError):
+        eref.check_sample_ratio(0)
+
+
+def test_merge_gathered_offsets_ordinals():
+    a = np.zeros(3, eref.RESULT_DTYPE); a["ordinal"] = [1, 2, 3]; a["el"] = [5, 0, 7]
+    b = np.zeros(2, eref.RESULT_DTYPE); b["ordinal"] = [1, 2]; b["el"] = [9, 1]
+    slot = 3
+    flat = np.concatenate([pad_records(a, slot), pad_records(b, slot)])
+    out = merge_gathered(flat, [3, 2], slot)
+    assert out["ordinal"].tolist() == [1, 2, 3, 4, 5]
+    assert out["el"].tolist() == [5, 0, 7, 9, 1]
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    from palace_b200.dist import allgather_records
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n = 4 if rank == 0 else 2                                  # ragged shards
+        rec = np.zeros(n, eref.RESULT_DTYPE)
+        rec["ordinal"] = np.arange(1, n + 1); rec["el"] = 100 * (rank + 1) + np.arange(n); rec["ref_len"] = 1000
+        merged = allgather_records(torch.from_numpy(rec.view(np.uint32).reshape(n, 4).astype(np.int32)), n)
+        q.put((rank, merged.tolist()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_allgather_records_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    ps = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[0] == got[1]                                        # allgather: every rank holds the merge
+    ords = [r[0] for r in got[0]]
+    assert ords == [1, 2, 3, 4, 5, 6]
+    assert [r[2] for r in got[0]] == [100, 101, 102, 103, 200, 201]
