@@ -1,0 +1,429 @@
+#!/usr/bin/env python
+"""bench.py — reference Gbp k-mer-screened per second on B200 (BASELINE.json's metric).
+
+A step = one pass of the whole `eref` hot path over one synthetic sample: zero the 2^32-slot table,
+frame+pack+count both FASTQ files, frame+pack the FASTA database, scan it (candidate filter, probes,
+500-position window rule, interval merge) down to one {ordinal, frag, el, ref_len} record per
+reference and, at N>1, allgather the records (the path's only collective).
+
+  value   inputs already resident in HBM (eref_*_device entry points), CUDA events, max over ranks
+  e2e     the same through the host-buffer C ABI calls (pinned host -> H2D -> ... -> D2H of the records)
+
+Workload at N=1: BASELINE.json configs[1] — 50 Mbp reads vs a 10,000-genome ~500 Mbp phage DB.
+At N>1 every rank holds its own 10,000-genome shard (weak scaling); the query is replicated.
+`--impl reference` times the reference's own CPU implementation (oracle/_ref/eref_ref, else the
+oracle port) on a bounded sample of the same generator on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "reference Gbp k-mer-screened/sec"
+UNIT = "Gbp/s"
+WORKLOADS = {
+    # name: (genomes per GPU shard, DB bp per shard, query bp total)
+    "c2": (10000, 500_000_000, 50_000_000),
+    "c1": (1000, 50_000_000, 5_000_000),
+    "small": (400, 20_000_000, 2_000_000),
+}
+WORKLOAD_DESC = {
+    "c2": "BASELINE configs[1]: 50 Mbp reads vs 10,000-genome ~500 Mbp synthetic phage DB per GPU",
+    "c1": "BASELINE configs[0]: 5 Mbp reads vs 1,000-genome ~50 Mbp synthetic phage DB per GPU",
+    "small": "development: 2 Mbp reads vs 400-genome 20 Mbp DB per GPU",
+}
+# algorithmic bytes per unit (restated in DESIGN.md)
+BYTES_PER_REF_BASE_FULL = 97.0        # 1 B text + 3 probes x 32 B sector
+BYTES_PER_QUERY_BASE_BUILD = 193.0    # 1 B text + 3 codes x (32 B sector fill + 32 B write-back)
+BYTES_PER_REF_BASE_SAMPLED = 0.375 + 8.0 + 1.0 / 32   # planes + one 32 B sector per 4 positions + 1 B/word out
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def gen_inputs(workload, rank, world):
+    from palace_b200 import synth
+    G, R, Q = WORKLOADS[workload]
+    db = synth.make_db(G, R, 1000 + rank)
+    f1, f2, _ = synth.make_reads(db, Q // world, 2000 + rank)
+    return db.text, f1, f2, int(db.lengths.sum())
+
+
+def gather_bytes(t_local, world, device):
+    """replicate the query: concatenate every rank's FASTQ part, in rank order (setup, not timed)"""
+    import torch
+    import torch.distributed as dist
+    n = torch.tensor([t_local.numel()], dtype=torch.int64, device=device)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n)
+    sizes = [int(s.item()) for s in sizes]
+    slot = max(sizes)
+    buf = torch.zeros(slot, dtype=torch.uint8, device=device)
+    buf[: t_local.numel()] = t_local
+    out = torch.empty(world * slot, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(out, buf)
+    return torch.cat([out[r * slot: r * slot + sizes[r]] for r in range(world)])
+
+
+PHASES = ("query_pack_ms", "query_count_ms", "ref_frame_ms", "ref_pack_ms", "scan_sample_ms", "scan_cand_ms",
+          "scan_probe_ms", "scan_window_ms", "scan_interval_ms")
+PHASE_KERNEL = {
+    "query_pack_ms": "k_count_newlines+k_pack_fastq", "query_count_ms": "k_count_kmers",
+    "ref_frame_ms": "FASTA framing kernels + scans", "ref_pack_ms": "k_pack_fasta",
+    "scan_sample_ms": "k_probe_sampled", "scan_cand_ms": "k_candidates+k_need", "scan_probe_ms": "k_probe_full",
+    "scan_window_ms": "k_window", "scan_interval_ms": "k_intervals",
+}
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from palace_b200 import eref
+    from palace_b200.dist import allgather_records
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the eref path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    fa_np, f1_np, f2_np, shard_bases = gen_inputs(args.workload, rank, world)
+    stream = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(stream):
+        fa_h = torch.from_numpy(fa_np).pin_memory()
+        fa_d = fa_h.to(dev, non_blocking=True)
+        f1_d = torch.from_numpy(f1_np).to(dev)
+        f2_d = torch.from_numpy(f2_np).to(dev)
+        if world > 1:
+            f1_d = gather_bytes(f1_d, world, dev)
+            f2_d = gather_bytes(f2_d, world, dev)
+        f1_h = f1_d.cpu().pin_memory()
+        f2_h = f2_d.cpu().pin_memory()
+    stream.synchronize()
+    query_bases = None
+
+    coder = eref.random_coder(1)                       # EREF_CODER_SEED=1 convention for GPU-only runs
+    g = eref.ErefGPU(coder, 0.9, 0.85, device=local, prune=not args.no_prune)
+    g.set_stream(stream.cuda_stream)
+    acc = {p: 0.0 for p in PHASES}
+    info = {}
+
+    def step_device(collect):
+        g.query_reset()
+        g.query_add_device(f1_d.data_ptr(), f1_d.numel())
+        t1 = g.timings()
+        g.query_add_device(f2_d.data_ptr(), f2_d.numel())
+        t2 = g.timings()
+        g.ref_set_device(fa_d.data_ptr(), fa_d.numel())
+        ptr, n = g.scan_device()
+        t3 = g.timings()
+        merged = None
+        if world > 1:
+            merged = allgather_records(device_records(ptr, n, dev), n)
+        if collect:
+            acc["query_pack_ms"] += t1["query_pack_ms"] + t2["query_pack_ms"]
+            acc["query_count_ms"] += t1["query_count_ms"] + t2["query_count_ms"]
+            for p in PHASES[2:]:
+                acc[p] += t3[p]
+            info.update(ref_bases=t3["ref_bases"], ref_words=t3["ref_words"], need_words=t3["ref_need_words"],
+                        seq_bytes=t1["query_seq_bytes"] + t2["query_seq_bytes"], n_records=n)
+        return merged
+
+    def step_host():
+        g.query_reset()
+        g.query_add(f1_h.numpy())
+        g.query_add(f2_h.numpy())
+        g.ref_set(fa_h.numpy())
+        if world > 1:
+            ptr, n = g.scan_device()
+            merged = allgather_records(device_records(ptr, n, dev), n)
+            return merged.cpu() if rank == 0 else None
+        return g.scan()
+
+    def device_records(ptr, n, dev):
+        # zero-copy view of the library's result buffer (n x 4 uint32) as a torch tensor
+        if n == 0:
+            return torch.zeros((0, 4), dtype=torch.int32, device=dev)
+        class _Arr:                                    # __cuda_array_interface__ v2
+            pass
+        a = _Arr()
+        a.__cuda_array_interface__ = {"shape": (n, 4), "typestr": "<i4", "data": (ptr, True), "version": 2}
+        return torch.as_tensor(a, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step_device(False)
+        barrier()
+        launches0 = g.timings()["kernel_launches"]
+        sampler = ClockSampler(local) if rank == 0 else None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            merged = step_device(True)
+        e1.record(stream)
+        barrier()
+        dev_ms = e0.elapsed_time(e1)
+        launches = g.timings()["kernel_launches"] - launches0
+        clocks = sampler.stop() if sampler else None
+        # ---- e2e: host buffers through the C ABI ----
+        for _ in range(min(args.warmup, 2)):
+            step_host()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            res = step_host()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+
+    dev_ms = max_over_ranks(dev_ms)
+    e2e_s = max_over_ranks(e2e_s)
+    total_bases = sum_over_ranks(float(info["ref_bases"]))
+    launches = int(sum_over_ranks(float(launches)))
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_per_step = dev_ms / args.steps
+    value = total_bases / 1e9 / (ms_per_step / 1e3)
+    e2e_value = total_bases / 1e9 / (e2e_s / args.steps)
+    peak, peak_src = peaks()
+    avg = {p: acc[p] / args.steps for p in PHASES}
+    dom = max(avg, key=avg.get)
+    qbases = info["seq_bytes"]
+    alg = {
+        "query_count_ms": BYTES_PER_QUERY_BASE_BUILD * qbases,
+        "query_pack_ms": 2.0 * (f1_d.numel() + f2_d.numel()),
+        "scan_probe_ms": BYTES_PER_REF_BASE_FULL * info["ref_bases"] if args.no_prune else
+        (96.0 + 0.625) * 32 * info["need_words"],
+        "scan_sample_ms": BYTES_PER_REF_BASE_SAMPLED * info["ref_bases"],
+        "ref_pack_ms": 1.0 * fa_d.numel() + 0.5 * info["ref_bases"],
+        "ref_frame_ms": 2.0 * fa_d.numel(),
+    }.get(dom, 0.0)
+    achieved = alg / 1e9 / (avg[dom] / 1e3) if avg[dom] > 0 else 0.0
+    scan_ms = sum(avg[p] for p in PHASES if p.startswith("scan_"))
+    out = {
+        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": WORKLOAD_DESC[args.workload], "db_bases_per_gpu": int(info["ref_bases"]),
+                   "query_seq_bases": int(qbases), "records_per_gpu": int(info["n_records"]), "k": 32,
+                   "hit_ratio": 0.9, "perfect_hit_ratio": 0.85, "parallelism": f"db-shard x{world}, query replicated",
+                   "candidate_filter": not args.no_prune,
+                   "l2": "inputs larger than L2: per step 1.5 GiB of table levels are rewritten and >0.5 GB of text read"},
+        "e2e": {"value": round(e2e_value, 3), "unit": UNIT,
+                "h2d_bytes_per_step": int(f1_h.numel() + f2_h.numel() + fa_h.numel()),
+                "d2h_bytes_per_step": int(info["n_records"]) * 16 + 24, "ms_per_step": round(e2e_s / args.steps * 1e3, 3)},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "phases_ms": {k: round(v, 4) for k, v in avg.items()},
+        "scan_only": {"ms": round(scan_ms, 4), "value": round(info["ref_bases"] / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT,
+                      "frac_of_hbm_at_97B_per_base": round(BYTES_PER_REF_BASE_FULL * info["ref_bases"] / 1e9 /
+                                                           (scan_ms / 1e3) / peak, 3)},
+        "roofline": {"bound": "hbm", "kernel": PHASE_KERNEL[dom], "achieved": round(achieved, 1), "peak": peak,
+                     "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4)},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(budget_runs=1)
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---- the reference's CPU implementation on the host cores -----------------------------------------
+
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "eref_ref")
+ORACLE_BIN = os.path.join(ROOT, "oracle", "eref_oracle")
+
+
+def _host_mem_gb():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable"):
+                return int(line.split()[1]) / 1e6
+    except Exception:
+        pass
+    return 0.0
+
+
+class CpuArm:
+    """A bounded sample of the bench workload (same generator, C1-sized by default) on disk, and one
+    timed invocation of the reference per step.  kind = "reference": the UNMODIFIED reference binary
+    built from /root/reference/bin/extract_ref.cpp (needs ~24 GB RAM, ~14 s fixed cost per run);
+    kind = "port": oracle/eref_oracle (the C restatement) when the binary or the memory is missing."""
+
+    def __init__(self, sample="c1", prefer_reference=True):
+        from palace_b200 import synth
+        G, R, Q = WORKLOADS[sample]
+        self.dir = tempfile.mkdtemp(prefix="eref_cpu_")
+        db = synth.make_db(G, R, 1000)
+        f1, f2, _ = synth.make_reads(db, Q, 2000)
+        db.text.tofile(os.path.join(self.dir, "db.fa"))
+        f1.tofile(os.path.join(self.dir, "r1.fq")); f2.tofile(os.path.join(self.dir, "r2.fq"))
+        self.bases = int(db.lengths.sum())
+        self.cores = os.cpu_count() or 1
+        use_ref = prefer_reference and os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK) and _host_mem_gb() > 30
+        self.kind = "reference" if use_ref else "port"
+        self.bin = REF_BIN if use_ref else ORACLE_BIN
+        if not use_ref and not os.path.exists(ORACLE_BIN):
+            subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "eref_oracle"], check=True, capture_output=True)
+        self.sample = (f"{G}-genome {self.bases / 1e6:.0f} Mbp DB + {Q / 1e6:.0f} Mbp reads (same generator and seeds as the "
+                       f"GPU arm, BASELINE configs[0] size), threads={self.cores}")
+        self.stdout = None
+
+    def run_once(self):
+        env = dict(os.environ, EREF_CODER_SEED="1", EREF_ORACLE_WRITE_INDEX="1")
+        t0 = time.perf_counter()
+        r = subprocess.run([self.bin, "r1.fq", "r2.fq", "db.fa", "tmp.txt", "0.9", "0.85", str(self.cores)], cwd=self.dir,
+                           capture_output=True, env=env)
+        dt = time.perf_counter() - t0
+        if r.returncode != 0:
+            raise RuntimeError(f"{self.bin} failed: {r.stderr.decode()[-400:]}")
+        self.stdout = r.stdout
+        return dt
+
+    def close(self):
+        import shutil
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
+def cpu_baseline(budget_runs=1):
+    arm = CpuArm("c1")
+    try:
+        cold = arm.run_once()                          # builds <db>.k32.index.dat serially (:1250)
+        warm = min(arm.run_once() for _ in range(budget_runs))
+        return {"value": round(arm.bases / 1e9 / warm, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
+                "sample": arm.sample + "; value = warm run (index on disk)", "warm_s": round(warm, 2),
+                "cold_s": round(cold, 2), "cold_value": round(arm.bases / 1e9 / cold, 6),
+                "selected_refs": arm.stdout.count(b"\n")}
+    finally:
+        arm.close()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    arm = CpuArm("c1" if args.steps + args.warmup <= 12 else "small", prefer_reference=args.steps + args.warmup <= 12)
+    try:
+        cold = arm.run_once()                          # index build, untimed setup
+        for _ in range(args.warmup):
+            arm.run_once()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            arm.run_once()
+        dt = time.perf_counter() - t0
+        ms = dt / args.steps * 1e3
+        value = arm.bases / 1e9 / (dt / args.steps)
+        out = {
+            "impl": "reference", "metric": METRIC, "value": round(value, 6), "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 2), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[args.workload], "k": 32, "hit_ratio": 0.9, "perfect_hit_ratio": 0.85},
+            "cpu_baseline": {"value": round(value, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
+                             "sample": arm.sample + "; each step = one whole eref process, index already on disk",
+                             "cold_s": round(cold, 2)},
+            "e2e": {"value": round(value, 6), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(out), flush=True)
+    finally:
+        arm.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-prune", action="store_true", help="probe all three streams at every position")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        print(f"bench.py: warmup {args.warmup} < 3 breaks the timing rules", file=sys.stderr)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
