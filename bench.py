@@ -116,10 +116,12 @@ def gather_bytes(t_local, world, device):
     return torch.cat([out[r * slot: r * slot + sizes[r]] for r in range(world)])
 
 
-PHASES = ("query_pack_ms", "query_count_ms", "ref_frame_ms", "ref_pack_ms", "scan_sample_ms", "scan_cand_ms",
-          "scan_probe_ms", "scan_window_ms", "scan_interval_ms")
+QUERY_PHASES = ("query_pack_ms", "query_bucket_ms", "query_count_ms")
+PHASES = QUERY_PHASES + ("ref_frame_ms", "ref_pack_ms", "scan_summary_ms", "scan_sample_ms", "scan_cand_ms",
+                         "scan_probe_ms", "scan_window_ms", "scan_interval_ms")
 PHASE_KERNEL = {
-    "query_pack_ms": "k_count_newlines+k_pack_fastq", "query_count_ms": "k_count_kmers",
+    "query_pack_ms": "k_count_newlines+k_pack_fastq", "query_bucket_ms": "k_bucket_codes<hist>+<scatter>",
+    "query_count_ms": "k_count_codes", "scan_summary_ms": "k_build_summary",
     "ref_frame_ms": "FASTA framing kernels + scans", "ref_pack_ms": "k_pack_fasta",
     "scan_sample_ms": "k_probe_sampled", "scan_cand_ms": "k_candidates+k_need", "scan_probe_ms": "k_probe_full",
     "scan_window_ms": "k_window", "scan_interval_ms": "k_intervals",
@@ -178,12 +180,13 @@ def run_b200(args):
         if world > 1:
             merged = allgather_records(device_records(ptr, n, dev), n)
         if collect:
-            acc["query_pack_ms"] += t1["query_pack_ms"] + t2["query_pack_ms"]
-            acc["query_count_ms"] += t1["query_count_ms"] + t2["query_count_ms"]
-            for p in PHASES[2:]:
+            for p in QUERY_PHASES:
+                acc[p] += t1[p] + t2[p]
+            for p in PHASES[len(QUERY_PHASES):]:
                 acc[p] += t3[p]
             info.update(ref_bases=t3["ref_bases"], ref_words=t3["ref_words"], need_words=t3["ref_need_words"],
-                        seq_bytes=t1["query_seq_bytes"] + t2["query_seq_bytes"], n_records=n)
+                        seq_bytes=t1["query_seq_bytes"] + t2["query_seq_bytes"], n_records=n,
+                        query_codes=t1["query_codes"] + t2["query_codes"])
         return merged
 
     def step_host():
@@ -268,6 +271,8 @@ def run_b200(args):
     qbases = info["seq_bytes"]
     alg = {
         "query_count_ms": BYTES_PER_QUERY_BASE_BUILD * qbases,
+        "query_bucket_ms": 2 * 0.375 * (f1_d.numel() + f2_d.numel()) + 4.0 * info["query_codes"],
+        "scan_summary_ms": 4.0 * (1 << 27) + 4.0 * (1 << 23),
         "query_pack_ms": 2.0 * (f1_d.numel() + f2_d.numel()),
         "scan_probe_ms": BYTES_PER_REF_BASE_FULL * info["ref_bases"] if args.no_prune else
         (96.0 + 0.625) * 32 * info["need_words"],

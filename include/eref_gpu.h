@@ -32,6 +32,7 @@ extern "C" {
 
 /* eref_create flags */
 #define EREF_FLAG_NO_PRUNE 1u          /* probe all three streams at every position (no candidate filter) */
+#define EREF_FLAG_DIRECT_COUNT 2u      /* count k-mers straight into the table (no code-range bucketing) */
 
 typedef struct eref_ctx eref_ctx;
 
@@ -45,12 +46,14 @@ typedef struct {
 
 /* CUDA-event times of the last call of each phase, in milliseconds, and launch counts */
 typedef struct {
-    float query_h2d_ms, query_pack_ms, query_count_ms;      /* last eref_query_add* */
-    float ref_h2d_ms, ref_frame_ms, ref_pack_ms;            /* last eref_ref_set*   */
-    float scan_sample_ms, scan_cand_ms, scan_probe_ms, scan_window_ms, scan_interval_ms, scan_d2h_ms;
+    float query_h2d_ms, query_pack_ms, query_bucket_ms, query_count_ms;   /* last eref_query_add* */
+    float ref_h2d_ms, ref_frame_ms, ref_pack_ms;                          /* last eref_ref_set*   */
+    float scan_summary_ms, scan_sample_ms, scan_cand_ms, scan_probe_ms, scan_window_ms, scan_interval_ms,
+          scan_d2h_ms;                                                    /* last eref_scan*      */
     uint64_t kernel_launches;                               /* since eref_create */
     uint64_t ref_bases, ref_words, ref_need_words;          /* last scan */
     uint64_t query_seq_bytes;                               /* last eref_query_add* (cal_sam_ratio's sum) */
+    uint64_t query_codes;                                   /* last eref_query_add*: codes counted (3 per valid 32-mer) */
 } eref_phase_times;
 
 const char* eref_last_error(void);

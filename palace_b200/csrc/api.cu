@@ -45,7 +45,7 @@ struct DevBuf {
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
-enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, EV_COUNT };
+enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, EV_COUNT };
 
 } // namespace
 
@@ -63,6 +63,11 @@ struct eref_ctx {
     DevBuf tile_counts, tile_prefix, cub_tmp, counters;      // counters: 4 x u64
     // query side
     DevBuf q_text, q_hi, q_lo, q_ok;
+    DevBuf bucket_ctr;                         // u64: hist[32] | tail[32] | off[33]
+    DevBuf q_codes;                            // bucket-ordered code list of the file being counted
+    uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
+    bool summary_stale = true;
+    unsigned long long h_hist[NBUCKETS_HOST] = {}, h_off[NBUCKETS_HOST + 1] = {};
     // reference side
     DevBuf r_text, nl_pos, line_val, line_cum, rec_hdr_line, rec_first, rec_len, rec_kept, rec_words,
         rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
@@ -145,15 +150,40 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     CUDA_TRY(cudaMemsetAsync(seq_bytes, 0, 8, st));
     LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), pl, seq_bytes, st));
     CUDA_TRY(cudaEventRecord(c->ev[E2], st));
-    LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
-    CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+    c->summary_stale = true;
+    unsigned long long total_codes = 0;
+    if (c->flags & EREF_FLAG_DIRECT_COUNT) {
+        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
+    } else {
+        // codes -> 32 code-range buckets (histogram, exact offsets, scatter), then bucket-ordered counting
+        CUDA_TRY(c->bucket_ctr.ensure((NBUCKETS_HOST * 2 + NBUCKETS_HOST + 1) * 8));
+        unsigned long long* hist = c->bucket_ctr.as<unsigned long long>();
+        unsigned long long* tail = hist + NBUCKETS_HOST;
+        unsigned long long* off = tail + NBUCKETS_HOST;
+        CUDA_TRY(cudaMemsetAsync(hist, 0, NBUCKETS_HOST * 2 * 8, st));
+        LAUNCH(c, launch_bucket_hist(pl, c->masks, hist, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_hist, hist, NBUCKETS_HOST * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        c->h_off[0] = 0;
+        for (int b = 0; b < NBUCKETS_HOST; b++) c->h_off[b + 1] = c->h_off[b] + c->h_hist[b];
+        total_codes = c->h_off[NBUCKETS_HOST];
+        CUDA_TRY(cudaMemcpyAsync(off, c->h_off, (NBUCKETS_HOST + 1) * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(c->q_codes.ensure((size_t)total_codes * 4 + 16));
+        LAUNCH(c, launch_bucket_scatter(pl, c->masks, off, tail, c->q_codes.as<uint32_t>(), st));
+        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        LAUNCH(c, launch_count_codes(c->q_codes.as<uint32_t>(), total_codes, c->bm[0], c->bm[1], c->bm[2], st));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[E4], st));
     unsigned long long h = 0;
     CUDA_TRY(cudaMemcpyAsync(&h, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     c->t.query_seq_bytes = h;
+    c->t.query_codes = total_codes;
     c->t.query_h2d_ms = ev_ms(c, E0, E1);
     c->t.query_pack_ms = ev_ms(c, E1, E2);
-    c->t.query_count_ms = ev_ms(c, E2, E3);
+    c->t.query_bucket_ms = ev_ms(c, E2, E3);
+    c->t.query_count_ms = ev_ms(c, E3, E4);
     return 0;
 }
 
@@ -269,10 +299,15 @@ int scan_impl(eref_ctx* c)
     const uint8_t* need = nullptr;
     unsigned long long* need_count = c->counters.as<unsigned long long>() + 1;
     CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+    if (prune && c->summary_stale) {
+        LAUNCH(c, launch_build_summary(c->bm[2], c->summary, st));
+        c->summary_stale = false;
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[E8], st));
     if (prune) {
         CUDA_TRY(c->sample_hits.ensure(nw + 1)); CUDA_TRY(c->cand.ensure(nw + 1)); CUDA_TRY(c->need.ensure(nw + 1));
         CUDA_TRY(cudaMemsetAsync(need_count, 0, 8, st));
-        LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->sample_hits.as<uint8_t>(), st));
+        LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->summary, c->sample_hits.as<uint8_t>(), st));
         CUDA_TRY(cudaEventRecord(c->ev[E1], st));
         LAUNCH(c, launch_candidates(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(),
                                     c->g_word.as<uint32_t>(), nw, min_sample_hits, c->cand.as<uint8_t>(), st));
@@ -297,7 +332,8 @@ int scan_impl(eref_ctx* c)
 
 void scan_times(eref_ctx* c, bool with_d2h)
 {
-    c->t.scan_sample_ms = ev_ms(c, E0, E1);
+    c->t.scan_summary_ms = ev_ms(c, E0, E8);
+    c->t.scan_sample_ms = ev_ms(c, E8, E1);
     c->t.scan_cand_ms = ev_ms(c, E1, E2);
     c->t.scan_probe_ms = ev_ms(c, E2, E3);
     c->t.scan_window_ms = ev_ms(c, E3, E4);
@@ -346,6 +382,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
     if (e == cudaSuccess) e = c->counters.ensure(64);
+    if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
     if (e != cudaSuccess) { eref_destroy(c); return eref_fail_cuda(e, "context allocation", __FILE__, __LINE__); }
     c->stream = c->own_stream;
     *out = c;
@@ -367,6 +404,8 @@ void eref_destroy(eref_ctx* c)
                       &c->codes_tmp};
     for (DevBuf* b : bufs) b->release();
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
+    if (c->summary) cudaFree(c->summary);
+    c->bucket_ctr.release(); c->q_codes.release();
     for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
@@ -386,6 +425,7 @@ int eref_query_reset(eref_ctx* c)
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
     CUDA_TRY(cudaSetDevice(c->device));
     for (int l = 0; l < 3; l++) CUDA_TRY(cudaMemsetAsync(c->bm[l], 0, (size_t)TABLE_WORDS * 4, c->stream));
+    c->summary_stale = true;
     return 0;
 }
 

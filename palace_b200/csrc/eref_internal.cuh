@@ -13,6 +13,8 @@ constexpr int      TILE_BYTES   = TILE_THREADS * 32;
 constexpr uint32_t TABLE_WORDS  = 1u << 27;          // 2^32 one-bit slots per level (bin/extract_ref.cpp:25)
 constexpr int      WINDOW       = 500;               // :510
 constexpr int      WIN_WORDS    = 16;                // a 500-position window reaches back 16 words
+constexpr uint32_t SUMMARY_WORDS = 1u << 23;         // level-3 summary: 1 bit per 16 slots = 32 MiB
+constexpr int      NBUCKETS_HOST = 32;               // code-range buckets of the table build (table.cu)
 constexpr int      SAMPLE_STRIDE = 4;                // candidate filter probes every 4th position
 
 // Per-stream select masks of the coder assignment: bit (31-z) of sel0[i] (sel2[i]) is set iff code
@@ -124,9 +126,15 @@ cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const uint32_t* n
 // table.cu
 cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
                                cudaStream_t st);
+cudaError_t launch_bucket_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st);
+cudaError_t launch_bucket_scatter(Planes pl, CoderMasks m, const unsigned long long* bucket_off,
+                                  unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st);
+cudaError_t launch_count_codes(const uint32_t* codes, uint64_t n, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
+                               cudaStream_t st);
+cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, cudaStream_t st);
 cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);
 // scan.cu
-cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, uint8_t* sample_hits,
+cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary, uint8_t* sample_hits,
                                  cudaStream_t st);
 cudaError_t launch_candidates(const uint8_t* sample_hits, const uint32_t* word_genome,
                               const uint32_t* g_word, uint64_t nwords, int min_sample_hits,

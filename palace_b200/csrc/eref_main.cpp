@@ -10,6 +10,7 @@
 //   EREF_GPUS=N|all     GPUs to shard the database over (default: one per 128 MiB of FASTA, <= visible)
 //   EREF_CODER_SEED=S   seed of the coder draw when <db>.k32.index.dat does not exist (default time(0), :1088)
 //   EREF_NO_PRUNE=1     probe all three streams everywhere (disables the exact candidate filter)
+//   EREF_DIRECT_COUNT=1 count k-mers straight into the table (disables the code-range bucketing)
 //   EREF_TIMING=1       per-phase CUDA-event times on stderr
 #include "eref_gpu.h"
 #include <cuda_runtime.h>
@@ -181,7 +182,8 @@ int main(int argc, char** argv)
         if (shards < 1 || shards > ndev) { fprintf(stderr, "eref: EREF_GPUS=%s but %d device(s) visible\n", g, ndev); return 3; }
     }
     std::vector<size_t> cut = shard_offsets(fa.p, fa.n, shards);
-    const unsigned flags = getenv("EREF_NO_PRUNE") ? EREF_FLAG_NO_PRUNE : 0u;
+    const unsigned flags = (getenv("EREF_NO_PRUNE") ? EREF_FLAG_NO_PRUNE : 0u) |
+                           (getenv("EREF_DIRECT_COUNT") ? EREF_FLAG_DIRECT_COUNT : 0u);
 
     std::vector<ncclComm_t> comms(shards);
     if (shards > 1) {
@@ -299,10 +301,10 @@ int main(int argc, char** argv)
         for (int i = 0; i < shards; i++) {
             const eref_phase_times& t = times[i];
             fprintf(stderr,
-                    "  gpu %d: fq2 h2d %.3f pack %.3f count %.3f | ref h2d %.3f frame %.3f pack %.3f | scan sample %.3f cand %.3f "
+                    "  gpu %d: fq2 h2d %.3f pack %.3f bucket %.3f count %.3f | ref h2d %.3f frame %.3f pack %.3f | scan summary %.3f sample %.3f cand %.3f "
                     "probe %.3f window %.3f intervals %.3f d2h %.3f ms | bases %llu need_words %llu/%llu launches %llu\n",
-                    i, t.query_h2d_ms, t.query_pack_ms, t.query_count_ms, t.ref_h2d_ms, t.ref_frame_ms, t.ref_pack_ms,
-                    t.scan_sample_ms, t.scan_cand_ms, t.scan_probe_ms, t.scan_window_ms, t.scan_interval_ms, t.scan_d2h_ms,
+                    i, t.query_h2d_ms, t.query_pack_ms, t.query_bucket_ms, t.query_count_ms, t.ref_h2d_ms, t.ref_frame_ms, t.ref_pack_ms,
+                    t.scan_summary_ms, t.scan_sample_ms, t.scan_cand_ms, t.scan_probe_ms, t.scan_window_ms, t.scan_interval_ms, t.scan_d2h_ms,
                     (unsigned long long)t.ref_bases, (unsigned long long)t.ref_need_words, (unsigned long long)t.ref_words,
                     (unsigned long long)t.kernel_launches);
         }

@@ -19,8 +19,11 @@ __device__ __forceinline__ uint32_t probe(const uint32_t* __restrict__ bm3, uint
 }
 
 // ---- P1: stream 0 at positions 0,4,...,28 of every word ------------------------------------------
+// The 32 MiB level-3 summary (1 bit per 16 slots, table.cu) answers most probes of an absent reference
+// from L2; only a set summary bit costs the DRAM sector of the real table.
 __global__ void __launch_bounds__(256)
-k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, uint8_t* __restrict__ sample_hits)
+k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const uint32_t* __restrict__ summary,
+                uint8_t* __restrict__ sample_hits)
 {
     uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= pl.nwords) return;
@@ -35,8 +38,13 @@ k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, uint8
             WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
             code[q] = ((vm >> (31 - s)) & 1u) ? stream_code(m, b, 0) : 0u;
         }
+        uint32_t maybe = 0;                          // first the summary (L2), all eight loads in flight
 #pragma unroll
-        for (int q = 0; q < 8; q++) out |= probe(bm3, code[q]) << (7 - q);
+        for (int q = 0; q < 8; q++)
+            maybe |= (code[q] ? (__ldg(summary + (code[q] >> 9)) >> ((code[q] >> 4) & 31)) & 1u : 0u) << (7 - q);
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            if ((maybe >> (7 - q)) & 1u) out |= ((__ldg(bm3 + (code[q] >> 5)) >> (code[q] & 31)) & 1u) << (7 - q);
     }
     sample_hits[w] = (uint8_t)out;
 }
@@ -244,11 +252,11 @@ __global__ void k_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uin
 
 static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
 
-cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, uint8_t* sample_hits,
-                                 cudaStream_t st)
+cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary,
+                                 uint8_t* sample_hits, cudaStream_t st)
 {
     if (!pl.nwords) return cudaSuccess;
-    k_probe_sampled<<<grid_for(pl.nwords, 256), 256, 0, st>>>(pl, m, bm3, sample_hits);
+    k_probe_sampled<<<grid_for(pl.nwords, 256), 256, 0, st>>>(pl, m, bm3, summary, sample_hits);
     return cudaGetLastError();
 }
 

@@ -24,6 +24,7 @@ EREF_BIN = os.path.join(_HERE, "bin", "eref")
 
 K = 32
 FLAG_NO_PRUNE = 1
+FLAG_DIRECT_COUNT = 2
 
 RESULT_DTYPE = np.dtype([("ordinal", "<u4"), ("frag", "<u4"), ("el", "<u4"), ("ref_len", "<u4")])
 
@@ -38,10 +39,10 @@ ABI_SYMBOLS = (
 
 class PhaseTimes(Structure):
     _fields_ = [(n, c_float) for n in (
-        "query_h2d_ms", "query_pack_ms", "query_count_ms", "ref_h2d_ms", "ref_frame_ms", "ref_pack_ms",
-        "scan_sample_ms", "scan_cand_ms", "scan_probe_ms", "scan_window_ms", "scan_interval_ms",
-        "scan_d2h_ms")] + [(n, c_uint64) for n in (
-        "kernel_launches", "ref_bases", "ref_words", "ref_need_words", "query_seq_bytes")]
+        "query_h2d_ms", "query_pack_ms", "query_bucket_ms", "query_count_ms", "ref_h2d_ms", "ref_frame_ms",
+        "ref_pack_ms", "scan_summary_ms", "scan_sample_ms", "scan_cand_ms", "scan_probe_ms", "scan_window_ms",
+        "scan_interval_ms", "scan_d2h_ms")] + [(n, c_uint64) for n in (
+        "kernel_launches", "ref_bases", "ref_words", "ref_need_words", "query_seq_bytes", "query_codes")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -126,7 +127,7 @@ class ErefGPU:
     """One context = one GPU: the query table, one reference text (whole DB or one shard), the scan."""
 
     def __init__(self, coder, hit_ratio: float = 0.9, perfect_hit_ratio: float = 0.85, device: int = 0,
-                 prune: bool = True):
+                 prune: bool = True, bucketed: bool = True):
         self.lib = load_library()
         if self.lib.eref_device_count() <= 0:
             raise ErefError("no CUDA device visible; liberef_gpu.so has no CPU fallback")
@@ -135,7 +136,8 @@ class ErefGPU:
             raise ErefError("coder must have 96 entries")
         self._h = c_void_p()
         rc = self.lib.eref_create(byref(self._h), device, c.ctypes.data_as(POINTER(c_int16)),
-                                  c_float(hit_ratio), c_float(perfect_hit_ratio), 0 if prune else FLAG_NO_PRUNE)
+                                  c_float(hit_ratio), c_float(perfect_hit_ratio),
+                                  (0 if prune else FLAG_NO_PRUNE) | (0 if bucketed else FLAG_DIRECT_COUNT))
         _check(self.lib, rc, "eref_create")
 
     def close(self):
@@ -262,7 +264,7 @@ def check_sample_ratio(seq_bytes_fq1: int):
 
 def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
              perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
-             return_results: bool = False):
+             bucketed: bool = True, return_results: bool = False):
     """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
 
     `devices`: GPUs to shard the database over (one context each, run one after the other here —
@@ -277,7 +279,7 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
     cuts = shard_offsets(fasta, len(devices))
     parts = []
     for i, dev in enumerate(devices):
-        with ErefGPU(coder, hit_ratio, perfect_hit_ratio, dev, prune) as g:
+        with ErefGPU(coder, hit_ratio, perfect_hit_ratio, dev, prune, bucketed) as g:
             check_sample_ratio(g.query_add(fq1))
             g.query_add(fq2)
             g.ref_set(fasta[cuts[i]:cuts[i + 1]])

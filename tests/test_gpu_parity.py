@@ -90,6 +90,21 @@ def test_table_levels_match_oracle_counts(oracle):
             assert g.query_popcount(level) == sum(1 for v in cnt.values() if v >= level)
 
 
+def test_bucketed_and_direct_builds_give_the_same_table():
+    """code-range bucketing only reorders commuting atomics: all three levels must be bit-identical"""
+    db, f1, f2, _ = _case(22, n_genomes=40, db_bp=1_000_000, q_bp=800_000)
+    coder = eref.random_coder(22)
+    pops, recs = [], []
+    for bucketed in (True, False):
+        with eref.ErefGPU(coder, bucketed=bucketed) as g:
+            g.query_add(f1); g.query_add(f2); g.ref_set(db.text)
+            pops.append([g.query_popcount(l) for l in (1, 2, 3)])
+            recs.append(g.scan().copy())
+            assert (g.timings()["query_codes"] > 0) == bucketed
+    assert pops[0] == pops[1] and pops[0][2] > 0
+    assert (recs[0] == recs[1]).all()
+
+
 def test_seq_bytes_matches_cal_sam_ratio_sum(oracle, golden):
     name, meta, fa, f1, f2 = golden
     with eref.ErefGPU(meta["coder"]) as g:
