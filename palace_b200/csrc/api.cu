@@ -64,7 +64,13 @@ struct eref_ctx {
     // query side
     DevBuf q_text, q_hi, q_lo, q_ok;
     DevBuf bucket_ctr;                         // u64: hist[32] | tail[32] | off[33]
-    DevBuf q_codes;                            // bucket-ordered code list of the file being counted
+    // bucket-ordered code lists of the files added since the last table update (counted lazily, bucket by
+    // bucket, by finalize_table so that every table slice is visited once while it sits in L2)
+    struct CodeList { DevBuf codes; unsigned long long off[NBUCKETS_HOST + 1]; unsigned long long n[NBUCKETS_HOST]; };
+    std::vector<CodeList> lists;
+    size_t n_pending = 0;
+    bool needs_zero = true;                    // table levels not zeroed yet since create / query_reset
+    cudaEvent_t evf[2]{};
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
     unsigned long long h_hist[NBUCKETS_HOST] = {}, h_off[NBUCKETS_HOST + 1] = {};
@@ -156,7 +162,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         CUDA_TRY(cudaEventRecord(c->ev[E3], st));
         LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
     } else {
-        // codes -> 32 code-range buckets (histogram, exact offsets, scatter), then bucket-ordered counting
+        // codes -> 32 code-range buckets (histogram, exact offsets, scatter); counted by finalize_table
         CUDA_TRY(c->bucket_ctr.ensure((NBUCKETS_HOST * 2 + NBUCKETS_HOST + 1) * 8));
         unsigned long long* hist = c->bucket_ctr.as<unsigned long long>();
         unsigned long long* tail = hist + NBUCKETS_HOST;
@@ -165,14 +171,19 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         LAUNCH(c, launch_bucket_hist(pl, c->masks, hist, st));
         CUDA_TRY(cudaMemcpyAsync(c->h_hist, hist, NBUCKETS_HOST * 8, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        c->h_off[0] = 0;
-        for (int b = 0; b < NBUCKETS_HOST; b++) c->h_off[b + 1] = c->h_off[b] + c->h_hist[b];
-        total_codes = c->h_off[NBUCKETS_HOST];
-        CUDA_TRY(cudaMemcpyAsync(off, c->h_off, (NBUCKETS_HOST + 1) * 8, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(c->q_codes.ensure((size_t)total_codes * 4 + 16));
-        LAUNCH(c, launch_bucket_scatter(pl, c->masks, off, tail, c->q_codes.as<uint32_t>(), st));
+        if (c->lists.size() <= c->n_pending) c->lists.resize(c->n_pending + 1);
+        eref_ctx::CodeList& L = c->lists[c->n_pending];
+        L.off[0] = 0;
+        for (int b = 0; b < NBUCKETS_HOST; b++) {               // bucket starts stay 16-byte aligned
+            L.n[b] = c->h_hist[b];
+            L.off[b + 1] = L.off[b] + ((c->h_hist[b] + 3) & ~3ull);
+            total_codes += c->h_hist[b];
+        }
+        CUDA_TRY(cudaMemcpyAsync(off, L.off, (NBUCKETS_HOST + 1) * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(L.codes.ensure((size_t)L.off[NBUCKETS_HOST] * 4 + 16));
+        LAUNCH(c, launch_bucket_scatter(pl, c->masks, off, tail, L.codes.as<uint32_t>(), st));
+        c->n_pending++;
         CUDA_TRY(cudaEventRecord(c->ev[E3], st));
-        LAUNCH(c, launch_count_codes(c->q_codes.as<uint32_t>(), total_codes, c->bm[0], c->bm[1], c->bm[2], st));
     }
     CUDA_TRY(cudaEventRecord(c->ev[E4], st));
     unsigned long long h = 0;
@@ -183,7 +194,38 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     c->t.query_h2d_ms = ev_ms(c, E0, E1);
     c->t.query_pack_ms = ev_ms(c, E1, E2);
     c->t.query_bucket_ms = ev_ms(c, E2, E3);
-    c->t.query_count_ms = ev_ms(c, E3, E4);
+    if (c->flags & EREF_FLAG_DIRECT_COUNT) c->t.query_count_ms = ev_ms(c, E3, E4);
+    return 0;
+}
+
+// Bring the table up to date: for each code-range bucket, zero its three 16 MiB level slices if the
+// table is fresh (the zeros are left dirty in L2, so the atomics that follow never wait for DRAM), then
+// count that bucket of every pending file.  DRAM sees each table sector once, as a write-back.
+int finalize_table(eref_ctx* c)
+{
+    if (c->flags & EREF_FLAG_DIRECT_COUNT) return 0;
+    if (!c->needs_zero && c->n_pending == 0) return 0;
+    cudaStream_t st = c->stream;
+    constexpr uint32_t SLICE = TABLE_WORDS / NBUCKETS_HOST;
+    CUDA_TRY(cudaEventRecord(c->evf[0], st));
+    for (int b = 0; b < NBUCKETS_HOST; b++) {
+        if (c->needs_zero)
+            LAUNCH(c, launch_zero_slices(c->bm[0] + (size_t)b * SLICE, c->bm[1] + (size_t)b * SLICE,
+                                         c->bm[2] + (size_t)b * SLICE, SLICE, st));
+        for (size_t k = 0; k < c->n_pending; k++) {
+            eref_ctx::CodeList& L = c->lists[k];
+            if (L.n[b])
+                LAUNCH(c, launch_count_codes(L.codes.as<uint32_t>() + L.off[b], L.n[b], c->bm[0], c->bm[1], c->bm[2], st));
+        }
+    }
+    CUDA_TRY(cudaEventRecord(c->evf[1], st));
+    c->needs_zero = false;
+    c->n_pending = 0;
+    c->summary_stale = true;
+    CUDA_TRY(cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->evf[0], c->evf[1]);
+    c->t.query_count_ms = ms;
     return 0;
 }
 
@@ -285,6 +327,8 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
 int scan_impl(eref_ctx* c)
 {
     if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "eref_scan before eref_ref_set");
+    int frc = finalize_table(c);
+    if (frc) return frc;
     cudaStream_t st = c->stream;
     const uint64_t nw = c->ref_words;
     const uint32_t G = c->n_genomes;
@@ -380,6 +424,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     c->three_min = (int)(WINDOW * perfect_hit_ratio);    // :514
     cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&c->evf[i]);
     for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
     if (e == cudaSuccess) e = c->counters.ensure(64);
     if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
@@ -405,7 +450,9 @@ void eref_destroy(eref_ctx* c)
     for (DevBuf* b : bufs) b->release();
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
     if (c->summary) cudaFree(c->summary);
-    c->bucket_ctr.release(); c->q_codes.release();
+    c->bucket_ctr.release();
+    for (auto& L : c->lists) L.codes.release();
+    for (int i = 0; i < 2; i++) if (c->evf[i]) cudaEventDestroy(c->evf[i]);
     for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
@@ -424,8 +471,13 @@ int eref_query_reset(eref_ctx* c)
 {
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
     CUDA_TRY(cudaSetDevice(c->device));
-    for (int l = 0; l < 3; l++) CUDA_TRY(cudaMemsetAsync(c->bm[l], 0, (size_t)TABLE_WORDS * 4, c->stream));
     c->summary_stale = true;
+    c->n_pending = 0;
+    if (c->flags & EREF_FLAG_DIRECT_COUNT) {
+        for (int l = 0; l < 3; l++) CUDA_TRY(cudaMemsetAsync(c->bm[l], 0, (size_t)TABLE_WORDS * 4, c->stream));
+    } else {
+        c->needs_zero = true;                  // zeroed slice by slice in finalize_table, right before use
+    }
     return 0;
 }
 
@@ -565,6 +617,8 @@ int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
 {
     if (!c || !out || level < 1 || level > 3) return eref_fail(EREF_ERR_ARG, "eref_query_popcount: bad argument");
     CUDA_TRY(cudaSetDevice(c->device));
+    int frc = finalize_table(c);
+    if (frc) return frc;
     unsigned long long* ctr = c->counters.as<unsigned long long>() + 2;
     CUDA_TRY(cudaMemsetAsync(ctr, 0, 8, c->stream));
     LAUNCH(c, launch_popcount(c->bm[level - 1], TABLE_WORDS, ctr, c->stream));

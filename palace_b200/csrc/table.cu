@@ -164,6 +164,16 @@ k_build_summary(const uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary
     summary[i] = out;
 }
 
+// zero one bucket's slice of all three levels; the lines stay dirty in L2 for the atomics that follow
+__global__ void __launch_bounds__(256)
+k_zero_slices(uint4* __restrict__ a, uint4* __restrict__ b, uint4* __restrict__ c, uint32_t nvec)
+{
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
+        a[i] = z; b[i] = z; c[i] = z;
+    }
+}
+
 __global__ void k_popcount(const uint32_t* __restrict__ bm, uint64_t nwords, unsigned long long* out)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -205,6 +215,13 @@ cudaError_t launch_count_codes(const uint32_t* codes, uint64_t n, uint32_t* bm1,
 {
     if (!n) return cudaSuccess;
     k_count_codes<<<(unsigned)((n + 1023) / 1024), 256, 0, st>>>(codes, n, bm1, bm2, bm3);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_zero_slices(uint32_t* a, uint32_t* b, uint32_t* c, uint32_t nwords, cudaStream_t st)
+{
+    k_zero_slices<<<148 * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(a), reinterpret_cast<uint4*>(b),
+                                          reinterpret_cast<uint4*>(c), nwords / 4);
     return cudaGetLastError();
 }
 
