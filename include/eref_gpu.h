@@ -89,6 +89,14 @@ int  eref_scan(eref_ctx* ctx, eref_result* out, size_t cap, size_t* n_out);
 /* same, results left on the device as n_kept x 4 uint32 (for an NCCL allgather by the caller) */
 int  eref_scan_device(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out);
 
+/* main() of the reference from the FASTQ passes on (:1242-1329) in one call, from HOST buffers (pinned for
+ * overlap): H2D copies run on a copy stream while the kernels work; the FASTA text is cut into `chunks`
+ * pieces at record boundaries and each piece is framed and scanned as soon as it has landed.  Writes
+ * min(cap, total) records in file order with global ordinals; *n_out = total.  Includes the table reset
+ * and the cal_sam_ratio guard (EREF_ERR_UNSUPPORTED when the reference would down-sample or divide by 0). */
+int  eref_run_host(eref_ctx* ctx, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta,
+                   size_t nf, int chunks, eref_result* out, size_t cap, size_t* n_out);
+
 /* the per-record body of <db>.k32.index.dat (:711-738): (len-31)*3 codes, 0 = invalid window.
  * ordinal is 1-based within the current reference text.  Test hook and index writer (f2). */
 int  eref_get_codes(eref_ctx* ctx, uint32_t ordinal, uint32_t* codes_host, size_t cap, size_t* n_out);

@@ -51,7 +51,9 @@ enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, EV_COUNT };
 
 struct eref_ctx {
     int device = 0;
-    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+    std::vector<cudaEvent_t> copy_ev;          // eref_run_host: one event per staged H2D copy
+    DevBuf q_text2, run_results;
     CoderMasks masks{};
     float hit_ratio = 0, perfect_hit_ratio = 0;
     int one_min = 0, three_min = 0;
@@ -423,6 +425,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     c->one_min = (int)(WINDOW * hit_ratio);              // :513 — int * float, truncated
     c->three_min = (int)(WINDOW * perfect_hit_ratio);    // :514
     cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&c->evf[i]);
     for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
@@ -455,6 +458,9 @@ void eref_destroy(eref_ctx* c)
     for (int i = 0; i < 2; i++) if (c->evf[i]) cudaEventDestroy(c->evf[i]);
     for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (cudaEvent_t e : c->copy_ev) cudaEventDestroy(e);
+    c->q_text2.release(); c->run_results.release();
     delete c;
 }
 
@@ -554,6 +560,117 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE) > 0;
     c->t.ref_need_words = pruned ? need_words : c->ref_words;
     if (n_out) *n_out = c->n_genomes;
+    return 0;
+}
+
+/* The whole path in one call, from HOST buffers, with the H2D copies overlapped with the kernels: both
+ * FASTQ files and the FASTA text (cut into `chunks` pieces at record boundaries) are queued on a copy
+ * stream; the compute stream counts each file as it lands, brings the table up to date while the database
+ * is still in flight, and frames+scans every database piece as soon as its copy completes.  Pieces are
+ * independent shards (a record's result depends only on its own bases, :846-896), so their records are
+ * concatenated with ordinals continuing in file order.  Host buffers should be pinned for the overlap. */
+int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
+                  int chunks, eref_result* out, size_t cap, size_t* n_out)
+{
+    if (!c || (n1 && !fq1) || (n2 && !fq2) || (nf && !fasta) || (cap && !out))
+        return eref_fail(EREF_ERR_ARG, "eref_run_host: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (chunks < 1) chunks = 1;
+    if (chunks > 64) chunks = 64;
+    // piece boundaries: offsets that start a header line ('>' right after a newline)
+    std::vector<size_t> cut(1, 0);
+    for (int k = 1; k < chunks; k++) {
+        size_t pos = nf / chunks * k;
+        if (pos < cut.back()) pos = cut.back();
+        size_t found = nf;
+        while (pos < nf) {
+            const char* nl = (const char*)memchr(fasta + pos, '\n', nf - pos);
+            if (!nl) break;
+            size_t q = (size_t)(nl - fasta) + 1;
+            if (q < nf && fasta[q] == '>') { found = q; break; }
+            pos = q;
+        }
+        if (found > cut.back() && found < nf) cut.push_back(found);
+    }
+    cut.push_back(nf);
+    const size_t npieces = cut.size() - 1;
+    while (c->copy_ev.size() < npieces + 2) {
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->copy_ev.push_back(e);
+    }
+    CUDA_TRY(c->q_text.ensure(n1 + 64));
+    CUDA_TRY(c->q_text2.ensure(n2 + 64));
+    CUDA_TRY(c->r_text.ensure(nf + 256 * (npieces + 1)));
+    cudaStream_t cs = c->copy_stream, st = c->stream;
+    // the copy stream must not overwrite buffers the compute stream may still be reading
+    CUDA_TRY(cudaEventRecord(c->ev[E9], st));
+    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev[E9], 0));
+    if (n1) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fq1, n1, cudaMemcpyHostToDevice, cs));
+    CUDA_TRY(cudaEventRecord(c->copy_ev[0], cs));
+    if (n2) CUDA_TRY(cudaMemcpyAsync(c->q_text2.p, fq2, n2, cudaMemcpyHostToDevice, cs));
+    CUDA_TRY(cudaEventRecord(c->copy_ev[1], cs));
+    std::vector<uint8_t*> piece_dev(npieces);
+    size_t doff = 0;
+    for (size_t k = 0; k < npieces; k++) {
+        piece_dev[k] = c->r_text.as<uint8_t>() + doff;
+        const size_t len = cut[k + 1] - cut[k];
+        if (len) CUDA_TRY(cudaMemcpyAsync(piece_dev[k], fasta + cut[k], len, cudaMemcpyHostToDevice, cs));
+        CUDA_TRY(cudaEventRecord(c->copy_ev[2 + k], cs));
+        doff += (len + 255) & ~(size_t)255;
+    }
+    int rc = eref_query_reset(c);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[0], 0));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+    rc = query_add_impl(c, c->q_text.as<uint8_t>(), n1);
+    if (rc) return rc;
+    eref_phase_times sum = c->t;
+    const unsigned long long seq1 = c->t.query_seq_bytes;
+    // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1)
+    if (seq1 == 0 || 100ull * 2000000000ull / (2ull * seq1) < 100ull) {
+        cudaStreamSynchronize(cs);
+        return seq1 == 0
+            ? eref_fail(EREF_ERR_UNSUPPORTED, "fq1 holds no sequence lines (the reference divides by zero here, :1145)")
+            : eref_fail(EREF_ERR_UNSUPPORTED, "fq1 holds more than 1 Gbase: the reference's rand()-driven down-sampling "
+                                              "(:955-960) is not implemented; refusing to diverge silently");
+    }
+    CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[1], 0));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+    rc = query_add_impl(c, c->q_text2.as<uint8_t>(), n2);
+    if (rc) return rc;
+    sum.query_pack_ms += c->t.query_pack_ms; sum.query_bucket_ms += c->t.query_bucket_ms;
+    sum.query_seq_bytes += c->t.query_seq_bytes; sum.query_codes += c->t.query_codes;
+    rc = finalize_table(c);
+    if (rc) return rc;
+    sum.query_count_ms = c->t.query_count_ms;
+    sum.ref_frame_ms = sum.ref_pack_ms = 0;
+    sum.scan_summary_ms = sum.scan_sample_ms = sum.scan_cand_ms = sum.scan_probe_ms = sum.scan_window_ms = 0;
+    sum.scan_interval_ms = sum.scan_d2h_ms = 0;
+    sum.ref_bases = sum.ref_words = sum.ref_need_words = 0;
+    size_t total = 0;
+    for (size_t k = 0; k < npieces; k++) {
+        CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[2 + k], 0));
+        CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+        rc = ref_set_impl(c, piece_dev[k], cut[k + 1] - cut[k]);
+        if (rc) return rc;
+        size_t got = 0;
+        const size_t room = cap > total ? cap - total : 0;
+        rc = eref_scan(c, room ? out + total : nullptr, room, &got);
+        if (rc) return rc;
+        const size_t wrote = got < room ? got : room;
+        for (size_t i = 0; i < wrote; i++) out[total + i].ordinal += (uint32_t)total;   // file-order ordinals
+        total += got;
+        sum.ref_frame_ms += c->t.ref_frame_ms; sum.ref_pack_ms += c->t.ref_pack_ms;
+        sum.scan_summary_ms += c->t.scan_summary_ms; sum.scan_sample_ms += c->t.scan_sample_ms;
+        sum.scan_cand_ms += c->t.scan_cand_ms; sum.scan_probe_ms += c->t.scan_probe_ms;
+        sum.scan_window_ms += c->t.scan_window_ms; sum.scan_interval_ms += c->t.scan_interval_ms;
+        sum.scan_d2h_ms += c->t.scan_d2h_ms;
+        sum.ref_bases += c->t.ref_bases; sum.ref_words += c->t.ref_words; sum.ref_need_words += c->t.ref_need_words;
+    }
+    c->t = sum;
+    c->have_ref = npieces == 1;               // per-record lookups only make sense for a single piece
+    if (n_out) *n_out = total;
     return 0;
 }
 

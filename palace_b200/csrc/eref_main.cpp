@@ -200,7 +200,7 @@ int main(int argc, char** argv)
     std::atomic<int> failed{0};
     Barrier bar(shards);
     size_t max_kept = 0;
-    bool go = false;
+    bool go = false, single_done = false;
 
     auto worker = [&](int i) {
         eref_ctx* ctx = nullptr;
@@ -210,8 +210,18 @@ int main(int argc, char** argv)
         };
         bool ok = true;
         if (eref_create(&ctx, i, coder, hit_ratio, perfect_hit_ratio, flags)) { fail("eref_create"); ok = false; }
-        if (ok && eref_query_add(ctx, f1.p, f1.n)) { fail("eref_query_add(fq1)"); ok = false; }
-        if (ok) {
+        if (ok && shards == 1) {
+            // one GPU: the pipelined entry point (copies overlapped with kernels, DB in 8 pieces)
+            size_t cap = 1;
+            for (size_t k = 0; k < fa.n; k++) cap += fa.p[k] == '>';
+            merged.resize(cap);
+            size_t n = 0;
+            if (eref_run_host(ctx, f1.p, f1.n, f2.p, f2.n, fa.p, fa.n, 8, merged.data(), cap, &n)) { fail("eref_run_host"); ok = false; }
+            merged.resize(ok ? std::min(n, cap) : 0);
+            single_done = ok;
+        }
+        if (ok && shards > 1 && eref_query_add(ctx, f1.p, f1.n)) { fail("eref_query_add(fq1)"); ok = false; }
+        if (ok && shards > 1) {
             // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1), integer division
             uint64_t seq = 0;
             eref_query_seq_bytes(ctx, &seq);
@@ -225,17 +235,15 @@ int main(int argc, char** argv)
                 }
             }
         }
-        if (ok && eref_query_add(ctx, f2.p, f2.n)) { fail("eref_query_add(fq2)"); ok = false; }
-        if (ok && eref_ref_set(ctx, fa.p + cut[i], cut[i + 1] - cut[i])) { fail("eref_ref_set"); ok = false; }
-        if (ok) eref_ref_count(ctx, &kept[i], nullptr, nullptr);
+        if (ok && shards > 1 && eref_query_add(ctx, f2.p, f2.n)) { fail("eref_query_add(fq2)"); ok = false; }
+        if (ok && shards > 1 && eref_ref_set(ctx, fa.p + cut[i], cut[i + 1] - cut[i])) { fail("eref_ref_set"); ok = false; }
+        if (ok && shards > 1) eref_ref_count(ctx, &kept[i], nullptr, nullptr);
         bar.wait();                                   // every shard's record count is known
         if (i == 0) { max_kept = *std::max_element(kept.begin(), kept.end()); go = failed.load() == 0; }
         bar.wait();
         const bool all_ok = go;                       // one decision for every shard: all enter the collective or none
-        if (all_ok && shards == 1) {
-            merged.resize(kept[0]);
-            size_t n = 0;
-            if (eref_scan(ctx, merged.data(), merged.size(), &n)) fail("eref_scan");
+        if (shards == 1) {
+            (void)single_done;                        // already scanned by eref_run_host
         } else if (all_ok) {
             // one collective: allgather of fixed-size records, shards padded to max_kept
             const uint32_t* dres = nullptr;

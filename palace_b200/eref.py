@@ -34,6 +34,7 @@ ABI_SYMBOLS = (
     "eref_query_reset", "eref_query_add", "eref_query_add_device", "eref_query_seq_bytes",
     "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device",
     "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
+    "eref_run_host",
 )
 
 
@@ -79,6 +80,8 @@ def load_library() -> ctypes.CDLL:
     lib.eref_ref_count.argtypes = [c_void_p, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_uint64)]
     lib.eref_scan.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_scan_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
+    lib.eref_run_host.argtypes = [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, c_int, c_void_p,
+                                  c_size_t, POINTER(c_size_t)]
     lib.eref_get_codes.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_ref_record.argtypes = [c_void_p, c_uint32, POINTER(c_uint64), POINTER(c_uint32), POINTER(c_uint32)]
     lib.eref_query_popcount.argtypes = [c_void_p, c_int, POINTER(c_uint64)]
@@ -193,6 +196,20 @@ class ErefGPU:
         _check(self.lib, self.lib.eref_scan(self._h, c_void_p(out.ctypes.data), kept, byref(n)), "eref_scan")
         return out[:n.value]
 
+    def run_host(self, fq1, fq2, fasta, chunks: int = 8, cap: int | None = None) -> np.ndarray:
+        """The whole path from host buffers in one pipelined call (H2D overlapped with the kernels)."""
+        a1, a2, af = _as_bytes_array(fq1), _as_bytes_array(fq2), _as_bytes_array(fasta)
+        if cap is None:
+            cap = int(af.size // 33 + 16)                 # every kept record has more than 32 bases
+        if getattr(self, "_run_out", None) is None or self._run_out.size < cap:
+            self._run_out = np.zeros(cap, RESULT_DTYPE)
+        n = c_size_t()
+        rc = self.lib.eref_run_host(self._h, c_void_p(a1.ctypes.data), a1.size, c_void_p(a2.ctypes.data), a2.size,
+                                    c_void_p(af.ctypes.data), af.size, chunks, c_void_p(self._run_out.ctypes.data), cap,
+                                    byref(n))
+        _check(self.lib, rc, "eref_run_host")
+        return self._run_out[:min(n.value, cap)]
+
     def scan_device(self):
         """Results stay in HBM: (device pointer to n x 4 uint32, n)."""
         p, n = c_void_p(), c_size_t()
@@ -264,7 +281,7 @@ def check_sample_ratio(seq_bytes_fq1: int):
 
 def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
              perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
-             bucketed: bool = True, return_results: bool = False):
+             bucketed: bool = True, pipelined: bool = False, chunks: int = 8, return_results: bool = False):
     """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
 
     `devices`: GPUs to shard the database over (one context each, run one after the other here —
@@ -280,6 +297,10 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
     parts = []
     for i, dev in enumerate(devices):
         with ErefGPU(coder, hit_ratio, perfect_hit_ratio, dev, prune, bucketed) as g:
+            if pipelined:
+                shard = fasta[cuts[i]:cuts[i + 1]]
+                parts.append(g.run_host(fq1, fq2, shard, chunks, cap=int(np.count_nonzero(shard == 62)) + 1).copy())
+                continue
             check_sample_ratio(g.query_add(fq1))
             g.query_add(fq2)
             g.ref_set(fasta[cuts[i]:cuts[i + 1]])

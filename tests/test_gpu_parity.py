@@ -155,6 +155,26 @@ def test_shard_invariance_and_idempotence(oracle):
         assert (c["el"] >= a["el"]).all()
 
 
+@pytest.mark.parametrize("chunks", [1, 3, 8, 64])
+def test_pipelined_run_host_matches_phase_api(golden, chunks):
+    """eref_run_host (copies overlapped, DB cut into pieces) == the phase-by-phase calls, record for record"""
+    name, meta, fa, f1, f2 = golden
+    _, a = eref.run_eref(f1, f2, fa, coder=meta["coder"], return_results=True)
+    text, b = eref.run_eref(f1, f2, fa, coder=meta["coder"], pipelined=True, chunks=chunks, return_results=True)
+    assert a.size == b.size and (a == b).all()
+    assert text == meta["stdout"]["0.9,0.85"]
+
+
+def test_run_host_refuses_empty_fq1():
+    coder = eref.random_coder(3)
+    fa = np.frombuffer(b">a\n" + b"ACGT" * 20 + b"\n", np.uint8)
+    fq = np.frombuffer(b"@r\n" + b"ACGT" * 10 + b"\n+\n" + b"I" * 40 + b"\n", np.uint8)
+    with eref.ErefGPU(coder) as g:
+        with pytest.raises(eref.ErefError):
+            g.run_host(np.zeros(0, np.uint8), fq, fa, cap=4)
+        assert g.run_host(fq, fq, fa, cap=4).size == 1           # and the context is still usable
+
+
 def test_strand_and_order_invariance():
     """reverse-complementing every read, or swapping fq1/fq2, leaves the table and the result unchanged"""
     db, f1, f2, _ = _case(41, n_genomes=40, db_bp=1_000_000, q_bp=300_000)
