@@ -52,6 +52,8 @@ enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, EV_COUNT };
 struct eref_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+    unsigned long long* h_pin = nullptr;       // pinned scratch for the small device->host reads
+    bool host_tables_valid = false;            // h_g_* mirrors fetched lazily (test hooks only)
     std::vector<cudaEvent_t> copy_ev;          // eref_run_host: one event per staged H2D copy
     DevBuf q_text2, run_results;
     CoderMasks masks{};
@@ -171,8 +173,9 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         unsigned long long* off = tail + NBUCKETS_HOST;
         CUDA_TRY(cudaMemsetAsync(hist, 0, NBUCKETS_HOST * 2 * 8, st));
         LAUNCH(c, launch_bucket_hist(pl, c->masks, hist, st));
-        CUDA_TRY(cudaMemcpyAsync(c->h_hist, hist, NBUCKETS_HOST * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, hist, NBUCKETS_HOST * 8, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
+        memcpy(c->h_hist, c->h_pin + 8, NBUCKETS_HOST * 8);
         if (c->lists.size() <= c->n_pending) c->lists.resize(c->n_pending + 1);
         eref_ctx::CodeList& L = c->lists[c->n_pending];
         L.off[0] = 0;
@@ -188,10 +191,9 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         CUDA_TRY(cudaEventRecord(c->ev[E3], st));
     }
     CUDA_TRY(cudaEventRecord(c->ev[E4], st));
-    unsigned long long h = 0;
-    CUDA_TRY(cudaMemcpyAsync(&h, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 5, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    c->t.query_seq_bytes = h;
+    c->t.query_seq_bytes = c->h_pin[5];
     c->t.query_codes = total_codes;
     c->t.query_h2d_ms = ev_ms(c, E0, E1);
     c->t.query_pack_ms = ev_ms(c, E1, E2);
@@ -243,9 +245,9 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     uint64_t ntiles = 0;
     int rc = newline_census(c, text, n, &ntiles);
     if (rc) return rc;
-    uint32_t n_nl = 0;
-    CUDA_TRY(cudaMemcpyAsync(&n_nl, c->tile_prefix.as<uint32_t>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 0, c->tile_prefix.as<uint32_t>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    const uint32_t n_nl = (uint32_t)(c->h_pin[0] & 0xFFFFFFFFull);
     const uint32_t n_lines = n_nl + 1;             // the last line may be empty: it then adds nothing
     CUDA_TRY(c->nl_pos.ensure(((size_t)n_nl + 1) * 4));
     CUDA_TRY(c->line_val.ensure(((size_t)n_lines + 1) * 8));
@@ -255,9 +257,9 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     LAUNCH(c, launch_line_info(text, n, c->nl_pos.as<uint32_t>(), n_nl, n_lines, c->line_val.as<uint64_t>(), st));
     rc = exclusive_scan<uint64_t>(c, c->line_val.as<uint64_t>(), c->line_cum.as<uint64_t>(), (size_t)n_lines + 1);
     if (rc) return rc;
-    uint64_t totals = 0;
-    CUDA_TRY(cudaMemcpyAsync(&totals, c->line_cum.as<uint64_t>() + n_lines, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 1, c->line_cum.as<uint64_t>() + n_lines, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    const uint64_t totals = c->h_pin[1];
     const uint32_t n_recs = (uint32_t)(totals >> 40) + 1;
     const uint64_t total_seq = totals & ((1ull << 40) - 1);
     // 3. records: first sequence byte, length, keep flag, packed size
@@ -268,16 +270,20 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     CUDA_TRY(c->rec_words_ex.ensure(rn * 4));
     LAUNCH(c, launch_record_starts(c->line_val.as<uint64_t>(), c->line_cum.as<uint64_t>(), n_lines,
                                    c->rec_hdr_line.as<uint32_t>(), c->rec_first.as<uint32_t>(), st));
+    CUDA_TRY(cudaMemsetAsync(c->counters.as<unsigned long long>() + 3, 0, 8, st));
     LAUNCH(c, launch_record_info(c->rec_first.as<uint32_t>(), n_recs, total_seq, c->rec_len.as<uint32_t>(),
-                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(), st));
+                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(),
+                                 c->counters.as<unsigned long long>() + 3, st));
     rc = exclusive_scan<uint32_t>(c, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(), rn);
     if (rc) return rc;
     rc = exclusive_scan<uint32_t>(c, c->rec_words.as<uint32_t>(), c->rec_words_ex.as<uint32_t>(), rn);
     if (rc) return rc;
-    uint32_t n_genomes = 0, n_words = 0;
-    CUDA_TRY(cudaMemcpyAsync(&n_genomes, c->rec_kept_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(&n_words, c->rec_words_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 2, c->rec_kept_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 3, c->rec_words_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 4, c->counters.as<unsigned long long>() + 3, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    const uint32_t n_genomes = (uint32_t)(c->h_pin[2] & 0xFFFFFFFFull), n_words = (uint32_t)(c->h_pin[3] & 0xFFFFFFFFull);
+    const uint64_t bases = c->h_pin[4];
     CUDA_TRY(cudaEventRecord(c->ev[E2], st));
     // 4. genome table + packed planes
     const size_t gn = (size_t)n_genomes + 1;
@@ -303,18 +309,8 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
                                     c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_first.as<uint32_t>(),
                                     n_genomes, pl, c->word_genome.as<uint32_t>(), st));
     CUDA_TRY(cudaEventRecord(c->ev[E3], st));
-    // host copies of the small tables (ordinal -> length / packed offset / header line)
-    c->h_g_len.assign(gn, 0); c->h_g_word.assign(gn, 0); c->h_g_rec.assign(gn, 0);
-    c->h_rec_hdr_line.assign(rn, 0);
-    if (n_genomes) {
-        CUDA_TRY(cudaMemcpyAsync(c->h_g_len.data(), c->g_len.p, (size_t)n_genomes * 4, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaMemcpyAsync(c->h_g_word.data(), c->g_word.p, gn * 4, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaMemcpyAsync(c->h_g_rec.data(), c->g_rec.p, (size_t)n_genomes * 4, cudaMemcpyDeviceToHost, st));
-    }
-    CUDA_TRY(cudaMemcpyAsync(c->h_rec_hdr_line.data(), c->rec_hdr_line.p, (size_t)n_recs * 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    uint64_t bases = 0;
-    for (uint32_t g = 0; g < n_genomes; g++) bases += c->h_g_len[g];
+    c->host_tables_valid = false;             // ordinal -> length / packed offset / header line: fetched on demand
     c->ref_text_dev = text; c->ref_text_n = n;
     c->n_nl = n_nl; c->n_lines = n_lines; c->n_recs = n_recs; c->n_genomes = n_genomes;
     c->ref_words = n_words; c->ref_bases = bases;
@@ -376,6 +372,21 @@ int scan_impl(eref_ctx* c)
     return 0;
 }
 
+int fetch_host_tables(eref_ctx* c)
+{
+    if (c->host_tables_valid) return 0;
+    const size_t gn = (size_t)c->n_genomes + 1, rn = (size_t)c->n_recs + 1;
+    c->h_g_len.assign(gn, 0); c->h_g_word.assign(gn, 0); c->h_g_rec.assign(gn, 0); c->h_rec_hdr_line.assign(rn, 0);
+    if (c->n_genomes) {
+        CUDA_TRY(cudaMemcpy(c->h_g_len.data(), c->g_len.p, (size_t)c->n_genomes * 4, cudaMemcpyDeviceToHost));
+        CUDA_TRY(cudaMemcpy(c->h_g_word.data(), c->g_word.p, gn * 4, cudaMemcpyDeviceToHost));
+        CUDA_TRY(cudaMemcpy(c->h_g_rec.data(), c->g_rec.p, (size_t)c->n_genomes * 4, cudaMemcpyDeviceToHost));
+    }
+    CUDA_TRY(cudaMemcpy(c->h_rec_hdr_line.data(), c->rec_hdr_line.p, (size_t)c->n_recs * 4, cudaMemcpyDeviceToHost));
+    c->host_tables_valid = true;
+    return 0;
+}
+
 void scan_times(eref_ctx* c, bool with_d2h)
 {
     c->t.scan_summary_ms = ev_ms(c, E0, E8);
@@ -430,6 +441,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&c->evf[i]);
     for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
     if (e == cudaSuccess) e = c->counters.ensure(64);
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, 64 * 8, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
     if (e != cudaSuccess) { eref_destroy(c); return eref_fail_cuda(e, "context allocation", __FILE__, __LINE__); }
     c->stream = c->own_stream;
@@ -453,6 +465,7 @@ void eref_destroy(eref_ctx* c)
     for (DevBuf* b : bufs) b->release();
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
     if (c->summary) cudaFree(c->summary);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
     c->bucket_ctr.release();
     for (auto& L : c->lists) L.codes.release();
     for (int i = 0; i < 2; i++) if (c->evf[i]) cudaEventDestroy(c->evf[i]);
@@ -552,13 +565,12 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     if (rc) return rc;
     size_t n = c->n_genomes < cap ? c->n_genomes : cap;
     if (n) CUDA_TRY(cudaMemcpyAsync(out, c->results.p, n * sizeof(eref_result), cudaMemcpyDeviceToHost, c->stream));
-    unsigned long long need_words = 0;
-    CUDA_TRY(cudaMemcpyAsync(&need_words, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev[E6], c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     scan_times(c, true);
     const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE) > 0;
-    c->t.ref_need_words = pruned ? need_words : c->ref_words;
+    c->t.ref_need_words = pruned ? c->h_pin[6] : c->ref_words;
     if (n_out) *n_out = c->n_genomes;
     return 0;
 }
@@ -693,6 +705,8 @@ int eref_get_codes(eref_ctx* c, uint32_t ordinal, uint32_t* codes_host, size_t c
     if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
     if (ordinal < 1 || ordinal > c->n_genomes) return eref_fail(EREF_ERR_ARG, "ordinal %u of %u", ordinal, c->n_genomes);
     CUDA_TRY(cudaSetDevice(c->device));
+    int hrc = fetch_host_tables(c);
+    if (hrc) return hrc;
     const uint32_t len = c->h_g_len[ordinal - 1];
     const size_t n = (size_t)(len - EREF_K + 1) * 3;
     if (n_out) *n_out = n;
@@ -713,6 +727,8 @@ int eref_ref_record(eref_ctx* c, uint32_t ordinal, uint64_t* hdr_off, uint32_t* 
     if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
     if (ordinal < 1 || ordinal > c->n_genomes) return eref_fail(EREF_ERR_ARG, "ordinal %u of %u", ordinal, c->n_genomes);
     CUDA_TRY(cudaSetDevice(c->device));
+    int hrc = fetch_host_tables(c);
+    if (hrc) return hrc;
     const uint32_t r = c->h_g_rec[ordinal - 1];
     if (len) *len = c->h_g_len[ordinal - 1];
     uint64_t off = 0; uint32_t hl = 0;

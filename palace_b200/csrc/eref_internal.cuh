@@ -112,7 +112,8 @@ cudaError_t launch_line_info(const uint8_t* text, uint64_t n, const uint32_t* nl
 cudaError_t launch_record_starts(const uint64_t* line_val, const uint64_t* line_cum, uint32_t n_lines,
                                  uint32_t* rec_hdr_line, uint32_t* rec_first, cudaStream_t st);
 cudaError_t launch_record_info(const uint32_t* rec_first, uint32_t n_recs, uint64_t total_seq,
-                               uint32_t* rec_len, uint32_t* rec_kept, uint32_t* rec_words, cudaStream_t st);
+                               uint32_t* rec_len, uint32_t* rec_kept, uint32_t* rec_words,
+                               unsigned long long* kept_bases, cudaStream_t st);
 cudaError_t launch_genome_table(const uint32_t* rec_len, const uint32_t* rec_kept,
                                 const uint32_t* rec_kept_ex, const uint32_t* rec_words_ex,
                                 const uint32_t* rec_first, const uint32_t* rec_hdr_line, uint32_t n_recs,

@@ -167,17 +167,24 @@ __global__ void k_record_starts(const uint64_t* __restrict__ line_val, const uin
 // leaves at least one invalid pad position after the record, so no 32-mer spans two records.
 __global__ void k_record_info(const uint32_t* __restrict__ rec_first, uint32_t n_recs, uint64_t total_seq,
                               uint32_t* __restrict__ rec_len, uint32_t* __restrict__ rec_kept,
-                              uint32_t* __restrict__ rec_words)
+                              uint32_t* __restrict__ rec_words, unsigned long long* __restrict__ kept_bases)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r > n_recs) return;
-    if (r == n_recs) { rec_len[r] = 0; rec_kept[r] = 0; rec_words[r] = 0; return; }
-    uint32_t next = r + 1 < n_recs ? rec_first[r + 1] : (uint32_t)total_seq;
-    uint32_t len = next - rec_first[r];
-    bool kept = len > (uint32_t)EREF_K;
-    rec_len[r] = len;
-    rec_kept[r] = kept;
-    rec_words[r] = kept ? (len >> 5) + 1 : 0;
+    unsigned long long mine = 0;
+    if (r < n_recs) {
+        uint32_t next = r + 1 < n_recs ? rec_first[r + 1] : (uint32_t)total_seq;
+        uint32_t len = next - rec_first[r];
+        bool kept = len > (uint32_t)EREF_K;
+        rec_len[r] = len;
+        rec_kept[r] = kept;
+        rec_words[r] = kept ? (len >> 5) + 1 : 0;
+        mine = kept ? len : 0;
+    } else if (r == n_recs) {
+        rec_len[r] = 0; rec_kept[r] = 0; rec_words[r] = 0;
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(kept_bases, mine);
 }
 
 __global__ void k_genome_table(const uint32_t* __restrict__ rec_len, const uint32_t* __restrict__ rec_kept,
@@ -287,10 +294,11 @@ cudaError_t launch_record_starts(const uint64_t* line_val, const uint64_t* line_
 }
 
 cudaError_t launch_record_info(const uint32_t* rec_first, uint32_t n_recs, uint64_t total_seq,
-                               uint32_t* rec_len, uint32_t* rec_kept, uint32_t* rec_words, cudaStream_t st)
+                               uint32_t* rec_len, uint32_t* rec_kept, uint32_t* rec_words,
+                               unsigned long long* kept_bases, cudaStream_t st)
 {
     k_record_info<<<grid_for((uint64_t)n_recs + 1, 256), 256, 0, st>>>(rec_first, n_recs, total_seq, rec_len,
-                                                                     rec_kept, rec_words);
+                                                                     rec_kept, rec_words, kept_bases);
     return cudaGetLastError();
 }
 
