@@ -422,7 +422,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-prune", action="store_true", help="probe all three streams at every position")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--chunks", type=int, default=8, help="database pieces of the pipelined host-buffer call (e2e)")
+    ap.add_argument("--chunks", type=int, default=4, help="database pieces of the pipelined host-buffer call (e2e)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         print(f"bench.py: warmup {args.warmup} < 3 breaks the timing rules", file=sys.stderr)

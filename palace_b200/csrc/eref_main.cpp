@@ -211,12 +211,12 @@ int main(int argc, char** argv)
         bool ok = true;
         if (eref_create(&ctx, i, coder, hit_ratio, perfect_hit_ratio, flags)) { fail("eref_create"); ok = false; }
         if (ok && shards == 1) {
-            // one GPU: the pipelined entry point (copies overlapped with kernels, DB in 8 pieces)
+            // one GPU: the pipelined entry point (copies overlapped with kernels, DB in 4 pieces)
             size_t cap = 1;
             for (size_t k = 0; k < fa.n; k++) cap += fa.p[k] == '>';
             merged.resize(cap);
             size_t n = 0;
-            if (eref_run_host(ctx, f1.p, f1.n, f2.p, f2.n, fa.p, fa.n, 8, merged.data(), cap, &n)) { fail("eref_run_host"); ok = false; }
+            if (eref_run_host(ctx, f1.p, f1.n, f2.p, f2.n, fa.p, fa.n, 4, merged.data(), cap, &n)) { fail("eref_run_host"); ok = false; }
             merged.resize(ok ? std::min(n, cap) : 0);
             single_done = ok;
         }

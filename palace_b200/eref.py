@@ -196,7 +196,7 @@ class ErefGPU:
         _check(self.lib, self.lib.eref_scan(self._h, c_void_p(out.ctypes.data), kept, byref(n)), "eref_scan")
         return out[:n.value]
 
-    def run_host(self, fq1, fq2, fasta, chunks: int = 8, cap: int | None = None) -> np.ndarray:
+    def run_host(self, fq1, fq2, fasta, chunks: int = 4, cap: int | None = None) -> np.ndarray:
         """The whole path from host buffers in one pipelined call (H2D overlapped with the kernels)."""
         a1, a2, af = _as_bytes_array(fq1), _as_bytes_array(fq2), _as_bytes_array(fasta)
         if cap is None:
@@ -281,7 +281,7 @@ def check_sample_ratio(seq_bytes_fq1: int):
 
 def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
              perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
-             bucketed: bool = True, pipelined: bool = False, chunks: int = 8, return_results: bool = False):
+             bucketed: bool = True, pipelined: bool = False, chunks: int = 4, return_results: bool = False):
     """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
 
     `devices`: GPUs to shard the database over (one context each, run one after the other here —
