@@ -207,7 +207,7 @@ def run_b200(args):
         class _Arr:                                    # __cuda_array_interface__ v2
             pass
         a = _Arr()
-        a.__cuda_array_interface__ = {"shape": (n, 4), "typestr": "<i4", "data": (ptr, True), "version": 2}
+        a.__cuda_array_interface__ = {"shape": (n, 4), "typestr": "<i4", "data": (ptr, False), "version": 2}
         return torch.as_tensor(a, device=dev)
 
     def barrier():

@@ -15,6 +15,7 @@
 #include "eref_gpu.h"
 #include <cuda_runtime.h>
 #include <nccl.h>
+#include <unistd.h>
 #include <algorithm>
 #include <atomic>
 #include <cerrno>
@@ -147,6 +148,11 @@ int main(int argc, char** argv)
         fprintf(stderr, "eref: bad numeric argument: %s\n", e.what());
         return 2;
     }
+    // stdout is the result channel (palace redirects it into ref_names.txt): keep libraries (e.g. NCCL's
+    // version banner) off it by parking the real stdout and pointing fd 1 at stderr until the results are ready
+    fflush(stdout);
+    const int result_fd = dup(1);
+    if (result_fd < 0 || dup2(2, 1) < 0) { fprintf(stderr, "eref: cannot set up the result channel\n"); return 3; }
     const bool timing = getenv("EREF_TIMING") != nullptr;
     auto t_start = std::chrono::steady_clock::now();
 
@@ -299,8 +305,13 @@ int main(int argc, char** argv)
         int k = eref_format_line(&r, line, sizeof line);    // :615-617
         if (k > 0) out.append(line, (size_t)k);
     }
-    fwrite(out.data(), 1, out.size(), stdout);
     fflush(stdout);
+    for (size_t done = 0; done < out.size();) {
+        ssize_t w = write(result_fd, out.data() + done, out.size() - done);
+        if (w <= 0) { fprintf(stderr, "eref: write to stdout failed\n"); return 3; }
+        done += (size_t)w;
+    }
+    close(result_fd);
 
     if (timing) {
         auto t_end = std::chrono::steady_clock::now();
