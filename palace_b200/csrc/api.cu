@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <vector>
 #include <new>
 
@@ -75,6 +76,10 @@ struct eref_ctx {
     size_t n_pending = 0;
     bool needs_zero = true;                    // table levels not zeroed yet since create / query_reset
     cudaEvent_t evf[2]{};
+    // tuning knobs of the table update (EREF_COUNT_STREAMS, EREF_COUNT_UNITS)
+    int count_streams = 2, count_units = 2;
+    cudaStream_t aux[4]{};
+    cudaEvent_t aux_ev[5]{};
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
     unsigned long long h_hist[NBUCKETS_HOST] = {}, h_off[NBUCKETS_HOST + 1] = {};
@@ -211,17 +216,32 @@ int finalize_table(eref_ctx* c)
     if (!c->needs_zero && c->n_pending == 0) return 0;
     cudaStream_t st = c->stream;
     constexpr uint32_t SLICE = TABLE_WORDS / NBUCKETS_HOST;
+    const int S = c->count_streams;
     CUDA_TRY(cudaEventRecord(c->evf[0], st));
+    if (S > 1) {                               // buckets round-robin over S streams: the tail of one bucket's
+        CUDA_TRY(cudaEventRecord(c->aux_ev[4], st));         // kernels overlaps the next bucket's start
+        for (int k = 0; k < S; k++) CUDA_TRY(cudaStreamWaitEvent(c->aux[k], c->aux_ev[4], 0));
+    }
     for (int b = 0; b < NBUCKETS_HOST; b++) {
+        cudaStream_t sb = S > 1 ? c->aux[b % S] : st;
         if (c->needs_zero)
             LAUNCH(c, launch_zero_slices(c->bm[0] + (size_t)b * SLICE, c->bm[1] + (size_t)b * SLICE,
-                                         c->bm[2] + (size_t)b * SLICE, SLICE, st));
-        for (size_t k = 0; k < c->n_pending; k++) {
-            eref_ctx::CodeList& L = c->lists[k];
-            if (L.n[b])
-                LAUNCH(c, launch_count_codes(L.codes.as<uint32_t>() + L.off[b], L.n[b], c->bm[0], c->bm[1], c->bm[2], st));
+                                         c->bm[2] + (size_t)b * SLICE, SLICE, sb));
+        for (size_t k = 0; k < c->n_pending; k += 2) {
+            eref_ctx::CodeList& A = c->lists[k];
+            const bool two = k + 1 < c->n_pending;
+            const uint32_t* p1 = two ? c->lists[k + 1].codes.as<uint32_t>() + c->lists[k + 1].off[b] : nullptr;
+            const uint64_t n1 = two ? c->lists[k + 1].n[b] : 0;
+            if (A.n[b] + n1)
+                LAUNCH(c, launch_count_codes(A.codes.as<uint32_t>() + A.off[b], A.n[b], p1, n1, c->count_units,
+                                             c->bm[0], c->bm[1], c->bm[2], sb));
         }
     }
+    if (S > 1)
+        for (int k = 0; k < S; k++) {
+            CUDA_TRY(cudaEventRecord(c->aux_ev[k], c->aux[k]));
+            CUDA_TRY(cudaStreamWaitEvent(st, c->aux_ev[k], 0));
+        }
     CUDA_TRY(cudaEventRecord(c->evf[1], st));
     c->needs_zero = false;
     c->n_pending = 0;
@@ -439,6 +459,10 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&c->evf[i]);
+    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking);
+    for (int i = 0; i < 5 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->aux_ev[i], cudaEventDisableTiming);
+    if (const char* v = getenv("EREF_COUNT_STREAMS")) { int k = atoi(v); if (k >= 1 && k <= 4) c->count_streams = k; }
+    if (const char* v = getenv("EREF_COUNT_UNITS")) { int k = atoi(v); if (k == 1 || k == 2 || k == 4) c->count_units = k; }
     for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
     if (e == cudaSuccess) e = c->counters.ensure(64);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, 64 * 8, cudaHostAllocDefault);
@@ -469,6 +493,8 @@ void eref_destroy(eref_ctx* c)
     c->bucket_ctr.release();
     for (auto& L : c->lists) L.codes.release();
     for (int i = 0; i < 2; i++) if (c->evf[i]) cudaEventDestroy(c->evf[i]);
+    for (int i = 0; i < 4; i++) if (c->aux[i]) cudaStreamDestroy(c->aux[i]);
+    for (int i = 0; i < 5; i++) if (c->aux_ev[i]) cudaEventDestroy(c->aux_ev[i]);
     for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);

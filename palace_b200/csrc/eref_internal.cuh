@@ -130,8 +130,8 @@ cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t*
 cudaError_t launch_bucket_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st);
 cudaError_t launch_bucket_scatter(Planes pl, CoderMasks m, const unsigned long long* bucket_off,
                                   unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st);
-cudaError_t launch_count_codes(const uint32_t* codes, uint64_t n, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
-                               cudaStream_t st);
+cudaError_t launch_count_codes(const uint32_t* c0, uint64_t n0, const uint32_t* c1, uint64_t n1, int units,
+                               uint32_t* bm1, uint32_t* bm2, uint32_t* bm3, cudaStream_t st);
 cudaError_t launch_zero_slices(uint32_t* a, uint32_t* b, uint32_t* c, uint32_t nwords, cudaStream_t st);
 cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, cudaStream_t st);
 cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);

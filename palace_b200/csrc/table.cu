@@ -119,28 +119,39 @@ k_bucket_codes(Planes pl, CoderMasks m, unsigned long long* __restrict__ g_hist,
     });
 }
 
-// counts a bucket-ordered code list: CTAs run in list order, so neighbouring CTAs share table slices
+// Counts one bucket of up to two bucket-ordered code lists (the two FASTQ files).  A thread owns U
+// 16-byte units, strided by the grid so that every LDG.128 of a warp is one contiguous 512 B run; all
+// level-1 atomics of a thread are issued before the first dependent level-2 atomic.
+template <int U>
 __global__ void __launch_bounds__(256)
-k_count_codes(const uint32_t* __restrict__ codes, uint64_t n, uint32_t* __restrict__ bm1,
-              uint32_t* __restrict__ bm2, uint32_t* __restrict__ bm3)
+k_count_codes(const uint32_t* __restrict__ c0, uint64_t n0, const uint32_t* __restrict__ c1, uint64_t n1,
+              uint32_t* __restrict__ bm1, uint32_t* __restrict__ bm2, uint32_t* __restrict__ bm3)
 {
-    const uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (i0 >= n) return;
-    uint32_t code[4], old[4];
-    int cnt;
-    if (i0 + 4 <= n) {
-        uint4 v = __ldg(reinterpret_cast<const uint4*>(codes + i0));
-        code[0] = v.x; code[1] = v.y; code[2] = v.z; code[3] = v.w; cnt = 4;
-    } else {
-        cnt = (int)(n - i0);
-        for (int q = 0; q < 4; q++) code[q] = q < cnt ? codes[i0 + q] : 0u;
+    const uint64_t units0 = (n0 + 3) >> 2, total = units0 + ((n1 + 3) >> 2);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t first = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t code[4 * U], old[4 * U];
+    uint32_t live = 0;                                   // bit q set: code[q] is a real code
+#pragma unroll
+    for (int j = 0; j < U; j++) {
+        const uint64_t u = first + (uint64_t)j * stride;
+        if (u < total) {
+            const bool second = u >= units0;
+            const uint64_t lu = second ? u - units0 : u;
+            const uint32_t* base = second ? c1 : c0;
+            const uint64_t n = second ? n1 : n0;
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(base) + lu);   // bucket starts are 16-byte aligned,
+            code[4 * j] = v.x; code[4 * j + 1] = v.y; code[4 * j + 2] = v.z; code[4 * j + 3] = v.w;   // padded to 4 codes
+            const uint64_t left = n - (lu << 2);
+            live |= (left >= 4 ? 0xFu : ((1u << left) - 1u)) << (4 * j);
+        }
     }
 #pragma unroll
-    for (int q = 0; q < 4; q++)
-        if (q < cnt) old[q] = atomicOr(bm1 + (code[q] >> 5), 1u << (code[q] & 31));
+    for (int q = 0; q < 4 * U; q++)
+        if ((live >> q) & 1u) old[q] = atomicOr(bm1 + (code[q] >> 5), 1u << (code[q] & 31));
 #pragma unroll
-    for (int q = 0; q < 4; q++)
-        if (q < cnt) count_code(code[q], old[q], bm2, bm3);
+    for (int q = 0; q < 4 * U; q++)
+        if ((live >> q) & 1u) count_code(code[q], old[q], bm2, bm3);
 }
 
 // summary bit = OR of 16 consecutive level-3 bits: a 32 MiB filter that stays in L2 during the scan
@@ -210,11 +221,14 @@ cudaError_t launch_bucket_scatter(Planes pl, CoderMasks m, const unsigned long l
     return cudaGetLastError();
 }
 
-cudaError_t launch_count_codes(const uint32_t* codes, uint64_t n, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
-                               cudaStream_t st)
+cudaError_t launch_count_codes(const uint32_t* c0, uint64_t n0, const uint32_t* c1, uint64_t n1, int units,
+                               uint32_t* bm1, uint32_t* bm2, uint32_t* bm3, cudaStream_t st)
 {
-    if (!n) return cudaSuccess;
-    k_count_codes<<<(unsigned)((n + 1023) / 1024), 256, 0, st>>>(codes, n, bm1, bm2, bm3);
+    const uint64_t total = ((n0 + 3) >> 2) + ((n1 + 3) >> 2);
+    if (!total) return cudaSuccess;
+    if (units >= 4) k_count_codes<4><<<(unsigned)((total + 1023) / 1024), 256, 0, st>>>(c0, n0, c1, n1, bm1, bm2, bm3);
+    else if (units == 2) k_count_codes<2><<<(unsigned)((total + 511) / 512), 256, 0, st>>>(c0, n0, c1, n1, bm1, bm2, bm3);
+    else k_count_codes<1><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(c0, n0, c1, n1, bm1, bm2, bm3);
     return cudaGetLastError();
 }
 
