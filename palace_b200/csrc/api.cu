@@ -8,6 +8,7 @@
 #include <cstring>
 #include <cstdlib>
 #include <vector>
+#include <algorithm>
 #include <new>
 
 namespace {
@@ -84,16 +85,15 @@ struct eref_ctx {
     bool summary_stale = true;
     unsigned long long h_hist[NBUCKETS_HOST] = {}, h_off[NBUCKETS_HOST + 1] = {};
     // reference side
-    DevBuf r_text, nl_pos, line_val, line_cum, rec_hdr_line, rec_first, rec_len, rec_kept, rec_words,
+    DevBuf r_text, tile_sum, tile_pre, rec_hdr_off, rec_first, rec_len, rec_kept, rec_words,
         rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
         sample_hits, cand, need, single, trio, good, results, codes_tmp;
     const uint8_t* ref_text_dev = nullptr;    // where the current reference text lives
     uint64_t ref_text_n = 0;
     bool have_ref = false;
-    uint32_t n_nl = 0, n_lines = 0, n_recs = 0, n_genomes = 0;
+    uint32_t n_recs = 0, n_genomes = 0;
     uint64_t ref_words = 0, ref_bases = 0;
-    std::vector<uint32_t> h_g_len, h_g_word, h_g_rec, h_rec_hdr_line;
-    std::vector<uint32_t> h_nl_hdr;           // unused placeholder for future name lookups
+    std::vector<uint32_t> h_g_len, h_g_word, h_g_rec, h_rec_hdr_off;
     eref_phase_times t{};
     uint64_t launches = 0;
 };
@@ -261,78 +261,72 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         return eref_fail(EREF_ERR_LIMIT, "reference text of %llu bytes: one shard must stay below 4 GiB",
                          (unsigned long long)n);
     CUDA_TRY(cudaEventRecord(c->ev[E1], st));
-    // 1. newline positions
-    uint64_t ntiles = 0;
-    int rc = newline_census(c, text, n, &ntiles);
-    if (rc) return rc;
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 0, c->tile_prefix.as<uint32_t>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
+    // 1. per-tile framing summaries and their prefix: line/header state, records and sequence bytes before each tile
+    const uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
+    CUDA_TRY(c->tile_sum.ensure((ntiles + 1) * sizeof(TileSum)));
+    CUDA_TRY(c->tile_pre.ensure((ntiles + 1) * sizeof(TileSum)));
+    TileSum* tiles = c->tile_sum.as<TileSum>();
+    TileSum* tile_pre = c->tile_pre.as<TileSum>();
+    CUDA_TRY(cudaMemsetAsync(tiles + ntiles, 0, sizeof(TileSum), st));          // sentinel: its prefix is the total
+    LAUNCH(c, launch_fasta_tiles(text, n, tiles, ntiles, st));
+    {
+        size_t bytes = 0;
+        const TileSum zero{0, 0, 0, 0};
+        CUDA_TRY(cub::DeviceScan::ExclusiveScan(nullptr, bytes, tiles, tile_pre, TileOp(), zero, (int)(ntiles + 1), st));
+        CUDA_TRY(c->cub_tmp.ensure(bytes));
+        CUDA_TRY(cub::DeviceScan::ExclusiveScan(c->cub_tmp.p, bytes, tiles, tile_pre, TileOp(), zero, (int)(ntiles + 1), st));
+        c->launches += 2;
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, tile_pre + ntiles, sizeof(TileSum), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    const uint32_t n_nl = (uint32_t)(c->h_pin[0] & 0xFFFFFFFFull);
-    const uint32_t n_lines = n_nl + 1;             // the last line may be empty: it then adds nothing
-    CUDA_TRY(c->nl_pos.ensure(((size_t)n_nl + 1) * 4));
-    CUDA_TRY(c->line_val.ensure(((size_t)n_lines + 1) * 8));
-    CUDA_TRY(c->line_cum.ensure(((size_t)n_lines + 1) * 8));
-    LAUNCH(c, launch_write_newlines(text, n, c->tile_prefix.as<uint32_t>(), c->nl_pos.as<uint32_t>(), ntiles, st));
-    // 2. per-line (header flag, sequence bytes) and their running sums
-    LAUNCH(c, launch_line_info(text, n, c->nl_pos.as<uint32_t>(), n_nl, n_lines, c->line_val.as<uint64_t>(), st));
-    rc = exclusive_scan<uint64_t>(c, c->line_val.as<uint64_t>(), c->line_cum.as<uint64_t>(), (size_t)n_lines + 1);
-    if (rc) return rc;
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 1, c->line_cum.as<uint64_t>() + n_lines, 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
-    const uint64_t totals = c->h_pin[1];
-    const uint32_t n_recs = (uint32_t)(totals >> 40) + 1;
-    const uint64_t total_seq = totals & ((1ull << 40) - 1);
-    // 3. records: first sequence byte, length, keep flag, packed size
+    TileSum total;
+    memcpy(&total, c->h_pin + 8, sizeof total);
+    const uint32_t n_recs = total.hdrs + 1;               // record 0 = whatever precedes the first header
+    const uint64_t total_seq = total.seqA + total.seqB;
+    // 2. records: first sequence byte, header offset, length, keep flag, packed size
     const size_t rn = (size_t)n_recs + 1;
-    CUDA_TRY(c->rec_hdr_line.ensure(rn * 4)); CUDA_TRY(c->rec_first.ensure(rn * 4));
+    CUDA_TRY(c->rec_hdr_off.ensure(rn * 4)); CUDA_TRY(c->rec_first.ensure(rn * 4));
     CUDA_TRY(c->rec_len.ensure(rn * 4)); CUDA_TRY(c->rec_kept.ensure(rn * 4));
     CUDA_TRY(c->rec_words.ensure(rn * 4)); CUDA_TRY(c->rec_kept_ex.ensure(rn * 4));
     CUDA_TRY(c->rec_words_ex.ensure(rn * 4));
-    LAUNCH(c, launch_record_starts(c->line_val.as<uint64_t>(), c->line_cum.as<uint64_t>(), n_lines,
-                                   c->rec_hdr_line.as<uint32_t>(), c->rec_first.as<uint32_t>(), st));
-    CUDA_TRY(cudaMemsetAsync(c->counters.as<unsigned long long>() + 3, 0, 8, st));
+    CUDA_TRY(c->g_rec.ensure(rn * 4)); CUDA_TRY(c->g_len.ensure(rn * 4));
+    CUDA_TRY(c->g_word.ensure(rn * 4)); CUDA_TRY(c->g_first.ensure(rn * 4));
+    const size_t words_ub = (size_t)(total_seq / 32) + n_recs + 2;   // every kept record: (len>>5)+1 words
+    CUDA_TRY(c->r_hi.ensure(words_ub * 4)); CUDA_TRY(c->r_lo.ensure(words_ub * 4));
+    CUDA_TRY(c->r_ok.ensure(words_ub * 4)); CUDA_TRY(c->word_genome.ensure(words_ub * 4));
+    LAUNCH(c, launch_fasta_records(text, n, tiles, tile_pre, ntiles, c->rec_first.as<uint32_t>(),
+                                   c->rec_hdr_off.as<uint32_t>(), st));
+    unsigned long long* totals = c->counters.as<unsigned long long>() + 3;      // bases | genomes | words
+    CUDA_TRY(cudaMemsetAsync(totals, 0, 24, st));
     LAUNCH(c, launch_record_info(c->rec_first.as<uint32_t>(), n_recs, total_seq, c->rec_len.as<uint32_t>(),
-                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(),
-                                 c->counters.as<unsigned long long>() + 3, st));
-    rc = exclusive_scan<uint32_t>(c, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(), rn);
+                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(), totals, st));
+    int rc = exclusive_scan<uint32_t>(c, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(), rn);
     if (rc) return rc;
     rc = exclusive_scan<uint32_t>(c, c->rec_words.as<uint32_t>(), c->rec_words_ex.as<uint32_t>(), rn);
     if (rc) return rc;
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 2, c->rec_kept_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 3, c->rec_words_ex.as<uint32_t>() + n_recs, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 4, c->counters.as<unsigned long long>() + 3, 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
-    const uint32_t n_genomes = (uint32_t)(c->h_pin[2] & 0xFFFFFFFFull), n_words = (uint32_t)(c->h_pin[3] & 0xFFFFFFFFull);
-    const uint64_t bases = c->h_pin[4];
-    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
-    // 4. genome table + packed planes
-    const size_t gn = (size_t)n_genomes + 1;
-    CUDA_TRY(c->g_rec.ensure(gn * 4)); CUDA_TRY(c->g_len.ensure(gn * 4));
-    CUDA_TRY(c->g_word.ensure(gn * 4)); CUDA_TRY(c->g_first.ensure(gn * 4));
     LAUNCH(c, launch_genome_table(c->rec_len.as<uint32_t>(), c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(),
-                                  c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(),
-                                  c->rec_hdr_line.as<uint32_t>(), n_recs, c->g_rec.as<uint32_t>(),
-                                  c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_first.as<uint32_t>(), st));
+                                  c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(), n_recs,
+                                  c->g_rec.as<uint32_t>(), c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(),
+                                  c->g_first.as<uint32_t>(), c->word_genome.as<uint32_t>(), totals + 1, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 2, totals, 24, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+    // 3. text -> planes (OR-ed into zeroed planes: words on tile boundaries are shared by two CTAs)
     Planes pl;
-    pl.nwords = n_words;
-    CUDA_TRY(c->r_hi.ensure(((size_t)n_words + 1) * 4));
-    CUDA_TRY(c->r_lo.ensure(((size_t)n_words + 1) * 4));
-    CUDA_TRY(c->r_ok.ensure(((size_t)n_words + 1) * 4));
-    CUDA_TRY(c->word_genome.ensure(((size_t)n_words + 1) * 4));
     pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
-    CUDA_TRY(cudaMemsetAsync(pl.hi + n_words, 0, 4, st));
-    CUDA_TRY(cudaMemsetAsync(pl.lo + n_words, 0, 4, st));
-    CUDA_TRY(cudaMemsetAsync(pl.ok + n_words, 0, 4, st));
-    if (n_genomes)
-        LAUNCH(c, launch_pack_fasta(text, n, c->nl_pos.as<uint32_t>(), n_nl, c->line_cum.as<uint64_t>(), n_lines,
-                                    c->rec_hdr_line.as<uint32_t>(), n_recs, c->g_rec.as<uint32_t>(),
-                                    c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_first.as<uint32_t>(),
-                                    n_genomes, pl, c->word_genome.as<uint32_t>(), st));
+    pl.nwords = 0;
+    CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, st));
+    LAUNCH(c, launch_pack_fasta(text, n, tile_pre, ntiles, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(),
+                                c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(), pl,
+                                c->word_genome.as<uint32_t>(), st));
     CUDA_TRY(cudaEventRecord(c->ev[E3], st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    c->host_tables_valid = false;             // ordinal -> length / packed offset / header line: fetched on demand
+    const uint64_t bases = c->h_pin[2];
+    const uint32_t n_genomes = (uint32_t)c->h_pin[3], n_words = (uint32_t)c->h_pin[4];
+    c->host_tables_valid = false;             // ordinal -> length / packed offset / header offset: fetched on demand
     c->ref_text_dev = text; c->ref_text_n = n;
-    c->n_nl = n_nl; c->n_lines = n_lines; c->n_recs = n_recs; c->n_genomes = n_genomes;
+    c->n_recs = n_recs; c->n_genomes = n_genomes;
     c->ref_words = n_words; c->ref_bases = bases;
     c->have_ref = true;
     c->t.ref_h2d_ms = ev_ms(c, E0, E1);
@@ -396,13 +390,13 @@ int fetch_host_tables(eref_ctx* c)
 {
     if (c->host_tables_valid) return 0;
     const size_t gn = (size_t)c->n_genomes + 1, rn = (size_t)c->n_recs + 1;
-    c->h_g_len.assign(gn, 0); c->h_g_word.assign(gn, 0); c->h_g_rec.assign(gn, 0); c->h_rec_hdr_line.assign(rn, 0);
+    c->h_g_len.assign(gn, 0); c->h_g_word.assign(gn, 0); c->h_g_rec.assign(gn, 0); c->h_rec_hdr_off.assign(rn, 0);
     if (c->n_genomes) {
         CUDA_TRY(cudaMemcpy(c->h_g_len.data(), c->g_len.p, (size_t)c->n_genomes * 4, cudaMemcpyDeviceToHost));
         CUDA_TRY(cudaMemcpy(c->h_g_word.data(), c->g_word.p, gn * 4, cudaMemcpyDeviceToHost));
         CUDA_TRY(cudaMemcpy(c->h_g_rec.data(), c->g_rec.p, (size_t)c->n_genomes * 4, cudaMemcpyDeviceToHost));
     }
-    CUDA_TRY(cudaMemcpy(c->h_rec_hdr_line.data(), c->rec_hdr_line.p, (size_t)c->n_recs * 4, cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(c->h_rec_hdr_off.data(), c->rec_hdr_off.p, (size_t)c->n_recs * 4, cudaMemcpyDeviceToHost));
     c->host_tables_valid = true;
     return 0;
 }
@@ -481,7 +475,7 @@ void eref_destroy(eref_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->q_text, &c->q_hi, &c->q_lo,
-                      &c->q_ok, &c->r_text, &c->nl_pos, &c->line_val, &c->line_cum, &c->rec_hdr_line, &c->rec_first,
+                      &c->q_ok, &c->r_text, &c->tile_sum, &c->tile_pre, &c->rec_hdr_off, &c->rec_first,
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
                       &c->g_len, &c->g_word, &c->g_first, &c->r_hi, &c->r_lo, &c->r_ok, &c->word_genome,
                       &c->sample_hits, &c->cand, &c->need, &c->single, &c->trio, &c->good, &c->results,
@@ -759,13 +753,19 @@ int eref_ref_record(eref_ctx* c, uint32_t ordinal, uint64_t* hdr_off, uint32_t* 
     if (len) *len = c->h_g_len[ordinal - 1];
     uint64_t off = 0; uint32_t hl = 0;
     if (r > 0) {                                      // record 0 has no header line
-        const uint32_t line = c->h_rec_hdr_line[r];
-        uint32_t se[2] = {0, 0};
-        if (line > 0) CUDA_TRY(cudaMemcpy(&se[0], c->nl_pos.as<uint32_t>() + (line - 1), 4, cudaMemcpyDeviceToHost));
-        if (line < c->n_nl) CUDA_TRY(cudaMemcpy(&se[1], c->nl_pos.as<uint32_t>() + line, 4, cudaMemcpyDeviceToHost));
-        else se[1] = (uint32_t)c->ref_text_n;
-        off = line > 0 ? (uint64_t)se[0] + 1 : 0;
-        hl = (uint32_t)(se[1] - off);
+        off = c->h_rec_hdr_off[r];
+        // the header runs to the next newline (or the end of the text): look for it 256 bytes at a time
+        char buf[256];
+        uint64_t pos = off;
+        bool found = false;
+        while (pos < c->ref_text_n && !found) {
+            const size_t k = (size_t)std::min<uint64_t>(sizeof buf, c->ref_text_n - pos);
+            CUDA_TRY(cudaMemcpy(buf, c->ref_text_dev + pos, k, cudaMemcpyDeviceToHost));
+            const void* nl = memchr(buf, '\n', k);
+            if (nl) { pos += (uint64_t)((const char*)nl - buf); found = true; }
+            else pos += k;
+        }
+        hl = (uint32_t)(pos - off);
     }
     if (hdr_off) *hdr_off = off;
     if (hdr_len) *hdr_len = hl;

@@ -34,6 +34,26 @@ struct Planes {
     uint64_t  nwords;        // without the pad word
 };
 
+// FASTA framing state of a text tile (frame.cu), combined left to right by TileOp: flags bit 0 = a line
+// starts inside the tile, bit 1 = the last line started inside it is a header; hdrs = header lines started;
+// seqA = non-newline bytes before the first line start, seqB = bytes of non-header lines after it.
+struct TileSum {
+    uint32_t flags, hdrs;
+    unsigned long long seqA, seqB;
+};
+
+struct TileOp {
+    __host__ __device__ __forceinline__ TileSum operator()(const TileSum& x, const TileSum& y) const
+    {
+        TileSum r;
+        r.flags = (y.flags & 1u) ? y.flags : (x.flags | (y.flags & 1u));
+        r.hdrs = x.hdrs + y.hdrs;
+        if (x.flags & 1u) { r.seqA = x.seqA; r.seqB = x.seqB + y.seqB + ((x.flags & 2u) ? 0ull : y.seqA); }
+        else              { r.seqA = x.seqA + y.seqA; r.seqB = y.seqB; }
+        return r;
+    }
+};
+
 __device__ __forceinline__ uint32_t bitsel(uint32_t mask, uint32_t a, uint32_t b)
 {
     return (a & mask) | (b & ~mask);                 // one LOP3
@@ -105,25 +125,19 @@ cudaError_t launch_count_newlines(const uint8_t* text, uint64_t n, uint32_t* til
                                   uint64_t ntiles, cudaStream_t st);
 cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
                               Planes pl, unsigned long long* seq_bytes, cudaStream_t st);
-cudaError_t launch_write_newlines(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
-                                  uint32_t* nl_pos, uint64_t ntiles, cudaStream_t st);
-cudaError_t launch_line_info(const uint8_t* text, uint64_t n, const uint32_t* nl_pos, uint32_t n_nl,
-                             uint32_t n_lines, uint64_t* line_val, cudaStream_t st);
-cudaError_t launch_record_starts(const uint64_t* line_val, const uint64_t* line_cum, uint32_t n_lines,
-                                 uint32_t* rec_hdr_line, uint32_t* rec_first, cudaStream_t st);
+cudaError_t launch_fasta_tiles(const uint8_t* text, uint64_t n, TileSum* tiles, uint64_t ntiles, cudaStream_t st);
+cudaError_t launch_fasta_records(const uint8_t* text, uint64_t n, const TileSum* tiles, const TileSum* tile_pre,
+                                 uint64_t ntiles, uint32_t* rec_first, uint32_t* rec_hdr_off, cudaStream_t st);
 cudaError_t launch_record_info(const uint32_t* rec_first, uint32_t n_recs, uint64_t total_seq,
                                uint32_t* rec_len, uint32_t* rec_kept, uint32_t* rec_words,
                                unsigned long long* kept_bases, cudaStream_t st);
-cudaError_t launch_genome_table(const uint32_t* rec_len, const uint32_t* rec_kept,
-                                const uint32_t* rec_kept_ex, const uint32_t* rec_words_ex,
-                                const uint32_t* rec_first, const uint32_t* rec_hdr_line, uint32_t n_recs,
+cudaError_t launch_genome_table(const uint32_t* rec_len, const uint32_t* rec_kept, const uint32_t* rec_kept_ex,
+                                const uint32_t* rec_words_ex, const uint32_t* rec_first, uint32_t n_recs,
                                 uint32_t* g_rec, uint32_t* g_len, uint32_t* g_word, uint32_t* g_first,
-                                cudaStream_t st);
-cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const uint32_t* nl_pos, uint32_t n_nl,
-                              const uint64_t* line_cum, uint32_t n_lines, const uint32_t* rec_hdr_line,
-                              uint32_t n_recs, const uint32_t* g_rec, const uint32_t* g_len,
-                              const uint32_t* g_word, const uint32_t* g_first, uint32_t n_genomes,
-                              Planes pl, uint32_t* word_genome, cudaStream_t st);
+                                uint32_t* word_genome, unsigned long long* totals, cudaStream_t st);
+cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const TileSum* tile_pre, uint64_t ntiles,
+                              const uint32_t* rec_kept, const uint32_t* rec_kept_ex, const uint32_t* rec_words_ex,
+                              const uint32_t* rec_first, Planes pl, uint32_t* word_genome, cudaStream_t st);
 // table.cu
 cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
                                cudaStream_t st);

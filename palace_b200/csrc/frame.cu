@@ -1,11 +1,17 @@
 // frame.cu — text framing and packing kernels (north_star part 1): FASTQ/FASTA bytes in HBM ->
 // three bit-planes (hi, lo, ok).  Replaces the getline loops of bin/extract_ref.cpp:686-756 (FASTA
 // records) and :940-947 (FASTQ sequence lines).
+//
+// Every kernel here is text-driven: a CTA of 256 threads owns an 8 KiB tile, a thread owns 32 bytes
+// (two LDG.128) and reduces them to 32-bit masks with SIMD-within-a-register arithmetic (four bytes per
+// integer op, bits gathered by one multiply), so the cost is a few integer instructions per byte and the
+// text is streamed at HBM speed.  Line/record state that crosses thread and tile boundaries is carried
+// by prefix scans over an associative "chunk summary" (FastaSum / TileSum).
 #include "eref_internal.cuh"
 
 namespace {
 
-constexpr uint64_t SEQ_MASK = (1ull << 40) - 1;      // line_val/line_cum: low 40 bits = sequence bytes
+// ---- 32 bytes -> masks (byte k of the chunk <-> bit 31-k) ------------------------------------------
 
 // 32 bytes of text starting at off (off is a multiple of 32; text is 16-byte aligned).
 // Bytes at or beyond n read as 0 (an invalid base that is not a newline).
@@ -20,18 +26,81 @@ __device__ __forceinline__ void load32(const uint8_t* __restrict__ text, uint64_
     } else {
 #pragma unroll
         for (int i = 0; i < 8; i++) w[i] = 0;
-        for (uint64_t k = off; k < n; k++) {
-            uint32_t j = (uint32_t)(k - off);
-            w[j >> 2] |= (uint32_t)text[k] << ((j & 3) * 8);
-        }
+#pragma unroll
+        for (int k = 0; k < 32; k++)
+            if (off + k < n) w[k >> 2] |= (uint32_t)text[off + k] << ((k & 3) * 8);
     }
 }
+
+// 0x01 in every byte of x that is zero (exact per byte, no cross-byte borrow)
+__device__ __forceinline__ uint32_t zero_bytes(uint32_t x)
+{
+    const uint32_t t = ((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x;       // bit 7 clear iff the byte is 0
+    return (~t >> 7) & 0x01010101u;
+}
+
+// Two sets of per-byte flags (a at bits 0,8,16,24; b at bits 4,12,20,28) -> one multiply puts the four
+// a flags in bits 27..24 and the four b flags in bits 31..28, first byte of the word most significant
+// (all partial products land on distinct bits, so there are no carries).
+__device__ __forceinline__ uint32_t gather2(uint32_t a01, uint32_t b10) { return (a01 | b10) * 0x08040201u; }
+
+template <int J> __device__ __forceinline__ uint32_t place_lo(uint32_t prod)   // nibble 27..24 -> bits 31-4J..28-4J
+{
+    const uint32_t nib = prod & 0x0F000000u;
+    return J == 0 ? nib << 4 : nib >> (J == 0 ? 0 : 4 * J - 4);
+}
+template <int J> __device__ __forceinline__ uint32_t place_hi(uint32_t prod)   // nibble 31..28 -> bits 31-4J..28-4J
+{
+    return (prod & 0xF0000000u) >> (4 * J);
+}
+
+struct Masks { uint32_t nl, hi, lo, ok; };
+
+// nl: byte == '\n'.  ok: byte is one of ACGTacgt (:978).  hi/lo: 2-bit base code A=00 C=01 G=10 T=11 from
+// ASCII bits 2 and 1 (hi = bit2, lo = bit1 ^ bit2), zero where ok is zero.
+template <int J>
+__device__ __forceinline__ void masks_word(uint32_t w, Masks& m)
+{
+    const uint32_t b2 = (w >> 2) & 0x01010101u;
+    const uint32_t b1 = (w >> 1) & 0x01010101u;
+    const uint32_t nl = zero_bytes(w ^ 0x0A0A0A0Au);
+    const uint32_t aceg = zero_bytes((w ^ 0x41414141u) & 0xD9D9D9D9u);   // 0x41 0x43 0x45 0x47, either case
+    const uint32_t tt = zero_bytes((w ^ 0x54545454u) & 0xDFDFDFDFu);     // 0x54, either case
+    const uint32_t ok = (aceg & ~(b2 & ~b1)) | tt;                       // drop 0x45/0x65 ('E'): bit2 set, bit1 clear
+    const uint32_t p0 = gather2(b2 & ok, ((b1 ^ b2) & ok) << 4);
+    const uint32_t p1 = gather2(ok, nl << 4);
+    m.hi |= place_lo<J>(p0); m.lo |= place_hi<J>(p0);
+    m.ok |= place_lo<J>(p1); m.nl |= place_hi<J>(p1);
+}
+
+__device__ __forceinline__ Masks chunk_masks(const uint32_t w[8])
+{
+    Masks m{0, 0, 0, 0};
+    masks_word<0>(w[0], m); masks_word<1>(w[1], m); masks_word<2>(w[2], m); masks_word<3>(w[3], m);
+    masks_word<4>(w[4], m); masks_word<5>(w[5], m); masks_word<6>(w[6], m); masks_word<7>(w[7], m);
+    return m;
+}
+
+template <int J>
+__device__ __forceinline__ uint32_t nl_word(uint32_t w)
+{
+    return place_lo<J>(zero_bytes(w ^ 0x0A0A0A0Au) * 0x08040201u);
+}
+
+__device__ __forceinline__ uint32_t chunk_newlines(const uint32_t w[8])
+{
+    return nl_word<0>(w[0]) | nl_word<1>(w[1]) | nl_word<2>(w[2]) | nl_word<3>(w[3]) |
+           nl_word<4>(w[4]) | nl_word<5>(w[5]) | nl_word<6>(w[6]) | nl_word<7>(w[7]);
+}
+
+// positions [0, k) of a chunk as a mask (k in 0..32)
+__device__ __forceinline__ uint32_t before(int k) { return k >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> k); }
 
 __device__ __forceinline__ uint32_t count_nl(const uint32_t w[8])
 {
     uint32_t c = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++) c += __popc(__vcmpeq4(w[i], 0x0A0A0A0Au) & 0x01010101u);
+    for (int i = 0; i < 8; i++) c += __popc(zero_bytes(w[i] ^ 0x0A0A0A0Au));
     return c;
 }
 
@@ -67,6 +136,8 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* t
     return r;
 }
 
+// ---- FASTQ ---------------------------------------------------------------------------------------------
+
 __global__ void __launch_bounds__(TILE_THREADS)
 k_count_newlines(const uint8_t* __restrict__ text, uint64_t n, uint32_t* __restrict__ tile_counts)
 {
@@ -86,28 +157,34 @@ __global__ void __launch_bounds__(TILE_THREADS)
 k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
              Planes pl, unsigned long long* __restrict__ seq_bytes)
 {
-    uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
+    const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     uint32_t w[8];
-    uint32_t c = 0;
     const bool live = off < n;
-    if (live) { load32(text, n, off, w); c = count_nl(w); }
-    uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(c, nullptr);
-    uint32_t hi = 0, lo = 0, ok = 0, nseq = 0;
+    load32(text, n, off, w);
+    const Masks m = chunk_masks(w);
+    uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(__popc(m.nl), nullptr);
+    uint32_t nseq = 0;
     if (live) {
-        const uint32_t lim = (uint32_t)min((uint64_t)32, n - off);
-#pragma unroll
-        for (int k = 0; k < 32; k++) {
-            uint32_t ch = (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
-            bool seq_line = (line & 3u) == 1u;
-            if (ch == 0x0Au) line++;
-            else if (seq_line && (uint32_t)k < lim) nseq++;
-            uint32_t b2 = (ch >> 2) & 1u, b1 = (ch >> 1) & 1u;
-            hi |= b2 << (31 - k);
-            lo |= (b1 ^ b2) << (31 - k);
-            ok |= (uint32_t)(seq_line && is_acgt(ch)) << (31 - k);
+        const uint32_t inr = before((int)min((uint64_t)32, n - off));
+        uint32_t seq = 0;                                 // bytes on a sequence line, newlines excluded
+        if (!m.nl) {
+            seq = (line & 3u) == 1u ? 0xFFFFFFFFu : 0u;
+        } else {
+            uint32_t rest = m.nl;
+            int start = 0;
+            while (true) {
+                const int k = rest ? __clz(rest) : 32;
+                if ((line & 3u) == 1u) seq |= before(k) & ~before(start);
+                if (k == 32) break;
+                rest &= ~(0x80000000u >> k);
+                start = k + 1; line++;
+            }
         }
-        uint64_t word = off >> 5;
-        pl.hi[word] = hi; pl.lo[word] = lo; pl.ok[word] = ok;
+        seq &= inr;
+        nseq = __popc(seq);
+        const uint32_t ok = m.ok & seq;
+        const uint64_t word = off >> 5;
+        pl.hi[word] = m.hi & ok; pl.lo[word] = m.lo & ok; pl.ok[word] = ok;
     }
     // cal_sam_ratio's sum (:1138-1140): all bytes of sequence lines, valid or not
 #pragma unroll
@@ -115,51 +192,175 @@ k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
     if ((threadIdx.x & 31) == 0 && nseq) atomicAdd(seq_bytes, (unsigned long long)nseq);
 }
 
-__global__ void __launch_bounds__(TILE_THREADS)
-k_write_newlines(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
-                 uint32_t* __restrict__ nl_pos)
+// ---- FASTA ---------------------------------------------------------------------------------------------
+// Lines end at '\n' only; a line is a header iff its first byte is '>' (:687); every other byte of every
+// other line is appended verbatim to the current record (:754), so '\r', blanks and N count as (invalid)
+// bases.  Record 0 is whatever precedes the first header; record r >= 1 starts at the r-th header.
+//
+// Chunk summary (associative, see TileSum in eref_internal.cuh): has = a line starts inside the chunk;
+// state = the last line started inside the chunk is a header; hdrs = header lines started; seqA = non-newline
+// bytes before the first line start (they belong to the line in progress and count only if that line is
+// not a header); seqB = bytes of non-header lines after the first line start.
+
+struct FastaSum {                       // per-thread / per-tile form, small counts
+    uint32_t has, state, hdrs, seqA, seqB;
+};
+
+__device__ __forceinline__ FastaSum combine(const FastaSum& x, const FastaSum& y)
 {
-    uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
-    uint32_t w[8];
-    uint32_t c = 0;
-    const bool live = off < n;
-    if (live) { load32(text, n, off, w); c = count_nl(w); }
-    uint32_t idx = tile_prefix[blockIdx.x] + block_exclusive_scan(c, nullptr);
-    if (live && c) {
+    FastaSum r;
+    r.has = x.has | y.has;
+    r.state = y.has ? y.state : x.state;
+    r.hdrs = x.hdrs + y.hdrs;
+    if (x.has) { r.seqA = x.seqA; r.seqB = x.seqB + y.seqB + (x.state ? 0u : y.seqA); }
+    else       { r.seqA = x.seqA + y.seqA; r.seqB = y.seqB; }
+    return r;
+}
+
+__device__ __forceinline__ unsigned long long pack_sum(const FastaSum& s)
+{
+    return (unsigned long long)s.seqB | ((unsigned long long)s.seqA << 16) | ((unsigned long long)s.hdrs << 32) |
+           ((unsigned long long)s.state << 48) | ((unsigned long long)s.has << 49);
+}
+
+__device__ __forceinline__ FastaSum unpack_sum(unsigned long long v)
+{
+    FastaSum s;
+    s.seqB = (uint32_t)(v & 0xFFFFu); s.seqA = (uint32_t)((v >> 16) & 0xFFFFu); s.hdrs = (uint32_t)((v >> 32) & 0xFFFFu);
+    s.state = (uint32_t)((v >> 48) & 1u); s.has = (uint32_t)((v >> 49) & 1u);
+    return s;
+}
+
+// exclusive scan of the chunk summaries over the CTA (thread order = text order); *total = whole tile
+__device__ __forceinline__ FastaSum block_scan_fasta(const FastaSum& mine, FastaSum* total)
+{
+    __shared__ unsigned long long warp_tot[TILE_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    FastaSum inc = mine;
 #pragma unroll
-        for (int k = 0; k < 32; k++) {
-            uint32_t ch = (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
-            if (ch == 0x0Au) nl_pos[idx++] = (uint32_t)(off + k);
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, pack_sum(inc), d);
+        if (lane >= d) inc = combine(unpack_sum(t), inc);
+    }
+    unsigned long long prev = __shfl_up_sync(0xffffffffu, pack_sum(inc), 1);
+    FastaSum ex = lane ? unpack_sum(prev) : FastaSum{0, 0, 0, 0, 0};
+    if (lane == 31) warp_tot[warp] = pack_sum(inc);
+    __syncthreads();
+    FastaSum before_warp{0, 0, 0, 0, 0}, all{0, 0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < TILE_THREADS / 32; k++) {
+        const FastaSum t = unpack_sum(warp_tot[k]);
+        if (k < warp) before_warp = combine(before_warp, t);
+        all = combine(all, t);
+    }
+    __syncthreads();
+    if (total) *total = all;
+    return combine(before_warp, ex);
+}
+
+struct FastaChunk {
+    Masks m;
+    uint32_t inr;       // bytes below n
+    uint32_t ls;        // line starts inside the chunk
+    uint32_t hs;        // ... that are header lines
+    uint32_t hm;        // bytes of header lines started inside the chunk
+    uint32_t pm;        // bytes before the first line start
+    FastaSum sum;
+};
+
+// FULL = false: only the newline mask is formed (hi/lo/ok stay 0) — enough for the summaries.
+template <bool FULL>
+__device__ __forceinline__ FastaChunk fasta_chunk(const uint8_t* __restrict__ text, uint64_t n, uint64_t off)
+{
+    FastaChunk c;
+    uint32_t w[8];
+    load32(text, n, off, w);
+    if (FULL) c.m = chunk_masks(w);
+    else { c.m.hi = c.m.lo = c.m.ok = 0; c.m.nl = chunk_newlines(w); }
+    const int lim = off < n ? (int)min((uint64_t)32, n - off) : 0;
+    c.inr = before(lim);
+    // the byte before the chunk decides whether byte 0 starts a line
+    uint32_t prev_nl = __shfl_up_sync(0xffffffffu, c.m.nl & 1u, 1);
+    if ((threadIdx.x & 31) == 0) prev_nl = off == 0 ? 1u : (off - 1 < n ? (uint32_t)(__ldg(text + off - 1) == 0x0Au) : 0u);
+    c.ls = ((c.m.nl >> 1) | (prev_nl << 31)) & c.inr;
+    c.hs = 0; c.hm = 0;
+    FastaSum s{0, 0, 0, 0, 0};
+    const uint32_t body = ~c.m.nl & c.inr;               // bytes that are not newlines
+    if (!c.ls) {
+        c.pm = 0xFFFFFFFFu;
+        s.seqA = __popc(body);
+    } else {
+        uint32_t rest = c.ls;
+        c.pm = before(__clz(rest));
+        s.has = 1;
+        while (rest) {
+            const int k = __clz(rest);
+            rest &= ~(0x80000000u >> k);
+            const bool hdr = __ldg(text + off + k) == (uint8_t)'>';
+            if (hdr) {
+                c.hs |= 0x80000000u >> k;
+                c.hm |= ~before(k) & before(rest ? __clz(rest) : 32);
+            }
+            s.state = hdr;
         }
+        s.hdrs = __popc(c.hs);
+        s.seqA = __popc(body & c.pm);
+        s.seqB = __popc(body & ~c.pm & ~c.hm);
+    }
+    c.sum = s;
+    return c;
+}
+
+// K1: one summary per tile
+__global__ void __launch_bounds__(TILE_THREADS)
+k_fasta_tiles(const uint8_t* __restrict__ text, uint64_t n, TileSum* __restrict__ tiles)
+{
+    const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
+    const FastaChunk c = fasta_chunk<false>(text, n, off);
+    FastaSum all;
+    block_scan_fasta(c.sum, &all);
+    if (threadIdx.x == 0) {
+        TileSum t;
+        t.flags = all.has | (all.state << 1); t.hdrs = all.hdrs; t.seqA = all.seqA; t.seqB = all.seqB;
+        tiles[blockIdx.x] = t;
     }
 }
 
-// One value per text line: (is_header << 40) | sequence_bytes.  A line is a header iff its first
-// byte is '>' (:687); every other line is appended verbatim to the current record (:754).
-__global__ void k_line_info(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ nl_pos,
-                            uint32_t n_nl, uint32_t n_lines, uint64_t* __restrict__ line_val)
+// what a thread knows about the text before its chunk, from the tile prefix and the in-tile scan
+struct Incoming { uint32_t in_header, rec, rank; };
+
+__device__ __forceinline__ Incoming incoming(const TileSum& tp, const FastaSum& ex)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i > n_lines) return;
-    if (i == n_lines) { line_val[i] = 0; return; }       // sentinel so the scan yields the totals
-    uint64_t start = i ? (uint64_t)nl_pos[i - 1] + 1 : 0;
-    uint64_t end = i < n_nl ? (uint64_t)nl_pos[i] : n;
-    bool hdr = end > start && text[start] == '>';
-    line_val[i] = hdr ? (1ull << 40) : (end - start);
+    Incoming in;
+    const uint32_t tile_state = (tp.flags & 1u) ? (tp.flags >> 1) & 1u : 0u;
+    in.in_header = ex.has ? ex.state : tile_state;
+    in.rec = tp.hdrs + ex.hdrs;
+    in.rank = (uint32_t)(tp.seqA + tp.seqB) + (tile_state ? 0u : ex.seqA) + ex.seqB;
+    return in;
 }
 
-// record r >= 1 starts at the r-th header line; record 0 is whatever precedes the first header.
-__global__ void k_record_starts(const uint64_t* __restrict__ line_val, const uint64_t* __restrict__ line_cum,
-                                uint32_t n_lines, uint32_t* __restrict__ rec_hdr_line,
-                                uint32_t* __restrict__ rec_first)
+// K3: first sequence rank and header offset of every record that starts in a tile with headers
+__global__ void __launch_bounds__(TILE_THREADS)
+k_fasta_records(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __restrict__ tiles,
+                const TileSum* __restrict__ tile_pre, uint32_t* __restrict__ rec_first,
+                uint32_t* __restrict__ rec_hdr_off)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) { rec_hdr_line[0] = 0xFFFFFFFFu; rec_first[0] = 0; }
-    if (i >= n_lines) return;
-    if (line_val[i] >> 40) {
-        uint32_t r = (uint32_t)(line_cum[i] >> 40) + 1;
-        rec_hdr_line[r] = i;
-        rec_first[r] = (uint32_t)(line_cum[i] & SEQ_MASK);
+    if (blockIdx.x == 0 && threadIdx.x == 0) { rec_first[0] = 0; rec_hdr_off[0] = 0xFFFFFFFFu; }
+    if (tiles[blockIdx.x].hdrs == 0) return;
+    const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
+    const FastaChunk c = fasta_chunk<false>(text, n, off);
+    const FastaSum ex = block_scan_fasta(c.sum, nullptr);
+    if (!c.hs) return;
+    const Incoming in = incoming(tile_pre[blockIdx.x], ex);
+    const uint32_t seq = ~c.m.nl & c.inr & ~c.hm & (in.in_header ? ~c.pm : 0xFFFFFFFFu);
+    uint32_t rest = c.hs;
+    uint32_t r = in.rec;
+    while (rest) {
+        const int k = __clz(rest);
+        rest &= ~(0x80000000u >> k);
+        r++;
+        rec_first[r] = in.rank + __popc(seq & before(k));
+        rec_hdr_off[r] = (uint32_t)(off + k);
     }
 }
 
@@ -187,66 +388,100 @@ __global__ void k_record_info(const uint32_t* __restrict__ rec_first, uint32_t n
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(kept_bases, mine);
 }
 
+// kept records -> genome table; also names the owner of each record's last word, which holds only pad
+// bits when len % 32 == 0 and is then never touched by k_pack_fasta
 __global__ void k_genome_table(const uint32_t* __restrict__ rec_len, const uint32_t* __restrict__ rec_kept,
                                const uint32_t* __restrict__ rec_kept_ex, const uint32_t* __restrict__ rec_words_ex,
                                const uint32_t* __restrict__ rec_first, uint32_t n_recs,
                                uint32_t* __restrict__ g_rec, uint32_t* __restrict__ g_len,
-                               uint32_t* __restrict__ g_word, uint32_t* __restrict__ g_first)
+                               uint32_t* __restrict__ g_word, uint32_t* __restrict__ g_first,
+                               uint32_t* __restrict__ word_genome, unsigned long long* __restrict__ totals)
 {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r > n_recs) return;
-    if (r == n_recs) { g_word[rec_kept_ex[r]] = rec_words_ex[r]; return; }   // end sentinel
+    if (r == n_recs) {                                    // end sentinel + the counts the host reads back
+        g_word[rec_kept_ex[r]] = rec_words_ex[r];
+        totals[0] = rec_kept_ex[r]; totals[1] = rec_words_ex[r];
+        return;
+    }
     if (!rec_kept[r]) return;
     uint32_t g = rec_kept_ex[r];
     g_rec[g] = r; g_len[g] = rec_len[r]; g_word[g] = rec_words_ex[r]; g_first[g] = rec_first[r];
+    word_genome[rec_words_ex[r] + (rec_len[r] >> 5)] = g;
 }
 
-// One thread per packed word: locate the record and the text line holding the word's first base,
-// then walk the text skipping newlines (the only bytes between two sequence lines of a record).
-__global__ void __launch_bounds__(256)
-k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ nl_pos, uint32_t n_nl,
-             const uint64_t* __restrict__ line_cum, uint32_t n_lines, const uint32_t* __restrict__ rec_hdr_line,
-             uint32_t n_recs, const uint32_t* __restrict__ g_rec, const uint32_t* __restrict__ g_len,
-             const uint32_t* __restrict__ g_word, const uint32_t* __restrict__ g_first, uint32_t n_genomes,
+// K5: text -> planes.  Within a chunk the sequence bytes of one line are one run of consecutive bytes
+// and land on consecutive plane bits (newlines and headers simply vanish), so a run is placed with one
+// shift: bit position = 32 * first word of the record + rank inside the record.  The CTA assembles its
+// (contiguous, < 512 words) piece of the planes in shared memory and writes whole words; the first and
+// last word may be shared with the neighbouring tiles and are OR-ed into the pre-zeroed planes.
+constexpr int RING = 512;
+
+__global__ void __launch_bounds__(TILE_THREADS)
+k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __restrict__ tile_pre,
+             const uint32_t* __restrict__ rec_kept, const uint32_t* __restrict__ rec_kept_ex,
+             const uint32_t* __restrict__ rec_words_ex, const uint32_t* __restrict__ rec_first,
              Planes pl, uint32_t* __restrict__ word_genome)
 {
-    uint64_t W = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (W >= pl.nwords) return;
-    // genome = last g with g_word[g] <= W
-    uint32_t lo = 0, hi = n_genomes;                 // invariant: g_word[lo] <= W < g_word[hi]
-    while (hi - lo > 1) {
-        uint32_t mid = (lo + hi) >> 1;
-        if ((uint64_t)g_word[mid] <= W) lo = mid; else hi = mid;
-    }
-    const uint32_t g = lo;
-    word_genome[W] = g;
-    const uint32_t len = g_len[g];
-    const uint32_t p0 = (uint32_t)(W - g_word[g]) << 5;
-    uint32_t vhi = 0, vlo = 0, vok = 0;
-    if (p0 < len) {
-        const uint32_t r = g_rec[g];
-        const uint64_t rank = (uint64_t)g_first[g] + p0;
-        uint32_t a = r ? rec_hdr_line[r] + 1 : 0;                     // first line of the record
-        uint32_t b = r + 1 < n_recs ? rec_hdr_line[r + 1] : n_lines;  // one past its last line
-        // last line i in [a, b) with seqcum(i) <= rank: the line that holds byte `rank`
-        while (b - a > 1) {
-            uint32_t mid = (a + b) >> 1;
-            if ((line_cum[mid] & SEQ_MASK) <= rank) a = mid; else b = mid;
+    __shared__ uint32_t s_hi[RING], s_lo[RING], s_ok[RING], s_g[RING];
+    __shared__ uint32_t s_min[TILE_THREADS / 32], s_max[TILE_THREADS / 32];
+    for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; s_g[i] = 0xFFFFFFFFu; }
+    const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
+    const FastaChunk c = fasta_chunk<true>(text, n, off);
+    const FastaSum ex = block_scan_fasta(c.sum, nullptr);          // (syncs: the ring is zeroed)
+    const Incoming in = incoming(tile_pre[blockIdx.x], ex);
+    const uint32_t seq = ~c.m.nl & c.inr & ~c.hm & (in.in_header ? ~c.pm : 0xFFFFFFFFu);
+    uint32_t wmin = 0xFFFFFFFFu, wmax = 0;
+    uint32_t rest = seq;
+    while (rest) {
+        const int k0 = __clz(rest);
+        const uint32_t inv = ~(rest << k0);
+        const int len = inv ? __clz(inv) : 32;
+        const uint32_t run = ~before(k0) & before(k0 + len);
+        rest &= ~run;
+        const uint32_t r = in.rec + __popc(c.hs & before(k0));
+        if (!rec_kept[r]) continue;
+        const uint32_t rank = in.rank + __popc(seq & before(k0));
+        const uint64_t dest = (uint64_t)rec_words_ex[r] * 32 + (rank - rec_first[r]);
+        const uint32_t g = rec_kept_ex[r];
+        const uint32_t wi = (uint32_t)(dest >> 5);
+        const int sh = (int)(dest & 31);
+        const uint32_t keep = before(len);
+        const uint32_t xh = (c.m.hi << k0) & keep, xl = (c.m.lo << k0) & keep, xo = (c.m.ok << k0) & keep;
+        const uint32_t i0 = wi & (RING - 1), i1 = (wi + 1) & (RING - 1);
+        if (xh >> sh) atomicOr(&s_hi[i0], xh >> sh);
+        if (xl >> sh) atomicOr(&s_lo[i0], xl >> sh);
+        if (xo >> sh) atomicOr(&s_ok[i0], xo >> sh);
+        s_g[i0] = g;
+        wmin = min(wmin, wi); wmax = max(wmax, wi);
+        if (sh + len > 32) {
+            const int up = 32 - sh;
+            if (xh << up) atomicOr(&s_hi[i1], xh << up);
+            if (xl << up) atomicOr(&s_lo[i1], xl << up);
+            if (xo << up) atomicOr(&s_ok[i1], xo << up);
+            s_g[i1] = g;
+            wmax = max(wmax, wi + 1);
         }
-        uint64_t pos = (a ? (uint64_t)nl_pos[a - 1] + 1 : 0) + (rank - (line_cum[a] & SEQ_MASK));
-        const uint32_t cnt = min(32u, len - p0);
-        uint32_t k = 0;
-        while (k < cnt && pos < n) {
-            uint32_t ch = text[pos++];
-            if (ch == 0x0Au) continue;
-            uint32_t b2 = (ch >> 2) & 1u, b1 = (ch >> 1) & 1u;
-            vhi |= b2 << (31 - k);
-            vlo |= (b1 ^ b2) << (31 - k);
-            vok |= (uint32_t)is_acgt(ch) << (31 - k);
-            k++;
-        }
     }
-    pl.hi[W] = vhi; pl.lo[W] = vlo; pl.ok[W] = vok;
+    wmin = __reduce_min_sync(0xffffffffu, wmin);
+    wmax = __reduce_max_sync(0xffffffffu, wmax);
+    if ((threadIdx.x & 31) == 0) { s_min[threadIdx.x >> 5] = wmin; s_max[threadIdx.x >> 5] = wmax; }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < TILE_THREADS / 32; k++) { wmin = min(wmin, s_min[k]); wmax = max(wmax, s_max[k]); }
+    if (wmin == 0xFFFFFFFFu) return;                      // no sequence byte of a kept record in this tile
+    for (uint32_t w = wmin + threadIdx.x; w <= wmax; w += TILE_THREADS) {
+        const uint32_t i = w & (RING - 1);
+        const uint32_t vh = s_hi[i], vl = s_lo[i], vo = s_ok[i], g = s_g[i];
+        if (w == wmin || w == wmax) {
+            if (vh) atomicOr(pl.hi + w, vh);
+            if (vl) atomicOr(pl.lo + w, vl);
+            if (vo) atomicOr(pl.ok + w, vo);
+        } else {
+            pl.hi[w] = vh; pl.lo[w] = vl; pl.ok[w] = vo;
+        }
+        if (g != 0xFFFFFFFFu) word_genome[w] = g;
+    }
 }
 
 } // namespace
@@ -270,26 +505,23 @@ cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* t
     return cudaGetLastError();
 }
 
-cudaError_t launch_write_newlines(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
-                                  uint32_t* nl_pos, uint64_t ntiles, cudaStream_t st)
+cudaError_t launch_fasta_tiles(const uint8_t* text, uint64_t n, TileSum* tiles, uint64_t ntiles, cudaStream_t st)
 {
     if (!ntiles) return cudaSuccess;
-    k_write_newlines<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, nl_pos);
+    k_fasta_tiles<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tiles);
     return cudaGetLastError();
 }
 
-cudaError_t launch_line_info(const uint8_t* text, uint64_t n, const uint32_t* nl_pos, uint32_t n_nl,
-                             uint32_t n_lines, uint64_t* line_val, cudaStream_t st)
+cudaError_t launch_fasta_records(const uint8_t* text, uint64_t n, const TileSum* tiles, const TileSum* tile_pre,
+                                 uint64_t ntiles, uint32_t* rec_first, uint32_t* rec_hdr_off, cudaStream_t st)
 {
-    k_line_info<<<grid_for((uint64_t)n_lines + 1, 256), 256, 0, st>>>(text, n, nl_pos, n_nl, n_lines, line_val);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_record_starts(const uint64_t* line_val, const uint64_t* line_cum, uint32_t n_lines,
-                                 uint32_t* rec_hdr_line, uint32_t* rec_first, cudaStream_t st)
-{
-    k_record_starts<<<grid_for((uint64_t)n_lines + 1, 256), 256, 0, st>>>(line_val, line_cum, n_lines,
-                                                                        rec_hdr_line, rec_first);
+    if (!ntiles) {                                        // empty text: record 0 only
+        const uint32_t init[1] = {0};
+        cudaError_t e = cudaMemcpyAsync(rec_first, init, 4, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return e;
+        return cudaMemsetAsync(rec_hdr_off, 0xFF, 4, st);
+    }
+    k_fasta_records<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tiles, tile_pre, rec_first, rec_hdr_off);
     return cudaGetLastError();
 }
 
@@ -303,25 +535,22 @@ cudaError_t launch_record_info(const uint32_t* rec_first, uint32_t n_recs, uint6
 }
 
 cudaError_t launch_genome_table(const uint32_t* rec_len, const uint32_t* rec_kept, const uint32_t* rec_kept_ex,
-                                const uint32_t* rec_words_ex, const uint32_t* rec_first,
-                                const uint32_t* /*rec_hdr_line*/, uint32_t n_recs, uint32_t* g_rec,
-                                uint32_t* g_len, uint32_t* g_word, uint32_t* g_first, cudaStream_t st)
+                                const uint32_t* rec_words_ex, const uint32_t* rec_first, uint32_t n_recs,
+                                uint32_t* g_rec, uint32_t* g_len, uint32_t* g_word, uint32_t* g_first,
+                                uint32_t* word_genome, unsigned long long* totals, cudaStream_t st)
 {
     k_genome_table<<<grid_for((uint64_t)n_recs + 1, 256), 256, 0, st>>>(rec_len, rec_kept, rec_kept_ex,
                                                                       rec_words_ex, rec_first, n_recs, g_rec,
-                                                                      g_len, g_word, g_first);
+                                                                      g_len, g_word, g_first, word_genome, totals);
     return cudaGetLastError();
 }
 
-cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const uint32_t* nl_pos, uint32_t n_nl,
-                              const uint64_t* line_cum, uint32_t n_lines, const uint32_t* rec_hdr_line,
-                              uint32_t n_recs, const uint32_t* g_rec, const uint32_t* g_len,
-                              const uint32_t* g_word, const uint32_t* g_first, uint32_t n_genomes, Planes pl,
-                              uint32_t* word_genome, cudaStream_t st)
+cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const TileSum* tile_pre, uint64_t ntiles,
+                              const uint32_t* rec_kept, const uint32_t* rec_kept_ex, const uint32_t* rec_words_ex,
+                              const uint32_t* rec_first, Planes pl, uint32_t* word_genome, cudaStream_t st)
 {
-    if (!pl.nwords) return cudaSuccess;
-    k_pack_fasta<<<grid_for(pl.nwords, 256), 256, 0, st>>>(text, n, nl_pos, n_nl, line_cum, n_lines,
-                                                           rec_hdr_line, n_recs, g_rec, g_len, g_word, g_first,
-                                                           n_genomes, pl, word_genome);
+    if (!ntiles) return cudaSuccess;
+    k_pack_fasta<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_pre, rec_kept, rec_kept_ex, rec_words_ex,
+                                                           rec_first, pl, word_genome);
     return cudaGetLastError();
 }
