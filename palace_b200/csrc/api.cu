@@ -69,21 +69,24 @@ struct eref_ctx {
     DevBuf tile_counts, tile_prefix, cub_tmp, counters;      // counters: 4 x u64
     // query side
     DevBuf q_text, q_hi, q_lo, q_ok;
-    DevBuf bucket_ctr;                         // u64: hist[32] | tail[32] | off[33]
-    // bucket-ordered code lists of the files added since the last table update (counted lazily, bucket by
-    // bucket, by finalize_table so that every table slice is visited once while it sits in L2)
-    struct CodeList { DevBuf codes; unsigned long long off[NBUCKETS_HOST + 1]; unsigned long long n[NBUCKETS_HOST]; };
+    // Table build (table.cu): every file added since the last reset is kept as a slice-ordered code list (codes
+    // radix-partitioned by their top 13 bits); a build counts all lists slice by slice in shared memory and
+    // writes level 3 and its summary.  Levels 1/2 exist in HBM only for the direct build (EREF_FLAG_DIRECT_COUNT).
+    struct CodeList { DevBuf codes, off, cnt; unsigned long long total = 0; };
     std::vector<CodeList> lists;
-    size_t n_pending = 0;
-    bool needs_zero = true;                    // table levels not zeroed yet since create / query_reset
-    cudaEvent_t evf[2]{};
-    // tuning knobs of the table update (EREF_COUNT_STREAMS, EREF_COUNT_UNITS)
-    int count_streams = 2, count_units = 2;
-    cudaStream_t aux[4]{};
-    cudaEvent_t aux_ev[5]{};
+    size_t n_lists = 0;
+    bool table_dirty = true;                   // files added / table reset since the last build
+    bool want_pop = false, have_pop = false;   // level populations are counted only once eref_query_popcount has asked
+    DevBuf part_ctr;                           // u64: hist[NSLICES] | slice tails[NSLICES] | coarse tails[256] | coarse_n[256]; u32 chunk_start[257]
+    DevBuf codes_coarse;                       // coarse-partitioned codes of the file being added
+    DevBuf level_pop;                          // 3 x u64: codes at level >= 1, 2, 3 after the last build
+    cudaEvent_t evf[2]{}, table_ready = nullptr;
+    cudaStream_t table_stream = nullptr;
+    bool table_inflight = false, count_time_pending = false;
+    cudaEvent_t aux_ev[2]{};
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
-    unsigned long long h_hist[NBUCKETS_HOST] = {}, h_off[NBUCKETS_HOST + 1] = {};
+    int bucket_bits = 5;                       // EREF_BUCKET_BITS: 2^bits coarse buckets, 2^(13-bits) slices per bucket
     // reference side
     DevBuf r_text, tile_sum, tile_pre, rec_hdr_off, rec_first, rec_len, rec_kept, rec_words,
         rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
@@ -105,6 +108,11 @@ namespace {
         (ctx)->launches++;                                                                 \
         CUDA_TRY(expr);                                                                    \
     } while (0)
+
+int start_table_update(eref_ctx* c);
+int wait_table(eref_ctx* c, cudaStream_t st);
+// layout of part_ctr after the u64 arrays: u32 chunk_start[260], then u64 totals[3]
+inline unsigned long long* chunk_start_end(uint32_t* chunk_start) { return reinterpret_cast<unsigned long long*>(chunk_start + 260); }
 
 template <class T>
 int exclusive_scan(eref_ctx* c, const T* in, T* out, size_t n)
@@ -148,6 +156,8 @@ int check_text_ptr(const void* p, size_t n)
 int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
 {
     cudaStream_t st = c->stream;
+    int wrc = wait_table(c, st);              // an update still in flight reads the code lists this call rewrites
+    if (wrc) return wrc;
     CUDA_TRY(cudaEventRecord(c->ev[E1], st));
     uint64_t ntiles = 0;
     int rc = newline_census(c, text, n, &ntiles);
@@ -171,28 +181,39 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         CUDA_TRY(cudaEventRecord(c->ev[E3], st));
         LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
     } else {
-        // codes -> 32 code-range buckets (histogram, exact offsets, scatter); counted by finalize_table
-        CUDA_TRY(c->bucket_ctr.ensure((NBUCKETS_HOST * 2 + NBUCKETS_HOST + 1) * 8));
-        unsigned long long* hist = c->bucket_ctr.as<unsigned long long>();
-        unsigned long long* tail = hist + NBUCKETS_HOST;
-        unsigned long long* off = tail + NBUCKETS_HOST;
-        CUDA_TRY(cudaMemsetAsync(hist, 0, NBUCKETS_HOST * 2 * 8, st));
-        LAUNCH(c, launch_bucket_hist(pl, c->masks, hist, st));
-        CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, hist, NBUCKETS_HOST * 8, cudaMemcpyDeviceToHost, st));
+        // codes -> slice-ordered list: histogram over the 8192 table slices, exact offsets, coarse scatter from the
+        // planes, fine partition through shared memory; counted by the next table build
+        if (c->n_lists >= (size_t)MAX_LISTS)
+            return eref_fail(EREF_ERR_LIMIT, "more than %d query files since the last eref_query_reset", MAX_LISTS);
+        const int cbits = c->bucket_bits;
+        CUDA_TRY(c->part_ctr.ensure(((size_t)NSLICES * 2 + 512 + 4) * 8 + 260 * 4));
+        unsigned long long* hist = c->part_ctr.as<unsigned long long>();
+        unsigned long long* slice_tail = hist + NSLICES;
+        unsigned long long* coarse_tail = slice_tail + NSLICES;
+        unsigned long long* coarse_n = coarse_tail + 256;
+        uint32_t* chunk_start = reinterpret_cast<uint32_t*>(coarse_n + 256);
+        CUDA_TRY(cudaMemsetAsync(hist, 0, ((size_t)NSLICES * 2 + 256) * 8, st));
+        LAUNCH(c, launch_slice_hist(pl, c->masks, hist, st));
+        unsigned long long* totals = chunk_start_end(chunk_start);     // {codes, padded size, chunks}
+        if (c->lists.size() <= c->n_lists) c->lists.resize(c->n_lists + 1);
+        eref_ctx::CodeList& L = c->lists[c->n_lists];
+        CUDA_TRY(L.off.ensure(((size_t)NSLICES + 1) * 8)); CUDA_TRY(L.cnt.ensure((size_t)NSLICES * 8));
+        LAUNCH(c, launch_slice_offsets(hist, cbits, L.off.as<unsigned long long>(), L.cnt.as<unsigned long long>(), coarse_n,
+                                       chunk_start, totals, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, totals, 24, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        memcpy(c->h_hist, c->h_pin + 8, NBUCKETS_HOST * 8);
-        if (c->lists.size() <= c->n_pending) c->lists.resize(c->n_pending + 1);
-        eref_ctx::CodeList& L = c->lists[c->n_pending];
-        L.off[0] = 0;
-        for (int b = 0; b < NBUCKETS_HOST; b++) {               // bucket starts stay 16-byte aligned
-            L.n[b] = c->h_hist[b];
-            L.off[b + 1] = L.off[b] + ((c->h_hist[b] + 3) & ~3ull);
-            total_codes += c->h_hist[b];
-        }
-        CUDA_TRY(cudaMemcpyAsync(off, L.off, (NBUCKETS_HOST + 1) * 8, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(L.codes.ensure((size_t)L.off[NBUCKETS_HOST] * 4 + 16));
-        LAUNCH(c, launch_bucket_scatter(pl, c->masks, off, tail, L.codes.as<uint32_t>(), st));
-        c->n_pending++;
+        total_codes = c->h_pin[8];
+        const unsigned long long padded = c->h_pin[9];
+        const uint32_t nchunks = (uint32_t)c->h_pin[10];
+        L.total = total_codes;
+        CUDA_TRY(L.codes.ensure((size_t)padded * 4 + 16));
+        CUDA_TRY(c->codes_coarse.ensure((size_t)padded * 4 + 16));
+        LAUNCH(c, launch_coarse_scatter(pl, c->masks, cbits, L.off.as<unsigned long long>(), coarse_tail,
+                                        c->codes_coarse.as<uint32_t>(), st));
+        LAUNCH(c, launch_fine_partition(c->codes_coarse.as<uint32_t>(), L.off.as<unsigned long long>(), coarse_n, chunk_start,
+                                        nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), st));
+        c->n_lists++;
+        c->table_dirty = true;
         CUDA_TRY(cudaEventRecord(c->ev[E3], st));
     }
     CUDA_TRY(cudaEventRecord(c->ev[E4], st));
@@ -207,49 +228,65 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     return 0;
 }
 
-// Bring the table up to date: for each code-range bucket, zero its three 16 MiB level slices if the
-// table is fresh (the zeros are left dirty in L2, so the atomics that follow never wait for DRAM), then
-// count that bucket of every pending file.  DRAM sees each table sector once, as a write-back.
-int finalize_table(eref_ctx* c)
+// Bring the table up to date, asynchronously: one CTA per 2^19-slot slice counts that slice's codes from every
+// file added since the last reset in shared memory and writes the level-3 slice and its summary
+// (k_count_slices).  The build is queued on the table stream behind everything already queued on the main
+// stream, so the reference framing/packing kernels the caller queues next can run beside it; wait_table()
+// makes a stream wait for the result.
+int start_table_update(eref_ctx* c)
 {
     if (c->flags & EREF_FLAG_DIRECT_COUNT) return 0;
-    if (!c->needs_zero && c->n_pending == 0) return 0;
-    cudaStream_t st = c->stream;
-    constexpr uint32_t SLICE = TABLE_WORDS / NBUCKETS_HOST;
-    const int S = c->count_streams;
-    CUDA_TRY(cudaEventRecord(c->evf[0], st));
-    if (S > 1) {                               // buckets round-robin over S streams: the tail of one bucket's
-        CUDA_TRY(cudaEventRecord(c->aux_ev[4], st));         // kernels overlaps the next bucket's start
-        for (int k = 0; k < S; k++) CUDA_TRY(cudaStreamWaitEvent(c->aux[k], c->aux_ev[4], 0));
+    if (!c->table_dirty) return 0;
+    cudaStream_t st = c->stream, ts = c->table_stream;
+    CUDA_TRY(cudaEventRecord(c->aux_ev[0], st));
+    CUDA_TRY(cudaStreamWaitEvent(ts, c->aux_ev[0], 0));
+    CUDA_TRY(cudaEventRecord(c->evf[0], ts));
+    CountLists cl{};
+    cl.n = (int)c->n_lists;
+    for (size_t k = 0; k < c->n_lists; k++) {
+        cl.codes[k] = c->lists[k].codes.as<uint32_t>();
+        cl.off[k] = c->lists[k].off.as<unsigned long long>();
+        cl.cnt[k] = c->lists[k].cnt.as<unsigned long long>();
     }
-    for (int b = 0; b < NBUCKETS_HOST; b++) {
-        cudaStream_t sb = S > 1 ? c->aux[b % S] : st;
-        if (c->needs_zero)
-            LAUNCH(c, launch_zero_slices(c->bm[0] + (size_t)b * SLICE, c->bm[1] + (size_t)b * SLICE,
-                                         c->bm[2] + (size_t)b * SLICE, SLICE, sb));
-        for (size_t k = 0; k < c->n_pending; k += 2) {
-            eref_ctx::CodeList& A = c->lists[k];
-            const bool two = k + 1 < c->n_pending;
-            const uint32_t* p1 = two ? c->lists[k + 1].codes.as<uint32_t>() + c->lists[k + 1].off[b] : nullptr;
-            const uint64_t n1 = two ? c->lists[k + 1].n[b] : 0;
-            if (A.n[b] + n1)
-                LAUNCH(c, launch_count_codes(A.codes.as<uint32_t>() + A.off[b], A.n[b], p1, n1, c->count_units,
-                                             c->bm[0], c->bm[1], c->bm[2], sb));
-        }
+    if (c->want_pop) CUDA_TRY(cudaMemsetAsync(c->level_pop.p, 0, 24, ts));
+    LAUNCH(c, launch_count_slices(cl, c->bm[2], c->summary, c->want_pop ? c->level_pop.as<unsigned long long>() : nullptr, ts));
+    c->have_pop = c->want_pop;
+    CUDA_TRY(cudaEventRecord(c->evf[1], ts));
+    CUDA_TRY(cudaEventRecord(c->table_ready, ts));
+    c->table_dirty = false;
+    c->summary_stale = false;
+    c->table_inflight = true;
+    c->count_time_pending = true;
+    return 0;
+}
+
+// make `st` wait for the table update queued last (no-op when none is outstanding)
+int wait_table(eref_ctx* c, cudaStream_t st)
+{
+    if (c->table_inflight) CUDA_TRY(cudaStreamWaitEvent(st, c->table_ready, 0));
+    return 0;
+}
+
+// after a host synchronisation that covers the table stream: collect the update's duration
+void table_done(eref_ctx* c)
+{
+    c->table_inflight = false;
+    if (c->count_time_pending) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, c->evf[0], c->evf[1]) == cudaSuccess) c->t.query_count_ms = ms;
+        else cudaGetLastError();
+        c->count_time_pending = false;
     }
-    if (S > 1)
-        for (int k = 0; k < S; k++) {
-            CUDA_TRY(cudaEventRecord(c->aux_ev[k], c->aux[k]));
-            CUDA_TRY(cudaStreamWaitEvent(st, c->aux_ev[k], 0));
-        }
-    CUDA_TRY(cudaEventRecord(c->evf[1], st));
-    c->needs_zero = false;
-    c->n_pending = 0;
-    c->summary_stale = true;
-    CUDA_TRY(cudaStreamSynchronize(st));
-    float ms = 0;
-    cudaEventElapsedTime(&ms, c->evf[0], c->evf[1]);
-    c->t.query_count_ms = ms;
+}
+
+int finalize_table(eref_ctx* c)
+{
+    int rc = start_table_update(c);
+    if (rc) return rc;
+    if (c->table_inflight) {
+        CUDA_TRY(cudaStreamSynchronize(c->table_stream));
+        table_done(c);
+    }
     return 0;
 }
 
@@ -260,6 +297,8 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     if (n >= 0xFFFFFF00ull)
         return eref_fail(EREF_ERR_LIMIT, "reference text of %llu bytes: one shard must stay below 4 GiB",
                          (unsigned long long)n);
+    int trc = start_table_update(c);          // pending query files are counted while this text is framed and packed
+    if (trc) return trc;
     CUDA_TRY(cudaEventRecord(c->ev[E1], st));
     // 1. per-tile framing summaries and their prefix: line/header state, records and sequence bytes before each tile
     const uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
@@ -339,9 +378,11 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
 int scan_impl(eref_ctx* c)
 {
     if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "eref_scan before eref_ref_set");
-    int frc = finalize_table(c);
+    int frc = start_table_update(c);
     if (frc) return frc;
     cudaStream_t st = c->stream;
+    frc = wait_table(c, st);
+    if (frc) return frc;
     const uint64_t nw = c->ref_words;
     const uint32_t G = c->n_genomes;
     Planes pl;
@@ -356,7 +397,7 @@ int scan_impl(eref_ctx* c)
     unsigned long long* need_count = c->counters.as<unsigned long long>() + 1;
     CUDA_TRY(cudaEventRecord(c->ev[E0], st));
     if (prune && c->summary_stale) {
-        LAUNCH(c, launch_build_summary(c->bm[2], c->summary, st));
+        LAUNCH(c, launch_build_summary(c->bm[2], c->summary, SUMMARY_WORDS, st));
         c->summary_stale = false;
     }
     CUDA_TRY(cudaEventRecord(c->ev[E8], st));
@@ -453,13 +494,16 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&c->evf[i]);
-    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking);
-    for (int i = 0; i < 5 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->aux_ev[i], cudaEventDisableTiming);
-    if (const char* v = getenv("EREF_COUNT_STREAMS")) { int k = atoi(v); if (k >= 1 && k <= 4) c->count_streams = k; }
-    if (const char* v = getenv("EREF_COUNT_UNITS")) { int k = atoi(v); if (k == 1 || k == 2 || k == 4) c->count_units = k; }
-    for (int l = 0; l < 3 && e == cudaSuccess; l++) e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->aux_ev[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->table_ready, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->table_stream, cudaStreamNonBlocking);
+    if (const char* v = getenv("EREF_BUCKET_BITS")) { int k = atoi(v); if (k >= 5 && k <= 8) c->bucket_bits = k; }
+    for (int l = (flags & EREF_FLAG_DIRECT_COUNT) ? 0 : 2; l < 3 && e == cudaSuccess; l++)
+        e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
+    if (e == cudaSuccess) e = c->level_pop.ensure(64);
+
     if (e == cudaSuccess) e = c->counters.ensure(64);
-    if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, 64 * 8, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, (8 + MAX_BUCKETS) * 8, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
     if (e != cudaSuccess) { eref_destroy(c); return eref_fail_cuda(e, "context allocation", __FILE__, __LINE__); }
     c->stream = c->own_stream;
@@ -474,6 +518,7 @@ void eref_destroy(eref_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->table_stream) cudaStreamSynchronize(c->table_stream);
     DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->q_text, &c->q_hi, &c->q_lo,
                       &c->q_ok, &c->r_text, &c->tile_sum, &c->tile_pre, &c->rec_hdr_off, &c->rec_first,
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
@@ -484,11 +529,12 @@ void eref_destroy(eref_ctx* c)
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
     if (c->summary) cudaFree(c->summary);
     if (c->h_pin) cudaFreeHost(c->h_pin);
-    c->bucket_ctr.release();
-    for (auto& L : c->lists) L.codes.release();
+    c->part_ctr.release(); c->codes_coarse.release(); c->level_pop.release();
+    for (auto& L : c->lists) { L.codes.release(); L.off.release(); L.cnt.release(); }
     for (int i = 0; i < 2; i++) if (c->evf[i]) cudaEventDestroy(c->evf[i]);
-    for (int i = 0; i < 4; i++) if (c->aux[i]) cudaStreamDestroy(c->aux[i]);
-    for (int i = 0; i < 5; i++) if (c->aux_ev[i]) cudaEventDestroy(c->aux_ev[i]);
+    for (int i = 0; i < 2; i++) if (c->aux_ev[i]) cudaEventDestroy(c->aux_ev[i]);
+    if (c->table_ready) cudaEventDestroy(c->table_ready);
+    if (c->table_stream) cudaStreamDestroy(c->table_stream);
     for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
@@ -511,11 +557,12 @@ int eref_query_reset(eref_ctx* c)
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
     CUDA_TRY(cudaSetDevice(c->device));
     c->summary_stale = true;
-    c->n_pending = 0;
+    c->n_lists = 0;
+    c->table_dirty = true;                     // rebuilt (to the empty table if nothing is added) before the next use
     if (c->flags & EREF_FLAG_DIRECT_COUNT) {
+        int wrc = wait_table(c, c->stream);
+        if (wrc) return wrc;
         for (int l = 0; l < 3; l++) CUDA_TRY(cudaMemsetAsync(c->bm[l], 0, (size_t)TABLE_WORDS * 4, c->stream));
-    } else {
-        c->needs_zero = true;                  // zeroed slice by slice in finalize_table, right before use
     }
     return 0;
 }
@@ -588,6 +635,7 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev[E6], c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    table_done(c);
     scan_times(c, true);
     const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE) > 0;
     c->t.ref_need_words = pruned ? c->h_pin[6] : c->ref_words;
@@ -673,9 +721,8 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     if (rc) return rc;
     sum.query_pack_ms += c->t.query_pack_ms; sum.query_bucket_ms += c->t.query_bucket_ms;
     sum.query_seq_bytes += c->t.query_seq_bytes; sum.query_codes += c->t.query_codes;
-    rc = finalize_table(c);
+    rc = start_table_update(c);               // counted while the first database piece is framed and packed
     if (rc) return rc;
-    sum.query_count_ms = c->t.query_count_ms;
     sum.ref_frame_ms = sum.ref_pack_ms = 0;
     sum.scan_summary_ms = sum.scan_sample_ms = sum.scan_cand_ms = sum.scan_probe_ms = sum.scan_window_ms = 0;
     sum.scan_interval_ms = sum.scan_d2h_ms = 0;
@@ -698,6 +745,7 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         sum.scan_cand_ms += c->t.scan_cand_ms; sum.scan_probe_ms += c->t.scan_probe_ms;
         sum.scan_window_ms += c->t.scan_window_ms; sum.scan_interval_ms += c->t.scan_interval_ms;
         sum.scan_d2h_ms += c->t.scan_d2h_ms;
+        sum.query_count_ms = c->t.query_count_ms;
         sum.ref_bases += c->t.ref_bases; sum.ref_words += c->t.ref_words; sum.ref_need_words += c->t.ref_need_words;
     }
     c->t = sum;
@@ -713,6 +761,7 @@ int eref_scan_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
     int rc = scan_impl(c);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    table_done(c);
     scan_times(c, false);
     *results_dev = c->results.as<uint32_t>();
     if (n_out) *n_out = c->n_genomes;
@@ -776,12 +825,19 @@ int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
 {
     if (!c || !out || level < 1 || level > 3) return eref_fail(EREF_ERR_ARG, "eref_query_popcount: bad argument");
     CUDA_TRY(cudaSetDevice(c->device));
+    if (!(c->flags & EREF_FLAG_DIRECT_COUNT) && !c->want_pop) { c->want_pop = true; c->table_dirty = true; }
+    if (!(c->flags & EREF_FLAG_DIRECT_COUNT) && !c->have_pop) c->table_dirty = true;
     int frc = finalize_table(c);
     if (frc) return frc;
+    unsigned long long h = 0;
+    if (!(c->flags & EREF_FLAG_DIRECT_COUNT)) {          // the build counted the levels while it had them in shared memory
+        CUDA_TRY(cudaMemcpy(&h, c->level_pop.as<unsigned long long>() + (level - 1), 8, cudaMemcpyDeviceToHost));
+        *out = h;
+        return 0;
+    }
     unsigned long long* ctr = c->counters.as<unsigned long long>() + 2;
     CUDA_TRY(cudaMemsetAsync(ctr, 0, 8, c->stream));
     LAUNCH(c, launch_popcount(c->bm[level - 1], TABLE_WORDS, ctr, c->stream));
-    unsigned long long h = 0;
     CUDA_TRY(cudaMemcpyAsync(&h, ctr, 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     *out = h;

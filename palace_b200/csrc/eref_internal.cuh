@@ -14,7 +14,12 @@ constexpr uint32_t TABLE_WORDS  = 1u << 27;          // 2^32 one-bit slots per l
 constexpr int      WINDOW       = 500;               // :510
 constexpr int      WIN_WORDS    = 16;                // a 500-position window reaches back 16 words
 constexpr uint32_t SUMMARY_WORDS = 1u << 23;         // level-3 summary: 1 bit per 16 slots = 32 MiB
-constexpr int      NBUCKETS_HOST = 32;               // code-range buckets of the table build (table.cu)
+constexpr int      MAX_BUCKETS = 256;                // coarse / fine partition fan-out of the table build (table.cu)
+constexpr int      SLICE_BITS  = 19;                 // a table slice = 2^19 slots: its three levels fit one CTA's shared memory
+constexpr int      NSLICES     = 1 << (32 - SLICE_BITS);
+constexpr int      SLICE_WORDS = 1 << (SLICE_BITS - 5);
+constexpr uint32_t SLICE_MASK  = (1u << SLICE_BITS) - 1u;
+constexpr int      MAX_LISTS   = 16;                 // query files counted by one table build
 constexpr int      SAMPLE_STRIDE = 4;                // candidate filter probes every 4th position
 
 // Per-stream select masks of the coder assignment: bit (31-z) of sel0[i] (sel2[i]) is set iff code
@@ -141,13 +146,25 @@ cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const TileSum* ti
 // table.cu
 cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
                                cudaStream_t st);
-cudaError_t launch_bucket_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st);
-cudaError_t launch_bucket_scatter(Planes pl, CoderMasks m, const unsigned long long* bucket_off,
+cudaError_t launch_slice_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st);
+cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
                                   unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st);
-cudaError_t launch_count_codes(const uint32_t* c0, uint64_t n0, const uint32_t* c1, uint64_t n1, int units,
-                               uint32_t* bm1, uint32_t* bm2, uint32_t* bm3, cudaStream_t st);
-cudaError_t launch_zero_slices(uint32_t* a, uint32_t* b, uint32_t* c, uint32_t nwords, cudaStream_t st);
-cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, cudaStream_t st);
+cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
+                                  const uint32_t* chunk_start, uint32_t nchunks, int cbits, unsigned long long* g_tail,
+                                  uint32_t* out, cudaStream_t st);
+cudaError_t launch_slice_offsets(const unsigned long long* hist, int cbits, unsigned long long* off, unsigned long long* cnt,
+                                 unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals, cudaStream_t st);
+// slice-ordered code lists of the files one table build counts: list l holds cnt[l][s] codes of slice s at
+// codes[l] + off[l][s] (16-byte aligned)
+struct CountLists {
+    const uint32_t* codes[MAX_LISTS];
+    const unsigned long long* off[MAX_LISTS];
+    const unsigned long long* cnt[MAX_LISTS];
+    int n;
+};
+cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t* summary, unsigned long long* level_pop,
+                                cudaStream_t st);
+cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, uint32_t summary_words, cudaStream_t st);
 cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);
 // scan.cu
 cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary, uint8_t* sample_hits,

@@ -32,26 +32,30 @@ __device__ __forceinline__ void load32(const uint8_t* __restrict__ text, uint64_
     }
 }
 
-// 0x01 in every byte of x that is zero (exact per byte, no cross-byte borrow)
-__device__ __forceinline__ uint32_t zero_bytes(uint32_t x)
+// Per-byte flags live in bit 7 of their byte.  A byte-equality test under a 7-bit mask is one LOP3 + one add:
+// ((w ^ pattern) & mask7) + 0x7F sets bit 7 iff the masked byte differs (no carry leaves the byte); OR-ing w in
+// also rejects bytes >= 0x80.
+constexpr uint32_t H7 = 0x80808080u;
+
+__device__ __forceinline__ uint32_t eq7(uint32_t w, uint32_t pattern, uint32_t mask7)
 {
-    const uint32_t t = ((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x;       // bit 7 clear iff the byte is 0
-    return (~t >> 7) & 0x01010101u;
+    const uint32_t t = ((w ^ pattern) & mask7) + 0x7F7F7F7Fu;
+    return ~(t | w) & H7;
 }
 
-// Two sets of per-byte flags (a at bits 0,8,16,24; b at bits 4,12,20,28) -> one multiply puts the four
-// a flags in bits 27..24 and the four b flags in bits 31..28, first byte of the word most significant
-// (all partial products land on distinct bits, so there are no carries).
-__device__ __forceinline__ uint32_t gather2(uint32_t a01, uint32_t b10) { return (a01 | b10) * 0x08040201u; }
+// Two sets of per-byte flags (a in bits 7,15,23,31; b in bits 3,11,19,27) -> one multiply gathers the a flags
+// into bits 28..31 and the b flags into bits 24..27, FIRST byte of the word in the LOWEST bit (all partial
+// products land on distinct bits: no carries).  The chunk masks are therefore assembled byte k <-> bit k and
+// bit-reversed once at the end.
+__device__ __forceinline__ uint32_t gather2(uint32_t a7, uint32_t b3) { return (a7 | b3) * 0x00204081u; }
 
-template <int J> __device__ __forceinline__ uint32_t place_lo(uint32_t prod)   // nibble 27..24 -> bits 31-4J..28-4J
+template <int J> __device__ __forceinline__ uint32_t place_a(uint32_t prod)    // bits 31..28 -> bits 4J+3..4J
 {
-    const uint32_t nib = prod & 0x0F000000u;
-    return J == 0 ? nib << 4 : nib >> (J == 0 ? 0 : 4 * J - 4);
+    return (prod >> (28 - 4 * J)) & (0xFu << (4 * J));
 }
-template <int J> __device__ __forceinline__ uint32_t place_hi(uint32_t prod)   // nibble 31..28 -> bits 31-4J..28-4J
+template <int J> __device__ __forceinline__ uint32_t place_b(uint32_t prod)    // bits 27..24 -> bits 4J+3..4J
 {
-    return (prod & 0xF0000000u) >> (4 * J);
+    return (J <= 6 ? prod >> (J <= 6 ? 24 - 4 * J : 0) : prod << (J <= 6 ? 0 : 4 * J - 24)) & (0xFu << (4 * J));
 }
 
 struct Masks { uint32_t nl, hi, lo, ok; };
@@ -61,16 +65,15 @@ struct Masks { uint32_t nl, hi, lo, ok; };
 template <int J>
 __device__ __forceinline__ void masks_word(uint32_t w, Masks& m)
 {
-    const uint32_t b2 = (w >> 2) & 0x01010101u;
-    const uint32_t b1 = (w >> 1) & 0x01010101u;
-    const uint32_t nl = zero_bytes(w ^ 0x0A0A0A0Au);
-    const uint32_t aceg = zero_bytes((w ^ 0x41414141u) & 0xD9D9D9D9u);   // 0x41 0x43 0x45 0x47, either case
-    const uint32_t tt = zero_bytes((w ^ 0x54545454u) & 0xDFDFDFDFu);     // 0x54, either case
-    const uint32_t ok = (aceg & ~(b2 & ~b1)) | tt;                       // drop 0x45/0x65 ('E'): bit2 set, bit1 clear
-    const uint32_t p0 = gather2(b2 & ok, ((b1 ^ b2) & ok) << 4);
-    const uint32_t p1 = gather2(ok, nl << 4);
-    m.hi |= place_lo<J>(p0); m.lo |= place_hi<J>(p0);
-    m.ok |= place_lo<J>(p1); m.nl |= place_hi<J>(p1);
+    const uint32_t nl = eq7(w, 0x0A0A0A0Au, 0x7F7F7F7Fu);
+    const uint32_t aceg = eq7(w, 0x41414141u, 0x59595959u);          // 0x41 0x43 0x45 0x47, either case
+    const uint32_t tt = eq7(w, 0x54545454u, 0x5F5F5F5Fu);            // 0x54, either case
+    const uint32_t h2 = w << 5, h1 = w << 6;                         // ASCII bit 2 / bit 1 in bit 7 of the byte
+    const uint32_t ok = (aceg & ~(h2 & ~h1)) | tt;                   // drop 0x45/0x65 ('E'): bit 2 set, bit 1 clear
+    const uint32_t p0 = gather2(h2 & ok, ((h1 ^ h2) & ok) >> 4);
+    const uint32_t p1 = gather2(ok, nl >> 4);
+    m.hi |= place_a<J>(p0); m.lo |= place_b<J>(p0);
+    m.ok |= place_a<J>(p1); m.nl |= place_b<J>(p1);
 }
 
 __device__ __forceinline__ Masks chunk_masks(const uint32_t w[8])
@@ -78,19 +81,20 @@ __device__ __forceinline__ Masks chunk_masks(const uint32_t w[8])
     Masks m{0, 0, 0, 0};
     masks_word<0>(w[0], m); masks_word<1>(w[1], m); masks_word<2>(w[2], m); masks_word<3>(w[3], m);
     masks_word<4>(w[4], m); masks_word<5>(w[5], m); masks_word<6>(w[6], m); masks_word<7>(w[7], m);
+    m.nl = __brev(m.nl); m.hi = __brev(m.hi); m.lo = __brev(m.lo); m.ok = __brev(m.ok);
     return m;
 }
 
 template <int J>
 __device__ __forceinline__ uint32_t nl_word(uint32_t w)
 {
-    return place_lo<J>(zero_bytes(w ^ 0x0A0A0A0Au) * 0x08040201u);
+    return place_a<J>(eq7(w, 0x0A0A0A0Au, 0x7F7F7F7Fu) * 0x00204081u);
 }
 
 __device__ __forceinline__ uint32_t chunk_newlines(const uint32_t w[8])
 {
-    return nl_word<0>(w[0]) | nl_word<1>(w[1]) | nl_word<2>(w[2]) | nl_word<3>(w[3]) |
-           nl_word<4>(w[4]) | nl_word<5>(w[5]) | nl_word<6>(w[6]) | nl_word<7>(w[7]);
+    return __brev(nl_word<0>(w[0]) | nl_word<1>(w[1]) | nl_word<2>(w[2]) | nl_word<3>(w[3]) |
+                  nl_word<4>(w[4]) | nl_word<5>(w[5]) | nl_word<6>(w[6]) | nl_word<7>(w[7]));
 }
 
 // positions [0, k) of a chunk as a mask (k in 0..32)
@@ -100,7 +104,7 @@ __device__ __forceinline__ uint32_t count_nl(const uint32_t w[8])
 {
     uint32_t c = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++) c += __popc(zero_bytes(w[i] ^ 0x0A0A0A0Au));
+    for (int i = 0; i < 8; i++) c += __popc(eq7(w[i], 0x0A0A0A0Au, 0x7F7F7F7Fu));
     return c;
 }
 
@@ -197,75 +201,18 @@ k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
 // other line is appended verbatim to the current record (:754), so '\r', blanks and N count as (invalid)
 // bases.  Record 0 is whatever precedes the first header; record r >= 1 starts at the r-th header.
 //
-// Chunk summary (associative, see TileSum in eref_internal.cuh): has = a line starts inside the chunk;
-// state = the last line started inside the chunk is a header; hdrs = header lines started; seqA = non-newline
-// bytes before the first line start (they belong to the line in progress and count only if that line is
-// not a header); seqB = bytes of non-header lines after the first line start.
-
-struct FastaSum {                       // per-thread / per-tile form, small counts
-    uint32_t has, state, hdrs, seqA, seqB;
-};
-
-__device__ __forceinline__ FastaSum combine(const FastaSum& x, const FastaSum& y)
-{
-    FastaSum r;
-    r.has = x.has | y.has;
-    r.state = y.has ? y.state : x.state;
-    r.hdrs = x.hdrs + y.hdrs;
-    if (x.has) { r.seqA = x.seqA; r.seqB = x.seqB + y.seqB + (x.state ? 0u : y.seqA); }
-    else       { r.seqA = x.seqA + y.seqA; r.seqB = y.seqB; }
-    return r;
-}
-
-__device__ __forceinline__ unsigned long long pack_sum(const FastaSum& s)
-{
-    return (unsigned long long)s.seqB | ((unsigned long long)s.seqA << 16) | ((unsigned long long)s.hdrs << 32) |
-           ((unsigned long long)s.state << 48) | ((unsigned long long)s.has << 49);
-}
-
-__device__ __forceinline__ FastaSum unpack_sum(unsigned long long v)
-{
-    FastaSum s;
-    s.seqB = (uint32_t)(v & 0xFFFFu); s.seqA = (uint32_t)((v >> 16) & 0xFFFFu); s.hdrs = (uint32_t)((v >> 32) & 0xFFFFu);
-    s.state = (uint32_t)((v >> 48) & 1u); s.has = (uint32_t)((v >> 49) & 1u);
-    return s;
-}
-
-// exclusive scan of the chunk summaries over the CTA (thread order = text order); *total = whole tile
-__device__ __forceinline__ FastaSum block_scan_fasta(const FastaSum& mine, FastaSum* total)
-{
-    __shared__ unsigned long long warp_tot[TILE_THREADS / 32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    FastaSum inc = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const unsigned long long t = __shfl_up_sync(0xffffffffu, pack_sum(inc), d);
-        if (lane >= d) inc = combine(unpack_sum(t), inc);
-    }
-    unsigned long long prev = __shfl_up_sync(0xffffffffu, pack_sum(inc), 1);
-    FastaSum ex = lane ? unpack_sum(prev) : FastaSum{0, 0, 0, 0, 0};
-    if (lane == 31) warp_tot[warp] = pack_sum(inc);
-    __syncthreads();
-    FastaSum before_warp{0, 0, 0, 0, 0}, all{0, 0, 0, 0, 0};
-#pragma unroll
-    for (int k = 0; k < TILE_THREADS / 32; k++) {
-        const FastaSum t = unpack_sum(warp_tot[k]);
-        if (k < warp) before_warp = combine(before_warp, t);
-        all = combine(all, t);
-    }
-    __syncthreads();
-    if (total) *total = all;
-    return combine(before_warp, ex);
-}
+// Per chunk: has = a line starts inside the chunk; state = the last line started inside it is a header;
+// hdrs = header lines started; seqA = non-newline bytes before the first line start (they belong to the
+// line in progress and count only if that line is not a header); seqB = bytes of non-header lines after
+// the first line start.  A tile is summarised the same way (TileSum in eref_internal.cuh).
 
 struct FastaChunk {
     Masks m;
     uint32_t inr;       // bytes below n
-    uint32_t ls;        // line starts inside the chunk
-    uint32_t hs;        // ... that are header lines
+    uint32_t hs;        // line starts inside the chunk that are header lines
     uint32_t hm;        // bytes of header lines started inside the chunk
     uint32_t pm;        // bytes before the first line start
-    FastaSum sum;
+    uint32_t has, state, hdrs, seqA, seqB;
 };
 
 // FULL = false: only the newline mask is formed (hi/lo/ok stay 0) — enough for the summaries.
@@ -282,17 +229,16 @@ __device__ __forceinline__ FastaChunk fasta_chunk(const uint8_t* __restrict__ te
     // the byte before the chunk decides whether byte 0 starts a line
     uint32_t prev_nl = __shfl_up_sync(0xffffffffu, c.m.nl & 1u, 1);
     if ((threadIdx.x & 31) == 0) prev_nl = off == 0 ? 1u : (off - 1 < n ? (uint32_t)(__ldg(text + off - 1) == 0x0Au) : 0u);
-    c.ls = ((c.m.nl >> 1) | (prev_nl << 31)) & c.inr;
-    c.hs = 0; c.hm = 0;
-    FastaSum s{0, 0, 0, 0, 0};
+    const uint32_t ls = ((c.m.nl >> 1) | (prev_nl << 31)) & c.inr;
+    c.hs = 0; c.hm = 0; c.has = 0; c.state = 0; c.hdrs = 0; c.seqB = 0;
     const uint32_t body = ~c.m.nl & c.inr;               // bytes that are not newlines
-    if (!c.ls) {
+    if (!ls) {
         c.pm = 0xFFFFFFFFu;
-        s.seqA = __popc(body);
+        c.seqA = __popc(body);
     } else {
-        uint32_t rest = c.ls;
+        uint32_t rest = ls;
         c.pm = before(__clz(rest));
-        s.has = 1;
+        c.has = 1;
         while (rest) {
             const int k = __clz(rest);
             rest &= ~(0x80000000u >> k);
@@ -301,27 +247,67 @@ __device__ __forceinline__ FastaChunk fasta_chunk(const uint8_t* __restrict__ te
                 c.hs |= 0x80000000u >> k;
                 c.hm |= ~before(k) & before(rest ? __clz(rest) : 32);
             }
-            s.state = hdr;
+            c.state = hdr;
         }
-        s.hdrs = __popc(c.hs);
-        s.seqA = __popc(body & c.pm);
-        s.seqB = __popc(body & ~c.pm & ~c.hm);
+        c.hdrs = __popc(c.hs);
+        c.seqA = __popc(body & c.pm);
+        c.seqB = __popc(body & ~c.pm & ~c.hm);
     }
-    c.sum = s;
     return c;
+}
+
+// Is the line in progress at the start of this thread's chunk a header?  Answered from the chunks before it
+// in the tile: *known = false when no line starts between the tile's first byte and the chunk (the tile's
+// own incoming state applies).  Also returns the tile's (has, state) pair in *tile_flags (bit 0, bit 1).
+__device__ __forceinline__ uint32_t incoming_state(const FastaChunk& c, bool* known, uint32_t* tile_flags)
+{
+    __shared__ unsigned long long s_warp;                 // one byte per warp: bit 0 has, bit 1 state
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t hasm = __ballot_sync(0xffffffffu, c.has);
+    const uint32_t stm = __ballot_sync(0xffffffffu, c.has && c.state);
+    if (lane == 0) {
+        const uint32_t last = hasm ? (stm >> (31 - __clz(hasm))) & 1u : 0u;
+        reinterpret_cast<uint8_t*>(&s_warp)[warp] = (uint8_t)((hasm ? 1u : 0u) | (last << 1));
+    }
+    __syncthreads();
+    const unsigned long long all = s_warp;
+    const unsigned long long hb = all & 0x0101010101010101ull;
+    if (tile_flags) {
+        uint32_t f = 0;
+        if (hb) { const int w = (63 - __clzll(hb)) >> 3; f = 1u | ((uint32_t)((all >> (8 * w + 1)) & 1ull) << 1); }
+        *tile_flags = f;
+    }
+    const uint32_t prior = hasm & ((1u << lane) - 1u);
+    if (prior) { *known = true; return (stm >> (31 - __clz(prior))) & 1u; }
+    const unsigned long long pw = hb & ((1ull << (8 * warp)) - 1ull);
+    if (pw) { *known = true; const int w = (63 - __clzll(pw)) >> 3; return (uint32_t)((all >> (8 * w + 1)) & 1ull); }
+    *known = false;
+    return 0;
 }
 
 // K1: one summary per tile
 __global__ void __launch_bounds__(TILE_THREADS)
 k_fasta_tiles(const uint8_t* __restrict__ text, uint64_t n, TileSum* __restrict__ tiles)
 {
+    __shared__ uint32_t s_a[TILE_THREADS / 32], s_b[TILE_THREADS / 32];
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     const FastaChunk c = fasta_chunk<false>(text, n, off);
-    FastaSum all;
-    block_scan_fasta(c.sum, &all);
+    bool known;
+    uint32_t flags;
+    const uint32_t in_hdr = incoming_state(c, &known, &flags);
+    // bytes before the tile's first line start wait for the tile's incoming state (seqA); the rest is decided here
+    uint32_t a = known ? 0u : c.seqA;
+    uint32_t b = ((known && !in_hdr) ? c.seqA : 0u) + c.seqB + (c.hdrs << 16);
+    a = __reduce_add_sync(0xffffffffu, a);
+    b = __reduce_add_sync(0xffffffffu, b);
+    if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = a; s_b[threadIdx.x >> 5] = b; }
+    __syncthreads();
     if (threadIdx.x == 0) {
+        a = 0; b = 0;
+#pragma unroll
+        for (int k = 0; k < TILE_THREADS / 32; k++) { a += s_a[k]; b += s_b[k]; }
         TileSum t;
-        t.flags = all.has | (all.state << 1); t.hdrs = all.hdrs; t.seqA = all.seqA; t.seqB = all.seqB;
+        t.flags = flags; t.hdrs = b >> 16; t.seqA = a; t.seqB = b & 0xFFFFu;
         tiles[blockIdx.x] = t;
     }
 }
@@ -329,13 +315,17 @@ k_fasta_tiles(const uint8_t* __restrict__ text, uint64_t n, TileSum* __restrict_
 // what a thread knows about the text before its chunk, from the tile prefix and the in-tile scan
 struct Incoming { uint32_t in_header, rec, rank; };
 
-__device__ __forceinline__ Incoming incoming(const TileSum& tp, const FastaSum& ex)
+__device__ __forceinline__ Incoming incoming(const FastaChunk& c, const TileSum& tp)
 {
+    bool known;
+    uint32_t in_hdr = incoming_state(c, &known, nullptr);
+    if (!known) in_hdr = (tp.flags & 1u) ? (tp.flags >> 1) & 1u : 0u;
+    const uint32_t mine = (in_hdr ? 0u : c.seqA) + c.seqB + (c.hdrs << 16);      // < 2^29 per tile
+    const uint32_t ex = block_exclusive_scan(mine, nullptr);
     Incoming in;
-    const uint32_t tile_state = (tp.flags & 1u) ? (tp.flags >> 1) & 1u : 0u;
-    in.in_header = ex.has ? ex.state : tile_state;
-    in.rec = tp.hdrs + ex.hdrs;
-    in.rank = (uint32_t)(tp.seqA + tp.seqB) + (tile_state ? 0u : ex.seqA) + ex.seqB;
+    in.in_header = in_hdr;
+    in.rec = tp.hdrs + (ex >> 16);
+    in.rank = (uint32_t)(tp.seqA + tp.seqB) + (ex & 0xFFFFu);
     return in;
 }
 
@@ -349,9 +339,8 @@ k_fasta_records(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __r
     if (tiles[blockIdx.x].hdrs == 0) return;
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     const FastaChunk c = fasta_chunk<false>(text, n, off);
-    const FastaSum ex = block_scan_fasta(c.sum, nullptr);
+    const Incoming in = incoming(c, tile_pre[blockIdx.x]);
     if (!c.hs) return;
-    const Incoming in = incoming(tile_pre[blockIdx.x], ex);
     const uint32_t seq = ~c.m.nl & c.inr & ~c.hm & (in.in_header ? ~c.pm : 0xFFFFFFFFu);
     uint32_t rest = c.hs;
     uint32_t r = in.rec;
@@ -428,8 +417,7 @@ k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __rest
     for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; s_g[i] = 0xFFFFFFFFu; }
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     const FastaChunk c = fasta_chunk<true>(text, n, off);
-    const FastaSum ex = block_scan_fasta(c.sum, nullptr);          // (syncs: the ring is zeroed)
-    const Incoming in = incoming(tile_pre[blockIdx.x], ex);
+    const Incoming in = incoming(c, tile_pre[blockIdx.x]);         // (syncs: the ring is zeroed)
     const uint32_t seq = ~c.m.nl & c.inr & ~c.hm & (in.in_header ? ~c.pm : 0xFFFFFFFFu);
     uint32_t wmin = 0xFFFFFFFFu, wmax = 0;
     uint32_t rest = seq;

@@ -1,11 +1,18 @@
 // table.cu — the query k-mer table (north_star parts 2+3).
 //
 // The reference keeps one saturating byte counter per 32-bit code, shared by the three code
-// streams (bin/extract_ref.cpp:25-26, :995-997), and only ever asks "count == 3" (:531).  In HBM
-// that is three 2^32-bit bitmaps, level L meaning "seen at least L times".  An occurrence sets its
-// bit in level 1; if it was already set it moves on to level 2, then level 3.  Of n occurrences of a
-// code exactly one finds level 1 clear and exactly one of the rest finds level 2 clear, so level 3
-// ends up set iff n >= 3, whatever the order the atomics land in: the build is deterministic.
+// streams (bin/extract_ref.cpp:25-26, :995-997), and only ever asks "count == 3" (:531).  Here that is
+// three bitmaps, level L meaning "seen at least L times".  An occurrence sets its bit in level 1; if it
+// was already set it moves on to level 2, then level 3.  Of n occurrences of a code exactly one finds
+// level 1 clear and exactly one of the rest finds level 2 clear, so level 3 ends up set iff n >= 3,
+// whatever the order the atomics land in: the build is deterministic.  Only level 3 is ever probed.
+//
+// Measured on B200 (tools/atomics_bench.cu): random L2-resident atomics that return the old value top out
+// at ~129 G/s whatever the occupancy, shared-memory atomics at ~1 T/s.  The build therefore never touches
+// the table with global atomics: the codes are radix-partitioned by their top 13 bits (a coarse scatter
+// from the bit-planes, then a fine partition staged through shared memory so that the writes stay
+// coalesced), and one CTA per 2^19-slot table slice counts its codes in a 192 KiB shared-memory copy of the
+// three levels and writes the finished level-3 slice (and its summary) to HBM with plain stores.
 #include "eref_internal.cuh"
 
 namespace {
@@ -22,8 +29,9 @@ __device__ __forceinline__ void count_code(uint32_t code, uint32_t old1, uint32_
     }
 }
 
-// One thread per plane word = 32 window starts.  Only starts whose 32 positions are all valid
-// bases are visited (valid_windows), so FASTQ headers/qualities cost one mask computation.
+// Direct build (EREF_FLAG_DIRECT_COUNT, kept as the cross-check of the partitioned build): global atomics
+// straight into three 2^32-bit levels.  One thread per plane word = 32 window starts; only starts whose 32
+// positions are all valid bases are visited (valid_windows).
 __global__ void __launch_bounds__(256)
 k_count_kmers(Planes pl, CoderMasks m, uint32_t* __restrict__ bm1, uint32_t* __restrict__ bm2,
               uint32_t* __restrict__ bm3)
@@ -57,15 +65,7 @@ k_count_kmers(Planes pl, CoderMasks m, uint32_t* __restrict__ bm1, uint32_t* __r
     }
 }
 
-// ---- bucketed build --------------------------------------------------------------------------------
-// Random atomics over three 512 MiB bitmaps miss L2 on every access (ncu: 4.6 % hit rate, ~80 B of DRAM
-// traffic per atomic).  The codes are therefore first partitioned by their top BUCKET_BITS bits; the
-// counting kernel then walks the buckets in order, so the 3 x 16 MiB of table slices it is updating at
-// any moment stay resident in the 126 MB L2 and DRAM sees each table sector about once.
-// Atomics commute, so the resulting bitmaps are identical to the direct kernel's.
-constexpr int BUCKET_BITS = 5;
-constexpr int NBUCKETS = 1 << BUCKET_BITS;
-constexpr int BUCKET_SHIFT = 32 - BUCKET_BITS;
+// ---- partitioned build -------------------------------------------------------------------------------
 
 template <class F>
 __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks& m, uint64_t w, F&& f)
@@ -82,83 +82,285 @@ __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks
     }
 }
 
-// SCATTER=false: global histogram of codes per bucket.  SCATTER=true: the CTA counts its codes per
-// bucket, reserves one contiguous range per bucket with 32 global atomics, then writes its codes there.
-template <bool SCATTER>
+// P0: histogram of the codes of one file over the NSLICES table slices (top 13 code bits).  Persistent grid:
+// a CTA accumulates in shared memory over all its tiles and flushes once.
 __global__ void __launch_bounds__(256)
-k_bucket_codes(Planes pl, CoderMasks m, unsigned long long* __restrict__ g_hist,
-               const unsigned long long* __restrict__ bucket_off, unsigned long long* __restrict__ g_tail,
-               uint32_t* __restrict__ codes_out)
+k_slice_hist(Planes pl, CoderMasks m, unsigned long long* __restrict__ g_hist)
 {
-    __shared__ uint32_t s_hist[8][NBUCKETS];
-    __shared__ unsigned long long s_base[NBUCKETS];
-    __shared__ uint32_t s_cursor[NBUCKETS];
+    __shared__ uint32_t s_hist[NSLICES];
+    for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) s_hist[i] = 0;
+    __syncthreads();
+    for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < pl.nwords; w += (uint64_t)gridDim.x * blockDim.x)
+        for_each_code(pl, m, w, [&](uint32_t code) { atomicAdd(&s_hist[code >> SLICE_BITS], 1u); });
+    __syncthreads();
+    for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) {
+        const uint32_t v = s_hist[i];
+        if (v) atomicAdd(g_hist + i, (unsigned long long)v);
+    }
+}
+
+// P1: coarse scatter by the top `32 - shift` bits.  The CTA counts its codes per bucket, reserves one
+// contiguous range per bucket with one global atomic each, then writes its codes there.  slice_off is the
+// slice offset table: coarse bucket b starts where its first slice starts.
+__global__ void __launch_bounds__(256)
+k_coarse_scatter(Planes pl, CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
+                 unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out)
+{
+    __shared__ uint32_t s_hist[8][MAX_BUCKETS];
+    __shared__ unsigned long long s_base[MAX_BUCKETS];
+    __shared__ uint32_t s_cursor[MAX_BUCKETS];
     const int warp = threadIdx.x >> 5;
-    s_hist[threadIdx.x >> 5][threadIdx.x & 31] = 0;
+    const int nb = 1 << (32 - shift);
+    for (int i = threadIdx.x; i < 8 * nb; i += blockDim.x) s_hist[i / nb][i % nb] = 0;
     __syncthreads();
     const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = w < pl.nwords;
-    if (live) for_each_code(pl, m, w, [&](uint32_t code) { atomicAdd(&s_hist[warp][code >> BUCKET_SHIFT], 1u); });
+    if (live) for_each_code(pl, m, w, [&](uint32_t code) { atomicAdd(&s_hist[warp][code >> shift], 1u); });
     __syncthreads();
-    if (threadIdx.x < NBUCKETS) {
+    if (threadIdx.x < nb) {
         uint32_t c = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) c += s_hist[k][threadIdx.x];
-        if (!SCATTER) {
-            if (c) atomicAdd(g_hist + threadIdx.x, (unsigned long long)c);
-        } else {
-            s_base[threadIdx.x] = bucket_off[threadIdx.x] + (c ? atomicAdd(g_tail + threadIdx.x, (unsigned long long)c) : 0ull);
-            s_cursor[threadIdx.x] = 0;
-        }
+        s_base[threadIdx.x] = slice_off[(size_t)threadIdx.x << (shift - SLICE_BITS)] +
+                              (c ? atomicAdd(g_tail + threadIdx.x, (unsigned long long)c) : 0ull);
+        s_cursor[threadIdx.x] = 0;
     }
-    if (!SCATTER) return;
     __syncthreads();
     if (live) for_each_code(pl, m, w, [&](uint32_t code) {
-        const uint32_t b = code >> BUCKET_SHIFT;
+        const uint32_t b = code >> shift;
         codes_out[s_base[b] + atomicAdd(&s_cursor[b], 1u)] = code;
     });
 }
 
-// Counts one bucket of up to two bucket-ordered code lists (the two FASTQ files).  A thread owns U
-// 16-byte units, strided by the grid so that every LDG.128 of a warp is one contiguous 512 B run; all
-// level-1 atomics of a thread are issued before the first dependent level-2 atomic.
-template <int U>
-__global__ void __launch_bounds__(256)
-k_count_codes(const uint32_t* __restrict__ c0, uint64_t n0, const uint32_t* __restrict__ c1, uint64_t n1,
-              uint32_t* __restrict__ bm1, uint32_t* __restrict__ bm2, uint32_t* __restrict__ bm3)
+// Slice offsets of one file from its slice histogram, on the device (no host round trip, no H2D copy that
+// would queue behind the database upload): off[s] = start of slice s (padded to 4 codes so that every slice
+// starts 16-byte aligned), cnt = copy of the histogram, coarse_n[b] = codes of coarse bucket b,
+// chunk_start[b] = first fine-partition chunk of bucket b, totals = {codes, padded size, chunks}.
+constexpr int FINE_CHUNK = 8192;
+constexpr int FINE_THREADS = 1024;
+constexpr int FINE_PER_THREAD = FINE_CHUNK / FINE_THREADS;
+
+__global__ void __launch_bounds__(1024)
+k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned long long* __restrict__ off,
+                unsigned long long* __restrict__ cnt, unsigned long long* __restrict__ coarse_n,
+                uint32_t* __restrict__ chunk_start, unsigned long long* __restrict__ totals)
 {
-    const uint64_t units0 = (n0 + 3) >> 2, total = units0 + ((n1 + 3) >> 2);
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    const uint64_t first = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t code[4 * U], old[4 * U];
-    uint32_t live = 0;                                   // bit q set: code[q] is a real code
+    __shared__ unsigned long long s_warp[32];
+    __shared__ unsigned long long s_coarse[MAX_BUCKETS];
+    constexpr int PER = NSLICES / 1024;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long v[PER], sum = 0;
 #pragma unroll
-    for (int j = 0; j < U; j++) {
-        const uint64_t u = first + (uint64_t)j * stride;
-        if (u < total) {
-            const bool second = u >= units0;
-            const uint64_t lu = second ? u - units0 : u;
-            const uint32_t* base = second ? c1 : c0;
-            const uint64_t n = second ? n1 : n0;
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(base) + lu);   // bucket starts are 16-byte aligned,
-            code[4 * j] = v.x; code[4 * j + 1] = v.y; code[4 * j + 2] = v.z; code[4 * j + 3] = v.w;   // padded to 4 codes
-            const uint64_t left = n - (lu << 2);
-            live |= (left >= 4 ? 0xFu : ((1u << left) - 1u)) << (4 * j);
+    for (int k = 0; k < PER; k++) { v[k] = hist[threadIdx.x * PER + k]; cnt[threadIdx.x * PER + k] = v[k]; sum += (v[k] + 3) & ~3ull; }
+    unsigned long long inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { unsigned long long t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    unsigned long long base = 0;
+    for (int k = 0; k < warp; k++) base += s_warp[k];
+    unsigned long long run = base + inc - sum;
+#pragma unroll
+    for (int k = 0; k < PER; k++) { off[threadIdx.x * PER + k] = run; run += (v[k] + 3) & ~3ull; }
+    if (threadIdx.x == 1023) off[NSLICES] = run;
+    const int fbits = 32 - SLICE_BITS - cbits, NC = 1 << cbits;
+    if (threadIdx.x < NC) {
+        unsigned long long nb = 0;
+        for (int f = 0; f < (1 << fbits); f++) nb += hist[((size_t)threadIdx.x << fbits) + f];
+        coarse_n[threadIdx.x] = nb;
+        s_coarse[threadIdx.x] = nb;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long total = 0;
+        uint32_t chunks = 0;
+        for (int b = 0; b < NC; b++) {
+            chunk_start[b] = chunks;
+            chunks += (uint32_t)((s_coarse[b] + FINE_CHUNK - 1) / FINE_CHUNK);
+            total += s_coarse[b];
+        }
+        chunk_start[NC] = chunks;
+        totals[0] = total; totals[2] = chunks;
+    }
+    if (threadIdx.x == 1023) totals[1] = run;
+}
+
+// P2: fine partition of one coarse bucket's codes into its 2^fbits slices.  A CTA takes a chunk of
+// FINE_CHUNK codes, ranks them per slice with shared-memory atomics, reserves one range per slice, sorts the
+// chunk by slice in shared memory and writes it out, consecutive threads to consecutive addresses.
+__global__ void __launch_bounds__(FINE_THREADS, 2)
+k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __restrict__ slice_off,
+                 const unsigned long long* __restrict__ coarse_n, const uint32_t* __restrict__ chunk_start,
+                 int cbits, unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ out)
+{
+    __shared__ uint32_t s_stage[FINE_CHUNK];
+    __shared__ uint32_t s_cnt[MAX_BUCKETS], s_off[MAX_BUCKETS + 1];
+    __shared__ unsigned long long s_gbase[MAX_BUCKETS];
+    __shared__ uint32_t s_warp[8];
+    const int fbits = 32 - SLICE_BITS - cbits, nf = 1 << fbits, ncoarse = 1 << cbits;
+    if (blockIdx.x >= chunk_start[ncoarse]) return;                         // the grid is sized from an upper bound
+    // which coarse bucket does this chunk belong to?
+    int lo = 0, hi = ncoarse;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (chunk_start[mid] <= blockIdx.x) lo = mid; else hi = mid; }
+    const int b = lo;
+    const uint64_t first = (uint64_t)(blockIdx.x - chunk_start[b]) * FINE_CHUNK;
+    const uint64_t nb = coarse_n[b];
+    if (first >= nb) return;
+    const uint32_t cnt = (uint32_t)min((uint64_t)FINE_CHUNK, nb - first);
+    const uint32_t* src = in + slice_off[(size_t)b << fbits] + first;       // 16-byte aligned: slice starts and chunks are
+    if (threadIdx.x < nf) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t code[FINE_PER_THREAD];
+    uint16_t rank[FINE_PER_THREAD];
+#pragma unroll
+    for (int j = 0; j < FINE_PER_THREAD / 4; j++) {
+        const uint32_t u = (uint32_t)(j * FINE_THREADS + threadIdx.x);      // 16-byte unit inside the chunk
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (u * 4 < cnt) v = __ldcs(reinterpret_cast<const uint4*>(src) + u);
+        code[4 * j] = v.x; code[4 * j + 1] = v.y; code[4 * j + 2] = v.z; code[4 * j + 3] = v.w;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (u * 4 + k < cnt) rank[4 * j + k] = (uint16_t)atomicAdd(&s_cnt[(code[4 * j + k] >> SLICE_BITS) & (nf - 1)], 1u);
+    }
+    __syncthreads();
+    // exclusive scan of the per-slice counts (nf <= 256: one value per thread of the first 8 warps) + global reservation
+    if (threadIdx.x < 256) {
+        const uint32_t v = threadIdx.x < nf ? s_cnt[threadIdx.x] : 0u;
+        uint32_t inc = v;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+        if (lane == 31) s_warp[warp] = inc;
+        asm volatile("bar.sync 1, 256;");                                   // the first 8 warps only
+        uint32_t base = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) if (k < warp) base += s_warp[k];
+        if (threadIdx.x < nf) {
+            s_off[threadIdx.x] = base + inc - v;
+            const size_t slice = ((size_t)b << fbits) + threadIdx.x;
+            s_gbase[threadIdx.x] = slice_off[slice] + (v ? atomicAdd(g_tail + slice, (unsigned long long)v) : 0ull);
         }
     }
+    __syncthreads();
 #pragma unroll
-    for (int q = 0; q < 4 * U; q++)
-        if ((live >> q) & 1u) old[q] = atomicOr(bm1 + (code[q] >> 5), 1u << (code[q] & 31));
+    for (int j = 0; j < FINE_PER_THREAD / 4; j++) {
+        const uint32_t u = (uint32_t)(j * FINE_THREADS + threadIdx.x);
 #pragma unroll
-    for (int q = 0; q < 4 * U; q++)
-        if ((live >> q) & 1u) count_code(code[q], old[q], bm2, bm3);
+        for (int k = 0; k < 4; k++)
+            if (u * 4 + k < cnt) s_stage[s_off[(code[4 * j + k] >> SLICE_BITS) & (nf - 1)] + rank[4 * j + k]] = code[4 * j + k];
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < cnt; i += FINE_THREADS) {
+        const uint32_t c = s_stage[i];
+        const uint32_t f = (c >> SLICE_BITS) & (nf - 1);
+        out[s_gbase[f] + (i - s_off[f])] = c;
+    }
+}
+
+// P3: one CTA per table slice.  The three levels of the slice live in shared memory (3 x 64 KiB); the codes
+// of the slice from every pending file are counted with shared-memory atomics; the finished level-3 slice
+// and its part of the summary (1 bit per 16 slots) go to HBM with plain, coalesced stores.  Also
+// accumulates the number of codes at each level (eref_query_popcount).
+constexpr int COUNT_THREADS = 1024;
+constexpr int COUNT_PRE = 2;                 // 16-byte units per thread and list fetched before the levels are zeroed
+
+__device__ __forceinline__ void count_unit(const uint4& v, uint32_t left, uint32_t* L1, uint32_t* L2, uint32_t* L3)
+{
+    const uint32_t code[4] = {v.x, v.y, v.z, v.w};
+    uint32_t old[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (k < left) old[k] = atomicOr(&L1[(code[k] & SLICE_MASK) >> 5], 1u << (code[k] & 31));
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (k < left) {
+            const uint32_t bit = 1u << (code[k] & 31), w = (code[k] & SLICE_MASK) >> 5;
+            if (old[k] & bit) {
+                const uint32_t old2 = atomicOr(&L2[w], bit);
+                if (old2 & bit) atomicOr(&L3[w], bit);
+            }
+        }
+}
+
+template <bool POP>
+__global__ void __launch_bounds__(COUNT_THREADS, 1)
+k_count_slices(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary,
+               unsigned long long* __restrict__ level_pop)
+{
+    extern __shared__ uint4 s_raw[];
+    uint32_t* L1 = reinterpret_cast<uint32_t*>(s_raw);
+    uint32_t* L2 = L1 + SLICE_WORDS;
+    uint32_t* L3 = L2 + SLICE_WORDS;
+    const uint32_t slice = blockIdx.x;
+    // the first codes of the first two lists are requested before the levels are zeroed, so that the HBM round
+    // trip overlaps the shared-memory stores
+    uint4 pre[2][COUNT_PRE];
+    uint64_t n_pre[2] = {0, 0};
+#pragma unroll
+    for (int l = 0; l < 2; l++)
+        if (l < lists.n) {
+            n_pre[l] = lists.cnt[l][slice];
+            const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);   // 16-byte aligned, padded to 4
+#pragma unroll
+            for (int j = 0; j < COUNT_PRE; j++) {
+                const uint64_t u = threadIdx.x + (uint64_t)j * COUNT_THREADS;
+                pre[l][j] = u * 4 < n_pre[l] ? __ldcs(src + u) : make_uint4(0, 0, 0, 0);
+            }
+        }
+    for (int i = threadIdx.x; i < 3 * SLICE_WORDS / 4; i += COUNT_THREADS) s_raw[i] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+#pragma unroll
+    for (int l = 0; l < 2; l++)
+#pragma unroll
+        for (int j = 0; j < COUNT_PRE; j++) {
+            const uint64_t u = threadIdx.x + (uint64_t)j * COUNT_THREADS;
+            if (u * 4 < n_pre[l]) count_unit(pre[l][j], (uint32_t)min((uint64_t)4, n_pre[l] - u * 4), L1, L2, L3);
+        }
+    for (int l = 0; l < lists.n; l++) {
+        const uint64_t n = lists.cnt[l][slice];
+        const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);
+        for (uint64_t u = threadIdx.x + (l < 2 ? (uint64_t)COUNT_PRE * COUNT_THREADS : 0ull); u * 4 < n; u += COUNT_THREADS)
+            count_unit(__ldcs(src + u), (uint32_t)min((uint64_t)4, n - u * 4), L1, L2, L3);
+    }
+    __syncthreads();
+    uint4* dst = reinterpret_cast<uint4*>(bm3 + (size_t)slice * SLICE_WORDS);
+    const uint4* l3 = reinterpret_cast<const uint4*>(L3);
+    for (int i = threadIdx.x; i < SLICE_WORDS / 4; i += COUNT_THREADS) __stcs(dst + i, l3[i]);
+    // summary word j of the slice covers table words 16j .. 16j+15
+    for (int j = threadIdx.x; j < SLICE_WORDS / 16; j += COUNT_THREADS) {
+        uint32_t out = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 v = l3[j * 4 + q];
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int word = q * 4 + k;
+                out |= (uint32_t)((w[k] & 0x0000FFFFu) != 0) << (word * 2);
+                out |= (uint32_t)((w[k] & 0xFFFF0000u) != 0) << (word * 2 + 1);
+            }
+        }
+        summary[(size_t)slice * (SLICE_WORDS / 16) + j] = out;
+    }
+    if (POP) {
+        uint32_t p1 = 0, p2 = 0, p3 = 0;
+        for (int i = threadIdx.x; i < SLICE_WORDS; i += COUNT_THREADS) { p1 += __popc(L1[i]); p2 += __popc(L2[i]); p3 += __popc(L3[i]); }
+        p1 = __reduce_add_sync(0xffffffffu, p1); p2 = __reduce_add_sync(0xffffffffu, p2); p3 = __reduce_add_sync(0xffffffffu, p3);
+        if ((threadIdx.x & 31) == 0) {
+            if (p1) atomicAdd(level_pop + 0, (unsigned long long)p1);
+            if (p2) atomicAdd(level_pop + 1, (unsigned long long)p2);
+            if (p3) atomicAdd(level_pop + 2, (unsigned long long)p3);
+        }
+    }
 }
 
 // summary bit = OR of 16 consecutive level-3 bits: a 32 MiB filter that stays in L2 during the scan
+// (direct build only; the partitioned build writes the summary from shared memory)
 __global__ void __launch_bounds__(256)
-k_build_summary(const uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary)
+k_build_summary(const uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary, uint32_t summary_words)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;          // summary word: 16 table words
+    if (i >= summary_words) return;
     const uint4* p = reinterpret_cast<const uint4*>(bm3) + (size_t)i * 4;
     uint32_t out = 0;
 #pragma unroll
@@ -173,16 +375,6 @@ k_build_summary(const uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary
         }
     }
     summary[i] = out;
-}
-
-// zero one bucket's slice of all three levels; the lines stay dirty in L2 for the atomics that follow
-__global__ void __launch_bounds__(256)
-k_zero_slices(uint4* __restrict__ a, uint4* __restrict__ b, uint4* __restrict__ c, uint32_t nvec)
-{
-    const uint4 z = make_uint4(0, 0, 0, 0);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
-        a[i] = z; b[i] = z; c[i] = z;
-    }
 }
 
 __global__ void k_popcount(const uint32_t* __restrict__ bm, uint64_t nwords, unsigned long long* out)
@@ -206,42 +398,53 @@ cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t*
     return cudaGetLastError();
 }
 
-cudaError_t launch_bucket_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st)
+cudaError_t launch_slice_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st)
 {
     if (!pl.nwords) return cudaSuccess;
-    k_bucket_codes<false><<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, g_hist, nullptr, nullptr, nullptr);
+    const uint64_t want = (pl.nwords + 255) / 256;
+    k_slice_hist<<<(unsigned)(want < 148 * 6 ? want : 148 * 6), 256, 0, st>>>(pl, m, g_hist);
     return cudaGetLastError();
 }
 
-cudaError_t launch_bucket_scatter(Planes pl, CoderMasks m, const unsigned long long* bucket_off,
+cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
                                   unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st)
 {
     if (!pl.nwords) return cudaSuccess;
-    k_bucket_codes<true><<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, nullptr, bucket_off, g_tail, codes_out);
+    k_coarse_scatter<<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, 32 - cbits, slice_off, g_tail, codes_out);
     return cudaGetLastError();
 }
 
-cudaError_t launch_count_codes(const uint32_t* c0, uint64_t n0, const uint32_t* c1, uint64_t n1, int units,
-                               uint32_t* bm1, uint32_t* bm2, uint32_t* bm3, cudaStream_t st)
+cudaError_t launch_slice_offsets(const unsigned long long* hist, int cbits, unsigned long long* off, unsigned long long* cnt,
+                                 unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals, cudaStream_t st)
 {
-    const uint64_t total = ((n0 + 3) >> 2) + ((n1 + 3) >> 2);
-    if (!total) return cudaSuccess;
-    if (units >= 4) k_count_codes<4><<<(unsigned)((total + 1023) / 1024), 256, 0, st>>>(c0, n0, c1, n1, bm1, bm2, bm3);
-    else if (units == 2) k_count_codes<2><<<(unsigned)((total + 511) / 512), 256, 0, st>>>(c0, n0, c1, n1, bm1, bm2, bm3);
-    else k_count_codes<1><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(c0, n0, c1, n1, bm1, bm2, bm3);
+    k_slice_offsets<<<1, 1024, 0, st>>>(hist, cbits, off, cnt, coarse_n, chunk_start, totals);
     return cudaGetLastError();
 }
 
-cudaError_t launch_zero_slices(uint32_t* a, uint32_t* b, uint32_t* c, uint32_t nwords, cudaStream_t st)
+cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
+                                  const uint32_t* chunk_start, uint32_t nchunks, int cbits, unsigned long long* g_tail,
+                                  uint32_t* out, cudaStream_t st)
 {
-    k_zero_slices<<<148 * 8, 256, 0, st>>>(reinterpret_cast<uint4*>(a), reinterpret_cast<uint4*>(b),
-                                          reinterpret_cast<uint4*>(c), nwords / 4);
+    if (!nchunks) return cudaSuccess;
+    k_fine_partition<<<nchunks, FINE_THREADS, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
     return cudaGetLastError();
 }
 
-cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, cudaStream_t st)
+cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t* summary, unsigned long long* level_pop,
+                                cudaStream_t st)
 {
-    k_build_summary<<<SUMMARY_WORDS / 256, 256, 0, st>>>(bm3, summary);
+    const int smem = 3 * SLICE_WORDS * 4;
+    cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                              : cudaFuncSetAttribute(k_count_slices<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    if (level_pop) k_count_slices<true><<<NSLICES, COUNT_THREADS, smem, st>>>(lists, bm3, summary, level_pop);
+    else k_count_slices<false><<<NSLICES, COUNT_THREADS, smem, st>>>(lists, bm3, summary, nullptr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, uint32_t summary_words, cudaStream_t st)
+{
+    k_build_summary<<<(summary_words + 255) / 256, 256, 0, st>>>(bm3, summary, summary_words);
     return cudaGetLastError();
 }
 
