@@ -60,7 +60,7 @@ struct eref_ctx {
     DevBuf q_text2, run_results;
     CoderMasks masks{};
     float hit_ratio = 0, perfect_hit_ratio = 0;
-    int one_min = 0, three_min = 0;
+    int one_min = 0, three_min = 0, sample_stride = 4;
     unsigned flags = 0;
     cudaEvent_t ev[EV_COUNT]{};
     // query table: level L bitmap = "code seen >= L times"
@@ -68,7 +68,7 @@ struct eref_ctx {
     // shared scratch
     DevBuf tile_counts, tile_prefix, cub_tmp, counters;      // counters: 4 x u64
     // query side
-    DevBuf q_text, q_hi, q_lo, q_ok;
+    DevBuf q_text, q_hi, q_lo, q_ok, tile_kept, tile_kept_pre;
     // Table build (table.cu): every file added since the last reset is kept as a slice-ordered code list (codes
     // radix-partitioned by their top 13 bits); a build counts all lists slice by slice in shared memory and
     // writes level 3 and its summary.  Levels 1/2 exist in HBM only for the direct build (EREF_FLAG_DIRECT_COUNT).
@@ -162,22 +162,33 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     uint64_t ntiles = 0;
     int rc = newline_census(c, text, n, &ntiles);
     if (rc) return rc;
+    // plane positions per tile (sequence-line bytes + their newlines) and their prefix: where each tile packs to
+    CUDA_TRY(c->tile_kept.ensure((ntiles + 1) * 8)); CUDA_TRY(c->tile_kept_pre.ensure((ntiles + 1) * 8));
+    unsigned long long* tile_kept = c->tile_kept.as<unsigned long long>();
+    unsigned long long* tile_kept_pre = c->tile_kept_pre.as<unsigned long long>();
+    CUDA_TRY(cudaMemsetAsync(tile_kept + ntiles, 0, 8, st));
+    LAUNCH(c, launch_fastq_kept(text, n, c->tile_prefix.as<uint32_t>(), tile_kept, ntiles, st));
+    rc = exclusive_scan<unsigned long long>(c, tile_kept, tile_kept_pre, ntiles + 1);
+    if (rc) return rc;
+    const unsigned long long* plane_bits = tile_kept_pre + ntiles;     // total, known to the device only for now
     Planes pl;
-    pl.nwords = (n + 31) / 32;
-    CUDA_TRY(c->q_hi.ensure((pl.nwords + 1) * 4));
-    CUDA_TRY(c->q_lo.ensure((pl.nwords + 1) * 4));
-    CUDA_TRY(c->q_ok.ensure((pl.nwords + 1) * 4));
+    const uint64_t words_ub = (n + 31) / 32 + 2;
+    CUDA_TRY(c->q_hi.ensure(words_ub * 4)); CUDA_TRY(c->q_lo.ensure(words_ub * 4)); CUDA_TRY(c->q_ok.ensure(words_ub * 4));
     pl.hi = c->q_hi.as<uint32_t>(); pl.lo = c->q_lo.as<uint32_t>(); pl.ok = c->q_ok.as<uint32_t>();
-    CUDA_TRY(cudaMemsetAsync(pl.hi + pl.nwords, 0, 4, st));
-    CUDA_TRY(cudaMemsetAsync(pl.lo + pl.nwords, 0, 4, st));
-    CUDA_TRY(cudaMemsetAsync(pl.ok + pl.nwords, 0, 4, st));
+    pl.nwords = 0;
+    CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, st));           // tiles OR their boundary words in; pad words stay 0
+    CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, st));
+    CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, st));
     unsigned long long* seq_bytes = c->counters.as<unsigned long long>();
     CUDA_TRY(cudaMemsetAsync(seq_bytes, 0, 8, st));
-    LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), pl, seq_bytes, st));
+    LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), tile_kept_pre, pl, seq_bytes, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 11, plane_bits, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaEventRecord(c->ev[E2], st));
     c->summary_stale = true;
     unsigned long long total_codes = 0;
     if (c->flags & EREF_FLAG_DIRECT_COUNT) {
+        CUDA_TRY(cudaStreamSynchronize(st));
+        pl.nwords = (c->h_pin[11] + 31) >> 5;
         CUDA_TRY(cudaEventRecord(c->ev[E3], st));
         LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
     } else {
@@ -193,7 +204,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         unsigned long long* coarse_n = coarse_tail + 256;
         uint32_t* chunk_start = reinterpret_cast<uint32_t*>(coarse_n + 256);
         CUDA_TRY(cudaMemsetAsync(hist, 0, ((size_t)NSLICES * 2 + 256) * 8, st));
-        LAUNCH(c, launch_slice_hist(pl, c->masks, hist, st));
+        LAUNCH(c, launch_slice_hist(pl, plane_bits, c->masks, hist, st));
         unsigned long long* totals = chunk_start_end(chunk_start);     // {codes, padded size, chunks}
         if (c->lists.size() <= c->n_lists) c->lists.resize(c->n_lists + 1);
         eref_ctx::CodeList& L = c->lists[c->n_lists];
@@ -205,6 +216,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
         total_codes = c->h_pin[8];
         const unsigned long long padded = c->h_pin[9];
         const uint32_t nchunks = (uint32_t)c->h_pin[10];
+        pl.nwords = (c->h_pin[11] + 31) >> 5;
         L.total = total_codes;
         CUDA_TRY(L.codes.ensure((size_t)padded * 4 + 16));
         CUDA_TRY(c->codes_coarse.ensure((size_t)padded * 4 + 16));
@@ -391,7 +403,7 @@ int scan_impl(eref_ctx* c)
     CUDA_TRY(c->single.ensure((nw + 1) * 4)); CUDA_TRY(c->trio.ensure((nw + 1) * 4));
     CUDA_TRY(c->good.ensure((nw + 1) * 4));
     CUDA_TRY(c->results.ensure(((size_t)G + 1) * 16));
-    const int min_sample_hits = c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE);
+    const int min_sample_hits = c->three_min - (WINDOW - WINDOW / c->sample_stride);
     const bool prune = !(c->flags & EREF_FLAG_NO_PRUNE) && min_sample_hits > 0;
     const uint8_t* need = nullptr;
     unsigned long long* need_count = c->counters.as<unsigned long long>() + 1;
@@ -402,14 +414,12 @@ int scan_impl(eref_ctx* c)
     }
     CUDA_TRY(cudaEventRecord(c->ev[E8], st));
     if (prune) {
-        CUDA_TRY(c->sample_hits.ensure(nw + 1)); CUDA_TRY(c->cand.ensure(nw + 1)); CUDA_TRY(c->need.ensure(nw + 1));
+        CUDA_TRY(c->sample_hits.ensure(nw + 1)); CUDA_TRY(c->need.ensure(nw + 1));
         CUDA_TRY(cudaMemsetAsync(need_count, 0, 8, st));
-        LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->summary, c->sample_hits.as<uint8_t>(), st));
+        LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->summary, c->sample_stride, c->sample_hits.as<uint8_t>(), st));
         CUDA_TRY(cudaEventRecord(c->ev[E1], st));
-        LAUNCH(c, launch_candidates(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(),
-                                    c->g_word.as<uint32_t>(), nw, min_sample_hits, c->cand.as<uint8_t>(), st));
-        LAUNCH(c, launch_need(c->cand.as<uint8_t>(), c->word_genome.as<uint32_t>(), nw, c->need.as<uint8_t>(),
-                              need_count, st));
+        LAUNCH(c, launch_need(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(), c->g_word.as<uint32_t>(), nw,
+                              min_sample_hits, c->need.as<uint8_t>(), need_count, st));
         need = c->need.as<uint8_t>();
     } else {
         CUDA_TRY(cudaEventRecord(c->ev[E1], st));
@@ -490,6 +500,13 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     c->hit_ratio = hit_ratio; c->perfect_hit_ratio = perfect_hit_ratio;
     c->one_min = (int)(WINDOW * hit_ratio);              // :513 — int * float, truncated
     c->three_min = (int)(WINDOW * perfect_hit_ratio);    // :514
+    // sampling stride of the candidate filter: any 500 consecutive positions hold >= floor(500/s) sampled ones, so a good
+    // window (>= three_min positions hit by all three streams) has >= three_min - (500 - floor(500/s)) sampled hits.
+    // Take the sparsest stride that still leaves a threshold of a few hits (EREF_SAMPLE_STRIDE overrides).
+    c->sample_stride = SAMPLE_STRIDE_MIN;
+    for (int s = SAMPLE_STRIDE_MAX; s > SAMPLE_STRIDE_MIN; s--)
+        if (c->three_min - (WINDOW - WINDOW / s) >= SAMPLE_MIN_HITS) { c->sample_stride = s; break; }
+    if (const char* v = getenv("EREF_SAMPLE_STRIDE")) { int k = atoi(v); if (k >= SAMPLE_STRIDE_MIN && k <= SAMPLE_STRIDE_MAX) c->sample_stride = k; }
     cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
@@ -519,7 +536,7 @@ void eref_destroy(eref_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->table_stream) cudaStreamSynchronize(c->table_stream);
-    DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->q_text, &c->q_hi, &c->q_lo,
+    DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->tile_kept, &c->tile_kept_pre, &c->q_text, &c->q_hi, &c->q_lo,
                       &c->q_ok, &c->r_text, &c->tile_sum, &c->tile_pre, &c->rec_hdr_off, &c->rec_first,
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
                       &c->g_len, &c->g_word, &c->g_first, &c->r_hi, &c->r_lo, &c->r_ok, &c->word_genome,
@@ -637,7 +654,7 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     table_done(c);
     scan_times(c, true);
-    const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / SAMPLE_STRIDE) > 0;
+    const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / c->sample_stride) > 0;
     c->t.ref_need_words = pruned ? c->h_pin[6] : c->ref_words;
     if (n_out) *n_out = c->n_genomes;
     return 0;

@@ -20,7 +20,8 @@ constexpr int      NSLICES     = 1 << (32 - SLICE_BITS);
 constexpr int      SLICE_WORDS = 1 << (SLICE_BITS - 5);
 constexpr uint32_t SLICE_MASK  = (1u << SLICE_BITS) - 1u;
 constexpr int      MAX_LISTS   = 16;                 // query files counted by one table build
-constexpr int      SAMPLE_STRIDE = 4;                // candidate filter probes every 4th position
+constexpr int      SAMPLE_STRIDE_MIN = 4, SAMPLE_STRIDE_MAX = 8;   // candidate filter probes every s-th position
+constexpr int      SAMPLE_MIN_HITS = 6;              // smallest hit threshold worth a sparser sampling stride
 
 // Per-stream select masks of the coder assignment: bit (31-z) of sel0[i] (sel2[i]) is set iff code
 // stream i uses 1-bit alphabet 0 (2) at window position z; alphabet 1 everywhere else (:972).
@@ -128,8 +129,11 @@ int eref_fail(int code, const char* fmt, ...);
 // frame.cu
 cudaError_t launch_count_newlines(const uint8_t* text, uint64_t n, uint32_t* tile_counts,
                                   uint64_t ntiles, cudaStream_t st);
+cudaError_t launch_fastq_kept(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, unsigned long long* tile_kept,
+                              uint64_t ntiles, cudaStream_t st);
 cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
-                              Planes pl, unsigned long long* seq_bytes, cudaStream_t st);
+                              const unsigned long long* tile_kept_pre, Planes pl, unsigned long long* seq_bytes,
+                              cudaStream_t st);
 cudaError_t launch_fasta_tiles(const uint8_t* text, uint64_t n, TileSum* tiles, uint64_t ntiles, cudaStream_t st);
 cudaError_t launch_fasta_records(const uint8_t* text, uint64_t n, const TileSum* tiles, const TileSum* tile_pre,
                                  uint64_t ntiles, uint32_t* rec_first, uint32_t* rec_hdr_off, cudaStream_t st);
@@ -146,7 +150,8 @@ cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const TileSum* ti
 // table.cu
 cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
                                cudaStream_t st);
-cudaError_t launch_slice_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st);
+cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, CoderMasks m, unsigned long long* g_hist,
+                              cudaStream_t st);
 cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
                                   unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st);
 cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
@@ -167,13 +172,10 @@ cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t
 cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, uint32_t summary_words, cudaStream_t st);
 cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);
 // scan.cu
-cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary, uint8_t* sample_hits,
-                                 cudaStream_t st);
-cudaError_t launch_candidates(const uint8_t* sample_hits, const uint32_t* word_genome,
-                              const uint32_t* g_word, uint64_t nwords, int min_sample_hits,
-                              uint8_t* cand, cudaStream_t st);
-cudaError_t launch_need(const uint8_t* cand, const uint32_t* word_genome, uint64_t nwords,
-                        uint8_t* need, unsigned long long* need_count, cudaStream_t st);
+cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary, int stride,
+                                 uint8_t* sample_hits, cudaStream_t st);
+cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, const uint32_t* g_word, uint64_t nwords,
+                        int min_sample_hits, uint8_t* need, unsigned long long* need_count, cudaStream_t st);
 cudaError_t launch_probe_full(Planes pl, CoderMasks m, const uint32_t* bm3, const uint8_t* need,
                               uint32_t* single, uint32_t* trio, cudaStream_t st);
 cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint8_t* need,

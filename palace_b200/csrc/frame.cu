@@ -155,45 +155,134 @@ k_count_newlines(const uint8_t* __restrict__ text, uint64_t n, uint32_t* __restr
 }
 
 // FASTQ: a byte is a base of the query iff it lies on a line with index % 4 == 1 (:947) and is one
-// of ACGTacgt (:978).  Everything else (headers, '+', qualities, '\n', '\r', N) clears the ok bit,
-// which breaks every 32-mer that would span it.
-__global__ void __launch_bounds__(TILE_THREADS)
-k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
-             Planes pl, unsigned long long* __restrict__ seq_bytes)
+// of ACGTacgt (:978).  Only the sequence lines go into the planes, each followed by ONE invalid position
+// (its newline), which breaks every 32-mer that would span two reads — headers, '+' lines and
+// qualities are dropped, so every plane word is dense with window starts.
+
+// bytes of the chunk that lie on a sequence line; with_nl: including the newline that ends such a line
+__device__ __forceinline__ uint32_t seq_line_bytes(uint32_t nl, uint32_t line, bool with_nl)
 {
+    uint32_t seq = 0;
+    if (!nl) return (line & 3u) == 1u ? 0xFFFFFFFFu : 0u;
+    uint32_t rest = nl;
+    int start = 0;
+    while (true) {
+        const int k = rest ? __clz(rest) : 32;
+        if ((line & 3u) == 1u) seq |= before(with_nl ? min(k + 1, 32) : k) & ~before(start);
+        if (k == 32) break;
+        rest &= ~(0x80000000u >> k);
+        start = k + 1; line++;
+    }
+    return seq;
+}
+
+// per tile: plane positions it produces (sequence-line bytes and their newlines)
+__global__ void __launch_bounds__(TILE_THREADS)
+k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
+             unsigned long long* __restrict__ tile_kept)
+{
+    __shared__ uint32_t s_part[TILE_THREADS / 32];
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     uint32_t w[8];
-    const bool live = off < n;
     load32(text, n, off, w);
-    const Masks m = chunk_masks(w);
-    uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(__popc(m.nl), nullptr);
-    uint32_t nseq = 0;
-    if (live) {
+    const uint32_t nl = chunk_newlines(w);
+    const uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(__popc(nl), nullptr);
+    uint32_t kept = 0;
+    if (off < n) kept = __popc(seq_line_bytes(nl, line, true) & before((int)min((uint64_t)32, n - off)));
+    kept = __reduce_add_sync(0xffffffffu, kept);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = kept;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int k = 0; k < TILE_THREADS / 32; k++) t += s_part[k];
+        tile_kept[blockIdx.x] = t;
+    }
+}
+
+constexpr int RING = 512;     // plane words a tile can touch (see k_pack_fasta), power of two
+
+// A run of `len` consecutive chunk bytes starting at byte k0 goes to plane bits dest .. dest+len-1: OR it into
+// the CTA's shared-memory piece of the planes (word index modulo RING) and track the words touched.
+__device__ __forceinline__ void ring_emit(const Masks& m, int k0, int len, uint64_t dest, uint32_t* s_hi, uint32_t* s_lo,
+                                          uint32_t* s_ok, uint32_t& wmin, uint32_t& wmax, uint32_t& i0, uint32_t& i1, bool& two)
+{
+    const uint32_t wi = (uint32_t)(dest >> 5);
+    const int sh = (int)(dest & 31);
+    const uint32_t keep = before(len);
+    const uint32_t xh = (m.hi << k0) & keep, xl = (m.lo << k0) & keep, xo = (m.ok << k0) & keep;
+    i0 = wi & (RING - 1); i1 = (wi + 1) & (RING - 1);
+    if (xh >> sh) atomicOr(&s_hi[i0], xh >> sh);
+    if (xl >> sh) atomicOr(&s_lo[i0], xl >> sh);
+    if (xo >> sh) atomicOr(&s_ok[i0], xo >> sh);
+    wmin = min(wmin, wi); wmax = max(wmax, wi);
+    two = sh + len > 32;
+    if (two) {
+        const int up = 32 - sh;
+        if (xh << up) atomicOr(&s_hi[i1], xh << up);
+        if (xl << up) atomicOr(&s_lo[i1], xl << up);
+        if (xo << up) atomicOr(&s_ok[i1], xo << up);
+        wmax = max(wmax, wi + 1);
+    }
+}
+
+// block-wide min / max of the touched word range; false when the CTA touched nothing
+__device__ __forceinline__ bool ring_range(uint32_t& wmin, uint32_t& wmax)
+{
+    __shared__ uint32_t s_min[TILE_THREADS / 32], s_max[TILE_THREADS / 32];
+    wmin = __reduce_min_sync(0xffffffffu, wmin);
+    wmax = __reduce_max_sync(0xffffffffu, wmax);
+    if ((threadIdx.x & 31) == 0) { s_min[threadIdx.x >> 5] = wmin; s_max[threadIdx.x >> 5] = wmax; }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < TILE_THREADS / 32; k++) { wmin = min(wmin, s_min[k]); wmax = max(wmax, s_max[k]); }
+    return wmin != 0xFFFFFFFFu;
+}
+
+__global__ void __launch_bounds__(TILE_THREADS)
+k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
+             const unsigned long long* __restrict__ tile_kept_pre, Planes pl, unsigned long long* __restrict__ seq_bytes)
+{
+    __shared__ uint32_t s_hi[RING], s_lo[RING], s_ok[RING];
+    for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; }
+    const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
+    uint32_t w[8];
+    load32(text, n, off, w);
+    Masks m = chunk_masks(w);
+    const uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(__popc(m.nl), nullptr);
+    uint32_t kept = 0, nseq = 0;
+    if (off < n) {
         const uint32_t inr = before((int)min((uint64_t)32, n - off));
-        uint32_t seq = 0;                                 // bytes on a sequence line, newlines excluded
-        if (!m.nl) {
-            seq = (line & 3u) == 1u ? 0xFFFFFFFFu : 0u;
-        } else {
-            uint32_t rest = m.nl;
-            int start = 0;
-            while (true) {
-                const int k = rest ? __clz(rest) : 32;
-                if ((line & 3u) == 1u) seq |= before(k) & ~before(start);
-                if (k == 32) break;
-                rest &= ~(0x80000000u >> k);
-                start = k + 1; line++;
-            }
-        }
-        seq &= inr;
-        nseq = __popc(seq);
-        const uint32_t ok = m.ok & seq;
-        const uint64_t word = off >> 5;
-        pl.hi[word] = m.hi & ok; pl.lo[word] = m.lo & ok; pl.ok[word] = ok;
+        kept = seq_line_bytes(m.nl, line, true) & inr;
+        nseq = __popc(kept & ~m.nl);
+        m.ok &= kept; m.hi &= m.ok; m.lo &= m.ok;         // (a newline is never ACGT: it stays an invalid position)
+    }
+    const uint64_t dest0 = tile_kept_pre[blockIdx.x] + block_exclusive_scan(__popc(kept), nullptr);
+    uint32_t wmin = 0xFFFFFFFFu, wmax = 0;
+    uint32_t rest = kept;
+    while (rest) {
+        const int k0 = __clz(rest);
+        const uint32_t inv = ~(rest << k0);
+        const int len = inv ? __clz(inv) : 32;
+        rest &= ~(~before(k0) & before(k0 + len));
+        uint32_t i0, i1; bool two;
+        ring_emit(m, k0, len, dest0 + __popc(kept & before(k0)), s_hi, s_lo, s_ok, wmin, wmax, i0, i1, two);
     }
     // cal_sam_ratio's sum (:1138-1140): all bytes of sequence lines, valid or not
-#pragma unroll
-    for (int d = 16; d; d >>= 1) nseq += __shfl_xor_sync(0xffffffffu, nseq, d);
+    nseq = __reduce_add_sync(0xffffffffu, nseq);
     if ((threadIdx.x & 31) == 0 && nseq) atomicAdd(seq_bytes, (unsigned long long)nseq);
+    if (!ring_range(wmin, wmax)) return;
+    for (uint32_t wd = wmin + threadIdx.x; wd <= wmax; wd += TILE_THREADS) {
+        const uint32_t i = wd & (RING - 1);
+        const uint32_t vh = s_hi[i], vl = s_lo[i], vo = s_ok[i];
+        if (wd == wmin || wd == wmax) {                   // shared with the neighbouring tiles: OR into the zeroed planes
+            if (vh) atomicOr(pl.hi + wd, vh);
+            if (vl) atomicOr(pl.lo + wd, vl);
+            if (vo) atomicOr(pl.ok + wd, vo);
+        } else {
+            pl.hi[wd] = vh; pl.lo[wd] = vl; pl.ok[wd] = vo;
+        }
+    }
 }
 
 // ---- FASTA ---------------------------------------------------------------------------------------------
@@ -404,8 +493,6 @@ __global__ void k_genome_table(const uint32_t* __restrict__ rec_len, const uint3
 // shift: bit position = 32 * first word of the record + rank inside the record.  The CTA assembles its
 // (contiguous, < 512 words) piece of the planes in shared memory and writes whole words; the first and
 // last word may be shared with the neighbouring tiles and are OR-ed into the pre-zeroed planes.
-constexpr int RING = 512;
-
 __global__ void __launch_bounds__(TILE_THREADS)
 k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __restrict__ tile_pre,
              const uint32_t* __restrict__ rec_kept, const uint32_t* __restrict__ rec_kept_ex,
@@ -413,7 +500,6 @@ k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __rest
              Planes pl, uint32_t* __restrict__ word_genome)
 {
     __shared__ uint32_t s_hi[RING], s_lo[RING], s_ok[RING], s_g[RING];
-    __shared__ uint32_t s_min[TILE_THREADS / 32], s_max[TILE_THREADS / 32];
     for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; s_g[i] = 0xFFFFFFFFu; }
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     const FastaChunk c = fasta_chunk<true>(text, n, off);
@@ -425,39 +511,18 @@ k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __rest
         const int k0 = __clz(rest);
         const uint32_t inv = ~(rest << k0);
         const int len = inv ? __clz(inv) : 32;
-        const uint32_t run = ~before(k0) & before(k0 + len);
-        rest &= ~run;
+        rest &= ~(~before(k0) & before(k0 + len));
         const uint32_t r = in.rec + __popc(c.hs & before(k0));
         if (!rec_kept[r]) continue;
         const uint32_t rank = in.rank + __popc(seq & before(k0));
         const uint64_t dest = (uint64_t)rec_words_ex[r] * 32 + (rank - rec_first[r]);
+        uint32_t i0, i1; bool two;
+        ring_emit(c.m, k0, len, dest, s_hi, s_lo, s_ok, wmin, wmax, i0, i1, two);
         const uint32_t g = rec_kept_ex[r];
-        const uint32_t wi = (uint32_t)(dest >> 5);
-        const int sh = (int)(dest & 31);
-        const uint32_t keep = before(len);
-        const uint32_t xh = (c.m.hi << k0) & keep, xl = (c.m.lo << k0) & keep, xo = (c.m.ok << k0) & keep;
-        const uint32_t i0 = wi & (RING - 1), i1 = (wi + 1) & (RING - 1);
-        if (xh >> sh) atomicOr(&s_hi[i0], xh >> sh);
-        if (xl >> sh) atomicOr(&s_lo[i0], xl >> sh);
-        if (xo >> sh) atomicOr(&s_ok[i0], xo >> sh);
         s_g[i0] = g;
-        wmin = min(wmin, wi); wmax = max(wmax, wi);
-        if (sh + len > 32) {
-            const int up = 32 - sh;
-            if (xh << up) atomicOr(&s_hi[i1], xh << up);
-            if (xl << up) atomicOr(&s_lo[i1], xl << up);
-            if (xo << up) atomicOr(&s_ok[i1], xo << up);
-            s_g[i1] = g;
-            wmax = max(wmax, wi + 1);
-        }
+        if (two) s_g[i1] = g;
     }
-    wmin = __reduce_min_sync(0xffffffffu, wmin);
-    wmax = __reduce_max_sync(0xffffffffu, wmax);
-    if ((threadIdx.x & 31) == 0) { s_min[threadIdx.x >> 5] = wmin; s_max[threadIdx.x >> 5] = wmax; }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < TILE_THREADS / 32; k++) { wmin = min(wmin, s_min[k]); wmax = max(wmax, s_max[k]); }
-    if (wmin == 0xFFFFFFFFu) return;                      // no sequence byte of a kept record in this tile
+    if (!ring_range(wmin, wmax)) return;                  // no sequence byte of a kept record in this tile
     for (uint32_t w = wmin + threadIdx.x; w <= wmax; w += TILE_THREADS) {
         const uint32_t i = w & (RING - 1);
         const uint32_t vh = s_hi[i], vl = s_lo[i], vo = s_ok[i], g = s_g[i];
@@ -484,12 +549,21 @@ cudaError_t launch_count_newlines(const uint8_t* text, uint64_t n, uint32_t* til
     return cudaGetLastError();
 }
 
-cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, Planes pl,
-                              unsigned long long* seq_bytes, cudaStream_t st)
+cudaError_t launch_fastq_kept(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, unsigned long long* tile_kept,
+                              uint64_t ntiles, cudaStream_t st)
+{
+    if (!ntiles) return cudaSuccess;
+    k_fastq_kept<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, tile_kept);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
+                              const unsigned long long* tile_kept_pre, Planes pl, unsigned long long* seq_bytes,
+                              cudaStream_t st)
 {
     uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
     if (!ntiles) return cudaSuccess;
-    k_pack_fastq<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, pl, seq_bytes);
+    k_pack_fastq<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, tile_kept_pre, pl, seq_bytes);
     return cudaGetLastError();
 }
 
@@ -504,8 +578,7 @@ cudaError_t launch_fasta_records(const uint8_t* text, uint64_t n, const TileSum*
                                  uint64_t ntiles, uint32_t* rec_first, uint32_t* rec_hdr_off, cudaStream_t st)
 {
     if (!ntiles) {                                        // empty text: record 0 only
-        const uint32_t init[1] = {0};
-        cudaError_t e = cudaMemcpyAsync(rec_first, init, 4, cudaMemcpyHostToDevice, st);
+        cudaError_t e = cudaMemsetAsync(rec_first, 0, 4, st);
         if (e != cudaSuccess) return e;
         return cudaMemsetAsync(rec_hdr_off, 0xFF, 4, st);
     }

@@ -18,69 +18,105 @@ __device__ __forceinline__ uint32_t probe(const uint32_t* __restrict__ bm3, uint
     return code ? (__ldg(bm3 + (code >> 5)) >> (code & 31)) & 1u : 0u;
 }
 
-// ---- P1: stream 0 at positions 0,4,...,28 of every word ------------------------------------------
-// The 32 MiB level-3 summary (1 bit per 16 slots, table.cu) answers most probes of an absent reference
-// from L2; only a set summary bit costs the DRAM sector of the real table.
+// ---- P1: stream 0 at every STRIDE-th plane position -------------------------------------------------
+// Sampled positions are the multiples of STRIDE in plane coordinates (a record is contiguous in the planes, so
+// any 500 consecutive positions of a record hold at least floor(500/STRIDE) of them).  The 32 MiB level-3
+// summary (1 bit per 16 slots, table.cu) answers most probes of an absent reference from L2; only a set
+// summary bit costs the DRAM sector of the real table.  Bit q of sample_hits[w] = q-th sampled position of word w.
+template <int STRIDE>
 __global__ void __launch_bounds__(256)
 k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const uint32_t* __restrict__ summary,
                 uint8_t* __restrict__ sample_hits)
 {
+    constexpr int NS = (32 + STRIDE - 1) / STRIDE;       // sampled positions per word, at most
     uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= pl.nwords) return;
     const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
+    const int first = (int)((STRIDE - (int)((w * 32) % STRIDE)) % STRIDE);
     uint32_t out = 0;
-    if (vm & 0x88888888u) {
+    if (vm) {
         const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
-        uint32_t code[8];
+        uint32_t code[NS];
 #pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const int s = q * SAMPLE_STRIDE;
-            WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
-            code[q] = ((vm >> (31 - s)) & 1u) ? stream_code(m, b, 0) : 0u;
+        for (int q = 0; q < NS; q++) {
+            const int s = first + q * STRIDE;
+            code[q] = 0u;
+            if (s < 32 && ((vm >> (31 - s)) & 1u)) {
+                WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                code[q] = stream_code(m, b, 0);
+            }
         }
-        uint32_t maybe = 0;                          // first the summary (L2), all eight loads in flight
+        uint32_t maybe = 0;                          // first the summary (L2), all loads in flight
 #pragma unroll
-        for (int q = 0; q < 8; q++)
-            maybe |= (code[q] ? (__ldg(summary + (code[q] >> 9)) >> ((code[q] >> 4) & 31)) & 1u : 0u) << (7 - q);
+        for (int q = 0; q < NS; q++)
+            maybe |= (code[q] ? (__ldg(summary + (code[q] >> 9)) >> ((code[q] >> 4) & 31)) & 1u : 0u) << q;
 #pragma unroll
-        for (int q = 0; q < 8; q++)
-            if ((maybe >> (7 - q)) & 1u) out |= ((__ldg(bm3 + (code[q] >> 5)) >> (code[q] & 31)) & 1u) << (7 - q);
+        for (int q = 0; q < NS; q++)
+            if ((maybe >> q) & 1u) out |= ((__ldg(bm3 + (code[q] >> 5)) >> (code[q] & 31)) & 1u) << q;
     }
     sample_hits[w] = (uint8_t)out;
 }
 
 // ---- P2: candidate words and the words they depend on --------------------------------------------
-// cand[w]: the sampled hits in words w-16..w (a superset of every window ending in word w) reach
-// min_sample_hits = three_min - (500 - 125).
-__global__ void k_candidates(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ word_genome,
-                             const uint32_t* __restrict__ g_word, uint64_t nwords, int min_sample_hits,
-                             uint8_t* __restrict__ cand)
+// cand[w]: the sampled hits in words w-16..w of the record (a superset of every window ending in word w)
+// reach min_sample_hits = three_min - (500 - 125).  need[w]: some word in w..w+16 of the same record is a
+// candidate, i.e. a position of word w lies inside a window that may be good.  One CTA produces need[] for
+// NEED_TILE words from a halo of 16 words on either side; both sliding sums are differences of block-wide
+// prefix sums.
+constexpr int NEED_TILE = 256;
+constexpr int NEED_THREADS = NEED_TILE + 2 * WIN_WORDS;      // one thread per word of tile + halo (9 warps)
+
+__device__ __forceinline__ uint32_t block_inclusive_scan_288(uint32_t v, uint32_t* s_warp)
 {
-    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= nwords) return;
-    const uint64_t gs = g_word[word_genome[w]];
-    int c = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
 #pragma unroll
-    for (int k = 0; k <= WIN_WORDS; k++)
-        if (w >= gs + k) c += __popc((uint32_t)sample_hits[w - k]);
-    cand[w] = c >= min_sample_hits;
+    for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+#pragma unroll
+    for (int k = 0; k < NEED_THREADS / 32; k++) if (k < warp) base += s_warp[k];
+    __syncthreads();
+    return base + inc;
 }
 
-// need[w]: some word in w..w+16 of the same record is a candidate, i.e. a position of word w lies
-// inside a window that may be good.
-__global__ void k_need(const uint8_t* __restrict__ cand, const uint32_t* __restrict__ word_genome,
-                       uint64_t nwords, uint8_t* __restrict__ need, unsigned long long* __restrict__ need_count)
+__global__ void __launch_bounds__(NEED_THREADS)
+k_need(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ word_genome,
+       const uint32_t* __restrict__ g_word, uint64_t nwords, int min_sample_hits, uint8_t* __restrict__ need,
+       unsigned long long* __restrict__ need_count)
 {
-    uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t v = 0;
-    if (w < nwords) {
+    __shared__ uint32_t s_P[NEED_THREADS + 1], s_C[NEED_THREADS + 1], s_warp[NEED_THREADS / 32];
+    const int e = threadIdx.x;
+    const int64_t first = (int64_t)blockIdx.x * NEED_TILE - WIN_WORDS;          // word of entry 0
+    const int64_t w = first + e;
+    const bool valid = w >= 0 && (uint64_t)w < nwords;
+    uint32_t pop = 0;
+    int64_t gs = 0, ge = 0;
+    if (valid) {
+        pop = __popc((uint32_t)sample_hits[w]);
         const uint32_t g = word_genome[w];
-#pragma unroll
-        for (int k = 0; k <= WIN_WORDS; k++)
-            if (w + k < nwords && word_genome[w + k] == g) v |= cand[w + k];
+        gs = g_word[g]; ge = g_word[g + 1];
+    }
+    const uint32_t P = block_inclusive_scan_288(pop, s_warp);
+    s_P[e + 1] = P;
+    if (e == 0) { s_P[0] = 0; s_C[0] = 0; }
+    __syncthreads();
+    uint32_t cand = 0;
+    if (valid && e >= WIN_WORDS) {
+        const int64_t lo = max(w - WIN_WORDS, gs);                              // first word of the look-back, inside the record
+        cand = (int)(P - s_P[lo - first]) >= min_sample_hits;
+    }
+    const uint32_t C = block_inclusive_scan_288(cand, s_warp);
+    s_C[e + 1] = C;
+    __syncthreads();
+    uint32_t v = 0;
+    if (valid && e >= WIN_WORDS && e < WIN_WORDS + NEED_TILE) {
+        const int64_t hi = min(w + WIN_WORDS, ge - 1);                          // last word of the look-ahead, inside the record
+        v = s_C[hi - first + 1] - s_C[e] > 0;
         need[w] = (uint8_t)v;
     }
-    uint32_t b = __ballot_sync(0xffffffffu, v != 0);
+    const uint32_t b = __ballot_sync(0xffffffffu, v != 0);
     if ((threadIdx.x & 31) == 0 && b) atomicAdd(need_count, (unsigned long long)__popc(b));
 }
 
@@ -252,28 +288,28 @@ __global__ void k_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uin
 
 static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
 
-cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary,
+cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary, int stride,
                                  uint8_t* sample_hits, cudaStream_t st)
 {
     if (!pl.nwords) return cudaSuccess;
-    k_probe_sampled<<<grid_for(pl.nwords, 256), 256, 0, st>>>(pl, m, bm3, summary, sample_hits);
+    const unsigned grid = grid_for(pl.nwords, 256);
+    switch (stride) {
+    case 4: k_probe_sampled<4><<<grid, 256, 0, st>>>(pl, m, bm3, summary, sample_hits); break;
+    case 5: k_probe_sampled<5><<<grid, 256, 0, st>>>(pl, m, bm3, summary, sample_hits); break;
+    case 6: k_probe_sampled<6><<<grid, 256, 0, st>>>(pl, m, bm3, summary, sample_hits); break;
+    case 7: k_probe_sampled<7><<<grid, 256, 0, st>>>(pl, m, bm3, summary, sample_hits); break;
+    case 8: k_probe_sampled<8><<<grid, 256, 0, st>>>(pl, m, bm3, summary, sample_hits); break;
+    default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
 }
 
-cudaError_t launch_candidates(const uint8_t* sample_hits, const uint32_t* word_genome, const uint32_t* g_word,
-                              uint64_t nwords, int min_sample_hits, uint8_t* cand, cudaStream_t st)
+cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, const uint32_t* g_word, uint64_t nwords,
+                        int min_sample_hits, uint8_t* need, unsigned long long* need_count, cudaStream_t st)
 {
     if (!nwords) return cudaSuccess;
-    k_candidates<<<grid_for(nwords, 256), 256, 0, st>>>(sample_hits, word_genome, g_word, nwords,
-                                                        min_sample_hits, cand);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_need(const uint8_t* cand, const uint32_t* word_genome, uint64_t nwords, uint8_t* need,
-                        unsigned long long* need_count, cudaStream_t st)
-{
-    if (!nwords) return cudaSuccess;
-    k_need<<<grid_for(nwords, 256), 256, 0, st>>>(cand, word_genome, nwords, need, need_count);
+    k_need<<<grid_for(nwords, NEED_TILE), NEED_THREADS, 0, st>>>(sample_hits, word_genome, g_word, nwords, min_sample_hits,
+                                                              need, need_count);
     return cudaGetLastError();
 }
 

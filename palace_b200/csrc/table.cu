@@ -85,12 +85,14 @@ __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks
 // P0: histogram of the codes of one file over the NSLICES table slices (top 13 code bits).  Persistent grid:
 // a CTA accumulates in shared memory over all its tiles and flushes once.
 __global__ void __launch_bounds__(256)
-k_slice_hist(Planes pl, CoderMasks m, unsigned long long* __restrict__ g_hist)
+k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, CoderMasks m,
+             unsigned long long* __restrict__ g_hist)
 {
     __shared__ uint32_t s_hist[NSLICES];
     for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
-    for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < pl.nwords; w += (uint64_t)gridDim.x * blockDim.x)
+    const uint64_t nwords = (*plane_bits + 31) >> 5;      // the host has not seen the packed size yet
+    for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += (uint64_t)gridDim.x * blockDim.x)
         for_each_code(pl, m, w, [&](uint32_t code) { atomicAdd(&s_hist[code >> SLICE_BITS], 1u); });
     __syncthreads();
     for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) {
@@ -398,11 +400,10 @@ cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t*
     return cudaGetLastError();
 }
 
-cudaError_t launch_slice_hist(Planes pl, CoderMasks m, unsigned long long* g_hist, cudaStream_t st)
+cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, CoderMasks m, unsigned long long* g_hist,
+                              cudaStream_t st)
 {
-    if (!pl.nwords) return cudaSuccess;
-    const uint64_t want = (pl.nwords + 255) / 256;
-    k_slice_hist<<<(unsigned)(want < 148 * 6 ? want : 148 * 6), 256, 0, st>>>(pl, m, g_hist);
+    k_slice_hist<<<148 * 6, 256, 0, st>>>(pl, plane_bits, m, g_hist);
     return cudaGetLastError();
 }
 
