@@ -41,10 +41,9 @@ WORKLOAD_DESC = {
     "c1": "BASELINE configs[0]: 5 Mbp reads vs 1,000-genome ~50 Mbp synthetic phage DB per GPU",
     "small": "development: 2 Mbp reads vs 400-genome 20 Mbp DB per GPU",
 }
-# algorithmic bytes per unit (restated in DESIGN.md)
+# algorithmic bytes per unit (restated in DESIGN.md §8)
 BYTES_PER_REF_BASE_FULL = 97.0        # 1 B text + 3 probes x 32 B sector
 BYTES_PER_QUERY_BASE_BUILD = 193.0    # 1 B text + 3 codes x (32 B sector fill + 32 B write-back)
-BYTES_PER_REF_BASE_SAMPLED = 0.375 + 8.0 + 1.0 / 32   # planes + one 32 B sector per 4 positions + 1 B/word out
 
 
 def peaks():
@@ -119,13 +118,32 @@ def gather_bytes(t_local, world, device):
 QUERY_PHASES = ("query_pack_ms", "query_bucket_ms", "query_count_ms")
 PHASES = QUERY_PHASES + ("ref_frame_ms", "ref_pack_ms", "scan_summary_ms", "scan_sample_ms", "scan_cand_ms",
                          "scan_probe_ms", "scan_window_ms", "scan_interval_ms")
-PHASE_KERNEL = {
-    "query_pack_ms": "k_count_newlines+k_pack_fastq", "query_bucket_ms": "k_bucket_codes<hist>+<scatter>",
-    "query_count_ms": "k_zero_slices+k_count_codes (32 buckets)", "scan_summary_ms": "k_build_summary",
-    "ref_frame_ms": "FASTA framing kernels + scans", "ref_pack_ms": "k_pack_fasta",
-    "scan_sample_ms": "k_probe_sampled", "scan_cand_ms": "k_candidates+k_need", "scan_probe_ms": "k_probe_full",
-    "scan_window_ms": "k_window", "scan_interval_ms": "k_intervals",
+# kernels of each phase (names as ncu prints them) and how often each runs per step
+PHASE_KERNELS = {
+    "query_pack_ms": (("k_count_newlines", 2), ("k_fastq_kept", 2), ("k_pack_fastq", 2)),
+    "query_bucket_ms": (("k_slice_hist", 2), ("k_slice_offsets", 2), ("k_coarse_scatter", 2), ("k_fine_partition", 2)),
+    "query_count_ms": (("k_count_slices", 1),),
+    "ref_frame_ms": (("k_fasta_tiles", 1), ("k_fasta_records", 1), ("k_record_info", 1), ("k_genome_table", 1)),
+    "ref_pack_ms": (("k_pack_fasta", 1),),
+    "scan_summary_ms": (("k_build_summary", 0),),
+    "scan_sample_ms": (("k_probe_sampled", 1),),
+    "scan_cand_ms": (("k_need", 1),),
+    "scan_probe_ms": (("k_probe_full", 1),),
+    "scan_window_ms": (("k_window", 1),),
+    "scan_interval_ms": (("k_intervals", 1),),
 }
+
+
+def ncu_traffic(phase):
+    """DRAM bytes per step of a phase's kernels from the committed `ncu --set full` capture (profiles/), or None"""
+    p = os.path.join(ROOT, "profiles", "ncu_kernels_r01.json")
+    if not os.path.exists(p):
+        return None
+    try:
+        k = json.load(open(p))["kernels"]
+        return int(sum(k[name]["dram_bytes_per_launch"] * times for name, times in PHASE_KERNELS[phase] if times))
+    except Exception:
+        return None
 
 
 def run_b200(args):
@@ -147,7 +165,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
 
     fa_np, f1_np, f2_np, shard_bases = gen_inputs(args.workload, rank, world)
-    stream = torch.cuda.Stream(device=dev)
+    stream = torch.cuda.Stream(device=dev)             # the library launches on this stream: its events time the step
     with torch.cuda.stream(stream):
         fa_h = torch.from_numpy(fa_np).pin_memory()
         fa_d = fa_h.to(dev, non_blocking=True)
@@ -269,16 +287,20 @@ def run_b200(args):
     avg = {p: acc[p] / args.steps for p in PHASES}
     dom = max(avg, key=avg.get)
     qbases = info["seq_bytes"]
+    ntext_q = f1_d.numel() + f2_d.numel()
+    codes = info["query_codes"]
+    stride = int(os.environ.get("EREF_SAMPLE_STRIDE", "6"))
     alg = {
-        "query_count_ms": BYTES_PER_QUERY_BASE_BUILD * qbases,
-        "query_bucket_ms": 2 * 0.375 * (f1_d.numel() + f2_d.numel()) + 4.0 * info["query_codes"],
-        "scan_summary_ms": 4.0 * (1 << 27) + 4.0 * (1 << 23),
-        "query_pack_ms": 2.0 * (f1_d.numel() + f2_d.numel()),
+        # bytes the phase's kernels must move given this design, per step
+        "query_pack_ms": 3.0 * ntext_q + 0.375 * qbases,                       # census, kept, pack read the text; planes written
+        "query_bucket_ms": 2 * 0.375 * qbases + 12.0 * codes,                  # planes read twice; codes written, read, written
+        "query_count_ms": 4.0 * codes + 4.0 * (1 << 27) + 4.0 * (1 << 23),     # codes read; level 3 + summary written
+        "ref_frame_ms": 1.0 * fa_d.numel(),
+        "ref_pack_ms": 1.0 * fa_d.numel() + (0.375 + 0.125) * info["ref_bases"],
+        "scan_sample_ms": (0.375 + 32.0 / stride + 1.0 / 32) * info["ref_bases"],
+        "scan_cand_ms": (1 + 4 + 1) / 32.0 * info["ref_bases"],
         "scan_probe_ms": BYTES_PER_REF_BASE_FULL * info["ref_bases"] if args.no_prune else
         (96.0 + 0.625) * 32 * info["need_words"],
-        "scan_sample_ms": BYTES_PER_REF_BASE_SAMPLED * info["ref_bases"],
-        "ref_pack_ms": 1.0 * fa_d.numel() + 0.5 * info["ref_bases"],
-        "ref_frame_ms": 2.0 * fa_d.numel(),
     }.get(dom, 0.0)
     achieved = alg / 1e9 / (avg[dom] / 1e3) if avg[dom] > 0 else 0.0
     scan_ms = sum(avg[p] for p in PHASES if p.startswith("scan_"))
@@ -299,11 +321,19 @@ def run_b200(args):
         "clocks": clocks,
         "phases_ms": {k: round(v, 4) for k, v in avg.items()},
         "scan_only": {"ms": round(scan_ms, 4), "value": round(info["ref_bases"] / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT,
-                      "frac_of_hbm_at_97B_per_base": round(BYTES_PER_REF_BASE_FULL * info["ref_bases"] / 1e9 /
-                                                           (scan_ms / 1e3) / peak, 3)},
-        "roofline": {"bound": "hbm", "kernel": PHASE_KERNEL[dom], "achieved": round(achieved, 1), "peak": peak,
-                     "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4)},
+                      "need_word_fraction": round(info["need_words"] / max(info["ref_words"], 1), 4)},
+        "roofline": {"bound": "hbm", "kernel": "+".join(n for n, _ in PHASE_KERNELS[dom]), "phase": dom,
+                     "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "traffic": ncu_traffic(dom), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4),
+                     "note": "per step, all launches of the phase; the table build (query_count) runs beside ref_frame, "
+                             "so the phase times add up to more than ms_per_step"},
+        "survey_8d": {"table_build": {"bytes_per_query_base": BYTES_PER_QUERY_BASE_BUILD,
+                                      "ms": round(sum(avg[p] for p in QUERY_PHASES), 4),
+                                      "frac_of_hbm": round(BYTES_PER_QUERY_BASE_BUILD * qbases / 1e9 /
+                                                           (sum(avg[p] for p in QUERY_PHASES) / 1e3) / peak, 3)},
+                      "scan": {"bytes_per_ref_base": BYTES_PER_REF_BASE_FULL, "ms": round(scan_ms, 4),
+                               "frac_of_hbm": round(BYTES_PER_REF_BASE_FULL * info["ref_bases"] / 1e9 / (scan_ms / 1e3) / peak, 3)}},
     }
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(budget_runs=1)

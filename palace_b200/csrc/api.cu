@@ -777,9 +777,12 @@ int eref_scan_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
     CUDA_TRY(cudaSetDevice(c->device));
     int rc = scan_impl(c);
     if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     table_done(c);
     scan_times(c, false);
+    c->t.ref_need_words = (!(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / c->sample_stride) > 0)
+                              ? c->h_pin[6] : c->ref_words;
     *results_dev = c->results.as<uint32_t>();
     if (n_out) *n_out = c->n_genomes;
     return 0;

@@ -227,3 +227,111 @@ def test_eref_binary_end_to_end(golden, tmp_path):
             assert r.returncode == 0, r.stderr.decode()
             assert r.stdout.decode() == expect, f"{name} {key} gpus={gpus}"
             assert (tmp_path / "tmp_out.txt").exists() and (tmp_path / "tmp_out.txt").stat().st_size == 0
+
+
+# ---- framing stress: line / record / tile boundaries in every position ----------------------------
+
+def _adversarial_fasta(rng, n_records, big=False):
+    """Records with random line widths (empty lines, lines longer than an 8 KiB tile, CRLF), headers of any
+    length (also longer than a tile), records of 0..40 bases around the len > 32 rule, '>' inside lines,
+    lower case, N and junk bytes, optional missing final newline and leading header-less sequence."""
+    alphabet = np.frombuffer(b"ACGTACGTACGTACGTacgtNn>-\r *", np.uint8)
+    parts = []
+    if rng.random() < 0.5:
+        parts.append(bytes(rng.choice(alphabet[:16], int(rng.integers(1, 200)))) + b"\n")    # record 0: no header
+    for r in range(n_records):
+        kind = rng.random()
+        hdr_len = int(rng.integers(0, 30)) if kind < 0.9 else int(rng.integers(8000, 20000))
+        parts.append(b">" + bytes(rng.choice(alphabet[:20], hdr_len)).replace(b"\n", b"") + b"\n")
+        u = rng.random()
+        if u < 0.25:
+            length = int(rng.integers(0, 70))
+        elif u < 0.9 or not big:
+            length = int(rng.integers(70, 3000))
+        else:
+            length = int(rng.integers(9000, 40000))
+        seq = rng.choice(alphabet if rng.random() < 0.3 else alphabet[:16], length)
+        seq = bytes(seq).replace(b"\n", b"")
+        pos = 0
+        while pos < len(seq):
+            w = int(rng.choice([1, 2, 31, 32, 33, 60, 70, 80, 255, 256, 257, 9000])) if rng.random() < 0.5 else 70
+            line = seq[pos:pos + w]
+            if line[:1] == b">":                      # a sequence line must not start with '>' (it would be a header)
+                line = b"A" + line[1:]
+            parts.append(line + (b"\r\n" if rng.random() < 0.05 else b"\n"))
+            pos += w
+            if rng.random() < 0.05:
+                parts.append(b"\n")
+    text = b"".join(parts)
+    if rng.random() < 0.5 and text.endswith(b"\n"):
+        text = text[:-1]
+    return np.frombuffer(text, np.uint8)
+
+
+@pytest.mark.parametrize("seed", [101, 102, 103, 104, 105, 106])
+def test_fasta_framing_stress(oracle, seed):
+    """records, lengths, ordinals and every code of every kept record == the oracle's getline framing (:686-756)"""
+    rng = np.random.default_rng(seed)
+    fa = _adversarial_fasta(rng, int(rng.integers(5, 400)), big=seed % 2 == 0)
+    coder = eref.random_coder(seed)
+    seqs, n_records = oracle.parse_fasta(fa)
+    with eref.ErefGPU(coder) as g:
+        g.ref_set(fa)
+        kept, recs, bases = g.ref_count()
+        assert kept == len(seqs)
+        assert bases == sum(len(s) for s in seqs)
+        raw = fa.tobytes()
+        for i in rng.permutation(len(seqs))[:60]:
+            off, hl, ln = g.ref_record(int(i) + 1)
+            assert ln == len(seqs[i])
+            if hl or off:
+                assert raw[off:off + 1] == b">" and b"\n" not in raw[off:off + hl]
+                assert off + hl == len(raw) or raw[off + hl:off + hl + 1] == b"\n"
+            want = oracle.record_codes(coder, seqs[i])
+            got = g.get_codes(int(i) + 1)
+            assert got.size == want.size and (got == want).all(), f"record {i}"
+
+
+def test_fasta_many_tiny_records_fill_a_tile(oracle):
+    """33-base records with 2-byte headers: the densest packing of plane words per text tile (ring bound)"""
+    rng = np.random.default_rng(7)
+    recs = [b">\n" + bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), 33)) + b"\n" for _ in range(3000)]
+    fa = np.frombuffer(b"".join(recs), np.uint8)
+    coder = eref.random_coder(9)
+    seqs, _ = oracle.parse_fasta(fa)
+    with eref.ErefGPU(coder) as g:
+        g.ref_set(fa)
+        assert g.ref_count()[0] == 3000 == len(seqs)
+        for i in (0, 1, 226, 227, 228, 1499, 2999):
+            assert (g.get_codes(i + 1) == oracle.record_codes(coder, seqs[i])).all()
+
+
+@pytest.mark.parametrize("seed", [201, 202, 203])
+def test_fastq_framing_stress(oracle, seed):
+    """FASTQ texts with empty lines, very long lines, CRLF and a missing final newline: the sequence-line byte
+    sum (:1138-1140) and the table levels equal an independent count over the lines with index % 4 == 1"""
+    import collections
+    rng = np.random.default_rng(seed)
+    alphabet = np.frombuffer(b"ACGTACGTACGTACGTacgtN", np.uint8)
+    lines = []
+    for _ in range(int(rng.integers(50, 1500))):
+        u = rng.random()
+        n = 0 if u < 0.1 else int(rng.integers(1, 400)) if u < 0.95 else int(rng.integers(8000, 30000))
+        lines.append(bytes(rng.choice(alphabet, n)) + (b"\r" if rng.random() < 0.03 else b""))
+    text = b"\n".join(lines) + (b"\n" if rng.random() < 0.5 else b"")
+    fq = np.frombuffer(text, np.uint8)
+    coder = eref.random_coder(seed)
+    cnt = collections.Counter()
+    seq_lines = text.split(b"\n")[1::4]
+    for s in seq_lines:
+        if len(s) >= 32:
+            c = oracle.record_codes(coder, s).reshape(-1, 3)
+            cnt.update(c[c.any(axis=1)].ravel().tolist())
+    with eref.ErefGPU(coder) as g:
+        assert g.query_add(fq) == sum(len(s) for s in seq_lines) == oracle.fastq_seq_bytes(fq)
+        for level in (1, 2, 3):
+            assert g.query_popcount(level) == sum(1 for v in cnt.values() if v >= level)
+        # the same file again: every count doubles
+        g.query_add(fq)
+        for level in (1, 2, 3):
+            assert g.query_popcount(level) == sum(1 for v in cnt.values() if 2 * v >= level)
