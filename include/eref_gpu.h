@@ -103,6 +103,17 @@ int  eref_get_codes(eref_ctx* ctx, uint32_t ordinal, uint32_t* codes_host, size_
 /* name offset/length of a kept record's header line inside the text given to eref_ref_set* */
 int  eref_ref_record(eref_ctx* ctx, uint32_t ordinal, uint64_t* hdr_off, uint32_t* hdr_len, uint32_t* len);
 
+/* every record of the current reference text in file order (kept or not; record 0 = whatever precedes the first
+ * header): its length (:694) and the offset of its header line (0xFFFFFFFF for record 0).  Writes min(cap, n)
+ * entries; *n_out = n.  With these a host writes <db>.genome.len.txt (:697, :800). */
+int  eref_ref_records(eref_ctx* ctx, uint32_t* len_out, uint32_t* hdr_off_out, size_t cap, size_t* n_out);
+/* the body of <db>.k32.index.dat (:698, :711-738) for as many whole kept records as fit into cap_words,
+ * starting at ordinal first (1-based): per record one word with its length, then 3 codes per window start
+ * (0 = invalid window).  *n_words = words written, *next = ordinal to continue with (n_kept + 1 at the end).
+ * A host streams the chunks to disk behind the 400-byte coder header to share a DB directory with the CPU
+ * eref. */
+int  eref_index_body(eref_ctx* ctx, uint32_t first, uint32_t* out_host, size_t cap_words, size_t* n_words, uint32_t* next);
+
 /* table inspection (tests): number of codes with count >= level (1..3) */
 int  eref_query_popcount(eref_ctx* ctx, int level, uint64_t* out);
 

@@ -97,6 +97,9 @@ struct eref_ctx {
     uint32_t n_recs = 0, n_genomes = 0;
     uint64_t ref_words = 0, ref_bases = 0;
     std::vector<uint32_t> h_g_len, h_g_word, h_g_rec, h_rec_hdr_off;
+    std::vector<unsigned long long> h_cell_pre;
+    DevBuf cell_pre;
+    bool cell_pre_valid = false;
     eref_phase_times t{};
     uint64_t launches = 0;
 };
@@ -376,6 +379,7 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     const uint64_t bases = c->h_pin[2];
     const uint32_t n_genomes = (uint32_t)c->h_pin[3], n_words = (uint32_t)c->h_pin[4];
     c->host_tables_valid = false;             // ordinal -> length / packed offset / header offset: fetched on demand
+    c->cell_pre_valid = false;
     c->ref_text_dev = text; c->ref_text_n = n;
     c->n_recs = n_recs; c->n_genomes = n_genomes;
     c->ref_words = n_words; c->ref_bases = bases;
@@ -541,7 +545,7 @@ void eref_destroy(eref_ctx* c)
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
                       &c->g_len, &c->g_word, &c->g_first, &c->r_hi, &c->r_lo, &c->r_ok, &c->word_genome,
                       &c->sample_hits, &c->cand, &c->need, &c->single, &c->trio, &c->good, &c->results,
-                      &c->codes_tmp};
+                      &c->codes_tmp, &c->cell_pre};
     for (DevBuf* b : bufs) b->release();
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
     if (c->summary) cudaFree(c->summary);
@@ -838,6 +842,60 @@ int eref_ref_record(eref_ctx* c, uint32_t ordinal, uint64_t* hdr_off, uint32_t* 
     }
     if (hdr_off) *hdr_off = off;
     if (hdr_len) *hdr_len = hl;
+    return 0;
+}
+
+int eref_ref_records(eref_ctx* c, uint32_t* len_out, uint32_t* hdr_off_out, size_t cap, size_t* n_out)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
+    CUDA_TRY(cudaSetDevice(c->device));
+    const size_t n = c->n_recs < cap ? c->n_recs : cap;
+    if (n && len_out) CUDA_TRY(cudaMemcpy(len_out, c->rec_len.p, n * 4, cudaMemcpyDeviceToHost));
+    if (n && hdr_off_out) CUDA_TRY(cudaMemcpy(hdr_off_out, c->rec_hdr_off.p, n * 4, cudaMemcpyDeviceToHost));
+    if (n_out) *n_out = c->n_recs;
+    return 0;
+}
+
+int eref_index_body(eref_ctx* c, uint32_t first, uint32_t* out_host, size_t cap_words, size_t* n_words, uint32_t* next)
+{
+    if (!c || !out_host || !n_words || !next) return eref_fail(EREF_ERR_ARG, "eref_index_body: null argument");
+    if (!c->have_ref) return eref_fail(EREF_ERR_STATE, "no reference set");
+    if (first < 1 || first > c->n_genomes + 1) return eref_fail(EREF_ERR_ARG, "ordinal %u of %u", first, c->n_genomes);
+    CUDA_TRY(cudaSetDevice(c->device));
+    int hrc = fetch_host_tables(c);
+    if (hrc) return hrc;
+    const uint32_t G = c->n_genomes;
+    if (!c->cell_pre_valid) {                             // cells (length word + window starts) before each kept record
+        c->h_cell_pre.assign((size_t)G + 1, 0);
+        for (uint32_t g = 0; g < G; g++) c->h_cell_pre[g + 1] = c->h_cell_pre[g] + (c->h_g_len[g] - (EREF_K - 2));
+        CUDA_TRY(c->cell_pre.ensure(((size_t)G + 1) * 8));
+        CUDA_TRY(cudaMemcpy(c->cell_pre.p, c->h_cell_pre.data(), ((size_t)G + 1) * 8, cudaMemcpyHostToDevice));
+        c->cell_pre_valid = true;
+    }
+    uint32_t g0 = first - 1, g1 = g0;
+    size_t words = 0;
+    while (g1 < G) {
+        const size_t w = 1 + 3 * (size_t)(c->h_g_len[g1] - (EREF_K - 1));
+        if (words + w > cap_words) break;
+        words += w; g1++;
+    }
+    if (g1 == g0 && g0 < G)
+        return eref_fail(EREF_ERR_LIMIT, "record %u needs %zu words, the buffer holds %zu", first,
+                         1 + 3 * (size_t)(c->h_g_len[g0] - (EREF_K - 1)), cap_words);
+    if (words) {
+        CUDA_TRY(c->codes_tmp.ensure(words * 4));
+        Planes pl;
+        pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
+        pl.nwords = c->ref_words;
+        LAUNCH(c, launch_index_body(pl, c->masks, c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(),
+                                    c->cell_pre.as<unsigned long long>(), g0, g1, c->h_cell_pre[g1] - c->h_cell_pre[g0],
+                                    c->codes_tmp.as<uint32_t>(), c->stream));
+        CUDA_TRY(cudaMemcpyAsync(out_host, c->codes_tmp.p, words * 4, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    *n_words = words;
+    *next = g1 + 1;
     return 0;
 }
 

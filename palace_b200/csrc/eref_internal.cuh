@@ -185,3 +185,6 @@ cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const
                              uint32_t n_genomes, uint32_t* results, cudaStream_t st);
 cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,
                                 uint32_t* codes, cudaStream_t st);
+cudaError_t launch_index_body(Planes pl, CoderMasks m, const uint32_t* g_word, const uint32_t* g_len,
+                              const unsigned long long* cell_pre, uint32_t g0, uint32_t g1, unsigned long long ncells,
+                              uint32_t* out, cudaStream_t st);

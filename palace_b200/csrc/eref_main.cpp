@@ -12,6 +12,8 @@
 //   EREF_NO_PRUNE=1     probe all three streams everywhere (disables the exact candidate filter)
 //   EREF_DIRECT_COUNT=1 count k-mers straight into the table (disables the code-range bucketing)
 //   EREF_TIMING=1       per-phase CUDA-event times on stderr
+//   EREF_WRITE_INDEX=1  also write <db>.k32.index.dat + <db>.genome.len.txt in the reference's format (when absent),
+//                       so that a CPU eref can share the DB directory (12 bytes per base: off by default)
 #include "eref_gpu.h"
 #include <cuda_runtime.h>
 #include <nccl.h>
@@ -116,6 +118,75 @@ std::vector<size_t> shard_offsets(const char* fa, size_t n, int shards)
     }
     cut.push_back(n);
     return cut;
+}
+
+// get_read_ID(line).substr(1) (:246-254, :689): the header up to the first '/', ' ' or tab, without '>'
+std::string record_name(const char* p, size_t n)
+{
+    size_t e = n;
+    for (char d : {'/', ' ', '\t'}) {
+        const void* q = memchr(p, d, e);
+        if (q) e = (size_t)((const char*)q - p);
+    }
+    return e > 1 ? std::string(p + 1, e - 1) : std::string();
+}
+
+// <db>.k32.index.dat (400-byte coder header :680-682, then per kept record its length and
+// 3 codes per window start :698, :711-738) and <db>.genome.len.txt (:697, :800), produced on GPU 0 shard by shard.
+bool write_index_files(const std::string& index_name, const std::string& len_name, const char* fa, size_t n,
+                       const int16_t coder[96], std::string& err)
+{
+    const std::string tmp = index_name + ".part";
+    FILE* fi = fopen(tmp.c_str(), "wb");
+    FILE* fl = fopen(len_name.c_str(), "w");
+    if (!fi || !fl) { err = "cannot create " + (fi ? len_name : tmp); if (fi) fclose(fi); if (fl) fclose(fl); return false; }
+    uint32_t hdr[100] = {0};
+    for (int j = 0; j < 96; j++) hdr[j] = (uint32_t)(uint16_t)coder[j] | (j < 95 ? (uint32_t)(uint16_t)coder[j + 1] << 16 : 0u);
+    bool ok = fwrite(hdr, 4, 100, fi) == 100;
+    eref_ctx* ctx = nullptr;
+    if (ok && eref_create(&ctx, 0, coder, 0.9f, 0.85f, 0)) { err = std::string("eref_create: ") + eref_last_error(); ok = false; }
+    const int shards = (int)(n >> 30) + 1;               // every piece stays far below the 4 GiB shard limit
+    std::vector<size_t> cut = shard_offsets(fa, n, shards);
+    const size_t cap = (size_t)1 << 26;                  // 256 MiB of body per round trip
+    std::vector<uint32_t> buf(cap), rlen, roff;
+    unsigned long long run = 0, hdrs_before = 0;
+    for (int s = 0; ok && s < shards; s++) {
+        const char* text = fa + cut[s];
+        const size_t len = cut[s + 1] - cut[s];
+        if (eref_ref_set(ctx, text, len)) { err = std::string("eref_ref_set: ") + eref_last_error(); ok = false; break; }
+        size_t kept = 0, nrec = 0;
+        eref_ref_count(ctx, &kept, &nrec, nullptr);
+        uint32_t first = 1;
+        while (ok && first <= kept) {
+            size_t nw = 0; uint32_t next = first;
+            int rc = eref_index_body(ctx, first, buf.data(), buf.size(), &nw, &next);
+            if (rc == EREF_ERR_LIMIT && buf.size() < ((size_t)1 << 31)) { buf.resize(buf.size() * 4); continue; }
+            if (rc) { err = std::string("eref_index_body: ") + eref_last_error(); ok = false; break; }
+            ok = fwrite(buf.data(), 4, nw, fi) == nw;
+            if (!ok) err = "short write on " + tmp;
+            first = next;
+        }
+        rlen.resize(nrec); roff.resize(nrec);
+        if (ok && eref_ref_records(ctx, rlen.data(), roff.data(), nrec, &nrec)) { err = eref_last_error(); ok = false; }
+        for (size_t r = 0; ok && r < nrec; r++) {
+            run += rlen[r];
+            if (rlen[r] <= (uint32_t)EREF_K) continue;
+            std::string name = "start";
+            if (r > 0) {
+                const char* h = text + roff[r];
+                const void* nl = memchr(h, '\n', len - roff[r]);
+                name = record_name(h, nl ? (size_t)((const char*)nl - h) : len - roff[r]);
+            }
+            fprintf(fl, "%s\t%llu\t%u\t%llu\n", name.c_str(), hdrs_before + r, rlen[r], run);
+        }
+        hdrs_before += nrec ? nrec - 1 : 0;
+    }
+    if (ctx) eref_destroy(ctx);
+    ok = (fclose(fi) == 0) && ok;
+    ok = (fclose(fl) == 0) && ok;
+    if (ok && rename(tmp.c_str(), index_name.c_str()) != 0) { err = "cannot rename " + tmp; ok = false; }
+    if (!ok) remove(tmp.c_str());
+    return ok;
 }
 
 struct Barrier {
@@ -312,6 +383,12 @@ int main(int argc, char** argv)
         done += (size_t)w;
     }
     close(result_fd);
+
+    if (getenv("EREF_WRITE_INDEX") && access(index_name.c_str(), F_OK) != 0) {
+        std::string werr;
+        if (!write_index_files(index_name, fasta + ".genome.len.txt", fa.p, fa.n, coder, werr))
+            fprintf(stderr, "eref: warning: index not written: %s\n", werr.c_str());   // the results above stand
+    }
 
     if (timing) {
         auto t_end = std::chrono::steady_clock::now();

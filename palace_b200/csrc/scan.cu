@@ -284,6 +284,32 @@ __global__ void k_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uin
     for (int i = 0; i < 3; i++) codes[(size_t)j * 3 + i] = v ? stream_code(m, b, i) : 0u;
 }
 
+// ---- index body of a run of records, in the layout of <db>.k32.index.dat (:698, :711-738) -----------
+// Per kept record: one word holding its length, then 3 codes per window start.  A "cell" is the length word
+// or one window start; cell_pre[g] = cells of the records before g.  One thread per cell.
+__global__ void __launch_bounds__(256)
+k_index_body(Planes pl, CoderMasks m, const uint32_t* __restrict__ g_word, const uint32_t* __restrict__ g_len,
+             const unsigned long long* __restrict__ cell_pre, uint32_t g0, uint32_t g1, unsigned long long ncells,
+             uint32_t* __restrict__ out)
+{
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ncells) return;
+    const unsigned long long cell0 = cell_pre[g0], cell = cell0 + t;
+    uint32_t lo = g0, hi = g1;                            // cell_pre[lo] <= cell < cell_pre[hi]
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (cell_pre[mid] <= cell) lo = mid; else hi = mid; }
+    const uint32_t g = lo;
+    const unsigned long long local = cell - cell_pre[g];
+    uint32_t* dst = out + 3 * (cell_pre[g] - cell0) - 2ull * (g - g0);
+    if (local == 0) { dst[0] = g_len[g]; return; }
+    const uint32_t j = (uint32_t)(local - 1);
+    const uint64_t w = (uint64_t)g_word[g] + (j >> 5);
+    const int s = j & 31;
+    const bool v = window32(pl.ok[w], pl.ok[w + 1], s) == 0xFFFFFFFFu;
+    WindowBits b = window_bits(window32(pl.hi[w], pl.hi[w + 1], s), window32(pl.lo[w], pl.lo[w + 1], s));
+#pragma unroll
+    for (int i = 0; i < 3; i++) dst[1 + (size_t)j * 3 + i] = v ? stream_code(m, b, i) : 0u;
+}
+
 } // namespace
 
 static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
@@ -344,5 +370,14 @@ cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, ui
 {
     if (len < (uint32_t)EREF_K) return cudaSuccess;
     k_record_codes<<<grid_for(len - EREF_K + 1, 256), 256, 0, st>>>(pl, m, first_word, len, codes);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_index_body(Planes pl, CoderMasks m, const uint32_t* g_word, const uint32_t* g_len,
+                              const unsigned long long* cell_pre, uint32_t g0, uint32_t g1, unsigned long long ncells,
+                              uint32_t* out, cudaStream_t st)
+{
+    if (!ncells) return cudaSuccess;
+    k_index_body<<<grid_for(ncells, 256), 256, 0, st>>>(pl, m, g_word, g_len, cell_pre, g0, g1, ncells, out);
     return cudaGetLastError();
 }

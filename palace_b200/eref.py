@@ -34,7 +34,7 @@ ABI_SYMBOLS = (
     "eref_query_reset", "eref_query_add", "eref_query_add_device", "eref_query_seq_bytes",
     "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device",
     "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
-    "eref_run_host",
+    "eref_run_host", "eref_ref_records", "eref_index_body",
 )
 
 
@@ -85,6 +85,8 @@ def load_library() -> ctypes.CDLL:
     lib.eref_get_codes.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_ref_record.argtypes = [c_void_p, c_uint32, POINTER(c_uint64), POINTER(c_uint32), POINTER(c_uint32)]
     lib.eref_query_popcount.argtypes = [c_void_p, c_int, POINTER(c_uint64)]
+    lib.eref_ref_records.argtypes = [c_void_p, c_void_p, c_void_p, c_size_t, POINTER(c_size_t)]
+    lib.eref_index_body.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t), POINTER(c_uint32)]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
     lib.eref_format_line.argtypes = [c_void_p, ctypes.c_char_p, c_size_t]
     _lib = lib
@@ -229,6 +231,30 @@ class ErefGPU:
         _check(self.lib, self.lib.eref_ref_record(self._h, ordinal, byref(off), byref(hl), byref(ln)), "eref_ref_record")
         return off.value, hl.value, ln.value
 
+    def ref_records(self):
+        """(lengths, header offsets) of EVERY record of the reference text, kept or not, in file order"""
+        n = c_size_t()
+        _check(self.lib, self.lib.eref_ref_records(self._h, None, None, 0, byref(n)), "eref_ref_records")
+        ln, off = np.zeros(n.value, "<u4"), np.zeros(n.value, "<u4")
+        _check(self.lib, self.lib.eref_ref_records(self._h, c_void_p(ln.ctypes.data), c_void_p(off.ctypes.data), n.value,
+                                                   byref(n)), "eref_ref_records")
+        return ln, off
+
+    def index_body(self, chunk_words: int = 1 << 26):
+        """yield the body of <db>.k32.index.dat (:698, :711-738) in chunks of whole records"""
+        kept = self.ref_count()[0]
+        buf = np.zeros(chunk_words, "<u4")
+        first = 1
+        while first <= kept:
+            n, nxt = c_size_t(), c_uint32()
+            rc = self.lib.eref_index_body(self._h, first, c_void_p(buf.ctypes.data), buf.size, byref(n), byref(nxt))
+            if rc == -4 and buf.size < (1 << 31):              # one record larger than the chunk: grow and retry
+                buf = np.zeros(buf.size * 4, "<u4")
+                continue
+            _check(self.lib, rc, "eref_index_body")
+            yield buf[:n.value].copy()
+            first = nxt.value
+
     def query_popcount(self, level: int) -> int:
         v = c_uint64()
         _check(self.lib, self.lib.eref_query_popcount(self._h, level, byref(v)), "eref_query_popcount")
@@ -238,6 +264,52 @@ class ErefGPU:
         t = PhaseTimes()
         _check(self.lib, self.lib.eref_timings(self._h, byref(t)), "eref_timings")
         return t.as_dict()
+
+
+def record_name(header_line: bytes) -> str:
+    """get_read_ID(line).substr(1) (:246-254, :689): the header up to the first '/', ' ' or tab, without '>'"""
+    s = header_line
+    for d in (b"/", b" ", b"\t"):
+        k = s.find(d)
+        if k >= 0:
+            s = s[:k]
+    return s[1:].decode("latin-1")
+
+
+def write_index(fasta, coder, index_path: str, len_path: str | None = None, device: int = 0):
+    """produce the reference's on-disk index for a FASTA text on the GPU —
+    <db>.k32.index.dat (400-byte coder header :680-682, then per kept record its length and 3 codes per window
+    start :698, :711-738) and <db>.genome.len.txt (name, record number, length, running length; :697, :800) —
+    so that a CPU `eref` can share the DB directory.  Returns the number of u32 words written."""
+    fasta = _as_bytes_array(fasta)
+    c = np.asarray(coder, dtype=np.int64)
+    hdr = np.zeros(100, "<u4")
+    # the reference writes 4 bytes from a short array: word j = coder[j] | coder[j+1] << 16 (:680-682); only the low
+    # halves are read back (:1104-1122)
+    hdr[:96] = (c[:96] & 0xFFFF).astype("<u4")
+    hdr[:95] |= ((c[1:96] & 0xFFFF) << 16).astype("<u4")
+    words = 100
+    with ErefGPU(coder, device=device) as g, open(index_path, "wb") as f:
+        g.ref_set(fasta)
+        f.write(hdr.tobytes())
+        for chunk in g.index_body():
+            f.write(chunk.tobytes())
+            words += chunk.size
+        if len_path:
+            ln, off = g.ref_records()
+            raw = fasta.tobytes()
+            run = 0
+            with open(len_path, "w") as lf:
+                for r in range(ln.size):
+                    run += int(ln[r])
+                    if ln[r] > K:
+                        if r == 0:
+                            name = "start"
+                        else:
+                            e = raw.find(b"\n", int(off[r]))
+                            name = record_name(raw[int(off[r]): e if e >= 0 else len(raw)])
+                        lf.write(f"{name}\t{r}\t{int(ln[r])}\t{run}\n")
+    return words
 
 
 def format_results(results: np.ndarray, ordinal_base: int = 0) -> str:

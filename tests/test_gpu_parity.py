@@ -335,3 +335,63 @@ def test_fastq_framing_stress(oracle, seed):
         g.query_add(fq)
         for level in (1, 2, 3):
             assert g.query_popcount(level) == sum(1 for v in cnt.values() if 2 * v >= level)
+
+
+# ---- the reference's on-disk index, produced on the GPU ---------------------
+
+def test_index_file_matches_the_reference(golden, tmp_path):
+    """<db>.k32.index.dat body (every code of every position) and <db>.genome.len.txt are byte-identical to
+    what the UNMODIFIED reference wrote for the same FASTA and coder header (tests/golden/make_golden.py)"""
+    import hashlib
+    name, meta, fa, f1, f2 = golden
+    idx, ln = str(tmp_path / "db.fa.k32.index.dat"), str(tmp_path / "db.fa.genome.len.txt")
+    words = eref.write_index(fa, meta["coder"], idx, ln)
+    assert words == meta["index_words"]
+    w = np.fromfile(idx, "<u4")
+    assert w.size == meta["index_words"]
+    assert [int(x) for x in (w[:96] & 0xFFFF)] == meta["coder"]          # what saved_random_coder reads back (:1104-1122)
+    assert hashlib.sha256(w[100:].tobytes()).hexdigest() == meta["index_body_sha256"]
+    assert open(ln).read() == meta["genome_len_txt"]
+    assert (eref.read_coder(idx) == np.asarray(meta["coder"])).all()
+
+
+def test_index_body_chunking(oracle):
+    """chunks of any size concatenate to the same body; a chunk smaller than one record is refused loudly"""
+    db, _, _, _ = _case(41, n_genomes=30, db_bp=400_000, q_bp=50_000)
+    coder = eref.random_coder(41)
+    with eref.ErefGPU(coder) as g:
+        g.ref_set(db.text)
+        whole = np.concatenate(list(g.index_body(1 << 24)))
+        small = np.concatenate(list(g.index_body(int(3 * db.lengths.max()) + 8)))
+        assert whole.size == small.size and (whole == small).all()
+        seqs, _ = oracle.parse_fasta(db.text)
+        assert whole[0] == len(seqs[0])
+        assert (whole[1:1 + 3 * (len(seqs[0]) - 31)] == oracle.record_codes(coder, seqs[0])).all()
+        buf = np.zeros(16, "<u4")
+        import ctypes
+        n, nxt = ctypes.c_size_t(), ctypes.c_uint32()
+        rc = g.lib.eref_index_body(g._h, 1, ctypes.c_void_p(buf.ctypes.data), buf.size, ctypes.byref(n), ctypes.byref(nxt))
+        assert rc == -4
+
+
+def test_eref_binary_writes_a_reference_index(golden, tmp_path):
+    """EREF_WRITE_INDEX=1: the executable leaves the reference's index files next to the DB (coder from the sidecar)"""
+    import hashlib
+    name, meta, fa, f1, f2 = golden
+    fa.tofile(tmp_path / "db.fa"); f1.tofile(tmp_path / "r1.fq"); f2.tofile(tmp_path / "r2.fq")
+    with open(tmp_path / "db.fa.k32.coder", "w") as f:
+        f.write(" ".join(str(x) for x in meta["coder"]) + "\n")
+    key, expect = next(iter(meta["stdout"].items()))
+    hr, phr = key.split(",")
+    r = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "1"], cwd=tmp_path,
+                       capture_output=True, env=dict(os.environ, EREF_WRITE_INDEX="1", EREF_GPUS="1"))
+    assert r.returncode == 0, r.stderr.decode()
+    assert r.stdout.decode() == expect
+    w = np.fromfile(tmp_path / "db.fa.k32.index.dat", "<u4")
+    assert w.size == meta["index_words"] and [int(x) for x in (w[:96] & 0xFFFF)] == meta["coder"]
+    assert hashlib.sha256(w[100:].tobytes()).hexdigest() == meta["index_body_sha256"]
+    assert open(tmp_path / "db.fa.genome.len.txt").read() == meta["genome_len_txt"]
+    # a second run finds the index, takes the coder from it and prints the same lines
+    r2 = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "1"], cwd=tmp_path,
+                        capture_output=True, env=dict(os.environ, EREF_GPUS="1"))
+    assert r2.returncode == 0 and r2.stdout.decode() == expect
