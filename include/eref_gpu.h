@@ -32,7 +32,8 @@ extern "C" {
 
 /* eref_create flags */
 #define EREF_FLAG_NO_PRUNE 1u          /* probe all three streams at every position (no candidate filter) */
-#define EREF_FLAG_DIRECT_COUNT 2u      /* count k-mers straight into the table (no code-range bucketing) */
+#define EREF_FLAG_DIRECT_COUNT 2u      /* count k-mers straight into the table (no code-range partitioning) */
+#define EREF_FLAG_KEEP_RAND_STATE 4u   /* eref_run_host: do not srand(1) before the down-sampling draws (:1236-1238) */
 
 typedef struct eref_ctx eref_ctx;
 
@@ -74,6 +75,20 @@ int  eref_query_reset(eref_ctx* ctx);
  * forms the three canonical codes of every valid 32-mer and counts them, saturating at 3. */
 int  eref_query_add(eref_ctx* ctx, const char* fastq_host, size_t n);
 int  eref_query_add_device(eref_ctx* ctx, const void* fastq_dev, size_t n);
+/* Down-sampling (:955-960, :1124-1148, :1239-1242).  When fq1 holds more than
+ * down_sampling_size / 2 bases the reference keeps a read only if rand() % 100 < ratio, one draw per sequence line,
+ * fq1 first then fq2, rand seeded with 1 by main().  The host replays it:
+ *   eref_query_census*   cal_sam_ratio's pass: bytes on sequence lines (index % 4 == 1) and the number of such lines
+ *   eref_sample_ratio    100 * down_sampling_size / (2 * bytes), as the reference's long division (2e9 there)
+ *   eref_draw_keep       n_lines draws of libc rand() % 100 < ratio -> one bit per sequence line (LSB first)
+ *   eref_query_add_masked*  read_fastq counting only the sequence lines whose bit is set (NULL = all)
+ * eref_run_host does all of this itself. */
+int  eref_query_census(eref_ctx* ctx, const char* fastq_host, size_t n, uint64_t* seq_bytes, uint64_t* seq_lines);
+int  eref_query_census_device(eref_ctx* ctx, const void* fastq_dev, size_t n, uint64_t* seq_bytes, uint64_t* seq_lines);
+int  eref_sample_ratio(uint64_t seq_bytes_fq1, uint64_t down_sampling_size, int* ratio);
+void eref_draw_keep(int ratio, uint64_t n_lines, uint32_t* keep_bits);
+int  eref_query_add_masked(eref_ctx* ctx, const char* fastq_host, size_t n, const uint32_t* keep_bits, uint64_t n_keep);
+int  eref_query_add_masked_device(eref_ctx* ctx, const void* fastq_dev, size_t n, const uint32_t* keep_bits, uint64_t n_keep);
 /* cal_sam_ratio's sum (:1133-1142) for the file of the last eref_query_add* call */
 int  eref_query_seq_bytes(eref_ctx* ctx, uint64_t* out);
 
@@ -93,7 +108,8 @@ int  eref_scan_device(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out
  * overlap): H2D copies run on a copy stream while the kernels work; the FASTA text is cut into `chunks`
  * pieces at record boundaries and each piece is framed and scanned as soon as it has landed.  Writes
  * min(cap, total) records in file order with global ordinals; *n_out = total.  Includes the table reset
- * and the cal_sam_ratio guard (EREF_ERR_UNSUPPORTED when the reference would down-sample or divide by 0). */
+ * the cal_sam_ratio pass and, when it yields a ratio below 100, the rand()-replayed down-sampling
+ * (EREF_ERR_UNSUPPORTED when the reference would divide by 0: fq1 without sequence lines). */
 int  eref_run_host(eref_ctx* ctx, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta,
                    size_t nf, int chunks, eref_result* out, size_t cap, size_t* n_out);
 

@@ -170,12 +170,19 @@ static void count_read(uint8_t* table, const eo_masks* mk, const unsigned char* 
 
 void eo_count_fastq(uint8_t* table, const int16_t coder[96], const char* text, size_t n)
 {
+    eo_count_fastq_sampled(table, coder, text, n, -1);
+}
+
+/* down_sam_ratio < 0: no draws at all (every read counted; the reference's result whenever ratio >= 100).
+ * Otherwise one r = rand() % 100 per sequence line and the read is counted iff r < down_sam_ratio (:955-960). */
+void eo_count_fastq_sampled(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int down_sam_ratio)
+{
     eo_masks mk; make_masks(coder, &mk);
     size_t pos = 0, line = 0;
     while (pos < n) {                                   /* getline loop, :940 */
         const char* nl = memchr(text + pos, '\n', n - pos);
         size_t end = nl ? (size_t)(nl - text) : n;
-        if (line % 4 == 1)                              /* :947 */
+        if (line % 4 == 1 && (down_sam_ratio < 0 || rand() % 100 < down_sam_ratio))     /* :947, :955-957 */
             count_read(table, &mk, (const unsigned char*)text + pos, (uint32_t)(end - pos));
         line++;
         pos = end + 1;
@@ -300,10 +307,23 @@ int eo_run(const char* fq1, size_t n1, const char* fq2, size_t n2, const char* f
            const int16_t coder[96], float hit_ratio, float perfect_hit_ratio, int threads,
            eo_result** out, size_t* n_out)
 {
+    return eo_run_sampled(fq1, n1, fq2, n2, fasta, nf, coder, hit_ratio, perfect_hit_ratio, threads, 2000000000L, out, n_out);
+}
+
+/* main() of a WARM reference run (index on disk) with down_sampling_size (:1230) as a parameter: srand(1) (:1236-1238),
+ * cal_sam_ratio (:1124-1148), then both FASTQ files under that ratio. */
+int eo_run_sampled(const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
+                   const int16_t coder[96], float hit_ratio, float perfect_hit_ratio, int threads,
+                   long down_sampling_size, eo_result** out, size_t* n_out)
+{
     uint8_t* table = eo_table_new();
     if (!table) return -1;
-    eo_count_fastq(table, coder, fq1, n1);                       /* :1269-1279 */
-    eo_count_fastq(table, coder, fq2, n2);                       /* :1281-1291 */
+    long sample_size = eo_fastq_seq_bytes(fq1, n1) * 2;          /* :1144 */
+    if (sample_size == 0) { eo_table_free(table); return -3; }   /* the reference divides by zero here (:1145) */
+    int ratio = (int)(100 * down_sampling_size / sample_size);   /* :1145 */
+    srand(1);                                                    /* :1236-1238 */
+    eo_count_fastq_sampled(table, coder, fq1, n1, ratio < 100 ? ratio : -1);   /* :1269-1279 */
+    eo_count_fastq_sampled(table, coder, fq2, n2, ratio < 100 ? ratio : -1);   /* :1281-1291 */
     unsigned char* seq; uint64_t* off; size_t kept;
     if (eo_parse_fasta(fasta, nf, &seq, &off, &kept, NULL)) { eo_table_free(table); return -2; }
     eo_result* res = (eo_result*)calloc(kept ? kept : 1, sizeof *res);

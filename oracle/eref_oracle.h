@@ -45,6 +45,8 @@ uint8_t* eo_table_new(void);
 void eo_table_free(uint8_t* t);
 /* read_fastq at one thread (:940-1004): every line with index%4==1 is a sequence line. */
 void eo_count_fastq(uint8_t* table, const int16_t coder[96], const char* text, size_t n);
+/* the same under down-sampling (:955-960): down_sam_ratio < 0 = count every read, no rand() draws */
+void eo_count_fastq_sampled(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int down_sam_ratio);
 /* cal_sam_ratio's sum (:1133-1142): bytes on lines with index%4==1 */
 long eo_fastq_seq_bytes(const char* text, size_t n);
 
@@ -65,6 +67,13 @@ void eo_scan_record(const uint8_t* table, const int16_t coder[96], const unsigne
 int eo_run(const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
            const int16_t coder[96], float hit_ratio, float perfect_hit_ratio, int threads,
            eo_result** out, size_t* n_out);
+
+/* the same with down_sampling_size (:1230, 2e9 in the reference) as a parameter, as a WARM reference run does it:
+ * srand(1) (:1236-1238), ratio = 100 * down_sampling_size / (2 * sequence bytes of fq1) (:1145), and below 100 one
+ * rand() % 100 draw per sequence line of fq1 then fq2 (:955-960).  Returns -3 where the reference divides by 0. */
+int eo_run_sampled(const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
+                   const int16_t coder[96], float hit_ratio, float perfect_hit_ratio, int threads,
+                   long down_sampling_size, eo_result** out, size_t* n_out);
 
 /* the stdout line of :617 (or 0 bytes if the record is not selected); returns bytes written */
 int eo_format_line(const eo_result* r, char* buf, size_t cap);

@@ -61,6 +61,7 @@ struct eref_ctx {
     CoderMasks masks{};
     float hit_ratio = 0, perfect_hit_ratio = 0;
     int one_min = 0, three_min = 0, sample_stride = 4;
+    uint64_t down_sampling_size = 2000000000ull;       // :1230 (EREF_DOWN_SAMPLING_SIZE: test hook)
     unsigned flags = 0;
     cudaEvent_t ev[EV_COUNT]{};
     // query table: level L bitmap = "code seen >= L times"
@@ -68,7 +69,7 @@ struct eref_ctx {
     // shared scratch
     DevBuf tile_counts, tile_prefix, cub_tmp, counters;      // counters: 4 x u64
     // query side
-    DevBuf q_text, q_hi, q_lo, q_ok, tile_kept, tile_kept_pre;
+    DevBuf q_text, q_hi, q_lo, q_ok, tile_kept, tile_kept_pre, q_keep;
     // Table build (table.cu): every file added since the last reset is kept as a slice-ordered code list (codes
     // radix-partitioned by their top 13 bits); a build counts all lists slice by slice in shared memory and
     // writes level 3 and its summary.  Levels 1/2 exist in HBM only for the direct build (EREF_FLAG_DIRECT_COUNT).
@@ -156,7 +157,32 @@ int check_text_ptr(const void* p, size_t n)
     return 0;
 }
 
-int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
+// cal_sam_ratio's pass over one FASTQ text (:1124-1148): bytes on its sequence lines and how many such lines it has
+int census_impl(eref_ctx* c, const uint8_t* text, uint64_t n, uint64_t* seq_bytes_out, uint64_t* seq_lines_out)
+{
+    cudaStream_t st = c->stream;
+    uint64_t ntiles = 0;
+    int rc = newline_census(c, text, n, &ntiles);
+    if (rc) return rc;
+    CUDA_TRY(c->tile_kept.ensure((ntiles + 1) * 8));
+    unsigned long long* seq_bytes = c->counters.as<unsigned long long>();
+    CUDA_TRY(cudaMemsetAsync(seq_bytes, 0, 8, st));
+    LAUNCH(c, launch_fastq_kept(text, n, c->tile_prefix.as<uint32_t>(), nullptr, c->tile_kept.as<unsigned long long>(), seq_bytes,
+                                ntiles, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 5, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 12, c->tile_prefix.as<uint32_t>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
+    uint8_t last = '\n';
+    if (n) CUDA_TRY(cudaMemcpyAsync(c->h_pin + 13, text + n - 1, 1, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (n) last = (uint8_t)(c->h_pin[13] & 0xFF);
+    // getline yields one line per newline plus an unterminated last one; lines 1, 5, 9, ... are sequence lines (:947)
+    const uint64_t lines = (c->h_pin[12] & 0xFFFFFFFFull) + (n && last != '\n' ? 1 : 0);
+    if (seq_bytes_out) *seq_bytes_out = c->h_pin[5];
+    if (seq_lines_out) *seq_lines_out = (lines + 2) / 4;
+    return 0;
+}
+
+int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t* keep_host = nullptr, uint64_t n_keep = 0)
 {
     cudaStream_t st = c->stream;
     int wrc = wait_table(c, st);              // an update still in flight reads the code lists this call rewrites
@@ -170,7 +196,19 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     unsigned long long* tile_kept = c->tile_kept.as<unsigned long long>();
     unsigned long long* tile_kept_pre = c->tile_kept_pre.as<unsigned long long>();
     CUDA_TRY(cudaMemsetAsync(tile_kept + ntiles, 0, 8, st));
-    LAUNCH(c, launch_fastq_kept(text, n, c->tile_prefix.as<uint32_t>(), tile_kept, ntiles, st));
+    const uint32_t* keep = nullptr;                     // down-sampling: one bit per sequence line (:955-960)
+    if (keep_host) {
+        const size_t words = (size_t)((n / 4 + 2 + 31) / 32) + 1;       // the kernels index the mask by line number: cover
+                                                                        // every line a text of n bytes can have, zero = drop
+        const size_t have = (size_t)((n_keep + 31) / 32);
+        CUDA_TRY(c->q_keep.ensure(words * 4));
+        CUDA_TRY(cudaMemsetAsync(c->q_keep.p, 0, words * 4, st));
+        if (have) CUDA_TRY(cudaMemcpyAsync(c->q_keep.p, keep_host, (have < words ? have : words) * 4, cudaMemcpyHostToDevice, st));
+        keep = c->q_keep.as<uint32_t>();
+    }
+    unsigned long long* seq_bytes = c->counters.as<unsigned long long>();
+    CUDA_TRY(cudaMemsetAsync(seq_bytes, 0, 8, st));
+    LAUNCH(c, launch_fastq_kept(text, n, c->tile_prefix.as<uint32_t>(), keep, tile_kept, seq_bytes, ntiles, st));
     rc = exclusive_scan<unsigned long long>(c, tile_kept, tile_kept_pre, ntiles + 1);
     if (rc) return rc;
     const unsigned long long* plane_bits = tile_kept_pre + ntiles;     // total, known to the device only for now
@@ -182,9 +220,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, st));           // tiles OR their boundary words in; pad words stay 0
     CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, st));
     CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, st));
-    unsigned long long* seq_bytes = c->counters.as<unsigned long long>();
-    CUDA_TRY(cudaMemsetAsync(seq_bytes, 0, 8, st));
-    LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), tile_kept_pre, pl, seq_bytes, st));
+    LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), keep, tile_kept_pre, pl, st));
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 11, plane_bits, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaEventRecord(c->ev[E2], st));
     c->summary_stale = true;
@@ -518,6 +554,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->aux_ev[i], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->table_ready, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->table_stream, cudaStreamNonBlocking);
+    if (const char* v = getenv("EREF_DOWN_SAMPLING_SIZE")) { long long k = atoll(v); if (k > 0) c->down_sampling_size = (uint64_t)k; }
     if (const char* v = getenv("EREF_BUCKET_BITS")) { int k = atoi(v); if (k >= 5 && k <= 8) c->bucket_bits = k; }
     for (int l = (flags & EREF_FLAG_DIRECT_COUNT) ? 0 : 2; l < 3 && e == cudaSuccess; l++)
         e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
@@ -540,7 +577,7 @@ void eref_destroy(eref_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->table_stream) cudaStreamSynchronize(c->table_stream);
-    DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->tile_kept, &c->tile_kept_pre, &c->q_text, &c->q_hi, &c->q_lo,
+    DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->tile_kept, &c->tile_kept_pre, &c->q_keep, &c->q_text, &c->q_hi, &c->q_lo,
                       &c->q_ok, &c->r_text, &c->tile_sum, &c->tile_pre, &c->rec_hdr_off, &c->rec_first,
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
                       &c->g_len, &c->g_word, &c->g_first, &c->r_hi, &c->r_lo, &c->r_ok, &c->word_genome,
@@ -606,6 +643,63 @@ int eref_query_add_device(eref_ctx* c, const void* fastq_dev, size_t n)
     CUDA_TRY(cudaSetDevice(c->device));
     CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
     return query_add_impl(c, static_cast<const uint8_t*>(fastq_dev), n);
+}
+
+int eref_query_add_masked(eref_ctx* c, const char* fastq_host, size_t n, const uint32_t* keep_bits, uint64_t n_keep)
+{
+    if (!c || (n && !fastq_host)) return eref_fail(EREF_ERR_ARG, "eref_query_add_masked: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(c->q_text.ensure(n + 64));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
+    if (n) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fastq_host, n, cudaMemcpyHostToDevice, c->stream));
+    return query_add_impl(c, c->q_text.as<uint8_t>(), n, keep_bits, n_keep);
+}
+
+int eref_query_add_masked_device(eref_ctx* c, const void* fastq_dev, size_t n, const uint32_t* keep_bits, uint64_t n_keep)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    int rc = check_text_ptr(fastq_dev, n);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
+    return query_add_impl(c, static_cast<const uint8_t*>(fastq_dev), n, keep_bits, n_keep);
+}
+
+int eref_query_census(eref_ctx* c, const char* fastq_host, size_t n, uint64_t* seq_bytes, uint64_t* seq_lines)
+{
+    if (!c || (n && !fastq_host)) return eref_fail(EREF_ERR_ARG, "eref_query_census: null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int wrc = wait_table(c, c->stream);
+    if (wrc) return wrc;
+    CUDA_TRY(c->q_text.ensure(n + 64));
+    if (n) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fastq_host, n, cudaMemcpyHostToDevice, c->stream));
+    return census_impl(c, c->q_text.as<uint8_t>(), n, seq_bytes, seq_lines);
+}
+
+int eref_query_census_device(eref_ctx* c, const void* fastq_dev, size_t n, uint64_t* seq_bytes, uint64_t* seq_lines)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    int rc = check_text_ptr(fastq_dev, n);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(c->device));
+    return census_impl(c, static_cast<const uint8_t*>(fastq_dev), n, seq_bytes, seq_lines);
+}
+
+int eref_sample_ratio(uint64_t seq_bytes_fq1, uint64_t down_sampling_size, int* ratio)
+{
+    if (!ratio) return eref_fail(EREF_ERR_ARG, "null argument");
+    if (seq_bytes_fq1 == 0)
+        return eref_fail(EREF_ERR_UNSUPPORTED, "fq1 holds no sequence lines (the reference divides by zero here, :1145)");
+    const long sample_size = (long)seq_bytes_fq1 * 2;                       // :1144 "pair"
+    *ratio = (int)(100L * (long)down_sampling_size / sample_size);          // :1145, long division narrowed to int
+    return 0;
+}
+
+void eref_draw_keep(int ratio, uint64_t n_lines, uint32_t* keep_bits)
+{
+    for (uint64_t i = 0; i < (n_lines + 31) / 32; i++) keep_bits[i] = 0;
+    for (uint64_t i = 0; i < n_lines; i++)
+        if (rand() % 100 < ratio) keep_bits[i >> 5] |= 1u << (i & 31);      // :955-957, one draw per sequence line
 }
 
 int eref_query_seq_bytes(eref_ctx* c, uint64_t* out)
@@ -729,16 +823,36 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     eref_phase_times sum = c->t;
     const unsigned long long seq1 = c->t.query_seq_bytes;
     // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1)
-    if (seq1 == 0 || 100ull * 2000000000ull / (2ull * seq1) < 100ull) {
-        cudaStreamSynchronize(cs);
-        return seq1 == 0
-            ? eref_fail(EREF_ERR_UNSUPPORTED, "fq1 holds no sequence lines (the reference divides by zero here, :1145)")
-            : eref_fail(EREF_ERR_UNSUPPORTED, "fq1 holds more than 1 Gbase: the reference's rand()-driven down-sampling "
-                                              "(:955-960) is not implemented; refusing to diverge silently");
+    int ratio = 0;
+    rc = eref_sample_ratio(seq1, c->down_sampling_size, &ratio);
+    if (rc) { cudaStreamSynchronize(cs); return rc; }
+    std::vector<uint32_t> keep1, keep2;
+    uint64_t lines1 = 0, lines2 = 0;
+    if (ratio < 100) {
+        // Down-sampling (:955-960): every sequence line of fq1, then of fq2, draws rand() % 100 and is counted iff the
+        // draw is below the ratio.  Replay the draws on the host in the reference's order (its main() seeds rand with
+        // 1, :1236-1238; EREF_FLAG_KEEP_RAND_STATE: the caller has positioned rand() already, like a cold reference run
+        // whose coder draw re-seeded it), then count both files again under the masks.
+        rc = census_impl(c, c->q_text.as<uint8_t>(), n1, nullptr, &lines1);
+        if (rc) return rc;
+        CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[1], 0));
+        rc = census_impl(c, c->q_text2.as<uint8_t>(), n2, nullptr, &lines2);
+        if (rc) return rc;
+        if (!(c->flags & EREF_FLAG_KEEP_RAND_STATE)) srand(1);
+        keep1.resize((lines1 + 31) / 32 + 1); keep2.resize((lines2 + 31) / 32 + 1);
+        eref_draw_keep(ratio, lines1, keep1.data());
+        eref_draw_keep(ratio, lines2, keep2.data());
+        rc = eref_query_reset(c);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+        rc = query_add_impl(c, c->q_text.as<uint8_t>(), n1, keep1.data(), lines1);
+        if (rc) return rc;
+        sum = c->t;
     }
     CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[1], 0));
     CUDA_TRY(cudaEventRecord(c->ev[E0], st));
-    rc = query_add_impl(c, c->q_text2.as<uint8_t>(), n2);
+    rc = ratio < 100 ? query_add_impl(c, c->q_text2.as<uint8_t>(), n2, keep2.data(), lines2)
+                     : query_add_impl(c, c->q_text2.as<uint8_t>(), n2);
     if (rc) return rc;
     sum.query_pack_ms += c->t.query_pack_ms; sum.query_bucket_ms += c->t.query_bucket_ms;
     sum.query_seq_bytes += c->t.query_seq_bytes; sum.query_codes += c->t.query_codes;

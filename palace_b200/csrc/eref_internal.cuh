@@ -129,11 +129,10 @@ int eref_fail(int code, const char* fmt, ...);
 // frame.cu
 cudaError_t launch_count_newlines(const uint8_t* text, uint64_t n, uint32_t* tile_counts,
                                   uint64_t ntiles, cudaStream_t st);
-cudaError_t launch_fastq_kept(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, unsigned long long* tile_kept,
-                              uint64_t ntiles, cudaStream_t st);
-cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
-                              const unsigned long long* tile_kept_pre, Planes pl, unsigned long long* seq_bytes,
-                              cudaStream_t st);
+cudaError_t launch_fastq_kept(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, const uint32_t* keep,
+                              unsigned long long* tile_kept, unsigned long long* seq_bytes, uint64_t ntiles, cudaStream_t st);
+cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, const uint32_t* keep,
+                              const unsigned long long* tile_kept_pre, Planes pl, cudaStream_t st);
 cudaError_t launch_fasta_tiles(const uint8_t* text, uint64_t n, TileSum* tiles, uint64_t ntiles, cudaStream_t st);
 cudaError_t launch_fasta_records(const uint8_t* text, uint64_t n, const TileSum* tiles, const TileSum* tile_pre,
                                  uint64_t ntiles, uint32_t* rec_first, uint32_t* rec_hdr_off, cudaStream_t st);

@@ -236,7 +236,9 @@ int main(int argc, char** argv)
     int16_t coder[96];
     const std::string index_name = fasta + ".k" + std::to_string(EREF_K) + ".index.dat";
     const std::string sidecar = fasta + ".k" + std::to_string(EREF_K) + ".coder";
+    bool coder_drawn_here = false;                   // then rand() continues from the coder draw, like a cold reference run
     if (!read_index_header(index_name, coder) && !read_sidecar(sidecar, coder)) {
+        coder_drawn_here = true;
         const char* s = getenv("EREF_CODER_SEED");
         draw_coder(s ? (unsigned)strtoul(s, nullptr, 10) : (unsigned)time(nullptr), coder);
         std::ofstream out(sidecar);
@@ -260,7 +262,12 @@ int main(int argc, char** argv)
     }
     std::vector<size_t> cut = shard_offsets(fa.p, fa.n, shards);
     const unsigned flags = (getenv("EREF_NO_PRUNE") ? EREF_FLAG_NO_PRUNE : 0u) |
-                           (getenv("EREF_DIRECT_COUNT") ? EREF_FLAG_DIRECT_COUNT : 0u);
+                           (getenv("EREF_DIRECT_COUNT") ? EREF_FLAG_DIRECT_COUNT : 0u) |
+                           (coder_drawn_here ? EREF_FLAG_KEEP_RAND_STATE : 0u);
+    uint64_t down_sampling_size = 2000000000ull;         // :1230
+    if (const char* v = getenv("EREF_DOWN_SAMPLING_SIZE")) { long long k = atoll(v); if (k > 0) down_sampling_size = (uint64_t)k; }
+    std::vector<uint32_t> keep1, keep2;                  // down-sampling masks, drawn once by shard 0
+    uint64_t lines1 = 0, lines2 = 0;
 
     std::vector<ncclComm_t> comms(shards);
     if (shards > 1) {
@@ -298,21 +305,33 @@ int main(int argc, char** argv)
             single_done = ok;
         }
         if (ok && shards > 1 && eref_query_add(ctx, f1.p, f1.n)) { fail("eref_query_add(fq1)"); ok = false; }
+        int ratio = 100;
         if (ok && shards > 1) {
             // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1), integer division
             uint64_t seq = 0;
             eref_query_seq_bytes(ctx, &seq);
-            if (seq == 0) { errors[i] = "fq1 holds no sequence lines (the reference divides by zero here, :1145)"; failed.store(1); ok = false; }
-            else {
-                long ratio = 100L * 2000000000L / (long)(2 * seq);
-                if (ratio < 100) {
-                    errors[i] = "fq1 holds more than 1 Gbase: the reference's rand()-driven down-sampling (:955-960) "
-                                "is not implemented; refusing to diverge silently";
-                    failed.store(1); ok = false;
+            if (eref_sample_ratio(seq, down_sampling_size, &ratio)) { fail("cal_sam_ratio"); ok = false; }
+        }
+        if (shards > 1) {
+            // down-sampling (:955-960): shard 0 replays the reference's rand() draws once, every shard counts under them
+            if (ok && ratio < 100 && i == 0) {
+                uint64_t l1 = 0, l2 = 0;
+                if (eref_query_census(ctx, f1.p, f1.n, nullptr, &l1) || eref_query_census(ctx, f2.p, f2.n, nullptr, &l2)) {
+                    fail("eref_query_census"); ok = false;
+                } else {
+                    if (!coder_drawn_here) srand(1);               // :1236-1238
+                    keep1.assign((l1 + 31) / 32 + 1, 0); keep2.assign((l2 + 31) / 32 + 1, 0);
+                    eref_draw_keep(ratio, l1, keep1.data()); eref_draw_keep(ratio, l2, keep2.data());
+                    lines1 = l1; lines2 = l2;
                 }
             }
+            bar.wait();                                   // the masks are drawn (or nobody needs them)
+            if (ok && ratio < 100) {
+                if (failed.load()) ok = false;
+                else if (eref_query_reset(ctx) || eref_query_add_masked(ctx, f1.p, f1.n, keep1.data(), lines1) ||
+                         eref_query_add_masked(ctx, f2.p, f2.n, keep2.data(), lines2)) { fail("eref_query_add_masked"); ok = false; }
+            } else if (ok && eref_query_add(ctx, f2.p, f2.n)) { fail("eref_query_add(fq2)"); ok = false; }
         }
-        if (ok && shards > 1 && eref_query_add(ctx, f2.p, f2.n)) { fail("eref_query_add(fq2)"); ok = false; }
         if (ok && shards > 1 && eref_ref_set(ctx, fa.p + cut[i], cut[i + 1] - cut[i])) { fail("eref_ref_set"); ok = false; }
         if (ok && shards > 1) eref_ref_count(ctx, &kept[i], nullptr, nullptr);
         bar.wait();                                   // every shard's record count is known

@@ -159,16 +159,25 @@ k_count_newlines(const uint8_t* __restrict__ text, uint64_t n, uint32_t* __restr
 // (its newline), which breaks every 32-mer that would span two reads — headers, '+' lines and
 // qualities are dropped, so every plane word is dense with window starts.
 
-// bytes of the chunk that lie on a sequence line; with_nl: including the newline that ends such a line
-__device__ __forceinline__ uint32_t seq_line_bytes(uint32_t nl, uint32_t line, bool with_nl)
+// Is text line `line` a sequence line that is counted?  keep (may be null = all): one bit per sequence line, in
+// file order — the reference's rand() % 100 < ratio draw for that read when it down-samples (:955-960).
+__device__ __forceinline__ bool seq_line(uint32_t line, const uint32_t* __restrict__ keep)
+{
+    if ((line & 3u) != 1u) return false;
+    const uint32_t i = line >> 2;
+    return !keep || ((__ldg(keep + (i >> 5)) >> (i & 31)) & 1u);
+}
+
+// bytes of the chunk that lie on a (kept) sequence line; with_nl: including the newline that ends such a line
+__device__ __forceinline__ uint32_t seq_line_bytes(uint32_t nl, uint32_t line, bool with_nl, const uint32_t* __restrict__ keep)
 {
     uint32_t seq = 0;
-    if (!nl) return (line & 3u) == 1u ? 0xFFFFFFFFu : 0u;
+    if (!nl) return seq_line(line, keep) ? 0xFFFFFFFFu : 0u;
     uint32_t rest = nl;
     int start = 0;
     while (true) {
         const int k = rest ? __clz(rest) : 32;
-        if ((line & 3u) == 1u) seq |= before(with_nl ? min(k + 1, 32) : k) & ~before(start);
+        if (seq_line(line, keep)) seq |= before(with_nl ? min(k + 1, 32) : k) & ~before(start);
         if (k == 32) break;
         rest &= ~(0x80000000u >> k);
         start = k + 1; line++;
@@ -176,10 +185,12 @@ __device__ __forceinline__ uint32_t seq_line_bytes(uint32_t nl, uint32_t line, b
     return seq;
 }
 
-// per tile: plane positions it produces (sequence-line bytes and their newlines)
+// per tile: plane positions it produces (bytes of the kept sequence lines and their newlines); also
+// cal_sam_ratio's sum (:1138-1140): all bytes of ALL sequence lines, valid or not
 __global__ void __launch_bounds__(TILE_THREADS)
 k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
-             unsigned long long* __restrict__ tile_kept)
+             const uint32_t* __restrict__ keep, unsigned long long* __restrict__ tile_kept,
+             unsigned long long* __restrict__ seq_bytes)
 {
     __shared__ uint32_t s_part[TILE_THREADS / 32];
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
@@ -187,9 +198,15 @@ k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
     load32(text, n, off, w);
     const uint32_t nl = chunk_newlines(w);
     const uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(__popc(nl), nullptr);
-    uint32_t kept = 0;
-    if (off < n) kept = __popc(seq_line_bytes(nl, line, true) & before((int)min((uint64_t)32, n - off)));
+    uint32_t kept = 0, nseq = 0;
+    if (off < n) {
+        const uint32_t inr = before((int)min((uint64_t)32, n - off));
+        kept = __popc(seq_line_bytes(nl, line, true, keep) & inr);
+        nseq = __popc(seq_line_bytes(nl, line, false, nullptr) & inr);
+    }
     kept = __reduce_add_sync(0xffffffffu, kept);
+    nseq = __reduce_add_sync(0xffffffffu, nseq);
+    if ((threadIdx.x & 31) == 0 && nseq) atomicAdd(seq_bytes, (unsigned long long)nseq);
     if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = kept;
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -241,7 +258,7 @@ __device__ __forceinline__ bool ring_range(uint32_t& wmin, uint32_t& wmax)
 
 __global__ void __launch_bounds__(TILE_THREADS)
 k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
-             const unsigned long long* __restrict__ tile_kept_pre, Planes pl, unsigned long long* __restrict__ seq_bytes)
+             const uint32_t* __restrict__ keep, const unsigned long long* __restrict__ tile_kept_pre, Planes pl)
 {
     __shared__ uint32_t s_hi[RING], s_lo[RING], s_ok[RING];
     for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; }
@@ -250,11 +267,9 @@ k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
     load32(text, n, off, w);
     Masks m = chunk_masks(w);
     const uint32_t line = tile_prefix[blockIdx.x] + block_exclusive_scan(__popc(m.nl), nullptr);
-    uint32_t kept = 0, nseq = 0;
+    uint32_t kept = 0;
     if (off < n) {
-        const uint32_t inr = before((int)min((uint64_t)32, n - off));
-        kept = seq_line_bytes(m.nl, line, true) & inr;
-        nseq = __popc(kept & ~m.nl);
+        kept = seq_line_bytes(m.nl, line, true, keep) & before((int)min((uint64_t)32, n - off));
         m.ok &= kept; m.hi &= m.ok; m.lo &= m.ok;         // (a newline is never ACGT: it stays an invalid position)
     }
     const uint64_t dest0 = tile_kept_pre[blockIdx.x] + block_exclusive_scan(__popc(kept), nullptr);
@@ -268,9 +283,6 @@ k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
         uint32_t i0, i1; bool two;
         ring_emit(m, k0, len, dest0 + __popc(kept & before(k0)), s_hi, s_lo, s_ok, wmin, wmax, i0, i1, two);
     }
-    // cal_sam_ratio's sum (:1138-1140): all bytes of sequence lines, valid or not
-    nseq = __reduce_add_sync(0xffffffffu, nseq);
-    if ((threadIdx.x & 31) == 0 && nseq) atomicAdd(seq_bytes, (unsigned long long)nseq);
     if (!ring_range(wmin, wmax)) return;
     for (uint32_t wd = wmin + threadIdx.x; wd <= wmax; wd += TILE_THREADS) {
         const uint32_t i = wd & (RING - 1);
@@ -549,21 +561,20 @@ cudaError_t launch_count_newlines(const uint8_t* text, uint64_t n, uint32_t* til
     return cudaGetLastError();
 }
 
-cudaError_t launch_fastq_kept(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, unsigned long long* tile_kept,
-                              uint64_t ntiles, cudaStream_t st)
+cudaError_t launch_fastq_kept(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, const uint32_t* keep,
+                              unsigned long long* tile_kept, unsigned long long* seq_bytes, uint64_t ntiles, cudaStream_t st)
 {
     if (!ntiles) return cudaSuccess;
-    k_fastq_kept<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, tile_kept);
+    k_fastq_kept<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, keep, tile_kept, seq_bytes);
     return cudaGetLastError();
 }
 
-cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix,
-                              const unsigned long long* tile_kept_pre, Planes pl, unsigned long long* seq_bytes,
-                              cudaStream_t st)
+cudaError_t launch_pack_fastq(const uint8_t* text, uint64_t n, const uint32_t* tile_prefix, const uint32_t* keep,
+                              const unsigned long long* tile_kept_pre, Planes pl, cudaStream_t st)
 {
     uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
     if (!ntiles) return cudaSuccess;
-    k_pack_fastq<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, tile_kept_pre, pl, seq_bytes);
+    k_pack_fastq<<<(unsigned)ntiles, TILE_THREADS, 0, st>>>(text, n, tile_prefix, keep, tile_kept_pre, pl);
     return cudaGetLastError();
 }
 

@@ -25,6 +25,8 @@ EREF_BIN = os.path.join(_HERE, "bin", "eref")
 K = 32
 FLAG_NO_PRUNE = 1
 FLAG_DIRECT_COUNT = 2
+FLAG_KEEP_RAND_STATE = 4
+DOWN_SAMPLING_SIZE = 2_000_000_000                       # bin/extract_ref.cpp:1230
 
 RESULT_DTYPE = np.dtype([("ordinal", "<u4"), ("frag", "<u4"), ("el", "<u4"), ("ref_len", "<u4")])
 
@@ -34,7 +36,8 @@ ABI_SYMBOLS = (
     "eref_query_reset", "eref_query_add", "eref_query_add_device", "eref_query_seq_bytes",
     "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device",
     "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
-    "eref_run_host", "eref_ref_records", "eref_index_body",
+    "eref_run_host", "eref_ref_records", "eref_index_body", "eref_query_census", "eref_query_census_device",
+    "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
 )
 
 
@@ -85,6 +88,13 @@ def load_library() -> ctypes.CDLL:
     lib.eref_get_codes.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_ref_record.argtypes = [c_void_p, c_uint32, POINTER(c_uint64), POINTER(c_uint32), POINTER(c_uint32)]
     lib.eref_query_popcount.argtypes = [c_void_p, c_int, POINTER(c_uint64)]
+    lib.eref_query_census.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_uint64), POINTER(c_uint64)]
+    lib.eref_query_census_device.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_uint64), POINTER(c_uint64)]
+    lib.eref_sample_ratio.argtypes = [c_uint64, c_uint64, POINTER(c_int)]
+    lib.eref_draw_keep.argtypes = [c_int, c_uint64, c_void_p]
+    lib.eref_draw_keep.restype = None
+    lib.eref_query_add_masked.argtypes = [c_void_p, c_void_p, c_size_t, c_void_p, c_uint64]
+    lib.eref_query_add_masked_device.argtypes = [c_void_p, c_void_p, c_size_t, c_void_p, c_uint64]
     lib.eref_ref_records.argtypes = [c_void_p, c_void_p, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_index_body.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t), POINTER(c_uint32)]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
@@ -168,6 +178,22 @@ class ErefGPU:
         """Count one FASTQ file held in HOST memory; returns its sequence-line byte sum (:1138-1140)."""
         a = _as_bytes_array(fastq)
         _check(self.lib, self.lib.eref_query_add(self._h, c_void_p(a.ctypes.data), a.size), "eref_query_add")
+        return self.query_seq_bytes()
+
+    def query_census(self, fastq):
+        """cal_sam_ratio's pass (:1124-1148): (bytes on sequence lines, number of sequence lines)"""
+        a = _as_bytes_array(fastq)
+        b, l = c_uint64(), c_uint64()
+        _check(self.lib, self.lib.eref_query_census(self._h, c_void_p(a.ctypes.data), a.size, byref(b), byref(l)),
+               "eref_query_census")
+        return b.value, l.value
+
+    def query_add_masked(self, fastq, keep_bits: np.ndarray, n_lines: int) -> int:
+        """read_fastq under down-sampling (:955-960): only the sequence lines whose bit is set are counted"""
+        a = _as_bytes_array(fastq)
+        k = np.ascontiguousarray(keep_bits, dtype="<u4")
+        _check(self.lib, self.lib.eref_query_add_masked(self._h, c_void_p(a.ctypes.data), a.size, c_void_p(k.ctypes.data),
+                                                        n_lines), "eref_query_add_masked")
         return self.query_seq_bytes()
 
     def query_add_device(self, ptr: int, n: int) -> int:
@@ -340,20 +366,30 @@ def shard_offsets(fasta: np.ndarray, shards: int):
     return cuts
 
 
-def check_sample_ratio(seq_bytes_fq1: int):
-    """cal_sam_ratio (:1124-1148).  Below 100 the reference down-samples with rand(): not implemented."""
-    if seq_bytes_fq1 == 0:
-        raise ErefError("fq1 holds no sequence lines (the reference divides by zero here, :1145)")
-    ratio = 100 * 2_000_000_000 // (2 * seq_bytes_fq1)
-    if ratio < 100:
-        raise ErefError("fq1 holds more than 1 Gbase: the reference's rand()-driven down-sampling (:955-960) is not "
-                        "implemented; refusing to diverge silently")
-    return ratio
+def sample_ratio(seq_bytes_fq1: int, down_sampling_size: int = DOWN_SAMPLING_SIZE) -> int:
+    """cal_sam_ratio (:1124-1148): 100 * down_sampling_size / (2 * sequence bytes of fq1); below 100 the
+    reference down-samples.  Raises where the reference divides by zero (empty fq1)."""
+    lib = load_library()
+    r = c_int()
+    _check(lib, lib.eref_sample_ratio(seq_bytes_fq1, down_sampling_size, byref(r)), "eref_sample_ratio")
+    return r.value
+
+
+def draw_keep(ratio: int, n_lines: int, reseed: bool = True) -> np.ndarray:
+    """The reference's per-read draws rand() % 100 < ratio (:955-957) as a bit mask, from libc's rand();
+    reseed: srand(1) first, as main() does (:1236-1238)."""
+    lib = load_library()
+    if reseed:
+        ctypes.CDLL("libc.so.6").srand(c_uint(1))
+    bits = np.zeros((n_lines + 31) // 32 + 1, "<u4")
+    lib.eref_draw_keep(ratio, n_lines, c_void_p(bits.ctypes.data))
+    return bits
 
 
 def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
              perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
-             bucketed: bool = True, pipelined: bool = False, chunks: int = 4, return_results: bool = False):
+             bucketed: bool = True, pipelined: bool = False, chunks: int = 4, return_results: bool = False,
+             down_sampling_size: int = DOWN_SAMPLING_SIZE):
     """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
 
     `devices`: GPUs to shard the database over (one context each, run one after the other here —
@@ -367,16 +403,34 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
     fq1, fq2, fasta = _as_bytes_array(fq1), _as_bytes_array(fq2), _as_bytes_array(fasta)
     cuts = shard_offsets(fasta, len(devices))
     parts = []
-    for i, dev in enumerate(devices):
-        with ErefGPU(coder, hit_ratio, perfect_hit_ratio, dev, prune, bucketed) as g:
-            if pipelined:
-                shard = fasta[cuts[i]:cuts[i + 1]]
-                parts.append(g.run_host(fq1, fq2, shard, chunks, cap=int(np.count_nonzero(shard == 62)) + 1).copy())
-                continue
-            check_sample_ratio(g.query_add(fq1))
-            g.query_add(fq2)
-            g.ref_set(fasta[cuts[i]:cuts[i + 1]])
-            parts.append(g.scan().copy())
+    masks = None                                           # down-sampling draws: once, shared by every shard
+    old_env = os.environ.get("EREF_DOWN_SAMPLING_SIZE")
+    os.environ["EREF_DOWN_SAMPLING_SIZE"] = str(down_sampling_size)     # read by eref_create (eref_run_host's ratio)
+    try:
+        for i, dev in enumerate(devices):
+            with ErefGPU(coder, hit_ratio, perfect_hit_ratio, dev, prune, bucketed) as g:
+                if pipelined:
+                    shard = fasta[cuts[i]:cuts[i + 1]]
+                    parts.append(g.run_host(fq1, fq2, shard, chunks, cap=int(np.count_nonzero(shard == 62)) + 1).copy())
+                    continue
+                ratio = sample_ratio(g.query_add(fq1), down_sampling_size)
+                if ratio < 100:                            # :955-960
+                    if masks is None:
+                        l1, l2 = g.query_census(fq1)[1], g.query_census(fq2)[1]
+                        k1 = draw_keep(ratio, l1)
+                        masks = (k1, l1, draw_keep(ratio, l2, reseed=False), l2)
+                    g.query_reset()
+                    g.query_add_masked(fq1, masks[0], masks[1])
+                    g.query_add_masked(fq2, masks[2], masks[3])
+                else:
+                    g.query_add(fq2)
+                g.ref_set(fasta[cuts[i]:cuts[i + 1]])
+                parts.append(g.scan().copy())
+    finally:
+        if old_env is None:
+            os.environ.pop("EREF_DOWN_SAMPLING_SIZE", None)
+        else:
+            os.environ["EREF_DOWN_SAMPLING_SIZE"] = old_env
     base = 0
     for p in parts:
         p["ordinal"] += base

@@ -27,6 +27,8 @@ class Oracle:
         lib.eo_record_codes.argtypes = [POINTER(c_int16), c_void_p, c_uint32, c_void_p]
         lib.eo_run.argtypes = [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, POINTER(c_int16), c_float,
                                c_float, c_int, POINTER(c_void_p), POINTER(c_size_t)]
+        lib.eo_run_sampled.argtypes = [c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, POINTER(c_int16), c_float,
+                                       c_float, c_int, ctypes.c_long, POINTER(c_void_p), POINTER(c_size_t)]
         lib.eo_format_line.argtypes = [c_void_p, c_char_p, c_size_t]
         lib.eo_write_index.argtypes = [c_char_p, POINTER(c_int16), c_void_p, c_size_t]
         self.libc = ctypes.CDLL("libc.so.6")
@@ -74,13 +76,14 @@ class Oracle:
         self.lib.eo_record_codes(cp, seq, len(seq), c_void_p(out.ctypes.data))
         return out
 
-    def run(self, fq1, fq2, fasta, coder, hit_ratio=0.9, perfect_hit_ratio=0.85, threads=1):
+    def run(self, fq1, fq2, fasta, coder, hit_ratio=0.9, perfect_hit_ratio=0.85, threads=1,
+            down_sampling_size=2_000_000_000):
         c, cp = self._coder(coder)
         a1, a2, af = (np.ascontiguousarray(x) for x in (fq1, fq2, fasta))
         res, n = c_void_p(), c_size_t()
-        rc = self.lib.eo_run(c_void_p(a1.ctypes.data), a1.size, c_void_p(a2.ctypes.data), a2.size,
-                             c_void_p(af.ctypes.data), af.size, cp, c_float(hit_ratio), c_float(perfect_hit_ratio),
-                             threads, byref(res), byref(n))
+        rc = self.lib.eo_run_sampled(c_void_p(a1.ctypes.data), a1.size, c_void_p(a2.ctypes.data), a2.size,
+                                     c_void_p(af.ctypes.data), af.size, cp, c_float(hit_ratio), c_float(perfect_hit_ratio),
+                                     threads, down_sampling_size, byref(res), byref(n))
         assert rc == 0
         if n.value:
             arr = np.frombuffer(ctypes.string_at(res, n.value * 16), RESULT_DTYPE).copy()

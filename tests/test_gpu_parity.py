@@ -395,3 +395,66 @@ def test_eref_binary_writes_a_reference_index(golden, tmp_path):
     r2 = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "1"], cwd=tmp_path,
                         capture_output=True, env=dict(os.environ, EREF_GPUS="1"))
     assert r2.returncode == 0 and r2.stdout.decode() == expect
+
+
+# ---- the reference's rand()-driven down-sampling -----------------------------
+
+def _downsample_fixture():
+    import json
+    from tests.conftest import load_golden, GOLDEN
+    ds = json.load(open(os.path.join(GOLDEN, "downsample.json")))
+    return (ds,) + load_golden(ds["inputs"])[1:]
+
+
+@pytest.mark.parametrize("pipelined", [False, True])
+def test_downsampling_matches_the_reference(oracle, pipelined):
+    """stdout of the diagnostic reference variant (down_sampling_size lowered so that the small fixture down-samples)"""
+    ds, fa, f1, f2 = _downsample_fixture()
+    for key, expect in ds["stdout"].items():
+        hr, phr = (float(x) for x in key.split(","))
+        text, got = eref.run_eref(f1, f2, fa, None, hr, phr, 1, coder=ds["coder"], pipelined=pipelined,
+                                  down_sampling_size=ds["down_sampling_size"], return_results=True)
+        assert text == expect, key
+        want = oracle.run(f1, f2, fa, ds["coder"], hr, phr, threads=2, down_sampling_size=ds["down_sampling_size"])
+        assert (got == want).all()
+    # two shards: the draws are made once and shared
+    text2 = eref.run_eref(f1, f2, fa, None, 0.9, 0.85, 1, coder=ds["coder"], devices=(0, 0),
+                          down_sampling_size=ds["down_sampling_size"])
+    assert text2 == ds["stdout"]["0.9,0.85"]
+
+
+def test_downsampling_table_counts_only_the_drawn_reads(oracle):
+    import collections
+    ds, fa, f1, f2 = _downsample_fixture()
+    coder = ds["coder"]
+    with eref.ErefGPU(coder) as g:
+        seq1, l1 = g.query_census(f1)
+        assert seq1 == oracle.fastq_seq_bytes(f1) and l1 == len(f1.tobytes().split(b"\n")[1::4])
+        ratio = eref.sample_ratio(seq1, ds["down_sampling_size"])
+        assert ratio == ds["ratio"]
+        k1 = eref.draw_keep(ratio, l1)
+        assert g.query_add_masked(f1, k1, l1) == seq1          # cal_sam_ratio's sum does not depend on the draws
+        cnt = collections.Counter()
+        for i, s in enumerate(f1.tobytes().split(b"\n")[1::4]):
+            if (int(k1[i >> 5]) >> (i & 31)) & 1 and len(s) >= 32:
+                c = oracle.record_codes(coder, s).reshape(-1, 3)
+                cnt.update(c[c.any(axis=1)].ravel().tolist())
+        for level in (1, 2, 3):
+            assert g.query_popcount(level) == sum(1 for v in cnt.values() if v >= level)
+
+
+def test_eref_binary_downsamples_like_the_reference(tmp_path):
+    ds, fa, f1, f2 = _downsample_fixture()
+    fa.tofile(tmp_path / "db.fa"); f1.tofile(tmp_path / "r1.fq"); f2.tofile(tmp_path / "r2.fq")
+    hdr = np.zeros(100, "<u4"); hdr[:96] = np.asarray(ds["coder"], np.uint32)
+    hdr.tofile(tmp_path / "db.fa.k32.index.dat")           # a warm run: the coder comes from the index, rand() from srand(1)
+    for gpus in ("1", "2"):
+        if gpus == "2" and eref.load_library().eref_device_count() < 2:
+            continue
+        for key, expect in ds["stdout"].items():
+            hr, phr = key.split(",")
+            r = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "1"], cwd=tmp_path,
+                               capture_output=True,
+                               env=dict(os.environ, EREF_GPUS=gpus, EREF_DOWN_SAMPLING_SIZE=str(ds["down_sampling_size"])))
+            assert r.returncode == 0, r.stderr.decode()
+            assert r.stdout.decode() == expect, f"{key} gpus={gpus}"

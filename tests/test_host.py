@@ -31,13 +31,25 @@ def test_shards_cover_all_records(oracle):
         assert parts == whole
 
 
-def test_sample_ratio_guard():
-    assert eref.check_sample_ratio(50_000_000) >= 100
-    assert eref.check_sample_ratio(1_000_000_000) == 100
+def test_sample_ratio_and_draws():
+    """cal_sam_ratio's integer arithmetic (:1144-1145) and the rand() % 100 replay (:955-957) — host-only entry points"""
+    import ctypes
+    assert eref.sample_ratio(50_000_000) == 2000
+    assert eref.sample_ratio(1_000_000_000) == 100
+    assert eref.sample_ratio(1_010_000_001) == 99                 # the reference starts to down-sample here
+    assert eref.sample_ratio(450_000, 400_000) == 44
     with pytest.raises(eref.ErefError):
-        eref.check_sample_ratio(1_000_000_001 + 10_000_000)       # ratio 99: the reference would down-sample
-    with pytest.raises(eref.ErefError):
-        eref.check_sample_ratio(0)
+        eref.sample_ratio(0)                                      # the reference divides by zero (:1145)
+    bits = eref.draw_keep(88, 1000)
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(ctypes.c_uint(1))
+    want = [libc.rand() % 100 < 88 for _ in range(1000)]
+    got = [bool((int(bits[i >> 5]) >> (i & 31)) & 1) for i in range(1000)]
+    assert got == want and 800 < sum(got) < 950
+    nxt = [libc.rand() % 100 < 88 for _ in range(10)]
+    eref.draw_keep(88, 1000)
+    more = eref.draw_keep(88, 10, reseed=False)                   # fq2 continues fq1's stream
+    assert [bool((int(more[0]) >> i) & 1) for i in range(10)] == nxt
 
 
 def test_merge_gathered_offsets_ordinals():

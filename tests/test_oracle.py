@@ -103,3 +103,19 @@ def test_live_reference_matches_oracle(oracle, tmp_path):
     from palace_b200 import eref
     coder = eref.read_coder(str(tmp_path / "db.fa.k32.index.dat"))
     assert oracle.format(oracle.run(f1, f2, db.text, coder)) == out
+
+
+def test_oracle_downsampling_matches_reference(oracle):
+    """the rand()-driven down-sampling branch (:955-960) against the diagnostic reference variant with
+    down_sampling_size lowered (tests/golden/make_golden_downsample.py)"""
+    import json
+    from tests.conftest import load_golden, GOLDEN
+    ds = json.load(open(os.path.join(GOLDEN, "downsample.json")))
+    meta, fa, f1, f2 = load_golden(ds["inputs"])
+    for key, expect in ds["stdout"].items():
+        hr, phr = (float(x) for x in key.split(","))
+        got = oracle.run(f1, f2, fa, ds["coder"], hr, phr, threads=2, down_sampling_size=ds["down_sampling_size"])
+        assert oracle.format(got) == expect, key
+    # and it really is a different answer from the unsampled run
+    full = oracle.run(f1, f2, fa, ds["coder"], 0.9, 0.85, threads=2)
+    assert oracle.format(full) != ds["stdout"]["0.9,0.85"]
