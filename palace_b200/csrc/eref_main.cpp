@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 #include <nccl.h>
 #include <unistd.h>
+#include <zlib.h>
 #include <algorithm>
 #include <atomic>
 #include <cerrno>
@@ -43,10 +44,39 @@ struct HostFile {                       // whole file in pinned host memory
     ~HostFile() { if (p) { if (pinned) cudaFreeHost(p); else free(p); } }
 };
 
+// a gzip (or bgzip, or multi-member) file is inflated on the way in; the reference itself only
+// reads plain text, so for plain files nothing changes.  The text ends up in pinned memory like any other input.
+bool read_gzip(const std::string& path, HostFile& f, std::string& err)
+{
+    gzFile gz = gzopen(path.c_str(), "rb");
+    if (!gz) { err = "cannot open " + path + ": " + strerror(errno); return false; }
+    gzbuffer(gz, 1 << 20);
+    std::vector<char> buf;
+    size_t got = 0;
+    for (;;) {
+        if (buf.size() - got < (1u << 24)) buf.resize(buf.size() + buf.size() / 2 + (1u << 26));
+        const int r = gzread(gz, buf.data() + got, (unsigned)std::min<size_t>(buf.size() - got, 1u << 30));
+        if (r < 0) { int e = 0; err = path + ": " + gzerror(gz, &e); gzclose(gz); return false; }
+        if (r == 0) break;
+        got += (size_t)r;
+    }
+    gzclose(gz);
+    void* q = nullptr;
+    if (cudaHostAlloc(&q, got + 64, cudaHostAllocDefault) == cudaSuccess) f.pinned = true;
+    else { cudaGetLastError(); q = malloc(got + 64); }
+    if (!q) { err = "out of memory reading " + path; return false; }
+    memcpy(q, buf.data(), got);
+    f.p = (char*)q; f.n = got;
+    return true;
+}
+
 bool read_file(const std::string& path, HostFile& f, std::string& err)
 {
     FILE* fp = fopen(path.c_str(), "rb");
     if (!fp) { err = "cannot open " + path + ": " + strerror(errno); return false; }
+    unsigned char magic[2] = {0, 0};
+    const size_t mg = fread(magic, 1, 2, fp);
+    if (mg == 2 && magic[0] == 0x1f && magic[1] == 0x8b) { fclose(fp); return read_gzip(path, f, err); }
     fseek(fp, 0, SEEK_END);
     long sz = ftell(fp);
     fseek(fp, 0, SEEK_SET);

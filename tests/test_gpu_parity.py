@@ -458,3 +458,20 @@ def test_eref_binary_downsamples_like_the_reference(tmp_path):
                                env=dict(os.environ, EREF_GPUS=gpus, EREF_DOWN_SAMPLING_SIZE=str(ds["down_sampling_size"])))
             assert r.returncode == 0, r.stderr.decode()
             assert r.stdout.decode() == expect, f"{key} gpus={gpus}"
+
+
+def test_eref_binary_reads_gzip_inputs(golden, tmp_path):
+    """gzip-compressed FASTQ / FASTA inputs give the stdout of the plain files"""
+    import shutil
+    name, meta, fa, f1, f2 = golden
+    from tests.conftest import GOLDEN
+    for ext, dst in (("fa", "db.fa.gz"), ("r1.fq", "r1.fq.gz"), ("r2.fq", "r2.fq.gz")):
+        shutil.copy(os.path.join(GOLDEN, f"{name}.{ext}.gz"), tmp_path / dst)
+    with open(tmp_path / "db.fa.gz.k32.coder", "w") as f:
+        f.write(" ".join(str(x) for x in meta["coder"]) + "\n")
+    key, expect = next(iter(meta["stdout"].items()))
+    hr, phr = key.split(",")
+    r = subprocess.run([eref.EREF_BIN, "r1.fq.gz", "r2.fq.gz", "db.fa.gz", "tmp_out.txt", hr, phr, "1"], cwd=tmp_path,
+                       capture_output=True, env=dict(os.environ, EREF_GPUS="1"))
+    assert r.returncode == 0, r.stderr.decode()
+    assert r.stdout.decode() == expect

@@ -99,3 +99,23 @@ def test_allgather_records_gloo_world2():
     ords = [r[0] for r in got[0]]
     assert ords == [1, 2, 3, 4, 5, 6]
     assert [r[2] for r in got[0]] == [100, 101, 102, 103, 200, 201]
+
+
+def test_get_ref_by_index_mirror(tmp_path):
+    """the consumer of eref's stdout (share/palace/scripts/get_ref_by_index.py), hand-computed:
+    index -> .fai line -> name -> single-line record; ascending index; the reference's index drift past short records"""
+    from palace_b200 import get_ref_by_index as g
+    fa = (b">p1 first phage\nACGT\nacgt \r\n>short\nAC\n>p2/1\tx\nTTTT\n\nGG\n>p3\nCCCC")
+    (tmp_path / "db.fa").write_bytes(fa)
+    (tmp_path / "db.fa.fai").write_text("p1\t8\t16\t4\t5\nshort\t2\t30\t2\t3\np2/1\t6\t41\t4\t5\np3\t4\t54\t4\t5\n")
+    # eref skipped `short` (<= 32 bases do not consume an ordinal), so its ordinal 2 is p2/1 — but the script maps
+    # ordinal 2 to the SECOND .fai line, as the reference does
+    (tmp_path / "names.txt").write_text("noise\nref_index\t3\t1\t3900\t4000\t0.975\nref_index\t1\t2\t10\t12\t0.833333\n"
+                                        "ref_index\t9\t1\t1\t1\t1\n")
+    g.main(["x", str(tmp_path / "db.fa"), str(tmp_path / "db.fa.fai"), str(tmp_path / "names.txt"),
+            str(tmp_path / "out.fa"), str(tmp_path / "out.txt")])
+    assert (tmp_path / "out.fa").read_text() == ">p1\nACGTacgt\n>p2/1\nTTTTGG\n"
+    assert (tmp_path / "out.txt").read_text() == "p1\t0.833333\np2/1\t0.975\n"
+    (tmp_path / "dup.fa").write_bytes(b">a x\nAC\n>a y\nGT\n")
+    with pytest.raises(ValueError):
+        g.fasta_records((tmp_path / "dup.fa").read_bytes())
