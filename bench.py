@@ -312,7 +312,7 @@ def run_b200(args):
                    "query_seq_bases": int(qbases), "records_per_gpu": int(info["n_records"]), "k": 32,
                    "hit_ratio": 0.9, "perfect_hit_ratio": 0.85, "parallelism": f"db-shard x{world}, query replicated",
                    "candidate_filter": not args.no_prune,
-                   "l2": "inputs larger than L2: per step 1.5 GiB of table levels are rewritten and >0.5 GB of text read"},
+                   "l2": "inputs larger than L2: per step the 512 MiB level-3 table is rewritten and 0.6 GB of text read"},
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT,
                 "h2d_bytes_per_step": int(f1_h.numel() + f2_h.numel() + fa_h.numel()),
                 "d2h_bytes_per_step": int(info["n_records"]) * 16 + 24, "ms_per_step": round(e2e_s / args.steps * 1e3, 3),

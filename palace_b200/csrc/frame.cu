@@ -219,6 +219,26 @@ k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
 
 constexpr int RING = 512;     // plane words a tile can touch (see k_pack_fasta), power of two
 
+// Keep the bits of the masks selected by sel, packed towards bit 31 in order; returns how many.  sel has few runs
+// (a newline or a header splits a chunk), so the loop runs once or twice.
+__device__ __forceinline__ int compress_masks(Masks& m, uint32_t sel)
+{
+    if (sel == 0xFFFFFFFFu) return 32;
+    uint32_t hi = 0, lo = 0, ok = 0, rest = sel;
+    int n = 0;
+    while (rest) {
+        const int k0 = __clz(rest);
+        const uint32_t inv = ~(rest << k0);
+        const int len = inv ? __clz(inv) : 32;
+        const uint32_t keep = before(len);
+        hi |= ((m.hi << k0) & keep) >> n; lo |= ((m.lo << k0) & keep) >> n; ok |= ((m.ok << k0) & keep) >> n;
+        n += len;
+        rest &= ~(~before(k0) & before(k0 + len));
+    }
+    m.hi = hi; m.lo = lo; m.ok = ok;
+    return n;
+}
+
 // A run of `len` consecutive chunk bytes starting at byte k0 goes to plane bits dest .. dest+len-1: OR it into
 // the CTA's shared-memory piece of the planes (word index modulo RING) and track the words touched.
 __device__ __forceinline__ void ring_emit(const Masks& m, int k0, int len, uint64_t dest, uint32_t* s_hi, uint32_t* s_lo,
@@ -518,21 +538,35 @@ k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __rest
     const Incoming in = incoming(c, tile_pre[blockIdx.x]);         // (syncs: the ring is zeroed)
     const uint32_t seq = ~c.m.nl & c.inr & ~c.hm & (in.in_header ? ~c.pm : 0xFFFFFFFFu);
     uint32_t wmin = 0xFFFFFFFFu, wmax = 0;
-    uint32_t rest = seq;
-    while (rest) {
-        const int k0 = __clz(rest);
-        const uint32_t inv = ~(rest << k0);
-        const int len = inv ? __clz(inv) : 32;
-        rest &= ~(~before(k0) & before(k0 + len));
-        const uint32_t r = in.rec + __popc(c.hs & before(k0));
-        if (!rec_kept[r]) continue;
-        const uint32_t rank = in.rank + __popc(seq & before(k0));
-        const uint64_t dest = (uint64_t)rec_words_ex[r] * 32 + (rank - rec_first[r]);
-        uint32_t i0, i1; bool two;
-        ring_emit(c.m, k0, len, dest, s_hi, s_lo, s_ok, wmin, wmax, i0, i1, two);
-        const uint32_t g = rec_kept_ex[r];
-        s_g[i0] = g;
-        if (two) s_g[i1] = g;
+    if (!c.hs) {
+        // no record starts inside the chunk: its sequence bytes are consecutive in the planes (newlines vanish)
+        if (seq && rec_kept[in.rec]) {
+            Masks m = c.m;
+            const int len = compress_masks(m, seq);
+            const uint64_t dest = (uint64_t)rec_words_ex[in.rec] * 32 + (in.rank - rec_first[in.rec]);
+            uint32_t i0, i1; bool two;
+            ring_emit(m, 0, len, dest, s_hi, s_lo, s_ok, wmin, wmax, i0, i1, two);
+            const uint32_t g = rec_kept_ex[in.rec];
+            s_g[i0] = g;
+            if (two) s_g[i1] = g;
+        }
+    } else {
+        uint32_t rest = seq;
+        while (rest) {                                    // one run per line piece; a header in between changes the record
+            const int k0 = __clz(rest);
+            const uint32_t inv = ~(rest << k0);
+            const int len = inv ? __clz(inv) : 32;
+            rest &= ~(~before(k0) & before(k0 + len));
+            const uint32_t r = in.rec + __popc(c.hs & before(k0));
+            if (!rec_kept[r]) continue;
+            const uint32_t rank = in.rank + __popc(seq & before(k0));
+            const uint64_t dest = (uint64_t)rec_words_ex[r] * 32 + (rank - rec_first[r]);
+            uint32_t i0, i1; bool two;
+            ring_emit(c.m, k0, len, dest, s_hi, s_lo, s_ok, wmin, wmax, i0, i1, two);
+            const uint32_t g = rec_kept_ex[r];
+            s_g[i0] = g;
+            if (two) s_g[i1] = g;
+        }
     }
     if (!ring_range(wmin, wmax)) return;                  // no sequence byte of a kept record in this tile
     for (uint32_t w = wmin + threadIdx.x; w <= wmax; w += TILE_THREADS) {

@@ -59,7 +59,7 @@ k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const
 
 // ---- P2: candidate words and the words they depend on --------------------------------------------
 // cand[w]: the sampled hits in words w-16..w of the record (a superset of every window ending in word w)
-// reach min_sample_hits = three_min - (500 - 125).  need[w]: some word in w..w+16 of the same record is a
+// reach min_sample_hits = three_min - (500 - floor(500/stride)).  need[w]: some word in w..w+16 of the same record is a
 // candidate, i.e. a position of word w lies inside a window that may be good.  One CTA produces need[] for
 // NEED_TILE words from a halo of 16 words on either side; both sliding sums are differences of block-wide
 // prefix sums.

@@ -14,6 +14,7 @@
 // coalesced), and one CTA per 2^19-slot table slice counts its codes in a 192 KiB shared-memory copy of the
 // three levels and writes the finished level-3 slice (and its summary) to HBM with plain stores.
 #include "eref_internal.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -139,8 +140,6 @@ k_coarse_scatter(Planes pl, CoderMasks m, int shift, const unsigned long long* _
 // starts 16-byte aligned), cnt = copy of the histogram, coarse_n[b] = codes of coarse bucket b,
 // chunk_start[b] = first fine-partition chunk of bucket b, totals = {codes, padded size, chunks}.
 constexpr int FINE_CHUNK = 8192;
-constexpr int FINE_THREADS = 1024;
-constexpr int FINE_PER_THREAD = FINE_CHUNK / FINE_THREADS;
 
 __global__ void __launch_bounds__(1024)
 k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned long long* __restrict__ off,
@@ -190,7 +189,8 @@ k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned
 // P2: fine partition of one coarse bucket's codes into its 2^fbits slices.  A CTA takes a chunk of
 // FINE_CHUNK codes, ranks them per slice with shared-memory atomics, reserves one range per slice, sorts the
 // chunk by slice in shared memory and writes it out, consecutive threads to consecutive addresses.
-__global__ void __launch_bounds__(FINE_THREADS, 2)
+template <int FINE_THREADS>
+__global__ void __launch_bounds__(FINE_THREADS, 2048 / FINE_THREADS >= 3 ? 3 : 2)
 k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __restrict__ slice_off,
                  const unsigned long long* __restrict__ coarse_n, const uint32_t* __restrict__ chunk_start,
                  int cbits, unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ out)
@@ -199,6 +199,7 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
     __shared__ uint32_t s_cnt[MAX_BUCKETS], s_off[MAX_BUCKETS + 1];
     __shared__ unsigned long long s_gbase[MAX_BUCKETS];
     __shared__ uint32_t s_warp[8];
+    constexpr int FINE_PER_THREAD = FINE_CHUNK / FINE_THREADS;
     const int fbits = 32 - SLICE_BITS - cbits, nf = 1 << fbits, ncoarse = 1 << cbits;
     if (blockIdx.x >= chunk_start[ncoarse]) return;                         // the grid is sized from an upper bound
     // which coarse bucket does this chunk belong to?
@@ -427,7 +428,10 @@ cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* 
                                   uint32_t* out, cudaStream_t st)
 {
     if (!nchunks) return cudaSuccess;
-    k_fine_partition<<<nchunks, FINE_THREADS, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
+    static const int threads = [] { const char* v = getenv("EREF_FINE_THREADS"); return v ? atoi(v) : 1024; }();
+    if (threads == 512) k_fine_partition<512><<<nchunks, 512, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
+    else if (threads == 256) k_fine_partition<256><<<nchunks, 256, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
+    else k_fine_partition<1024><<<nchunks, 1024, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
     return cudaGetLastError();
 }
 

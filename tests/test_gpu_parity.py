@@ -70,6 +70,19 @@ def test_seeded_parity_all_records(oracle, seed, ratios):
     assert (want["el"] > 0).any()
 
 
+@pytest.mark.parametrize("stride", [4, 5, 6, 7, 8])
+def test_every_sampling_stride_gives_the_same_records(oracle, stride, monkeypatch):
+    """the candidate filter is a bound, not an estimate: any stride 4..8, thresholds where the
+    filter is sharp (0.99), ordinary (0.85) and vacuous (0.5), same records as the oracle"""
+    monkeypatch.setenv("EREF_SAMPLE_STRIDE", str(stride))
+    db, f1, f2, _ = _case(15, cov_lo=1.0, cov_hi=6.0)
+    coder = eref.random_coder(15)
+    for ratios in ((0.9, 0.85), (0.99, 0.99), (0.8, 0.5)):
+        want = oracle.run(f1, f2, db.text, coder, *ratios, threads=4)
+        _, got = eref.run_eref(f1, f2, db.text, None, *ratios, 1, coder=coder, return_results=True)
+        assert (got == want).all(), f"stride {stride} ratios {ratios}"
+
+
 def test_table_levels_match_oracle_counts(oracle):
     """level-L bitmap popcounts == number of codes the byte table holds at >= L (bin/extract_ref.cpp:995-997)"""
     db, f1, f2, _ = _case(21, n_genomes=20, db_bp=300_000, q_bp=200_000)
