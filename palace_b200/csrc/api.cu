@@ -341,11 +341,13 @@ int finalize_table(eref_ctx* c)
     return 0;
 }
 
+constexpr uint64_t REF_TEXT_LIMIT = 0xFFFFFF00ull;     // text offsets and plane positions of one shard are 32-bit
+
 int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
 {
     cudaStream_t st = c->stream;
     c->have_ref = false;
-    if (n >= 0xFFFFFF00ull)
+    if (n >= REF_TEXT_LIMIT)
         return eref_fail(EREF_ERR_LIMIT, "reference text of %llu bytes: one shard must stay below 4 GiB",
                          (unsigned long long)n);
     int trc = start_table_update(c);          // pending query files are counted while this text is framed and packed
@@ -712,6 +714,9 @@ int eref_query_seq_bytes(eref_ctx* c, uint64_t* out)
 int eref_ref_set(eref_ctx* c, const char* fasta_host, size_t n)
 {
     if (!c || (n && !fasta_host)) return eref_fail(EREF_ERR_ARG, "eref_ref_set: null argument");
+    if (n >= REF_TEXT_LIMIT)
+        return eref_fail(EREF_ERR_LIMIT, "reference text of %llu bytes: one shard must stay below 4 GiB",
+                         (unsigned long long)n);
     CUDA_TRY(cudaSetDevice(c->device));
     CUDA_TRY(c->r_text.ensure(n + 64));
     CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
@@ -771,6 +776,7 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         return eref_fail(EREF_ERR_ARG, "eref_run_host: null argument");
     CUDA_TRY(cudaSetDevice(c->device));
     if (chunks < 1) chunks = 1;
+    if ((uint64_t)chunks < (nf >> 31) + 1) chunks = (int)std::min<uint64_t>((nf >> 31) + 1, 64);   // pieces of <= 2 GiB
     if (chunks > 64) chunks = 64;
     // piece boundaries: offsets that start a header line ('>' right after a newline)
     std::vector<size_t> cut(1, 0);
