@@ -46,6 +46,9 @@ BYTES_PER_REF_BASE_FULL = 97.0        # 1 B text + 3 probes x 32 B sector
 BYTES_PER_QUERY_BASE_BUILD = 193.0    # 1 B text + 3 codes x (32 B sector fill + 32 B write-back)
 
 
+_emit = print
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -150,7 +153,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from palace_b200 import eref
-    from palace_b200.dist import allgather_records
+    from palace_b200.dist import agree_slot, allgather_records
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -198,7 +201,9 @@ def run_b200(args):
         t3 = g.timings()
         merged = None
         if world > 1:
-            merged = allgather_records(device_records(ptr, n, dev), n)
+            if "slot" not in info:
+                info["slot"] = agree_slot(n, dev)     # once per sharded database
+            merged = allgather_records(device_records(ptr, n, dev), n, info["slot"])
         if collect:
             for p in ("query_pack_ms", "query_bucket_ms"):
                 acc[p] += t1[p] + t2[p]
@@ -214,7 +219,7 @@ def run_b200(args):
         rec = g.run_host(f1_np_h, f2_np_h, fa_np_h, chunks=args.chunks, cap=host_cap)
         if world > 1:
             t = torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(dev)
-            merged = allgather_records(t, rec.size)
+            merged = allgather_records(t, rec.size, info.get("slot"))
             return merged.cpu() if rank == 0 else None
         return rec
 
@@ -337,7 +342,7 @@ def run_b200(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(budget_runs=1)
-    print(json.dumps(out), flush=True)
+    _emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
@@ -438,7 +443,7 @@ def run_reference(args):
             "e2e": {"value": round(value, 6), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
         }
-        print(json.dumps(out), flush=True)
+        _emit(json.dumps(out))
     finally:
         arm.close()
 
@@ -456,6 +461,13 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         print(f"bench.py: warmup {args.warmup} < 3 breaks the timing rules", file=sys.stderr)
+    # stdout carries the ONE JSON line and nothing else: whatever libraries print there (NCCL's version banner,
+    # the reference's own result lines) goes to stderr while the run is in progress
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+    _emit = lambda line: os.write(json_fd, (line + "\n").encode())
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -30,18 +30,28 @@ def merge_gathered(flat: np.ndarray, counts, slot: int) -> np.ndarray:
     return np.concatenate(parts) if parts else np.zeros(0, RESULT_DTYPE)
 
 
-def allgather_records(local, n_local: int):
+def agree_slot(n_local: int, device) -> int:
+    """largest shard's record count: one scalar all_reduce(MAX).  A property of how the database was sharded, so
+    a caller that screens many samples against the same shards agrees on it once."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([n_local], dtype=torch.int64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return int(t.item())
+
+
+def allgather_records(local, n_local: int, slot: int | None = None):
     """local: (n_local, 4) int32 tensor on this rank's device (cuda under NCCL, cpu under gloo).
     Returns the merged (sum n, 4) int64 tensor on every rank, ordinals offset into file order.
-    The count of each shard travels in the same collective: one extra header row per block."""
+    The count of each shard travels in the same collective (one extra header row per block) and the merge is
+    done on the device without reading the counts back, so the step has ONE collective and one host sync."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size()
-    # the slot size must be agreed before the gather; it is data-independent host knowledge when the
-    # caller shards by record count, otherwise one tiny all_reduce(MAX) of a scalar precedes it
-    slot_t = torch.tensor([n_local], dtype=torch.int64, device=local.device)
-    dist.all_reduce(slot_t, op=dist.ReduceOp.MAX)
-    slot = int(slot_t.item())
+    if slot is None:
+        slot = agree_slot(n_local, local.device)
+    if n_local > slot:
+        raise ValueError(f"shard holds {n_local} records, agreed slot is {slot}")
     block = torch.zeros((slot + 1, 4), dtype=torch.int32, device=local.device)
     block[0, 0] = n_local
     if n_local:
@@ -49,11 +59,9 @@ def allgather_records(local, n_local: int):
     out = torch.empty((world * (slot + 1), 4), dtype=torch.int32, device=local.device)
     dist.all_gather_into_tensor(out, block)
     out = out.view(world, slot + 1, 4).to(torch.int64)
-    parts, base = [], 0
-    for r in range(world):
-        n = int(out[r, 0, 0].item())
-        p = out[r, 1: n + 1].clone()
-        p[:, 0] += base
-        base += n
-        parts.append(p)
-    return torch.cat(parts) if parts else out.new_zeros((0, 4))
+    counts = out[:, 0, 0]
+    base = torch.cumsum(counts, 0) - counts                      # records of the shards before each one
+    body = out[:, 1:, :].clone()
+    body[:, :, 0] += base[:, None]
+    valid = torch.arange(slot, device=local.device)[None, :] < counts[:, None]
+    return body[valid]
