@@ -131,8 +131,8 @@ PHASE_KERNELS = {
     "scan_summary_ms": (("k_build_summary", 0),),
     "scan_sample_ms": (("k_probe_sampled", 1),),
     "scan_cand_ms": (("k_need", 1),),
-    "scan_probe_ms": (("k_probe_full", 1),),
-    "scan_window_ms": (("k_window", 1),),
+    "scan_probe_ms": (("k_probe_list", 1),),
+    "scan_window_ms": (("k_window_list", 1),),
     "scan_interval_ms": (("k_intervals", 1),),
 }
 
@@ -267,6 +267,23 @@ def run_b200(args):
         dev_ms = e0.elapsed_time(e1)
         launches = g.timings()["kernel_launches"] - launches0
         clocks = sampler.stop() if sampler else None
+        # ---- the same sample against a database whose planes stay in HBM (eref_ref_set once, many samples) ----
+        def step_resident():
+            g.query_reset()
+            g.query_add_device(f1_d.data_ptr(), f1_d.numel())
+            g.query_add_device(f2_d.data_ptr(), f2_d.numel())
+            ptr, n = g.scan_device()
+            if world > 1:
+                allgather_records(device_records(ptr, n, dev), n, info["slot"])
+        step_resident()
+        barrier()
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record(stream)
+        for _ in range(args.steps):
+            step_resident()
+        r1.record(stream)
+        barrier()
+        res_ms = r0.elapsed_time(r1)
         # ---- e2e: host buffers through the C ABI ----
         for _ in range(min(args.warmup, 2)):
             step_host()
@@ -278,6 +295,7 @@ def run_b200(args):
         e2e_s = time.perf_counter() - t0
 
     dev_ms = max_over_ranks(dev_ms)
+    res_ms = max_over_ranks(res_ms)
     e2e_s = max_over_ranks(e2e_s)
     total_bases = sum_over_ranks(float(info["ref_bases"]))
     launches = int(sum_over_ranks(float(launches)))
@@ -290,24 +308,35 @@ def run_b200(args):
     e2e_value = total_bases / 1e9 / (e2e_s / args.steps)
     peak, peak_src = peaks()
     avg = {p: acc[p] / args.steps for p in PHASES}
-    dom = max(avg, key=avg.get)
     qbases = info["seq_bytes"]
     ntext_q = f1_d.numel() + f2_d.numel()
     codes = info["query_codes"]
     stride = int(os.environ.get("EREF_SAMPLE_STRIDE", "6"))
-    alg = {
-        # bytes the phase's kernels must move given this design, per step
+    probed_bases = info["ref_bases"] if args.no_prune else 32 * info["need_words"]
+    design = {
+        # bytes each phase's kernels must move GIVEN THIS DESIGN, per step
         "query_pack_ms": 3.0 * ntext_q + 0.375 * qbases,                       # census, kept, pack read the text; planes written
         "query_bucket_ms": 2 * 0.375 * qbases + 12.0 * codes,                  # planes read twice; codes written, read, written
         "query_count_ms": 4.0 * codes + 4.0 * (1 << 27) + 4.0 * (1 << 23),     # codes read; level 3 + summary written
         "ref_frame_ms": 1.0 * fa_d.numel(),
-        "ref_pack_ms": 1.0 * fa_d.numel() + (0.375 + 0.125) * info["ref_bases"],
+        "ref_pack_ms": 1.0 * fa_d.numel() + 2 * (0.375 + 0.125) * info["ref_bases"],   # planes zeroed, then written
         "scan_sample_ms": (0.375 + 32.0 / stride + 1.0 / 32) * info["ref_bases"],
-        "scan_cand_ms": (1 + 4 + 1) / 32.0 * info["ref_bases"],
-        "scan_probe_ms": BYTES_PER_REF_BASE_FULL * info["ref_bases"] if args.no_prune else
-        (96.0 + 0.625) * 32 * info["need_words"],
-    }.get(dom, 0.0)
+        "scan_cand_ms": (1 + 4.0 / 8 + 1 + 12) / 32.0 * info["ref_bases"],     # hits, record ids, need, zeroed single/trio/good
+        "scan_probe_ms": (96.0 + 0.625) * probed_bases,
+        "scan_window_ms": (0.25 + 0.125) * probed_bases,
+        "scan_interval_ms": 0.125 * info["ref_bases"],
+    }
+    phases = {p: {"ms": round(avg[p], 4), "design_bytes": int(design.get(p, 0)),
+                  "frac_of_hbm": round(design.get(p, 0) / 1e9 / (avg[p] / 1e3) / peak, 3) if avg[p] > 0 else None,
+                  "kernels": [n for n, t in PHASE_KERNELS[p] if t], "ncu_dram_bytes": ncu_traffic(p)}
+              for p in PHASES}
+    # the dominant KERNEL: the full probe (one launch per step = the whole scan_probe phase).  SURVEY 8(d): 97 B per
+    # reference base = 1 B of text + 3 probes x one 32 B DRAM sector; the units of a launch are the bases it probes.
+    dom = "scan_probe_ms"
+    dom_kernel = "k_probe_full" if args.no_prune else "k_probe_list"
+    alg = BYTES_PER_REF_BASE_FULL * probed_bases
     achieved = alg / 1e9 / (avg[dom] / 1e3) if avg[dom] > 0 else 0.0
+    largest = max(avg, key=avg.get)
     scan_ms = sum(avg[p] for p in PHASES if p.startswith("scan_"))
     out = {
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -327,12 +356,22 @@ def run_b200(args):
         "phases_ms": {k: round(v, 4) for k, v in avg.items()},
         "scan_only": {"ms": round(scan_ms, 4), "value": round(info["ref_bases"] / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT,
                       "need_word_fraction": round(info["need_words"] / max(info["ref_words"], 1), 4)},
-        "roofline": {"bound": "hbm", "kernel": "+".join(n for n, _ in PHASE_KERNELS[dom]), "phase": dom,
+        "db_resident": {"ms_per_step": round(res_ms / args.steps, 4),
+                        "value": round(total_bases / 1e9 / (res_ms / args.steps / 1e3), 2), "unit": UNIT,
+                        "note": "not the headline: the same step when the database's bit-planes stay in HBM across "
+                                "samples (eref_ref_set once), i.e. table build + scan + all-gather"},
+        "roofline": {"bound": "hbm", "kernel": dom_kernel, "phase": dom,
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "traffic": ncu_traffic(dom), "peak_source": peak_src,
+                     "algorithmic_bytes_per_unit": BYTES_PER_REF_BASE_FULL, "units_per_launch": int(probed_bases),
+                     "unit_name": "reference bases probed by the launch (all three streams)",
                      "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4),
-                     "note": "per step, all launches of the phase; the table build (query_count) runs beside ref_frame, "
-                             "so the phase times add up to more than ms_per_step"},
+                     "probes_per_s": round(3.0 * probed_bases / (avg[dom] / 1e3) / 1e9, 1),
+                     "note": "random 4-byte probes of a 512 MiB bitmap: this B200 answers 57-58 G/s whatever the load "
+                             "flavour (tools/probe_bench.cu; 49 G/s when nothing hits L2), and DRAM moves 64-128 B per "
+                             "32 B sector asked for, hence traffic above the algorithmic bytes",
+                     "largest_phase": largest},
+        "phases": phases,
         "survey_8d": {"table_build": {"bytes_per_query_base": BYTES_PER_QUERY_BASE_BUILD,
                                       "ms": round(sum(avg[p] for p in QUERY_PHASES), 4),
                                       "frac_of_hbm": round(BYTES_PER_QUERY_BASE_BUILD * qbases / 1e9 /

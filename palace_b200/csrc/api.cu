@@ -87,11 +87,12 @@ struct eref_ctx {
     cudaEvent_t aux_ev[2]{};
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
+    int probe_parts = 4;                       // EREF_PROBE_PARTS: rounds of the listed-word probe, 1 = whole table at once
     int bucket_bits = 5;                       // EREF_BUCKET_BITS: 2^bits coarse buckets, 2^(13-bits) slices per bucket
     // reference side
     DevBuf r_text, tile_sum, tile_pre, rec_hdr_off, rec_first, rec_len, rec_kept, rec_words,
         rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
-        sample_hits, cand, need, single, trio, good, results, codes_tmp;
+        sample_hits, need, need_list, hits0, hits1, hits2, single, trio, good, results, codes_tmp;
     const uint8_t* ref_text_dev = nullptr;    // where the current reference text lives
     uint64_t ref_text_n = 0;
     bool have_ref = false;
@@ -442,12 +443,11 @@ int scan_impl(eref_ctx* c)
     Planes pl;
     pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
     pl.nwords = nw;
-    CUDA_TRY(c->single.ensure((nw + 1) * 4)); CUDA_TRY(c->trio.ensure((nw + 1) * 4));
-    CUDA_TRY(c->good.ensure((nw + 1) * 4));
+    CUDA_TRY(c->single.ensure((nw + 64) * 4)); CUDA_TRY(c->trio.ensure((nw + 64) * 4));
+    CUDA_TRY(c->good.ensure((nw + 64) * 4));
     CUDA_TRY(c->results.ensure(((size_t)G + 1) * 16));
     const int min_sample_hits = c->three_min - (WINDOW - WINDOW / c->sample_stride);
     const bool prune = !(c->flags & EREF_FLAG_NO_PRUNE) && min_sample_hits > 0;
-    const uint8_t* need = nullptr;
     unsigned long long* need_count = c->counters.as<unsigned long long>() + 1;
     CUDA_TRY(cudaEventRecord(c->ev[E0], st));
     if (prune && c->summary_stale) {
@@ -456,22 +456,45 @@ int scan_impl(eref_ctx* c)
     }
     CUDA_TRY(cudaEventRecord(c->ev[E8], st));
     if (prune) {
-        CUDA_TRY(c->sample_hits.ensure(nw + 1)); CUDA_TRY(c->need.ensure(nw + 1));
+        // the sampled probe, then the exact candidate filter: k_need lists the words whose windows may still be good
+        // and zeroes single/trio/good everywhere; the full probe and the window rule run on the listed words only
+        CUDA_TRY(c->sample_hits.ensure(nw + 64)); CUDA_TRY(c->need.ensure(nw + 64));
+        CUDA_TRY(c->need_list.ensure((nw + 64) * 4));
         CUDA_TRY(cudaMemsetAsync(need_count, 0, 8, st));
         LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->summary, c->sample_stride, c->sample_hits.as<uint8_t>(), st));
         CUDA_TRY(cudaEventRecord(c->ev[E1], st));
-        LAUNCH(c, launch_need(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(), c->g_word.as<uint32_t>(), nw,
-                              min_sample_hits, c->need.as<uint8_t>(), need_count, st));
-        need = c->need.as<uint8_t>();
+        LAUNCH(c, launch_need(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(), nw, min_sample_hits,
+                              c->need.as<uint8_t>(), c->need_list.as<uint32_t>(), need_count, c->single.as<uint32_t>(),
+                              c->trio.as<uint32_t>(), c->good.as<uint32_t>(), st));
+        CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+        if (c->probe_parts > 1) {
+            // the table is walked one L2-sized part at a time (scan.cu, P3')
+            CUDA_TRY(c->hits0.ensure((nw + 64) * 4)); CUDA_TRY(c->hits1.ensure((nw + 64) * 4));
+            CUDA_TRY(c->hits2.ensure((nw + 64) * 4));
+            int extra = 0;
+            cudaError_t pe = launch_probe_parts(pl, c->masks, c->bm[2], c->need_list.as<uint32_t>(), need_count,
+                                                c->probe_parts, c->hits0.as<uint32_t>(), c->hits1.as<uint32_t>(),
+                                                c->hits2.as<uint32_t>(), c->single.as<uint32_t>(), c->trio.as<uint32_t>(),
+                                                st, &extra);
+            if (pe != cudaSuccess) return eref_fail(EREF_ERR_CUDA, "probe parts: %s", cudaGetErrorString(pe));
+            c->launches += extra;
+        } else {
+            LAUNCH(c, launch_probe_list(pl, c->masks, c->bm[2], c->need_list.as<uint32_t>(), need_count,
+                                        c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
+        }
+        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        LAUNCH(c, launch_window_list(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), c->need_list.as<uint32_t>(), need_count,
+                                     c->word_genome.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), nw,
+                                     c->one_min, c->three_min, c->good.as<uint32_t>(), st));
     } else {
         CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+        CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+        LAUNCH(c, launch_probe_full(pl, c->masks, c->bm[2], nullptr, c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
+        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        LAUNCH(c, launch_window(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), c->word_genome.as<uint32_t>(),
+                                c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), nw, c->one_min, c->three_min,
+                                c->good.as<uint32_t>(), st));
     }
-    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
-    LAUNCH(c, launch_probe_full(pl, c->masks, c->bm[2], need, c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
-    CUDA_TRY(cudaEventRecord(c->ev[E3], st));
-    LAUNCH(c, launch_window(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), need, c->word_genome.as<uint32_t>(),
-                            c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), nw, c->one_min, c->three_min,
-                            c->good.as<uint32_t>(), st));
     CUDA_TRY(cudaEventRecord(c->ev[E4], st));
     LAUNCH(c, launch_intervals(c->good.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), G,
                                c->results.as<uint32_t>(), st));
@@ -557,6 +580,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->table_ready, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->table_stream, cudaStreamNonBlocking);
     if (const char* v = getenv("EREF_DOWN_SAMPLING_SIZE")) { long long k = atoll(v); if (k > 0) c->down_sampling_size = (uint64_t)k; }
+    if (const char* v = getenv("EREF_PROBE_PARTS")) { int k = atoi(v); if (k == 1 || k == 2 || k == 4 || k == 8 || k == 16 || k == 32) c->probe_parts = k; }
     if (const char* v = getenv("EREF_BUCKET_BITS")) { int k = atoi(v); if (k >= 5 && k <= 8) c->bucket_bits = k; }
     for (int l = (flags & EREF_FLAG_DIRECT_COUNT) ? 0 : 2; l < 3 && e == cudaSuccess; l++)
         e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
@@ -583,7 +607,7 @@ void eref_destroy(eref_ctx* c)
                       &c->q_ok, &c->r_text, &c->tile_sum, &c->tile_pre, &c->rec_hdr_off, &c->rec_first,
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
                       &c->g_len, &c->g_word, &c->g_first, &c->r_hi, &c->r_lo, &c->r_ok, &c->word_genome,
-                      &c->sample_hits, &c->cand, &c->need, &c->single, &c->trio, &c->good, &c->results,
+                      &c->sample_hits, &c->need, &c->need_list, &c->hits0, &c->hits1, &c->hits2, &c->single, &c->trio, &c->good, &c->results,
                       &c->codes_tmp, &c->cell_pre};
     for (DevBuf* b : bufs) b->release();
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);

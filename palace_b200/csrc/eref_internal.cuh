@@ -173,13 +173,23 @@ cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long l
 // scan.cu
 cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* summary, int stride,
                                  uint8_t* sample_hits, cudaStream_t st);
-cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, const uint32_t* g_word, uint64_t nwords,
-                        int min_sample_hits, uint8_t* need, unsigned long long* need_count, cudaStream_t st);
+cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, uint64_t nwords, int min_sample_hits,
+                        uint8_t* need, uint32_t* list, unsigned long long* need_count, uint32_t* single,
+                        uint32_t* trio, uint32_t* good, cudaStream_t st);
 cudaError_t launch_probe_full(Planes pl, CoderMasks m, const uint32_t* bm3, const uint8_t* need,
                               uint32_t* single, uint32_t* trio, cudaStream_t st);
-cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint8_t* need,
-                          const uint32_t* word_genome, const uint32_t* g_word, const uint32_t* g_len,
-                          uint64_t nwords, int one_min, int three_min, uint32_t* good, cudaStream_t st);
+cudaError_t launch_probe_list(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* list,
+                              const unsigned long long* n_list, uint32_t* single, uint32_t* trio, cudaStream_t st);
+cudaError_t launch_probe_parts(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* list,
+                               const unsigned long long* n_list, int parts, uint32_t* h0w, uint32_t* h1w, uint32_t* h2w,
+                               uint32_t* single, uint32_t* trio, cudaStream_t st, int* launches);
+cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint32_t* word_genome,
+                          const uint32_t* g_word, const uint32_t* g_len, uint64_t nwords, int one_min, int three_min,
+                          uint32_t* good, cudaStream_t st);
+cudaError_t launch_window_list(const uint32_t* single, const uint32_t* trio, const uint32_t* list,
+                               const unsigned long long* n_list, const uint32_t* word_genome, const uint32_t* g_word,
+                               const uint32_t* g_len, uint64_t nwords, int one_min, int three_min, uint32_t* good,
+                               cudaStream_t st);
 cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const uint32_t* g_len,
                              uint32_t n_genomes, uint32_t* results, cudaStream_t st);
 cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,

@@ -201,8 +201,14 @@ k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
     uint32_t kept = 0, nseq = 0;
     if (off < n) {
         const uint32_t inr = before((int)min((uint64_t)32, n - off));
-        kept = __popc(seq_line_bytes(nl, line, true, keep) & inr);
-        nseq = __popc(seq_line_bytes(nl, line, false, nullptr) & inr);
+        if (keep) {
+            kept = __popc(seq_line_bytes(nl, line, true, keep) & inr);
+            nseq = __popc(seq_line_bytes(nl, line, false, nullptr) & inr);
+        } else {                                          // every sequence line is kept: one pass gives both
+            const uint32_t with_nl = seq_line_bytes(nl, line, true, nullptr) & inr;
+            kept = __popc(with_nl);
+            nseq = __popc(with_nl & ~nl);
+        }
     }
     kept = __reduce_add_sync(0xffffffffu, kept);
     nseq = __reduce_add_sync(0xffffffffu, nseq);

@@ -3,11 +3,11 @@
 // {ordinal, frag, el, ref_len}.  Replaces read_index (:813-903) + slide_window (:504-624).
 //
 // Exact candidate filter.  A window is "good" only if at least three_min of its 500 positions are
-// hit by ALL three code streams (:561), hence by stream 0.  Probing stream 0 at every 4th position
-// bounds that count from above: trio(window) <= sampled_hits(window) + 375.  Words whose bound stays
-// below three_min can never be good, so the full three-stream probe runs only on the words that can
-// influence a window that still might be.  The selected records and their numbers are unchanged;
-// random-sector probes drop from 3 per base to ~0.25 per base plus 3 per base on candidate regions.
+// hit by ALL three code streams (:561), hence by stream 0.  Probing stream 0 at every s-th position
+// bounds that count from above: trio(window) <= sampled_hits(window) + 500 - floor(500/s).  Words whose bound
+// stays below three_min can never be good, so the full three-stream probe and the window rule run only on the
+// (listed) words that can influence a window that still might be.  The selected records and their numbers are
+// unchanged; random-sector probes drop from 3 per base to 1/s per base plus 3 per base on candidate regions.
 #include "eref_internal.cuh"
 
 namespace {
@@ -58,66 +58,163 @@ k_probe_sampled(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const
 }
 
 // ---- P2: candidate words and the words they depend on --------------------------------------------
-// cand[w]: the sampled hits in words w-16..w of the record (a superset of every window ending in word w)
-// reach min_sample_hits = three_min - (500 - floor(500/stride)).  need[w]: some word in w..w+16 of the same record is a
-// candidate, i.e. a position of word w lies inside a window that may be good.  One CTA produces need[] for
-// NEED_TILE words from a halo of 16 words on either side; both sliding sums are differences of block-wide
-// prefix sums.
-constexpr int NEED_TILE = 256;
-constexpr int NEED_THREADS = NEED_TILE + 2 * WIN_WORDS;      // one thread per word of tile + halo (9 warps)
+// cand[x]: the sampled hits in words x-16..x of the record (a superset of every window ending in word x)
+// reach min_sample_hits = three_min - (500 - floor(500/stride)).  need[w]: some word in w..w+16 of the same record
+// is a candidate, i.e. a position of word w lies inside a window that may be good.
+// A thread owns NEED_SPAN = 8 consecutive words and reads the 40 hit bytes w0-16 .. w0+23 around them (five
+// 8-byte loads); both sliding sums run in registers.  When the 40 words belong to one record (two loads of
+// word_genome tell) no clipping is needed; otherwise every term is guarded by "same record".  Needed words are
+// appended to `list` (one atomicAdd per warp), and the thread zeroes single/trio/good of its words: the probe
+// and window kernels then touch only the listed words (elsewhere single = trio = good = 0, as in the reference
+// for positions no window can use).
+constexpr int NEED_SPAN = 8;
+constexpr int NEED_HALO = WIN_WORDS;                       // 16 words either side
+constexpr int NEED_N = NEED_SPAN + 2 * NEED_HALO;          // 40 entries
 
-__device__ __forceinline__ uint32_t block_inclusive_scan_288(uint32_t v, uint32_t* s_warp)
+__device__ __forceinline__ uint64_t byte_popcounts(uint64_t x)
 {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t inc = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
-    if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();
-    uint32_t base = 0;
-#pragma unroll
-    for (int k = 0; k < NEED_THREADS / 32; k++) if (k < warp) base += s_warp[k];
-    __syncthreads();
-    return base + inc;
+    x = x - ((x >> 1) & 0x5555555555555555ull);
+    x = (x & 0x3333333333333333ull) + ((x >> 2) & 0x3333333333333333ull);
+    return (x + (x >> 4)) & 0x0F0F0F0F0F0F0F0Full;
 }
 
-__global__ void __launch_bounds__(NEED_THREADS)
-k_need(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ word_genome,
-       const uint32_t* __restrict__ g_word, uint64_t nwords, int min_sample_hits, uint8_t* __restrict__ need,
-       unsigned long long* __restrict__ need_count)
+// byte i of the 40-byte string held in five 64-bit words (static i after unrolling)
+#define NEED_P(i) ((int)((pc[(i) >> 3] >> (8 * ((i) & 7))) & 0xFFull))
+
+__global__ void __launch_bounds__(256)
+k_need(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ word_genome, uint64_t nwords,
+       int min_sample_hits, uint8_t* __restrict__ need, uint32_t* __restrict__ list,
+       unsigned long long* __restrict__ need_count, uint32_t* __restrict__ single, uint32_t* __restrict__ trio,
+       uint32_t* __restrict__ good)
 {
-    __shared__ uint32_t s_P[NEED_THREADS + 1], s_C[NEED_THREADS + 1], s_warp[NEED_THREADS / 32];
-    const int e = threadIdx.x;
-    const int64_t first = (int64_t)blockIdx.x * NEED_TILE - WIN_WORDS;          // word of entry 0
-    const int64_t w = first + e;
-    const bool valid = w >= 0 && (uint64_t)w < nwords;
-    uint32_t pop = 0;
-    int64_t gs = 0, ge = 0;
-    if (valid) {
-        pop = __popc((uint32_t)sample_hits[w]);
-        const uint32_t g = word_genome[w];
-        gs = g_word[g]; ge = g_word[g + 1];
+    const uint64_t w0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * NEED_SPAN;
+    uint32_t bits = 0;                                     // bit j: word w0+j is needed
+    if (w0 < nwords) {
+        // entry i = word w0 - 16 + i, i = 0..39
+        uint64_t pc[NEED_N / 8];                           // per-entry hit counts, one byte each
+        const bool inside = w0 >= NEED_HALO && w0 + NEED_SPAN + NEED_HALO <= nwords;
+        bool one_record = false;
+        if (inside) {
+            const uint64_t* src = reinterpret_cast<const uint64_t*>(sample_hits + (w0 - NEED_HALO));
+#pragma unroll
+            for (int q = 0; q < NEED_N / 8; q++) pc[q] = byte_popcounts(src[q]);
+            one_record = word_genome[w0 - NEED_HALO] == word_genome[w0 + NEED_SPAN + NEED_HALO - 1];
+        }
+        // sliding sums over full look-backs: Sfull(k) = entries k..k+16, for candidate word w0+k
+        if (one_record) {
+            int S = 0;
+#pragma unroll
+            for (int i = 0; i <= NEED_HALO; i++) S += NEED_P(i);
+            uint32_t cm = 0;                               // bit k: word w0+k is a candidate, k = 0..23
+#pragma unroll
+            for (int k = 0; k < NEED_SPAN + NEED_HALO; k++) {
+                cm |= (uint32_t)(S >= min_sample_hits) << k;
+                if (k + 1 < NEED_SPAN + NEED_HALO) S += NEED_P(NEED_HALO + k + 1) - NEED_P(k);
+            }
+#pragma unroll
+            for (int j = 0; j < NEED_SPAN; j++) bits |= (uint32_t)(((cm >> j) & 0x1FFFFu) != 0) << j;
+        } else {
+            // general case: a record boundary (or the end of the planes) inside the 40 entries.
+            // bnd bit i: entry i starts a segment (first word of a record, or outside the planes); vld bit i: inside.
+            uint64_t bnd = 0, vld = 0;
+            if (inside) {
+                vld = (1ull << NEED_N) - 1;
+                const uint4* gsrc = reinterpret_cast<const uint4*>(word_genome + (w0 - NEED_HALO));
+                uint32_t prev = 0;
+#pragma unroll
+                for (int q = 0; q < NEED_N / 4; q++) {
+                    const uint4 g = gsrc[q];
+                    if (q) bnd |= (uint64_t)(g.x != prev) << (4 * q);
+                    bnd |= (uint64_t)(g.y != g.x) << (4 * q + 1);
+                    bnd |= (uint64_t)(g.z != g.y) << (4 * q + 2);
+                    bnd |= (uint64_t)(g.w != g.z) << (4 * q + 3);
+                    prev = g.w;
+                }
+            } else {
+                uint64_t raw[NEED_N / 8];
+#pragma unroll
+                for (int q = 0; q < NEED_N / 8; q++) raw[q] = 0;
+                uint32_t prev = 0xFFFFFFFFu;
+#pragma unroll
+                for (int i = 0; i < NEED_N; i++) {
+                    const int64_t x = (int64_t)w0 - NEED_HALO + i;
+                    const bool in = x >= 0 && (uint64_t)x < nwords;
+                    const uint32_t g = in ? word_genome[x] : 0xFFFFFFFFu;
+                    raw[i >> 3] |= (uint64_t)(in ? sample_hits[x] : (uint8_t)0) << (8 * (i & 7));
+                    vld |= (uint64_t)in << i;
+                    bnd |= (uint64_t)(!in || g != prev) << i;
+                    prev = g;
+                }
+#pragma unroll
+                for (int q = 0; q < NEED_N / 8; q++) pc[q] = byte_popcounts(raw[q]);
+            }
+            int S = 0;
+#pragma unroll
+            for (int i = 0; i <= NEED_HALO; i++) S += NEED_P(i);
+            uint32_t cm = 0;
+#pragma unroll
+            for (int k = 0; k < NEED_SPAN + NEED_HALO; k++) {
+                const int i = NEED_HALO + k;
+                // the look-back stops at the first word of the record: drop the entries k .. seg-1
+                const uint64_t below = bnd & ((2ull << i) - 1);
+                const int seg = below ? 63 - __clzll((long long)below) : 0;
+                int Sk = S;
+                if (seg > k) {
+                    const int drop = seg - k;              // 1..16 leading bytes of the 17-byte window
+                    // bytes k..k+7 and k+8..k+15 of the string
+                    const int q = k >> 3, r = 8 * (k & 7);
+                    uint64_t a = pc[q] >> r, b2 = pc[q + 1] >> r;
+                    if (r) { a |= pc[q + 1] << (64 - r); b2 |= pc[q + 2 < NEED_N / 8 ? q + 2 : q + 1] << (64 - r); }
+                    const uint64_t ma = drop >= 8 ? ~0ull : (1ull << (8 * drop)) - 1;
+                    const uint64_t mb = drop > 8 ? (drop >= 16 ? ~0ull : (1ull << (8 * (drop - 8))) - 1) : 0ull;
+                    Sk -= (int)((((a & ma) * 0x0101010101010101ull) >> 56) + (((b2 & mb) * 0x0101010101010101ull) >> 56));
+                }
+                cm |= (uint32_t)(((vld >> i) & 1ull) && Sk >= min_sample_hits) << k;
+                if (k + 1 < NEED_SPAN + NEED_HALO) S += NEED_P(NEED_HALO + k + 1) - NEED_P(k);
+            }
+#pragma unroll
+            for (int j = 0; j < NEED_SPAN; j++) {
+                const int i = NEED_HALO + j;
+                const uint64_t above = bnd >> (i + 1);     // boundaries after entry i
+                const int t = above ? __ffsll((long long)above) - 1 : 64;     // entries i .. i+t share the record
+                const int reach = t < NEED_HALO ? t : NEED_HALO;
+                const uint32_t any = (cm >> j) & ((2u << reach) - 1);
+                bits |= (uint32_t)(((vld >> i) & 1ull) && any != 0) << j;
+            }
+        }
+        if (w0 + NEED_SPAN <= nwords) {
+            uint2 nb;
+            nb.x = (bits & 1u) | ((bits & 2u) << 7) | ((bits & 4u) << 14) | ((bits & 8u) << 21);
+            nb.y = ((bits >> 4) & 1u) | ((bits & 32u) << 3) | ((bits & 64u) << 10) | ((bits & 128u) << 17);
+            *reinterpret_cast<uint2*>(need + w0) = nb;
+            const uint4 z = make_uint4(0, 0, 0, 0);
+            reinterpret_cast<uint4*>(single + w0)[0] = z; reinterpret_cast<uint4*>(single + w0)[1] = z;
+            reinterpret_cast<uint4*>(trio + w0)[0] = z;   reinterpret_cast<uint4*>(trio + w0)[1] = z;
+            reinterpret_cast<uint4*>(good + w0)[0] = z;   reinterpret_cast<uint4*>(good + w0)[1] = z;
+        } else {
+            for (int j = 0; w0 + j < nwords; j++) {
+                need[w0 + j] = (uint8_t)((bits >> j) & 1u);
+                single[w0 + j] = 0; trio[w0 + j] = 0; good[w0 + j] = 0;
+            }
+        }
     }
-    const uint32_t P = block_inclusive_scan_288(pop, s_warp);
-    s_P[e + 1] = P;
-    if (e == 0) { s_P[0] = 0; s_C[0] = 0; }
-    __syncthreads();
-    uint32_t cand = 0;
-    if (valid && e >= WIN_WORDS) {
-        const int64_t lo = max(w - WIN_WORDS, gs);                              // first word of the look-back, inside the record
-        cand = (int)(P - s_P[lo - first]) >= min_sample_hits;
+    // append the needed words to the list: exclusive prefix of the counts inside the warp, one atomic per warp
+    const int lane = threadIdx.x & 31;
+    const uint32_t cnt = __popc(bits);
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    if (total == 0) return;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(need_count, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    uint32_t* dst = list + base + (inc - cnt);
+    while (bits) {
+        const int j = __ffs(bits) - 1;
+        bits &= bits - 1;
+        *dst++ = (uint32_t)(w0 + j);
     }
-    const uint32_t C = block_inclusive_scan_288(cand, s_warp);
-    s_C[e + 1] = C;
-    __syncthreads();
-    uint32_t v = 0;
-    if (valid && e >= WIN_WORDS && e < WIN_WORDS + NEED_TILE) {
-        const int64_t hi = min(w + WIN_WORDS, ge - 1);                          // last word of the look-ahead, inside the record
-        v = s_C[hi - first + 1] - s_C[e] > 0;
-        need[w] = (uint8_t)v;
-    }
-    const uint32_t b = __ballot_sync(0xffffffffu, v != 0);
-    if ((threadIdx.x & 31) == 0 && b) atomicAdd(need_count, (unsigned long long)__popc(b));
 }
 
 // ---- P3: all three streams at every position of the needed words ----------------------------------
@@ -157,6 +254,132 @@ k_probe_full(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const ui
     single[w] = one; trio[w] = three;
 }
 
+// The same probes for the words k_need listed.  LPW lanes share a word (32/LPW positions each) so that a short
+// list still spreads over the whole GPU; the loop is warp-uniform (32/LPW list entries per warp and round), the
+// partial bit-words are OR-ed with shuffles.
+template <int LPW>
+__global__ void __launch_bounds__(256)
+k_probe_list(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const uint32_t* __restrict__ list,
+             const unsigned long long* __restrict__ n_list, uint32_t* __restrict__ single, uint32_t* __restrict__ trio)
+{
+    constexpr int PER = 32 / LPW;                          // positions per lane
+    constexpr int EPW = 32 / LPW;                          // list entries per warp and round
+    constexpr int BATCH = PER < 8 ? PER : 8;
+    const unsigned long long n = *n_list;
+    const int lane = threadIdx.x & 31, q = lane & (LPW - 1);
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long base = warp * EPW; base < n; base += nwarps * EPW) {
+        const unsigned long long e = base + (lane / LPW);
+        uint32_t one = 0, three = 0, w = 0;
+        if (e < n) {
+            w = list[e];
+            const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
+            const uint32_t mine = PER == 32 ? vm : (vm >> (32 - PER - PER * q)) & ((1u << (PER & 31)) - 1u);
+            if (mine) {
+                const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
+#pragma unroll
+                for (int s0 = 0; s0 < PER; s0 += BATCH) {
+                    uint32_t code[BATCH * 3];
+#pragma unroll
+                    for (int j = 0; j < BATCH; j++) {
+                        const int s = PER * q + s0 + j;
+                        WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                        const bool v = (vm >> (31 - s)) & 1u;
+#pragma unroll
+                        for (int i = 0; i < 3; i++) code[j * 3 + i] = v ? stream_code(m, b, i) : 0u;
+                    }
+#pragma unroll
+                    for (int j = 0; j < BATCH; j++) {
+                        const uint32_t h0 = probe(bm3, code[j * 3]), h1 = probe(bm3, code[j * 3 + 1]),
+                                       h2 = probe(bm3, code[j * 3 + 2]);
+                        one |= (h0 | h1 | h2) << (31 - PER * q - s0 - j);
+                        three |= (h0 & h1 & h2) << (31 - PER * q - s0 - j);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int d = 1; d < LPW; d <<= 1) {
+            one |= __shfl_xor_sync(0xffffffffu, one, d);
+            three |= __shfl_xor_sync(0xffffffffu, three, d);
+        }
+        if (e < n && q == 0) { single[w] = one; trio[w] = three; }
+    }
+}
+
+// ---- P3': the same probes with the table walked one part at a time ----------------------------------
+// A B200 answers random 4-byte probes at ~58 G/s when the bitmap is 512 MiB (DRAM, 64-128 B moved per probe), ~123
+// G/s at 128 MiB and ~288 G/s at <= 64 MiB (L2) — tools/probe_bench.cu.  So the listed words are probed in `parts`
+// rounds: in round r every listed word computes its codes again (cheap) and probes only those whose top bits equal
+// r, which keeps the working set of a round at 512/parts MiB.  Measured on the bench workload: 0.65 ms in one
+// round, 0.56 in two, 0.50 in four, 0.60 in eight (every round costs ~0.05 ms of code arithmetic); streaming each
+// part into L2 first (k_table_prefetch, EREF_PROBE_PREFETCH=1) does not pay.  Hits are collected per stream in
+// h0/h1/h2 (round 0 stores, later rounds OR; a word belongs to one lane quad, so no atomics), the last round
+// turns them into single = h0|h1|h2 and trio = h0&h1&h2.
+__global__ void __launch_bounds__(256)
+k_table_prefetch(const uint32_t* __restrict__ part, uint32_t lines)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < lines; i += gridDim.x * blockDim.x)
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(part + (size_t)i * 32));
+}
+
+template <int LPW>
+__global__ void __launch_bounds__(256)
+k_probe_part(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const uint32_t* __restrict__ list,
+             const unsigned long long* __restrict__ n_list, uint32_t part, int part_shift, bool first, bool last,
+             uint32_t* __restrict__ h0w, uint32_t* __restrict__ h1w, uint32_t* __restrict__ h2w,
+             uint32_t* __restrict__ single, uint32_t* __restrict__ trio)
+{
+    constexpr int PER = 32 / LPW;
+    constexpr int EPW = 32 / LPW;
+    const unsigned long long n = *n_list;
+    const int lane = threadIdx.x & 31, q = lane & (LPW - 1);
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long base = warp * EPW; base < n; base += nwarps * EPW) {
+        const unsigned long long e = base + (lane / LPW);
+        uint32_t a0 = 0, a1 = 0, a2 = 0, w = 0;
+        if (e < n) {
+            w = list[e];
+            const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
+            const uint32_t mine = (vm >> (32 - PER - PER * q)) & ((1u << PER) - 1u);
+            if (mine) {
+                const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
+                uint32_t code[PER * 3];
+#pragma unroll
+                for (int j = 0; j < PER; j++) {
+                    const int s = PER * q + j;
+                    WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                    const bool v = (vm >> (31 - s)) & 1u;
+#pragma unroll
+                    for (int i = 0; i < 3; i++) {
+                        const uint32_t c = stream_code(m, b, i);
+                        code[j * 3 + i] = (v && (c >> part_shift) == part) ? c : 0u;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < PER; j++) {
+                    a0 |= probe(bm3, code[j * 3]) << (31 - PER * q - j);
+                    a1 |= probe(bm3, code[j * 3 + 1]) << (31 - PER * q - j);
+                    a2 |= probe(bm3, code[j * 3 + 2]) << (31 - PER * q - j);
+                }
+            }
+        }
+#pragma unroll
+        for (int d = 1; d < LPW; d <<= 1) {
+            a0 |= __shfl_xor_sync(0xffffffffu, a0, d);
+            a1 |= __shfl_xor_sync(0xffffffffu, a1, d);
+            a2 |= __shfl_xor_sync(0xffffffffu, a2, d);
+        }
+        if (e < n && q == 0) {
+            if (!first) { a0 |= h0w[w]; a1 |= h1w[w]; a2 |= h2w[w]; }
+            if (last) { single[w] = a0 | a1 | a2; trio[w] = a0 & a1 & a2; }
+            else { h0w[w] = a0; h1w[w] = a1; h2w[w] = a2; }
+        }
+    }
+}
+
 // ---- P4: window counts -> good bit per position (:548-566) -----------------------------------------
 // Position p of a record looks back over [max(0,p-499), p].  For the first position of word w that is
 // bit 31 of word w, words w-1..w-15 and the low 19 bits of word w-16; each further position adds the
@@ -175,41 +398,65 @@ __device__ __forceinline__ void window_load(const uint32_t* __restrict__ plane, 
     leave = ((uint64_t)w16 << 32) | w15;
 }
 
+__device__ __forceinline__ uint32_t window_word(const uint32_t* __restrict__ single, const uint32_t* __restrict__ trio,
+                                                const uint32_t* __restrict__ word_genome,
+                                                const uint32_t* __restrict__ g_word, const uint32_t* __restrict__ g_len,
+                                                uint64_t w, int one_min, int three_min)
+{
+    const uint32_t g = word_genome[w];
+    const uint64_t gs = g_word[g];
+    const uint32_t len = g_len[g];
+    const uint32_t p0 = (uint32_t)(w - gs) << 5;
+    uint32_t s_cur, s_body, t_cur, t_body;
+    uint64_t s_leave, t_leave;
+    window_load(single, w, gs, s_cur, s_body, s_leave);
+    window_load(trio, w, gs, t_cur, t_body, t_leave);
+    int c1 = (int)s_body + (int)(s_cur >> 31);
+    int c3 = (int)t_body + (int)(t_cur >> 31);
+    uint32_t out = 0;
+#pragma unroll
+    for (int s = 0; s < 32; s++) {
+        if (c1 >= one_min && c3 >= three_min && p0 + s < len) out |= 0x80000000u >> s;
+        if (s < 31) {
+            c1 += (int)((s_cur >> (30 - s)) & 1u) - (int)((s_leave >> (50 - s)) & 1ull);
+            c3 += (int)((t_cur >> (30 - s)) & 1u) - (int)((t_leave >> (50 - s)) & 1ull);
+        }
+    }
+    return out;
+}
+
+// every word (unpruned scan)
 __global__ void __launch_bounds__(256)
-k_window(const uint32_t* __restrict__ single, const uint32_t* __restrict__ trio, const uint8_t* __restrict__ need,
+k_window(const uint32_t* __restrict__ single, const uint32_t* __restrict__ trio,
          const uint32_t* __restrict__ word_genome, const uint32_t* __restrict__ g_word,
          const uint32_t* __restrict__ g_len, uint64_t nwords, int one_min, int three_min,
          uint32_t* __restrict__ good)
 {
     uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= nwords) return;
-    uint32_t out = 0;
-    if (!need || need[w]) {
-        const uint32_t g = word_genome[w];
-        const uint64_t gs = g_word[g];
-        const uint32_t len = g_len[g];
-        const uint32_t p0 = (uint32_t)(w - gs) << 5;
-        uint32_t s_cur, s_body, t_cur, t_body;
-        uint64_t s_leave, t_leave;
-        window_load(single, w, gs, s_cur, s_body, s_leave);
-        window_load(trio, w, gs, t_cur, t_body, t_leave);
-        int c1 = (int)s_body + (int)(s_cur >> 31);
-        int c3 = (int)t_body + (int)(t_cur >> 31);
-#pragma unroll
-        for (int s = 0; s < 32; s++) {
-            if (c1 >= one_min && c3 >= three_min && p0 + s < len) out |= 0x80000000u >> s;
-            if (s < 31) {
-                c1 += (int)((s_cur >> (30 - s)) & 1u) - (int)((s_leave >> (50 - s)) & 1ull);
-                c3 += (int)((t_cur >> (30 - s)) & 1u) - (int)((t_leave >> (50 - s)) & 1ull);
-            }
-        }
+    good[w] = window_word(single, trio, word_genome, g_word, g_len, w, one_min, three_min);
+}
+
+// the listed words only (good is zero elsewhere, written by k_need)
+__global__ void __launch_bounds__(256)
+k_window_list(const uint32_t* __restrict__ single, const uint32_t* __restrict__ trio,
+              const uint32_t* __restrict__ list, const unsigned long long* __restrict__ n_list,
+              const uint32_t* __restrict__ word_genome, const uint32_t* __restrict__ g_word,
+              const uint32_t* __restrict__ g_len, int one_min, int three_min, uint32_t* __restrict__ good)
+{
+    const unsigned long long n = *n_list;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += stride) {
+        const uint32_t w = list[e];
+        good[w] = window_word(single, trio, word_genome, g_word, g_len, w, one_min, three_min);
     }
-    good[w] = out;
 }
 
 // ---- P5: good runs -> padded, merged intervals -> {ordinal, frag, el, ref_len} (:568-617) ------------
 // One warp per record walks its good words in order; the (rare) rising/falling edges are replayed by
 // every lane in lock step, so the state machine stays warp-uniform.
+constexpr int IV_UNROLL = 8;                          // 128-byte rows of a record in flight per warp
+
 __global__ void __launch_bounds__(128)
 k_intervals(const uint32_t* __restrict__ good, const uint32_t* __restrict__ g_word,
             const uint32_t* __restrict__ g_len, uint32_t n_genomes, uint32_t* __restrict__ results)
@@ -223,42 +470,57 @@ k_intervals(const uint32_t* __restrict__ good, const uint32_t* __restrict__ g_wo
     int start = 0, last_end = 0, frag = 0, el = 0;
     bool open = false;
     uint32_t carry = 0;                               // good bit of the previous position
-    for (uint32_t base = 0; base < nw; base += 32) {
-        const uint32_t idx = base + lane;
-        uint32_t x = idx < nw ? good[gs + idx] : 0u;
-        uint32_t vmask = 0;
-        if (idx < nw) {
-            uint32_t rem = (uint32_t)len - (idx << 5);
-            vmask = rem >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> rem);
+    for (uint32_t base0 = 0; base0 < nw; base0 += 32 * IV_UNROLL) {
+        uint32_t xs[IV_UNROLL];
+#pragma unroll
+        for (int u = 0; u < IV_UNROLL; u++) {
+            const uint32_t idx = base0 + u * 32 + lane;
+            xs[u] = idx < nw ? good[gs + idx] : 0u;
         }
-        x &= vmask;
-        uint32_t pb = __shfl_up_sync(0xffffffffu, x & 1u, 1);
-        if (lane == 0) pb = carry;
-        const uint32_t prev = (x >> 1) | (pb << 31);
-        const uint32_t rise = x & ~prev & vmask, fall = ~x & prev & vmask;
-        uint32_t pending = __ballot_sync(0xffffffffu, (rise | fall) != 0);
-        while (pending) {
-            const int l = __ffs(pending) - 1;
-            pending &= pending - 1;
-            const uint32_t r = __shfl_sync(0xffffffffu, rise, l), f = __shfl_sync(0xffffffffu, fall, l);
-            uint32_t e = r | f;
-            while (e) {
-                const int s = __clz(e);
-                const uint32_t bit = 0x80000000u >> s;
-                e &= ~bit;
-                const int j = (int)((base + l) << 5) + s;
-                if (r & bit) {                        // :568-574
-                    start = j - 2 * WINDOW; if (start < 1) start = 1;
-                    open = true;
-                } else {                              // :575-589
-                    int end = j + 2 * WINDOW; if (end > len) end = len;
-                    if (frag > 0 && start - last_end < WINDOW) el += end - last_end;
-                    else { frag++; el += end - start; }
-                    last_end = end; open = false;
+        uint32_t any = 0;
+#pragma unroll
+        for (int u = 0; u < IV_UNROLL; u++) any |= xs[u];
+        if (!__any_sync(0xffffffffu, any != 0) && !carry) continue;      // all clear and no run in progress
+#pragma unroll
+        for (int u = 0; u < IV_UNROLL; u++) {
+            const uint32_t base = base0 + u * 32;
+            if (base >= nw) break;
+            const uint32_t idx = base + lane;
+            uint32_t x = xs[u];
+            uint32_t vmask = 0;
+            if (idx < nw) {
+                uint32_t rem = (uint32_t)len - (idx << 5);
+                vmask = rem >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> rem);
+            }
+            x &= vmask;
+            uint32_t pb = __shfl_up_sync(0xffffffffu, x & 1u, 1);
+            if (lane == 0) pb = carry;
+            const uint32_t prev = (x >> 1) | (pb << 31);
+            const uint32_t rise = x & ~prev & vmask, fall = ~x & prev & vmask;
+            uint32_t pending = __ballot_sync(0xffffffffu, (rise | fall) != 0);
+            while (pending) {
+                const int l = __ffs(pending) - 1;
+                pending &= pending - 1;
+                const uint32_t r = __shfl_sync(0xffffffffu, rise, l), f = __shfl_sync(0xffffffffu, fall, l);
+                uint32_t e = r | f;
+                while (e) {
+                    const int s = __clz(e);
+                    const uint32_t bit = 0x80000000u >> s;
+                    e &= ~bit;
+                    const int j = (int)((base + l) << 5) + s;
+                    if (r & bit) {                        // :568-574
+                        start = j - 2 * WINDOW; if (start < 1) start = 1;
+                        open = true;
+                    } else {                              // :575-589
+                        int end = j + 2 * WINDOW; if (end > len) end = len;
+                        if (frag > 0 && start - last_end < WINDOW) el += end - last_end;
+                        else { frag++; el += end - start; }
+                        last_end = end; open = false;
+                    }
                 }
             }
+            carry = __shfl_sync(0xffffffffu, x & 1u, 31);
         }
-        carry = __shfl_sync(0xffffffffu, x & 1u, 31);
     }
     if (open) {                                       // :599-609
         if (frag > 0 && start - last_end < WINDOW) el += len - last_end;
@@ -330,12 +592,14 @@ cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, c
     return cudaGetLastError();
 }
 
-cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, const uint32_t* g_word, uint64_t nwords,
-                        int min_sample_hits, uint8_t* need, unsigned long long* need_count, cudaStream_t st)
+cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, uint64_t nwords, int min_sample_hits,
+                        uint8_t* need, uint32_t* list, unsigned long long* need_count, uint32_t* single,
+                        uint32_t* trio, uint32_t* good, cudaStream_t st)
 {
     if (!nwords) return cudaSuccess;
-    k_need<<<grid_for(nwords, NEED_TILE), NEED_THREADS, 0, st>>>(sample_hits, word_genome, g_word, nwords, min_sample_hits,
-                                                              need, need_count);
+    k_need<<<grid_for((nwords + NEED_SPAN - 1) / NEED_SPAN, 256), 256, 0, st>>>(sample_hits, word_genome, nwords,
+                                                                              min_sample_hits, need, list, need_count,
+                                                                              single, trio, good);
     return cudaGetLastError();
 }
 
@@ -347,13 +611,82 @@ cudaError_t launch_probe_full(Planes pl, CoderMasks m, const uint32_t* bm3, cons
     return cudaGetLastError();
 }
 
-cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint8_t* need,
-                          const uint32_t* word_genome, const uint32_t* g_word, const uint32_t* g_len,
-                          uint64_t nwords, int one_min, int three_min, uint32_t* good, cudaStream_t st)
+static unsigned list_grid(int per_sm)
+{
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    return (unsigned)(sms * per_sm);
+}
+
+cudaError_t launch_probe_list(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* list,
+                              const unsigned long long* n_list, uint32_t* single, uint32_t* trio, cudaStream_t st)
+{
+    if (!pl.nwords) return cudaSuccess;
+    static int lpw = 0, per_sm = 0;
+    if (!lpw) {
+        const char* v = getenv("EREF_PROBE_LPW");
+        lpw = v ? atoi(v) : 4;
+        v = getenv("EREF_PROBE_CTAS");
+        per_sm = v ? atoi(v) : 16;                      // measured: 0.70 ms at 8, 0.65 ms at 16 (bench workload)
+        if (per_sm < 1 || per_sm > 64) per_sm = 16;
+    }
+    const unsigned grid = list_grid(per_sm);
+    switch (lpw) {
+    case 1: k_probe_list<1><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, single, trio); break;
+    case 2: k_probe_list<2><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, single, trio); break;
+    case 8: k_probe_list<8><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, single, trio); break;
+    default: k_probe_list<4><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, single, trio); break;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_probe_parts(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* list,
+                               const unsigned long long* n_list, int parts, uint32_t* h0w, uint32_t* h1w, uint32_t* h2w,
+                               uint32_t* single, uint32_t* trio, cudaStream_t st, int* launches)
+{
+    if (!pl.nwords) return cudaSuccess;
+    static int per_sm = 0, prefetch = 0;          // measured: the prefetch does not pay (0.52 ms with, 0.50 without)
+    if (!per_sm) {
+        const char* v = getenv("EREF_PROBE_CTAS");
+        per_sm = v ? atoi(v) : 16;
+        if (per_sm < 1 || per_sm > 64) per_sm = 16;
+        v = getenv("EREF_PROBE_PREFETCH");
+        if (v) prefetch = atoi(v);
+    }
+    int log2p = 0;
+    while ((1 << log2p) < parts) log2p++;
+    const uint32_t part_words = TABLE_WORDS >> log2p;
+    for (int r = 0; r < parts; r++) {
+        if (prefetch) k_table_prefetch<<<list_grid(8), 256, 0, st>>>(bm3 + (size_t)r * part_words, part_words / 32);
+        k_probe_part<4><<<list_grid(per_sm), 256, 0, st>>>(pl, m, bm3, list, n_list, (uint32_t)r, 32 - log2p, r == 0,
+                                                          r == parts - 1, h0w, h1w, h2w, single, trio);
+        if (launches) *launches += 2;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_window(const uint32_t* single, const uint32_t* trio, const uint32_t* word_genome,
+                          const uint32_t* g_word, const uint32_t* g_len, uint64_t nwords, int one_min, int three_min,
+                          uint32_t* good, cudaStream_t st)
 {
     if (!nwords) return cudaSuccess;
-    k_window<<<grid_for(nwords, 256), 256, 0, st>>>(single, trio, need, word_genome, g_word, g_len, nwords,
-                                                    one_min, three_min, good);
+    k_window<<<grid_for(nwords, 256), 256, 0, st>>>(single, trio, word_genome, g_word, g_len, nwords, one_min, three_min,
+                                                    good);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_window_list(const uint32_t* single, const uint32_t* trio, const uint32_t* list,
+                               const unsigned long long* n_list, const uint32_t* word_genome, const uint32_t* g_word,
+                               const uint32_t* g_len, uint64_t nwords, int one_min, int three_min, uint32_t* good,
+                               cudaStream_t st)
+{
+    if (!nwords) return cudaSuccess;
+    k_window_list<<<list_grid(8), 256, 0, st>>>(single, trio, list, n_list, word_genome, g_word, g_len, one_min, three_min,
+                                               good);
     return cudaGetLastError();
 }
 
