@@ -272,7 +272,7 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
 {
     __shared__ uint32_t s_stage[FINE_CHUNK];
     __shared__ uint32_t s_cnt[MAX_BUCKETS], s_off[MAX_BUCKETS + 1];
-    __shared__ unsigned long long s_gbase[MAX_BUCKETS];
+    __shared__ uint32_t s_delta[MAX_BUCKETS];
     __shared__ uint32_t s_warp[8];
     constexpr int FINE_PER_THREAD = FINE_CHUNK / FINE_THREADS;
     const int fbits = 32 - SLICE_BITS - cbits, nf = 1 << fbits, ncoarse = 1 << cbits;
@@ -316,7 +316,9 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
         if (threadIdx.x < nf) {
             s_off[threadIdx.x] = base + inc - v;
             const size_t slice = ((size_t)b << fbits) + threadIdx.x;
-            s_gbase[threadIdx.x] = slice_off[slice] + (v ? atomicAdd(g_tail + slice, (unsigned long long)v) : 0ull);
+            // where element i of the sorted chunk goes, relative to the bucket's first code: s_delta[f] + i
+            s_delta[threadIdx.x] = (uint32_t)(slice_off[slice] - slice_off[(size_t)b << fbits] +
+                                              (v ? atomicAdd(g_tail + slice, (unsigned long long)v) : 0ull)) - (base + inc - v);
         }
     }
     __syncthreads();
@@ -328,10 +330,10 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
             if (u * 4 + k < cnt) s_stage[s_off[(code[4 * j + k] >> SLICE_BITS) & (nf - 1)] + rank[4 * j + k]] = code[4 * j + k];
     }
     __syncthreads();
+    uint32_t* out_b = out + slice_off[(size_t)b << fbits];
     for (uint32_t i = threadIdx.x; i < cnt; i += FINE_THREADS) {
         const uint32_t c = s_stage[i];
-        const uint32_t f = (c >> SLICE_BITS) & (nf - 1);
-        out[s_gbase[f] + (i - s_off[f])] = c;
+        out_b[s_delta[(c >> SLICE_BITS) & (nf - 1)] + i] = c;
     }
 }
 
@@ -432,6 +434,98 @@ k_count_slices(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restric
     }
 }
 
+// P3 (persistent): one CTA per SM walks the slices blockIdx.x, blockIdx.x + gridDim.x, ...  While a slice is being
+// counted and written out, the first codes of the NEXT slice are already on their way into registers, so the HBM
+// round trip and the CTA turn-around of k_count_slices (about a third of its 8.8 us per slice) disappear.
+template <bool POP>
+__global__ void __launch_bounds__(COUNT_THREADS, 1)
+k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary,
+                          unsigned long long* __restrict__ level_pop)
+{
+    extern __shared__ uint4 s_raw[];
+    uint32_t* L1 = reinterpret_cast<uint32_t*>(s_raw);
+    uint32_t* L2 = L1 + SLICE_WORDS;
+    uint32_t* L3 = L2 + SLICE_WORDS;
+    uint4 pre[2][COUNT_PRE];
+    uint64_t n_pre[2] = {0, 0};
+    auto fetch = [&](uint32_t slice) {
+#pragma unroll
+        for (int l = 0; l < 2; l++) {
+            n_pre[l] = 0;
+            if (l < lists.n && slice < (uint32_t)NSLICES) {
+                n_pre[l] = lists.cnt[l][slice];
+                const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);
+#pragma unroll
+                for (int j = 0; j < COUNT_PRE; j++) {
+                    const uint64_t u = threadIdx.x + (uint64_t)j * COUNT_THREADS;
+                    pre[l][j] = u * 4 < n_pre[l] ? __ldcs(src + u) : make_uint4(0, 0, 0, 0);
+                }
+            }
+        }
+    };
+    uint32_t p1 = 0, p2 = 0, p3 = 0;
+    fetch(blockIdx.x);
+    for (int i = threadIdx.x; i < 3 * SLICE_WORDS / 4; i += COUNT_THREADS) s_raw[i] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    for (uint32_t slice = blockIdx.x; slice < (uint32_t)NSLICES; slice += gridDim.x) {
+        // the prefetched units of this slice, then whatever the registers could not hold
+        uint4 cur[2][COUNT_PRE];
+        uint64_t n_cur[2];
+#pragma unroll
+        for (int l = 0; l < 2; l++) {
+            n_cur[l] = n_pre[l];
+#pragma unroll
+            for (int j = 0; j < COUNT_PRE; j++) cur[l][j] = pre[l][j];
+        }
+        fetch(slice + gridDim.x);                          // next slice: in flight during the atomics and the write-out
+#pragma unroll
+        for (int l = 0; l < 2; l++)
+#pragma unroll
+            for (int j = 0; j < COUNT_PRE; j++) {
+                const uint64_t u = threadIdx.x + (uint64_t)j * COUNT_THREADS;
+                if (u * 4 < n_cur[l]) count_unit(cur[l][j], (uint32_t)min((uint64_t)4, n_cur[l] - u * 4), L1, L2, L3);
+            }
+        for (int l = 0; l < lists.n; l++) {
+            const uint64_t n = lists.cnt[l][slice];
+            const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);
+            for (uint64_t u = threadIdx.x + (l < 2 ? (uint64_t)COUNT_PRE * COUNT_THREADS : 0ull); u * 4 < n; u += COUNT_THREADS)
+                count_unit(__ldcs(src + u), (uint32_t)min((uint64_t)4, n - u * 4), L1, L2, L3);
+        }
+        __syncthreads();
+        if (POP) for (int i = threadIdx.x; i < SLICE_WORDS; i += COUNT_THREADS) { p1 += __popc(L1[i]); p2 += __popc(L2[i]); p3 += __popc(L3[i]); }
+        // level 3 out, one 16-byte unit per thread and round; summary word j covers table words 16j .. 16j+15 = four
+        // consecutive units, i.e. four neighbouring lanes: 8 summary bits each, combined with two shuffles
+        uint4* dst = reinterpret_cast<uint4*>(bm3 + (size_t)slice * SLICE_WORDS);
+        const uint4* l3 = reinterpret_cast<const uint4*>(L3);
+        for (int i = threadIdx.x; i < SLICE_WORDS / 4; i += COUNT_THREADS) {
+            const uint4 v = l3[i];
+            __stcs(dst + i, v);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            uint32_t out = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                out |= (uint32_t)((w[k] & 0x0000FFFFu) != 0) << (k * 2);
+                out |= (uint32_t)((w[k] & 0xFFFF0000u) != 0) << (k * 2 + 1);
+            }
+            out <<= 8 * (i & 3);
+            out |= __shfl_xor_sync(0xffffffffu, out, 1);
+            out |= __shfl_xor_sync(0xffffffffu, out, 2);
+            if ((i & 3) == 0) summary[(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 3 * SLICE_WORDS / 4; i += COUNT_THREADS) s_raw[i] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+    }
+    if (POP) {
+        p1 = __reduce_add_sync(0xffffffffu, p1); p2 = __reduce_add_sync(0xffffffffu, p2); p3 = __reduce_add_sync(0xffffffffu, p3);
+        if ((threadIdx.x & 31) == 0) {
+            if (p1) atomicAdd(level_pop + 0, (unsigned long long)p1);
+            if (p2) atomicAdd(level_pop + 1, (unsigned long long)p2);
+            if (p3) atomicAdd(level_pop + 2, (unsigned long long)p3);
+        }
+    }
+}
+
 // summary bit = OR of 16 consecutive level-3 bits: a 32 MiB filter that stays in L2 during the scan
 // (direct build only; the partitioned build writes the summary from shared memory)
 __global__ void __launch_bounds__(256)
@@ -523,6 +617,21 @@ cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t
                                 cudaStream_t st)
 {
     const int smem = 3 * SLICE_WORDS * 4;
+    static const int persistent = [] { const char* v = getenv("EREF_COUNT_PERSISTENT"); return v ? atoi(v) : 1; }();
+    if (persistent) {
+        static int sms = 0;
+        if (!sms) {
+            int dev = 0;
+            sms = 148;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        }
+        cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                                  : cudaFuncSetAttribute(k_count_slices_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        if (level_pop) k_count_slices_persistent<true><<<sms, COUNT_THREADS, smem, st>>>(lists, bm3, summary, level_pop);
+        else k_count_slices_persistent<false><<<sms, COUNT_THREADS, smem, st>>>(lists, bm3, summary, nullptr);
+        return cudaGetLastError();
+    }
     cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                               : cudaFuncSetAttribute(k_count_slices<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
