@@ -192,7 +192,7 @@ k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
              const uint32_t* __restrict__ keep, unsigned long long* __restrict__ tile_kept,
              unsigned long long* __restrict__ seq_bytes)
 {
-    __shared__ uint32_t s_part[TILE_THREADS / 32];
+    __shared__ uint32_t s_part[TILE_THREADS / 32], s_seq[TILE_THREADS / 32];
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     uint32_t w[8];
     load32(text, n, off, w);
@@ -212,14 +212,14 @@ k_fastq_kept(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
     }
     kept = __reduce_add_sync(0xffffffffu, kept);
     nseq = __reduce_add_sync(0xffffffffu, nseq);
-    if ((threadIdx.x & 31) == 0 && nseq) atomicAdd(seq_bytes, (unsigned long long)nseq);
-    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = kept;
+    if ((threadIdx.x & 31) == 0) { s_part[threadIdx.x >> 5] = kept; s_seq[threadIdx.x >> 5] = nseq; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        uint32_t t = 0;
+        uint32_t t = 0, q = 0;
 #pragma unroll
-        for (int k = 0; k < TILE_THREADS / 32; k++) t += s_part[k];
+        for (int k = 0; k < TILE_THREADS / 32; k++) { t += s_part[k]; q += s_seq[k]; }
         tile_kept[blockIdx.x] = t;
+        if (q) atomicAdd(seq_bytes, (unsigned long long)q);       // one atomic per tile: they all hit one address
     }
 }
 
