@@ -294,6 +294,18 @@ def run_b200(args):
         barrier()
         e2e_s = time.perf_counter() - t0
 
+        # ---- what the bus alone takes: the same three pinned buffers copied to the device, nothing else running ----
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        scratch = [torch.empty_like(f1_d), torch.empty_like(f2_d), torch.empty_like(fa_d)]
+        for _ in range(2):
+            c0.record(stream)
+            for dst, src in zip(scratch, (f1_h, f2_h, fa_h)):
+                dst.copy_(src, non_blocking=True)
+            c1.record(stream)
+            stream.synchronize()
+        h2d_floor_ms = c0.elapsed_time(c1)
+        del scratch
         # ---- host-buffer sample against the resident database: what a PALACE batch does per sample ----
         def step_host_resident():
             g.query_reset()
@@ -369,7 +381,9 @@ def run_b200(args):
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT,
                 "h2d_bytes_per_step": int(f1_h.numel() + f2_h.numel() + fa_h.numel()),
                 "d2h_bytes_per_step": int(info["n_records"]) * 16 + 24, "ms_per_step": round(e2e_s / args.steps * 1e3, 3),
-                "api": f"eref_run_host(chunks={args.chunks}): pinned host buffers, H2D overlapped with kernels"},
+                "api": f"eref_run_host(chunks={args.chunks}): pinned host buffers, H2D overlapped with kernels",
+                "h2d_alone_ms": round(h2d_floor_ms, 3),
+                "h2d_alone_GBps": round((f1_h.numel() + f2_h.numel() + fa_h.numel()) / 1e6 / h2d_floor_ms, 1)},
         "gpu_launches": launches,
         "clocks": clocks,
         "phases_ms": {k: round(v, 4) for k, v in avg.items()},

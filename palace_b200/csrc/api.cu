@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <chrono>
 #include <vector>
 #include <algorithm>
 #include <new>
@@ -47,7 +48,7 @@ struct DevBuf {
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
-enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, EV_COUNT };
+enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, E10, E11, EV_COUNT };
 
 } // namespace
 
@@ -803,6 +804,9 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     if ((uint64_t)chunks < (nf >> 31) + 1) chunks = (int)std::min<uint64_t>((nf >> 31) + 1, 64);   // pieces of <= 2 GiB
     if (chunks > 64) chunks = 64;
     // piece boundaries: offsets that start a header line ('>' right after a newline)
+    // Equal pieces.  Measured alternative that lost: geometrically shrinking pieces (a small last piece should leave
+    // a short tail after the last byte lands) — every piece costs ~0.5 ms of launches and host round trips, so the
+    // small pieces queue up behind each other and the tail grows (0.65 ms with 4 equal pieces, 0.76-1.1 ms shrinking).
     std::vector<size_t> cut(1, 0);
     for (int k = 1; k < chunks; k++) {
         size_t pos = nf / chunks * k;
@@ -831,6 +835,9 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     // the copy stream must not overwrite buffers the compute stream may still be reading
     CUDA_TRY(cudaEventRecord(c->ev[E9], st));
     CUDA_TRY(cudaStreamWaitEvent(cs, c->ev[E9], 0));
+    static const bool trace = getenv("EREF_TRACE_E2E") != nullptr;
+    const auto h0 = std::chrono::steady_clock::now();
+    CUDA_TRY(cudaEventRecord(c->ev[E10], cs));
     if (n1) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fq1, n1, cudaMemcpyHostToDevice, cs));
     CUDA_TRY(cudaEventRecord(c->copy_ev[0], cs));
     if (n2) CUDA_TRY(cudaMemcpyAsync(c->q_text2.p, fq2, n2, cudaMemcpyHostToDevice, cs));
@@ -844,6 +851,8 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         CUDA_TRY(cudaEventRecord(c->copy_ev[2 + k], cs));
         doff += (len + 255) & ~(size_t)255;
     }
+    CUDA_TRY(cudaEventRecord(c->ev[E11], cs));
+    const auto h1 = std::chrono::steady_clock::now();
     int rc = eref_query_reset(c);
     if (rc) return rc;
     CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[0], 0));
@@ -912,6 +921,16 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         sum.scan_d2h_ms += c->t.scan_d2h_ms;
         sum.query_count_ms = c->t.query_count_ms;
         sum.ref_bases += c->t.ref_bases; sum.ref_words += c->t.ref_words; sum.ref_need_words += c->t.ref_need_words;
+    }
+    if (trace) {
+        const auto h2 = std::chrono::steady_clock::now();
+        float copy_ms = 0, tail_ms = 0;
+        cudaEventElapsedTime(&copy_ms, c->ev[E10], c->ev[E11]);
+        cudaEventElapsedTime(&tail_ms, c->ev[E11], c->ev[E6]);
+        fprintf(stderr, "eref_run_host: queued copies after %.3f ms, returned after %.3f ms; copies took %.3f ms on the "
+                        "device, last copy -> last result %.3f ms\n",
+                std::chrono::duration<double, std::milli>(h1 - h0).count(),
+                std::chrono::duration<double, std::milli>(h2 - h0).count(), copy_ms, tail_ms);
     }
     c->t = sum;
     c->have_ref = npieces == 1;               // per-record lookups only make sense for a single piece
