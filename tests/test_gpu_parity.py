@@ -83,6 +83,19 @@ def test_every_sampling_stride_gives_the_same_records(oracle, stride, monkeypatc
         assert (got == want).all(), f"stride {stride} ratios {ratios}"
 
 
+def test_short_read_heavy_query(oracle):
+    """BASELINE configs[4]: reads of 20-150 bases, many shorter than k (no window at all) — the dense FASTQ planes
+    hold many one-read words and reads that end inside a word"""
+    db, f1, f2, _ = _case(16, q_bp=1_500_000, min_len=20, max_len=150, cov_lo=2.0, cov_hi=8.0)
+    coder = eref.random_coder(16)
+    for ratios in ((0.9, 0.85), (0.5, 0.3)):
+        want = oracle.run(f1, f2, db.text, coder, *ratios, threads=4)
+        for pipelined in (False, True):
+            _, got = eref.run_eref(f1, f2, db.text, None, *ratios, 1, coder=coder, pipelined=pipelined, return_results=True)
+            assert (got == want).all(), f"ratios {ratios} pipelined={pipelined}"
+    assert (want["el"] > 0).any()
+
+
 def test_table_levels_match_oracle_counts(oracle):
     """level-L bitmap popcounts == number of codes the byte table holds at >= L (bin/extract_ref.cpp:995-997)"""
     db, f1, f2, _ = _case(21, n_genomes=20, db_bp=300_000, q_bp=200_000)
