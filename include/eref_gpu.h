@@ -109,7 +109,9 @@ int  eref_scan_device(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out
  * pieces at record boundaries and each piece is framed and scanned as soon as it has landed.  Writes
  * min(cap, total) records in file order with global ordinals; *n_out = total.  Includes the table reset
  * the cal_sam_ratio pass and, when it yields a ratio below 100, the rand()-replayed down-sampling
- * (EREF_ERR_UNSUPPORTED when the reference would divide by 0: fq1 without sequence lines). */
+ * (EREF_ERR_UNSUPPORTED when the reference would divide by 0: fq1 without sequence lines).
+ * fasta == NULL (nf == 0): the sample is screened against the reference already set with eref_ref_set* — one
+ * database kept in HBM, many samples — and only the two FASTQ uploads are pipelined. */
 int  eref_run_host(eref_ctx* ctx, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta,
                    size_t nf, int chunks, eref_result* out, size_t cap, size_t* n_out);
 

@@ -800,6 +800,10 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     if (!c || (n1 && !fq1) || (n2 && !fq2) || (nf && !fasta) || (cap && !out))
         return eref_fail(EREF_ERR_ARG, "eref_run_host: null argument");
     CUDA_TRY(cudaSetDevice(c->device));
+    // fasta == NULL: screen this sample against the reference that is already set (one database, many samples)
+    const bool resident = !fasta && nf == 0;
+    if (resident && !c->have_ref)
+        return eref_fail(EREF_ERR_STATE, "eref_run_host without a database needs one set by eref_ref_set");
     if (chunks < 1) chunks = 1;
     if ((uint64_t)chunks < (nf >> 31) + 1) chunks = (int)std::min<uint64_t>((nf >> 31) + 1, 64);   // pieces of <= 2 GiB
     if (chunks > 64) chunks = 64;
@@ -830,7 +834,7 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     }
     CUDA_TRY(c->q_text.ensure(n1 + 64));
     CUDA_TRY(c->q_text2.ensure(n2 + 64));
-    CUDA_TRY(c->r_text.ensure(nf + 256 * (npieces + 1)));
+    if (!resident) CUDA_TRY(c->r_text.ensure(nf + 256 * (npieces + 1)));
     cudaStream_t cs = c->copy_stream, st = c->stream;
     // the copy stream must not overwrite buffers the compute stream may still be reading
     CUDA_TRY(cudaEventRecord(c->ev[E9], st));
@@ -902,7 +906,18 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     sum.scan_interval_ms = sum.scan_d2h_ms = 0;
     sum.ref_bases = sum.ref_words = sum.ref_need_words = 0;
     size_t total = 0;
-    for (size_t k = 0; k < npieces; k++) {
+    if (resident) {
+        size_t got = 0;
+        rc = eref_scan(c, out, cap, &got);
+        if (rc) return rc;
+        total = got;
+        sum.scan_summary_ms = c->t.scan_summary_ms; sum.scan_sample_ms = c->t.scan_sample_ms;
+        sum.scan_cand_ms = c->t.scan_cand_ms; sum.scan_probe_ms = c->t.scan_probe_ms;
+        sum.scan_window_ms = c->t.scan_window_ms; sum.scan_interval_ms = c->t.scan_interval_ms;
+        sum.scan_d2h_ms = c->t.scan_d2h_ms; sum.query_count_ms = c->t.query_count_ms;
+        sum.ref_bases = c->t.ref_bases; sum.ref_words = c->t.ref_words; sum.ref_need_words = c->t.ref_need_words;
+    }
+    for (size_t k = 0; k < npieces && !resident; k++) {
         CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[2 + k], 0));
         CUDA_TRY(cudaEventRecord(c->ev[E0], st));
         rc = ref_set_impl(c, piece_dev[k], cut[k + 1] - cut[k]);
@@ -933,7 +948,7 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
                 std::chrono::duration<double, std::milli>(h2 - h0).count(), copy_ms, tail_ms);
     }
     c->t = sum;
-    c->have_ref = npieces == 1;               // per-record lookups only make sense for a single piece
+    if (!resident) c->have_ref = npieces == 1;   // per-record lookups only make sense for a single piece
     if (n_out) *n_out = total;
     return 0;
 }

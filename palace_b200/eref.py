@@ -226,14 +226,21 @@ class ErefGPU:
 
     def run_host(self, fq1, fq2, fasta, chunks: int = 4, cap: int | None = None) -> np.ndarray:
         """The whole path from host buffers in one pipelined call (H2D overlapped with the kernels)."""
-        a1, a2, af = _as_bytes_array(fq1), _as_bytes_array(fq2), _as_bytes_array(fasta)
+        a1, a2 = _as_bytes_array(fq1), _as_bytes_array(fq2)
+        if fasta is None:                                 # screen against the database already set (eref_ref_set)
+            af = np.zeros(0, np.uint8)
+            if cap is None:
+                cap = self.ref_count()[0] + 1
+        else:
+            af = _as_bytes_array(fasta)
         if cap is None:
             cap = int(af.size // 33 + 16)                 # every kept record has more than 32 bases
         if getattr(self, "_run_out", None) is None or self._run_out.size < cap:
             self._run_out = np.zeros(cap, RESULT_DTYPE)
         n = c_size_t()
         rc = self.lib.eref_run_host(self._h, c_void_p(a1.ctypes.data), a1.size, c_void_p(a2.ctypes.data), a2.size,
-                                    c_void_p(af.ctypes.data), af.size, chunks, c_void_p(self._run_out.ctypes.data), cap,
+                                    c_void_p(af.ctypes.data if fasta is not None else None), af.size, chunks,
+                                    c_void_p(self._run_out.ctypes.data), cap,
                                     byref(n))
         _check(self.lib, rc, "eref_run_host")
         return self._run_out[:min(n.value, cap)]

@@ -191,6 +191,23 @@ def test_pipelined_run_host_matches_phase_api(golden, chunks):
     assert text == meta["stdout"]["0.9,0.85"]
 
 
+def test_run_host_against_a_resident_database(golden):
+    """eref_run_host(fq1, fq2, NULL): the sample against the database set before, several samples in a row"""
+    name, meta, fa, f1, f2 = golden
+    with eref.ErefGPU(meta["coder"]) as g:
+        with pytest.raises(eref.ErefError):
+            g.run_host(f1, f2, None)                       # nothing set yet
+        g.ref_set(fa)
+        g.query_add(f1); g.query_add(f2)
+        want = g.scan().copy()
+        for a, b in ((f1, f2), (f2, f1), (f1, f2)):
+            got = g.run_host(a, b, None).copy()
+            assert (got == want).all(), name               # the table does not depend on the order of the files
+        with pytest.raises(eref.ErefError):
+            g.run_host(f1[:0], f2, None)                   # empty fq1: the reference divides by zero (:1145)
+        assert (g.run_host(f1, f2, None) == want).all()    # and the database is still set
+
+
 def test_run_host_refuses_empty_fq1():
     coder = eref.random_coder(3)
     fa = np.frombuffer(b">a\n" + b"ACGT" * 20 + b"\n", np.uint8)
