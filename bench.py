@@ -214,9 +214,32 @@ def run_b200(args):
                         query_codes=t1["query_codes"] + t2["query_codes"])
         return merged
 
+    # N > 1: the query is the same on every rank, so each rank uploads 1/N of it and NCCL all-gathers the text
+    # over NVLink; the library takes the gathered (device) text and this rank's database shard (host)
+    share = None
+    if world > 1:
+        share = []
+        for h in (f1_h, f2_h):
+            slot = (h.numel() + world - 1) // world
+            lo, hi = min(rank * slot, h.numel()), min((rank + 1) * slot, h.numel())
+            share.append({"host": h[lo:hi], "mine": torch.zeros(slot, dtype=torch.uint8, device=dev),
+                          "full": torch.empty(world * slot, dtype=torch.uint8, device=dev), "n": h.numel()})
+
+    def gathered_query():
+        out = []
+        for s_ in share:
+            s_["mine"][: s_["host"].numel()].copy_(s_["host"], non_blocking=True)
+            dist.all_gather_into_tensor(s_["full"], s_["mine"])
+            out.append(eref.DeviceBytes(s_["full"].data_ptr(), s_["n"]))
+        return out
+
     def step_host():
         # the public host-buffer call: pinned host -> (overlapped H2D) -> kernels -> D2H of the records
-        rec = g.run_host(f1_np_h, f2_np_h, fa_np_h, chunks=args.chunks, cap=host_cap)
+        if world > 1:
+            q1, q2 = gathered_query()
+            rec = g.run_host(q1, q2, fa_np_h, chunks=args.chunks, cap=host_cap)
+        else:
+            rec = g.run_host(f1_np_h, f2_np_h, fa_np_h, chunks=args.chunks, cap=host_cap)
         if world > 1:
             t = torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(dev)
             merged = allgather_records(t, rec.size, info.get("slot"))
@@ -297,10 +320,12 @@ def run_b200(args):
         # ---- what the bus alone takes: the same three pinned buffers copied to the device, nothing else running ----
         barrier()
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        scratch = [torch.empty_like(f1_d), torch.empty_like(f2_d), torch.empty_like(fa_d)]
+        h2d_srcs = (f1_h, f2_h, fa_h) if world == 1 else (share[0]["host"], share[1]["host"], fa_h)
+        h2d_bytes = sum(int(x.numel()) for x in h2d_srcs)
+        scratch = [torch.empty(x.numel(), dtype=torch.uint8, device=dev) for x in h2d_srcs]
         for _ in range(2):
             c0.record(stream)
-            for dst, src in zip(scratch, (f1_h, f2_h, fa_h)):
+            for dst, src in zip(scratch, h2d_srcs):
                 dst.copy_(src, non_blocking=True)
             c1.record(stream)
             stream.synchronize()
@@ -308,7 +333,11 @@ def run_b200(args):
         del scratch
         # ---- host-buffer sample against the resident database: what a PALACE batch does per sample ----
         def step_host_resident():
-            rec = g.run_host(f1_np_h, f2_np_h, None, cap=host_cap)     # FASTQ uploads pipelined with the table build
+            if world > 1:
+                q1, q2 = gathered_query()
+                rec = g.run_host(q1, q2, None, cap=host_cap)
+            else:
+                rec = g.run_host(f1_np_h, f2_np_h, None, cap=host_cap)  # FASTQ uploads pipelined with the table build
             if world > 1:
                 t = torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(dev)
                 allgather_records(t, rec.size, info.get("slot"))
@@ -376,11 +405,12 @@ def run_b200(args):
                    "candidate_filter": not args.no_prune,
                    "l2": "inputs larger than L2: per step the 512 MiB level-3 table is rewritten and 0.6 GB of text read"},
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT,
-                "h2d_bytes_per_step": int(f1_h.numel() + f2_h.numel() + fa_h.numel()),
+                "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(info["n_records"]) * 16 + 24, "ms_per_step": round(e2e_s / args.steps * 1e3, 3),
-                "api": f"eref_run_host(chunks={args.chunks}): pinned host buffers, H2D overlapped with kernels",
+                "api": f"eref_run_host(chunks={args.chunks}): pinned host buffers, H2D overlapped with kernels" +
+                       ("" if world == 1 else "; each rank uploads 1/N of the query text, NCCL all-gathers it over NVLink"),
                 "h2d_alone_ms": round(h2d_floor_ms, 3),
-                "h2d_alone_GBps": round((f1_h.numel() + f2_h.numel() + fa_h.numel()) / 1e6 / h2d_floor_ms, 1)},
+                "h2d_alone_GBps": round(h2d_bytes / 1e6 / h2d_floor_ms, 1)},
         "gpu_launches": launches,
         "clocks": clocks,
         "phases_ms": {k: round(v, 4) for k, v in avg.items()},

@@ -842,16 +842,17 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     static const bool trace = getenv("EREF_TRACE_E2E") != nullptr;
     const auto h0 = std::chrono::steady_clock::now();
     CUDA_TRY(cudaEventRecord(c->ev[E10], cs));
-    if (n1) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fq1, n1, cudaMemcpyHostToDevice, cs));
+    // cudaMemcpyDefault: the texts may also be device pointers (e.g. a query all-gathered over NVLink by the caller)
+    if (n1) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fq1, n1, cudaMemcpyDefault, cs));
     CUDA_TRY(cudaEventRecord(c->copy_ev[0], cs));
-    if (n2) CUDA_TRY(cudaMemcpyAsync(c->q_text2.p, fq2, n2, cudaMemcpyHostToDevice, cs));
+    if (n2) CUDA_TRY(cudaMemcpyAsync(c->q_text2.p, fq2, n2, cudaMemcpyDefault, cs));
     CUDA_TRY(cudaEventRecord(c->copy_ev[1], cs));
     std::vector<uint8_t*> piece_dev(npieces);
     size_t doff = 0;
     for (size_t k = 0; k < npieces; k++) {
         piece_dev[k] = c->r_text.as<uint8_t>() + doff;
         const size_t len = cut[k + 1] - cut[k];
-        if (len) CUDA_TRY(cudaMemcpyAsync(piece_dev[k], fasta + cut[k], len, cudaMemcpyHostToDevice, cs));
+        if (len) CUDA_TRY(cudaMemcpyAsync(piece_dev[k], fasta + cut[k], len, cudaMemcpyDefault, cs));
         CUDA_TRY(cudaEventRecord(c->copy_ev[2 + k], cs));
         doff += (len + 255) & ~(size_t)255;
     }

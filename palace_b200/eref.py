@@ -138,6 +138,13 @@ def _as_bytes_array(buf) -> np.ndarray:
     return np.frombuffer(bytes(buf) if not isinstance(buf, (bytes, bytearray, memoryview)) else buf, dtype=np.uint8)
 
 
+class DeviceBytes:
+    """n bytes of text that already sit in device memory (eref_run_host takes either kind of pointer for the FASTQ files)"""
+
+    def __init__(self, ptr: int, n: int):
+        self.ptr, self.size = int(ptr), int(n)
+
+
 class ErefGPU:
     """One context = one GPU: the query table, one reference text (whole DB or one shard), the scan."""
 
@@ -226,7 +233,10 @@ class ErefGPU:
 
     def run_host(self, fq1, fq2, fasta, chunks: int = 4, cap: int | None = None) -> np.ndarray:
         """The whole path from host buffers in one pipelined call (H2D overlapped with the kernels)."""
-        a1, a2 = _as_bytes_array(fq1), _as_bytes_array(fq2)
+        a1 = fq1 if isinstance(fq1, DeviceBytes) else _as_bytes_array(fq1)
+        a2 = fq2 if isinstance(fq2, DeviceBytes) else _as_bytes_array(fq2)
+        p1 = a1.ptr if isinstance(a1, DeviceBytes) else a1.ctypes.data
+        p2 = a2.ptr if isinstance(a2, DeviceBytes) else a2.ctypes.data
         if fasta is None:                                 # screen against the database already set (eref_ref_set)
             af = np.zeros(0, np.uint8)
             if cap is None:
@@ -238,7 +248,7 @@ class ErefGPU:
         if getattr(self, "_run_out", None) is None or self._run_out.size < cap:
             self._run_out = np.zeros(cap, RESULT_DTYPE)
         n = c_size_t()
-        rc = self.lib.eref_run_host(self._h, c_void_p(a1.ctypes.data), a1.size, c_void_p(a2.ctypes.data), a2.size,
+        rc = self.lib.eref_run_host(self._h, c_void_p(p1), a1.size, c_void_p(p2), a2.size,
                                     c_void_p(af.ctypes.data if fasta is not None else None), af.size, chunks,
                                     c_void_p(self._run_out.ctypes.data), cap,
                                     byref(n))

@@ -208,6 +208,17 @@ def test_run_host_against_a_resident_database(golden):
         assert (g.run_host(f1, f2, None) == want).all()    # and the database is still set
 
 
+def test_run_host_takes_the_query_from_device_memory(golden):
+    """the FASTQ texts may already be in HBM (a query all-gathered over NVLink): same records"""
+    import torch
+    name, meta, fa, f1, f2 = golden
+    d1, d2 = torch.from_numpy(np.array(f1)).cuda(), torch.from_numpy(np.array(f2)).cuda()
+    with eref.ErefGPU(meta["coder"]) as g:
+        want = g.run_host(f1, f2, fa).copy()
+        got = g.run_host(eref.DeviceBytes(d1.data_ptr(), d1.numel()), eref.DeviceBytes(d2.data_ptr(), d2.numel()), fa)
+        assert (got == want).all(), name
+
+
 def test_run_host_refuses_empty_fq1():
     coder = eref.random_coder(3)
     fa = np.frombuffer(b">a\n" + b"ACGT" * 20 + b"\n", np.uint8)
