@@ -122,6 +122,7 @@ QUERY_PHASES = ("query_pack_ms", "query_bucket_ms", "query_count_ms")
 PHASES = QUERY_PHASES + ("ref_frame_ms", "ref_pack_ms", "scan_summary_ms", "scan_sample_ms", "scan_cand_ms",
                          "scan_probe_ms", "scan_window_ms", "scan_interval_ms")
 # kernels of each phase (names as ncu prints them) and how often each runs per step
+PHASE_STEPS = 3                                # instrumented steps (phase times), not part of the timed region
 PHASE_KERNELS = {
     "query_pack_ms": (("k_count_newlines", 2), ("k_fastq_kept", 2), ("k_pack_fastq", 2)),
     "query_bucket_ms": (("k_slice_hist", 2), ("k_slice_offsets", 2), ("k_coarse_scatter_staged", 2), ("k_fine_partition", 2)),
@@ -191,27 +192,24 @@ def run_b200(args):
     info = {}
 
     def step_device(collect):
+        # no call below waits for its own kernels beyond the sizes the host needs for allocations; the phase times
+        # are read (which does wait) only in the instrumented steps, outside the timed region
         g.query_reset()
-        g.query_add_device(f1_d.data_ptr(), f1_d.numel())
-        t1 = g.timings()
-        g.query_add_device(f2_d.data_ptr(), f2_d.numel())
-        t2 = g.timings()
+        g.query_add_device(f1_d.data_ptr(), f1_d.numel(), want_bytes=False)
+        g.query_add_device(f2_d.data_ptr(), f2_d.numel(), want_bytes=False)
         g.ref_set_device(fa_d.data_ptr(), fa_d.numel())
-        ptr, n = g.scan_device()
-        t3 = g.timings()
+        ptr, n = g.scan_device(wait=False)
         merged = None
         if world > 1:
             if "slot" not in info:
                 info["slot"] = agree_slot(n, dev)     # once per sharded database
             merged = allgather_records(device_records(ptr, n, dev), n, info["slot"])
         if collect:
-            for p in ("query_pack_ms", "query_bucket_ms"):
-                acc[p] += t1[p] + t2[p]
-            for p in PHASES[2:]:                      # the table update itself runs lazily, inside the scan call
-                acc[p] += t3[p]
-            info.update(ref_bases=t3["ref_bases"], ref_words=t3["ref_words"], need_words=t3["ref_need_words"],
-                        seq_bytes=t1["query_seq_bytes"] + t2["query_seq_bytes"], n_records=n,
-                        query_codes=t1["query_codes"] + t2["query_codes"])
+            t = g.timings()                           # query times: sums over both files
+            for p in PHASES:
+                acc[p] += t[p]
+            info.update(ref_bases=t["ref_bases"], ref_words=t["ref_words"], need_words=t["ref_need_words"],
+                        seq_bytes=t["query_seq_bytes"], n_records=n, query_codes=t["query_codes"])
         return merged
 
     # N > 1: the query is the same on every rank, so each rank uploads 1/N of it and NCCL all-gathers the text
@@ -278,13 +276,15 @@ def run_b200(args):
     with torch.cuda.stream(stream):
         for _ in range(args.warmup):
             step_device(False)
+        for _ in range(PHASE_STEPS):                   # instrumented steps: per-phase times, outside the timed region
+            step_device(True)
         barrier()
         launches0 = g.timings()["kernel_launches"]
         sampler = ClockSampler(local) if rank == 0 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(args.steps):
-            merged = step_device(True)
+            merged = step_device(False)
         e1.record(stream)
         barrier()
         dev_ms = e0.elapsed_time(e1)
@@ -293,9 +293,9 @@ def run_b200(args):
         # ---- the same sample against a database whose planes stay in HBM (eref_ref_set once, many samples) ----
         def step_resident():
             g.query_reset()
-            g.query_add_device(f1_d.data_ptr(), f1_d.numel())
-            g.query_add_device(f2_d.data_ptr(), f2_d.numel())
-            ptr, n = g.scan_device()
+            g.query_add_device(f1_d.data_ptr(), f1_d.numel(), want_bytes=False)
+            g.query_add_device(f2_d.data_ptr(), f2_d.numel(), want_bytes=False)
+            ptr, n = g.scan_device(wait=False)
             if world > 1:
                 allgather_records(device_records(ptr, n, dev), n, info["slot"])
         step_resident()
@@ -364,7 +364,7 @@ def run_b200(args):
     value = total_bases / 1e9 / (ms_per_step / 1e3)
     e2e_value = total_bases / 1e9 / (e2e_s / args.steps)
     peak, peak_src = peaks()
-    avg = {p: acc[p] / args.steps for p in PHASES}
+    avg = {p: acc[p] / PHASE_STEPS for p in PHASES}
     qbases = info["seq_bytes"]
     ntext_q = f1_d.numel() + f2_d.numel()
     codes = info["query_codes"]

@@ -47,7 +47,7 @@ typedef struct {
 
 /* CUDA-event times of the last call of each phase, in milliseconds, and launch counts */
 typedef struct {
-    float query_h2d_ms, query_pack_ms, query_bucket_ms, query_count_ms;   /* last eref_query_add* */
+    float query_h2d_ms, query_pack_ms, query_bucket_ms, query_count_ms;   /* pack/bucket: sums over the files added since the last reset */
     float ref_h2d_ms, ref_frame_ms, ref_pack_ms;                          /* last eref_ref_set*   */
     float scan_summary_ms, scan_sample_ms, scan_cand_ms, scan_probe_ms, scan_window_ms, scan_interval_ms,
           scan_d2h_ms;                                                    /* last eref_scan*      */
@@ -103,6 +103,9 @@ int  eref_ref_count(eref_ctx* ctx, size_t* n_kept, size_t* n_records, uint64_t* 
 int  eref_scan(eref_ctx* ctx, eref_result* out, size_t cap, size_t* n_out);
 /* same, results left on the device as n_kept x 4 uint32 (for an NCCL allgather by the caller) */
 int  eref_scan_device(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out);
+/* same without waiting: the records are valid in stream order on the context's stream (eref_set_stream), e.g. for
+ * a collective the caller queues on that stream */
+int  eref_scan_device_async(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out);
 
 /* main() of the reference from the FASTQ passes on (:1242-1329) in one call, from HOST buffers (pinned for
  * overlap): H2D copies run on a copy stream while the kernels work; the FASTA text is cut into `chunks`
@@ -135,6 +138,8 @@ int  eref_index_body(eref_ctx* ctx, uint32_t first, uint32_t* out_host, size_t c
 /* table inspection (tests): number of codes with count >= level (1..3) */
 int  eref_query_popcount(eref_ctx* ctx, int level, uint64_t* out);
 
+/* Phase times are read from CUDA events lazily: the call waits for the context's stream when events of earlier
+ * calls are still outstanding. */
 int  eref_timings(eref_ctx* ctx, eref_phase_times* out);
 
 /* the stdout line of :615-617; returns bytes written, 0 if the record is not selected */

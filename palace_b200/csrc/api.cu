@@ -48,7 +48,10 @@ struct DevBuf {
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
-enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, E10, E11, EV_COUNT };
+enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, E10, E11,
+          R1, R2, R3,                              // eref_ref_set: text landed, framed, packed (E0 = before the upload)
+          S0, S1, S2, S3, S4, S5, S6, S7,          // scan: start, summary, sampled, need, probed, windows, records, copied out
+          EV_COUNT };
 
 } // namespace
 
@@ -105,6 +108,11 @@ struct eref_ctx {
     bool cell_pre_valid = false;
     eref_phase_times t{};
     uint64_t launches = 0;
+    // Phase times are collected lazily (collect_times): the calls below do not wait for their own kernels any more
+    // than they must, so the events of a call are read only after a later synchronisation covers them.
+    std::vector<cudaEvent_t> qev;              // 4 events per query file since the last reset: start, packed, partitioned, end
+    bool q_pending = false, ref_pending = false, scan_pending = false, scan_pending_d2h = false;
+    cudaEvent_t totals_ev = nullptr;           // eref_ref_set: the packed sizes have reached the host
 };
 
 namespace {
@@ -135,6 +143,59 @@ float ev_ms(eref_ctx* c, int a, int b)
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]);
     return ms;
+}
+
+cudaEvent_t* list_events(eref_ctx* c, size_t k)
+{
+    while (c->qev.size() < 4 * (k + 1)) {
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+        c->qev.push_back(e);
+    }
+    return c->qev.data() + 4 * k;
+}
+
+constexpr int HPIN_SEQ = 32;                   // h_pin[HPIN_SEQ + k]: sequence-line bytes of query file k
+
+void table_done(eref_ctx* c);
+
+// Read the events of the calls made since the last collection.  Only valid after a host synchronisation that
+// covers the main stream (and through it the table stream).
+void collect_times(eref_ctx* c)
+{
+    auto ms = [](cudaEvent_t a, cudaEvent_t b) { float v = 0; if (cudaEventElapsedTime(&v, a, b) != cudaSuccess) { cudaGetLastError(); v = 0; } return v; };
+    if (c->q_pending) {
+        float pack = 0, bucket = 0;
+        unsigned long long seq = 0, codes = 0;
+        for (size_t k = 0; k < c->n_lists; k++) {
+            cudaEvent_t* e = c->qev.data() + 4 * k;
+            pack += ms(e[0], e[1]); bucket += ms(e[1], e[2]);
+            seq += c->h_pin[HPIN_SEQ + k]; codes += c->lists[k].total;
+        }
+        // sums over the files added since the last reset
+        c->t.query_pack_ms = pack; c->t.query_bucket_ms = bucket;
+        c->t.query_seq_bytes = seq; c->t.query_codes = codes;
+        c->q_pending = false;
+    }
+    if (c->ref_pending) {
+        c->t.ref_h2d_ms = ms(c->ev[E0], c->ev[R1]);
+        c->t.ref_frame_ms = ms(c->ev[R1], c->ev[R2]);
+        c->t.ref_pack_ms = ms(c->ev[R2], c->ev[R3]);
+        c->ref_pending = false;
+    }
+    if (c->scan_pending) {
+        table_done(c);
+        c->t.scan_summary_ms = ms(c->ev[S0], c->ev[S1]);
+        c->t.scan_sample_ms = ms(c->ev[S1], c->ev[S2]);
+        c->t.scan_cand_ms = ms(c->ev[S2], c->ev[S3]);
+        c->t.scan_probe_ms = ms(c->ev[S3], c->ev[S4]);
+        c->t.scan_window_ms = ms(c->ev[S4], c->ev[S5]);
+        c->t.scan_interval_ms = ms(c->ev[S5], c->ev[S6]);
+        c->t.scan_d2h_ms = c->scan_pending_d2h ? ms(c->ev[S6], c->ev[S7]) : 0.f;
+        const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / c->sample_stride) > 0;
+        c->t.ref_need_words = pruned ? c->h_pin[6] : c->ref_words;
+        c->scan_pending = false;
+    }
 }
 
 // newline census of a text: tile_prefix[t] = newlines before tile t, tile_prefix[ntiles] = total
@@ -189,7 +250,13 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     cudaStream_t st = c->stream;
     int wrc = wait_table(c, st);              // an update still in flight reads the code lists this call rewrites
     if (wrc) return wrc;
-    CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+    const bool direct = (c->flags & EREF_FLAG_DIRECT_COUNT) != 0;
+    if (!direct && c->n_lists >= (size_t)MAX_LISTS)
+        return eref_fail(EREF_ERR_LIMIT, "more than %d query files since the last eref_query_reset", MAX_LISTS);
+    // events of this file: E1..E4 for the direct build (read at the end of this call), a set of its own otherwise
+    cudaEvent_t* qe = direct ? &c->ev[E1] : list_events(c, c->n_lists);
+    if (!qe) return eref_fail(EREF_ERR_CUDA, "cudaEventCreate failed");
+    CUDA_TRY(cudaEventRecord(qe[0], st));
     uint64_t ntiles = 0;
     int rc = newline_census(c, text, n, &ntiles);
     if (rc) return rc;
@@ -224,19 +291,17 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, st));
     LAUNCH(c, launch_pack_fastq(text, n, c->tile_prefix.as<uint32_t>(), keep, tile_kept_pre, pl, st));
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 11, plane_bits, 8, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+    CUDA_TRY(cudaEventRecord(qe[1], st));
     c->summary_stale = true;
     unsigned long long total_codes = 0;
-    if (c->flags & EREF_FLAG_DIRECT_COUNT) {
+    if (direct) {
         CUDA_TRY(cudaStreamSynchronize(st));
         pl.nwords = (c->h_pin[11] + 31) >> 5;
-        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        CUDA_TRY(cudaEventRecord(qe[2], st));
         LAUNCH(c, launch_count_kmers(pl, c->masks, c->bm[0], c->bm[1], c->bm[2], st));
     } else {
         // codes -> slice-ordered list: histogram over the 8192 table slices, exact offsets, coarse scatter from the
         // planes, fine partition through shared memory; counted by the next table build
-        if (c->n_lists >= (size_t)MAX_LISTS)
-            return eref_fail(EREF_ERR_LIMIT, "more than %d query files since the last eref_query_reset", MAX_LISTS);
         const int cbits = c->bucket_bits;
         CUDA_TRY(c->part_ctr.ensure(((size_t)NSLICES * 2 + 512 + 4) * 8 + 260 * 4));
         unsigned long long* hist = c->part_ctr.as<unsigned long long>();
@@ -265,11 +330,16 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
                                         c->codes_coarse.as<uint32_t>(), st));
         LAUNCH(c, launch_fine_partition(c->codes_coarse.as<uint32_t>(), L.off.as<unsigned long long>(), coarse_n, chunk_start,
                                         nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), st));
+        // the partition kernels are queued; nothing below waits for them (times and byte counts: collect_times)
+        CUDA_TRY(cudaEventRecord(qe[2], st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_pin + HPIN_SEQ + c->n_lists, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaEventRecord(qe[3], st));
         c->n_lists++;
         c->table_dirty = true;
-        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        c->q_pending = true;
+        return 0;
     }
-    CUDA_TRY(cudaEventRecord(c->ev[E4], st));
+    CUDA_TRY(cudaEventRecord(qe[3], st));
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 5, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     c->t.query_seq_bytes = c->h_pin[5];
@@ -277,9 +347,19 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     c->t.query_h2d_ms = ev_ms(c, E0, E1);
     c->t.query_pack_ms = ev_ms(c, E1, E2);
     c->t.query_bucket_ms = ev_ms(c, E2, E3);
-    if (c->flags & EREF_FLAG_DIRECT_COUNT) c->t.query_count_ms = ev_ms(c, E3, E4);
+    c->t.query_count_ms = ev_ms(c, E3, E4);
     return 0;
 }
+
+// sequence-line bytes of the file added last (cal_sam_ratio's sum): waits for that file's kernels
+int last_file_seq_bytes(eref_ctx* c, unsigned long long* out)
+{
+    if ((c->flags & EREF_FLAG_DIRECT_COUNT) || !c->n_lists) { *out = c->t.query_seq_bytes; return 0; }
+    CUDA_TRY(cudaEventSynchronize(c->qev[4 * (c->n_lists - 1) + 3]));
+    *out = c->h_pin[HPIN_SEQ + c->n_lists - 1];
+    return 0;
+}
+
 
 // Bring the table up to date, asynchronously: one CTA per 2^19-slot slice counts that slice's codes from every
 // file added since the last reset in shared memory and writes the level-3 slice and its summary
@@ -354,7 +434,7 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
                          (unsigned long long)n);
     int trc = start_table_update(c);          // pending query files are counted while this text is framed and packed
     if (trc) return trc;
-    CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+    CUDA_TRY(cudaEventRecord(c->ev[R1], st));
     // 1. per-tile framing summaries and their prefix: line/header state, records and sequence bytes before each tile
     const uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
     CUDA_TRY(c->tile_sum.ensure((ntiles + 1) * sizeof(TileSum)));
@@ -403,7 +483,8 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
                                   c->g_rec.as<uint32_t>(), c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(),
                                   c->g_first.as<uint32_t>(), c->word_genome.as<uint32_t>(), totals + 1, st));
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 2, totals, 24, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+    CUDA_TRY(cudaEventRecord(c->totals_ev, st));
+    CUDA_TRY(cudaEventRecord(c->ev[R2], st));
     // 3. text -> planes (OR-ed into zeroed planes: words on tile boundaries are shared by two CTAs)
     Planes pl;
     pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
@@ -414,8 +495,8 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     LAUNCH(c, launch_pack_fasta(text, n, tile_pre, ntiles, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(),
                                 c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(), pl,
                                 c->word_genome.as<uint32_t>(), st));
-    CUDA_TRY(cudaEventRecord(c->ev[E3], st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaEventRecord(c->ev[R3], st));
+    CUDA_TRY(cudaEventSynchronize(c->totals_ev));     // the sizes are here; the packing kernel is still running
     const uint64_t bases = c->h_pin[2];
     const uint32_t n_genomes = (uint32_t)c->h_pin[3], n_words = (uint32_t)c->h_pin[4];
     c->host_tables_valid = false;             // ordinal -> length / packed offset / header offset: fetched on demand
@@ -424,9 +505,7 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     c->n_recs = n_recs; c->n_genomes = n_genomes;
     c->ref_words = n_words; c->ref_bases = bases;
     c->have_ref = true;
-    c->t.ref_h2d_ms = ev_ms(c, E0, E1);
-    c->t.ref_frame_ms = ev_ms(c, E1, E2);
-    c->t.ref_pack_ms = ev_ms(c, E2, E3);
+    c->ref_pending = true;
     c->t.ref_bases = bases; c->t.ref_words = n_words;
     return 0;
 }
@@ -450,12 +529,12 @@ int scan_impl(eref_ctx* c)
     const int min_sample_hits = c->three_min - (WINDOW - WINDOW / c->sample_stride);
     const bool prune = !(c->flags & EREF_FLAG_NO_PRUNE) && min_sample_hits > 0;
     unsigned long long* need_count = c->counters.as<unsigned long long>() + 1;
-    CUDA_TRY(cudaEventRecord(c->ev[E0], st));
+    CUDA_TRY(cudaEventRecord(c->ev[S0], st));
     if (prune && c->summary_stale) {
         LAUNCH(c, launch_build_summary(c->bm[2], c->summary, SUMMARY_WORDS, st));
         c->summary_stale = false;
     }
-    CUDA_TRY(cudaEventRecord(c->ev[E8], st));
+    CUDA_TRY(cudaEventRecord(c->ev[S1], st));
     if (prune) {
         // the sampled probe, then the exact candidate filter: k_need lists the words whose windows may still be good
         // and zeroes single/trio/good everywhere; the full probe and the window rule run on the listed words only
@@ -463,11 +542,11 @@ int scan_impl(eref_ctx* c)
         CUDA_TRY(c->need_list.ensure((nw + 64) * 4));
         CUDA_TRY(cudaMemsetAsync(need_count, 0, 8, st));
         LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->summary, c->sample_stride, c->sample_hits.as<uint8_t>(), st));
-        CUDA_TRY(cudaEventRecord(c->ev[E1], st));
+        CUDA_TRY(cudaEventRecord(c->ev[S2], st));
         LAUNCH(c, launch_need(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(), nw, min_sample_hits,
                               c->need.as<uint8_t>(), c->need_list.as<uint32_t>(), need_count, c->single.as<uint32_t>(),
                               c->trio.as<uint32_t>(), c->good.as<uint32_t>(), st));
-        CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+        CUDA_TRY(cudaEventRecord(c->ev[S3], st));
         if (c->probe_parts > 1) {
             // the table is walked one L2-sized part at a time (scan.cu, P3')
             CUDA_TRY(c->hits0.ensure((nw + 64) * 4)); CUDA_TRY(c->hits1.ensure((nw + 64) * 4));
@@ -483,23 +562,23 @@ int scan_impl(eref_ctx* c)
             LAUNCH(c, launch_probe_list(pl, c->masks, c->bm[2], c->need_list.as<uint32_t>(), need_count,
                                         c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
         }
-        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        CUDA_TRY(cudaEventRecord(c->ev[S4], st));
         LAUNCH(c, launch_window_list(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), c->need_list.as<uint32_t>(), need_count,
                                      c->word_genome.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), nw,
                                      c->one_min, c->three_min, c->good.as<uint32_t>(), st));
     } else {
-        CUDA_TRY(cudaEventRecord(c->ev[E1], st));
-        CUDA_TRY(cudaEventRecord(c->ev[E2], st));
+        CUDA_TRY(cudaEventRecord(c->ev[S2], st));
+        CUDA_TRY(cudaEventRecord(c->ev[S3], st));
         LAUNCH(c, launch_probe_full(pl, c->masks, c->bm[2], nullptr, c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
-        CUDA_TRY(cudaEventRecord(c->ev[E3], st));
+        CUDA_TRY(cudaEventRecord(c->ev[S4], st));
         LAUNCH(c, launch_window(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), c->word_genome.as<uint32_t>(),
                                 c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), nw, c->one_min, c->three_min,
                                 c->good.as<uint32_t>(), st));
     }
-    CUDA_TRY(cudaEventRecord(c->ev[E4], st));
+    CUDA_TRY(cudaEventRecord(c->ev[S5], st));
     LAUNCH(c, launch_intervals(c->good.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), G,
                                c->results.as<uint32_t>(), st));
-    CUDA_TRY(cudaEventRecord(c->ev[E5], st));
+    CUDA_TRY(cudaEventRecord(c->ev[S6], st));
     return 0;
 }
 
@@ -516,17 +595,6 @@ int fetch_host_tables(eref_ctx* c)
     CUDA_TRY(cudaMemcpy(c->h_rec_hdr_off.data(), c->rec_hdr_off.p, (size_t)c->n_recs * 4, cudaMemcpyDeviceToHost));
     c->host_tables_valid = true;
     return 0;
-}
-
-void scan_times(eref_ctx* c, bool with_d2h)
-{
-    c->t.scan_summary_ms = ev_ms(c, E0, E8);
-    c->t.scan_sample_ms = ev_ms(c, E8, E1);
-    c->t.scan_cand_ms = ev_ms(c, E1, E2);
-    c->t.scan_probe_ms = ev_ms(c, E2, E3);
-    c->t.scan_window_ms = ev_ms(c, E3, E4);
-    c->t.scan_interval_ms = ev_ms(c, E4, E5);
-    c->t.scan_d2h_ms = with_d2h ? ev_ms(c, E5, E6) : 0.f;
 }
 
 } // namespace
@@ -579,6 +647,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreate(&c->evf[i]);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&c->aux_ev[i], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->table_ready, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->totals_ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->table_stream, cudaStreamNonBlocking);
     if (const char* v = getenv("EREF_DOWN_SAMPLING_SIZE")) { long long k = atoll(v); if (k > 0) c->down_sampling_size = (uint64_t)k; }
     if (const char* v = getenv("EREF_PROBE_PARTS")) { int k = atoi(v); if (k == 1 || k == 2 || k == 4 || k == 8 || k == 16 || k == 32) c->probe_parts = k; }
@@ -619,6 +688,8 @@ void eref_destroy(eref_ctx* c)
     for (int i = 0; i < 2; i++) if (c->evf[i]) cudaEventDestroy(c->evf[i]);
     for (int i = 0; i < 2; i++) if (c->aux_ev[i]) cudaEventDestroy(c->aux_ev[i]);
     if (c->table_ready) cudaEventDestroy(c->table_ready);
+    if (c->totals_ev) cudaEventDestroy(c->totals_ev);
+    for (cudaEvent_t e : c->qev) cudaEventDestroy(e);
     if (c->table_stream) cudaStreamDestroy(c->table_stream);
     for (int i = 0; i < EV_COUNT; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -643,6 +714,7 @@ int eref_query_reset(eref_ctx* c)
     CUDA_TRY(cudaSetDevice(c->device));
     c->summary_stale = true;
     c->n_lists = 0;
+    c->q_pending = false;
     c->table_dirty = true;                     // rebuilt (to the empty table if nothing is added) before the next use
     if (c->flags & EREF_FLAG_DIRECT_COUNT) {
         int wrc = wait_table(c, c->stream);
@@ -732,7 +804,10 @@ void eref_draw_keep(int ratio, uint64_t n_lines, uint32_t* keep_bits)
 int eref_query_seq_bytes(eref_ctx* c, uint64_t* out)
 {
     if (!c || !out) return eref_fail(EREF_ERR_ARG, "null argument");
-    *out = c->t.query_seq_bytes;
+    unsigned long long v = 0;
+    int rc = last_file_seq_bytes(c, &v);
+    if (rc) return rc;
+    *out = v;
     return 0;
 }
 
@@ -778,12 +853,10 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     size_t n = c->n_genomes < cap ? c->n_genomes : cap;
     if (n) CUDA_TRY(cudaMemcpyAsync(out, c->results.p, n * sizeof(eref_result), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaEventRecord(c->ev[E6], c->stream));
+    CUDA_TRY(cudaEventRecord(c->ev[S7], c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
-    table_done(c);
-    scan_times(c, true);
-    const bool pruned = !(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / c->sample_stride) > 0;
-    c->t.ref_need_words = pruned ? c->h_pin[6] : c->ref_words;
+    c->scan_pending = true; c->scan_pending_d2h = true;
+    collect_times(c);
     if (n_out) *n_out = c->n_genomes;
     return 0;
 }
@@ -864,8 +937,10 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     CUDA_TRY(cudaEventRecord(c->ev[E0], st));
     rc = query_add_impl(c, c->q_text.as<uint8_t>(), n1);
     if (rc) return rc;
+    unsigned long long seq1 = 0;
+    rc = last_file_seq_bytes(c, &seq1);       // cal_sam_ratio needs fq1's byte count before fq2 is counted
+    if (rc) return rc;
     eref_phase_times sum = c->t;
-    const unsigned long long seq1 = c->t.query_seq_bytes;
     // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1)
     int ratio = 0;
     rc = eref_sample_ratio(seq1, c->down_sampling_size, &ratio);
@@ -891,15 +966,12 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         CUDA_TRY(cudaEventRecord(c->ev[E0], st));
         rc = query_add_impl(c, c->q_text.as<uint8_t>(), n1, keep1.data(), lines1);
         if (rc) return rc;
-        sum = c->t;
     }
     CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[1], 0));
     CUDA_TRY(cudaEventRecord(c->ev[E0], st));
     rc = ratio < 100 ? query_add_impl(c, c->q_text2.as<uint8_t>(), n2, keep2.data(), lines2)
                      : query_add_impl(c, c->q_text2.as<uint8_t>(), n2);
     if (rc) return rc;
-    sum.query_pack_ms += c->t.query_pack_ms; sum.query_bucket_ms += c->t.query_bucket_ms;
-    sum.query_seq_bytes += c->t.query_seq_bytes; sum.query_codes += c->t.query_codes;
     rc = start_table_update(c);               // counted while the first database piece is framed and packed
     if (rc) return rc;
     sum.ref_frame_ms = sum.ref_pack_ms = 0;
@@ -942,32 +1014,41 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         const auto h2 = std::chrono::steady_clock::now();
         float copy_ms = 0, tail_ms = 0;
         cudaEventElapsedTime(&copy_ms, c->ev[E10], c->ev[E11]);
-        cudaEventElapsedTime(&tail_ms, c->ev[E11], c->ev[E6]);
+        cudaEventElapsedTime(&tail_ms, c->ev[E11], c->ev[S7]);
         fprintf(stderr, "eref_run_host: queued copies after %.3f ms, returned after %.3f ms; copies took %.3f ms on the "
                         "device, last copy -> last result %.3f ms\n",
                 std::chrono::duration<double, std::milli>(h1 - h0).count(),
                 std::chrono::duration<double, std::milli>(h2 - h0).count(), copy_ms, tail_ms);
     }
+    // the query times are sums over both files (collected by the first eref_scan's synchronisation)
+    sum.query_pack_ms = c->t.query_pack_ms; sum.query_bucket_ms = c->t.query_bucket_ms;
+    sum.query_seq_bytes = c->t.query_seq_bytes; sum.query_codes = c->t.query_codes;
+    if (c->flags & EREF_FLAG_DIRECT_COUNT) sum.query_count_ms = c->t.query_count_ms;
     c->t = sum;
     if (!resident) c->have_ref = npieces == 1;   // per-record lookups only make sense for a single piece
     if (n_out) *n_out = total;
     return 0;
 }
 
-int eref_scan_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
+int eref_scan_device_async(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
 {
     if (!c || !results_dev) return eref_fail(EREF_ERR_ARG, "eref_scan_device: null argument");
     CUDA_TRY(cudaSetDevice(c->device));
     int rc = scan_impl(c);
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaStreamSynchronize(c->stream));
-    table_done(c);
-    scan_times(c, false);
-    c->t.ref_need_words = (!(c->flags & EREF_FLAG_NO_PRUNE) && c->three_min - (WINDOW - WINDOW / c->sample_stride) > 0)
-                              ? c->h_pin[6] : c->ref_words;
+    c->scan_pending = true; c->scan_pending_d2h = false;
     *results_dev = c->results.as<uint32_t>();
     if (n_out) *n_out = c->n_genomes;
+    return 0;
+}
+
+int eref_scan_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
+{
+    int rc = eref_scan_device_async(c, results_dev, n_out);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    collect_times(c);
     return 0;
 }
 
@@ -1104,6 +1185,11 @@ int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
 int eref_timings(eref_ctx* c, eref_phase_times* out)
 {
     if (!c || !out) return eref_fail(EREF_ERR_ARG, "null argument");
+    if (c->q_pending || c->ref_pending || c->scan_pending) {
+        CUDA_TRY(cudaSetDevice(c->device));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        collect_times(c);
+    }
     *out = c->t;
     out->kernel_launches = c->launches;
     return 0;

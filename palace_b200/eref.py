@@ -34,7 +34,7 @@ RESULT_DTYPE = np.dtype([("ordinal", "<u4"), ("frag", "<u4"), ("el", "<u4"), ("r
 ABI_SYMBOLS = (
     "eref_last_error", "eref_device_count", "eref_create", "eref_destroy", "eref_set_stream",
     "eref_query_reset", "eref_query_add", "eref_query_add_device", "eref_query_seq_bytes",
-    "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device",
+    "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device", "eref_scan_device_async",
     "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
     "eref_run_host", "eref_ref_records", "eref_index_body", "eref_query_census", "eref_query_census_device",
     "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
@@ -83,6 +83,7 @@ def load_library() -> ctypes.CDLL:
     lib.eref_ref_count.argtypes = [c_void_p, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_uint64)]
     lib.eref_scan.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_scan_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
+    lib.eref_scan_device_async.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
     lib.eref_run_host.argtypes = [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, c_int, c_void_p,
                                   c_size_t, POINTER(c_size_t)]
     lib.eref_get_codes.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]
@@ -203,9 +204,10 @@ class ErefGPU:
                                                         n_lines), "eref_query_add_masked")
         return self.query_seq_bytes()
 
-    def query_add_device(self, ptr: int, n: int) -> int:
+    def query_add_device(self, ptr: int, n: int, want_bytes: bool = True):
+        """want_bytes=False: do not wait for the file's kernels (the byte count of cal_sam_ratio is not asked for)"""
         _check(self.lib, self.lib.eref_query_add_device(self._h, c_void_p(ptr), n), "eref_query_add_device")
-        return self.query_seq_bytes()
+        return self.query_seq_bytes() if want_bytes else None
 
     def query_seq_bytes(self) -> int:
         v = c_uint64()
@@ -255,10 +257,12 @@ class ErefGPU:
         _check(self.lib, rc, "eref_run_host")
         return self._run_out[:min(n.value, cap)]
 
-    def scan_device(self):
-        """Results stay in HBM: (device pointer to n x 4 uint32, n)."""
+    def scan_device(self, wait: bool = True):
+        """Results stay in HBM: (device pointer to n x 4 uint32, n).  wait=False: valid in stream order on the
+        context's stream (set_stream), nothing is waited for."""
         p, n = c_void_p(), c_size_t()
-        _check(self.lib, self.lib.eref_scan_device(self._h, byref(p), byref(n)), "eref_scan_device")
+        fn = self.lib.eref_scan_device if wait else self.lib.eref_scan_device_async
+        _check(self.lib, fn(self._h, byref(p), byref(n)), "eref_scan_device")
         return p.value, n.value
 
     def get_codes(self, ordinal: int) -> np.ndarray:
