@@ -35,10 +35,15 @@ WORKLOADS = {
     "c2": (10000, 500_000_000, 50_000_000),
     "c1": (1000, 50_000_000, 5_000_000),
     "small": (400, 20_000_000, 2_000_000),
+    # BASELINE configs[2] and [3] are 8-GPU configurations: a 30,000-genome ~1.5 Gbp database sharded over 8 GPUs
+    "c3": (3750, 187_500_000, 50_000_000),
+    "c4": (3750, 187_500_000, 500_000_000),
 }
 WORKLOAD_DESC = {
     "c2": "BASELINE configs[1]: 50 Mbp reads vs 10,000-genome ~500 Mbp synthetic phage DB per GPU",
     "c1": "BASELINE configs[0]: 5 Mbp reads vs 1,000-genome ~50 Mbp synthetic phage DB per GPU",
+    "c3": "BASELINE configs[2] at 8 GPUs: 50 Mbp reads vs 3,750 genomes ~187.5 Mbp of a 30,000-genome ~1.5 Gbp DB per GPU",
+    "c4": "BASELINE configs[3] at 8 GPUs: 500 Mbp reads vs 3,750 genomes ~187.5 Mbp of a 30,000-genome ~1.5 Gbp DB per GPU",
     "small": "development: 2 Mbp reads vs 400-genome 20 Mbp DB per GPU",
 }
 # algorithmic bytes per unit (restated in DESIGN.md §8)
