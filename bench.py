@@ -137,7 +137,7 @@ PHASE_KERNELS = {
     "scan_summary_ms": (("k_build_summary", 0),),
     "scan_sample_ms": (("k_probe_sampled", 1),),
     "scan_cand_ms": (("k_need", 1),),
-    "scan_probe_ms": (("k_probe_part", 4),),
+    "scan_probe_ms": (("k_probe_part", 8),),
     "scan_window_ms": (("k_window_list", 1),),
     "scan_interval_ms": (("k_intervals", 1),),
 }
@@ -395,7 +395,7 @@ def run_b200(args):
     # the dominant KERNEL: the full probe (one launch per step = the whole scan_probe phase).  SURVEY 8(d): 97 B per
     # reference base = 1 B of text + 3 probes x one 32 B DRAM sector; the units of a launch are the bases it probes.
     dom = "scan_probe_ms"
-    dom_kernel = "k_probe_full" if args.no_prune else "k_probe_part (4 launches: the table in 4 parts)"
+    dom_kernel = "k_probe_full" if args.no_prune else "k_probe_part (8 launches: the table in 8 parts)"
     alg = BYTES_PER_REF_BASE_FULL * probed_bases
     achieved = alg / 1e9 / (avg[dom] / 1e3) if avg[dom] > 0 else 0.0
     largest = max(avg, key=avg.get)

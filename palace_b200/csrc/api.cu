@@ -91,7 +91,7 @@ struct eref_ctx {
     cudaEvent_t aux_ev[2]{};
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
-    int probe_parts = 4;                       // EREF_PROBE_PARTS: rounds of the listed-word probe, 1 = whole table at once
+    int probe_parts = 8;                       // EREF_PROBE_PARTS: rounds of the listed-word probe, 1 = whole table at once
     int bucket_bits = 5;                       // EREF_BUCKET_BITS: 2^bits coarse buckets, 2^(13-bits) slices per bucket
     // reference side
     DevBuf r_text, tile_sum, tile_pre, rec_hdr_off, rec_first, rec_len, rec_kept, rec_words,

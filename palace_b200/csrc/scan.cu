@@ -312,11 +312,13 @@ k_probe_list(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const ui
 // A B200 answers random 4-byte probes at ~58 G/s when the bitmap is 512 MiB (DRAM, 64-128 B moved per probe), ~123
 // G/s at 128 MiB and ~288 G/s at <= 64 MiB (L2) — tools/probe_bench.cu.  So the listed words are probed in `parts`
 // rounds: in round r every listed word computes its codes again (cheap) and probes only those whose top bits equal
-// r, which keeps the working set of a round at 512/parts MiB.  Measured on the bench workload: 0.65 ms in one
-// round, 0.56 in two, 0.50 in four, 0.60 in eight (every round costs ~0.05 ms of code arithmetic); streaming each
-// part into L2 first (k_table_prefetch, EREF_PROBE_PREFETCH=1) does not pay.  Hits are collected per stream in
-// h0/h1/h2 (round 0 stores, later rounds OR; a word belongs to one lane quad, so no atomics), the last round
-// turns them into single = h0|h1|h2 and trio = h0&h1&h2.
+// r, which keeps the working set of a round at 512/parts MiB.  Measured on the bench workload (2.5 % of the words
+// listed), one thread per word: 0.65 ms in one round, 0.55 in two, 0.43 in four and in eight, 0.73 in sixteen; on a
+// dense table (BASELINE configs[3], 90 % of the words listed): 9.0 / 4.75 / 4.3 / 8.2 ms for 1 / 4 / 8 / 16 rounds.
+// Four lanes per word (8 positions each) cost 0.50 and 6.1 ms in four rounds: the per-word overhead repeats in
+// every round.  Streaming each part into L2 first (k_table_prefetch, EREF_PROBE_PREFETCH=1) does not pay.
+// Hits are collected per stream in h0/h1/h2 (round 0 stores, later rounds OR; a word belongs to one thread or one
+// lane group, so no atomics), the last round turns them into single = h0|h1|h2 and trio = h0&h1&h2.
 __global__ void __launch_bounds__(256)
 k_table_prefetch(const uint32_t* __restrict__ part, uint32_t lines)
 {
@@ -343,26 +345,30 @@ k_probe_part(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const ui
         if (e < n) {
             w = list[e];
             const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
-            const uint32_t mine = (vm >> (32 - PER - PER * q)) & ((1u << PER) - 1u);
+            const uint32_t mine = PER == 32 ? vm : (vm >> ((32 - PER - PER * q) & 31)) & ((1u << (PER & 31)) - 1u);
             if (mine) {
                 const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
-                uint32_t code[PER * 3];
+                constexpr int BATCH = PER < 8 ? PER : 8;
 #pragma unroll
-                for (int j = 0; j < PER; j++) {
-                    const int s = PER * q + j;
-                    WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
-                    const bool v = (vm >> (31 - s)) & 1u;
+                for (int s0 = 0; s0 < PER; s0 += BATCH) {
+                    uint32_t code[BATCH * 3];
 #pragma unroll
-                    for (int i = 0; i < 3; i++) {
-                        const uint32_t c = stream_code(m, b, i);
-                        code[j * 3 + i] = (v && (c >> part_shift) == part) ? c : 0u;
+                    for (int j = 0; j < BATCH; j++) {
+                        const int s = PER * q + s0 + j;
+                        WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                        const bool v = (vm >> (31 - s)) & 1u;
+#pragma unroll
+                        for (int i = 0; i < 3; i++) {
+                            const uint32_t c = stream_code(m, b, i);
+                            code[j * 3 + i] = (v && (c >> part_shift) == part) ? c : 0u;
+                        }
                     }
-                }
 #pragma unroll
-                for (int j = 0; j < PER; j++) {
-                    a0 |= probe(bm3, code[j * 3]) << (31 - PER * q - j);
-                    a1 |= probe(bm3, code[j * 3 + 1]) << (31 - PER * q - j);
-                    a2 |= probe(bm3, code[j * 3 + 2]) << (31 - PER * q - j);
+                    for (int j = 0; j < BATCH; j++) {
+                        a0 |= probe(bm3, code[j * 3]) << (31 - PER * q - s0 - j);
+                        a1 |= probe(bm3, code[j * 3 + 1]) << (31 - PER * q - s0 - j);
+                        a2 |= probe(bm3, code[j * 3 + 2]) << (31 - PER * q - s0 - j);
+                    }
                 }
             }
         }
@@ -649,6 +655,7 @@ cudaError_t launch_probe_parts(Planes pl, CoderMasks m, const uint32_t* bm3, con
                                uint32_t* single, uint32_t* trio, cudaStream_t st, int* launches)
 {
     if (!pl.nwords) return cudaSuccess;
+    static int lpw = 1;                                  // lanes per word: 1 measured best once the table is walked in parts
     static int per_sm = 0, prefetch = 0;          // measured: the prefetch does not pay (0.52 ms with, 0.50 without)
     if (!per_sm) {
         const char* v = getenv("EREF_PROBE_CTAS");
@@ -656,14 +663,21 @@ cudaError_t launch_probe_parts(Planes pl, CoderMasks m, const uint32_t* bm3, con
         if (per_sm < 1 || per_sm > 64) per_sm = 16;
         v = getenv("EREF_PROBE_PREFETCH");
         if (v) prefetch = atoi(v);
+        v = getenv("EREF_PROBE_LPW");
+        if (v) lpw = atoi(v);
     }
     int log2p = 0;
     while ((1 << log2p) < parts) log2p++;
     const uint32_t part_words = TABLE_WORDS >> log2p;
     for (int r = 0; r < parts; r++) {
         if (prefetch) k_table_prefetch<<<list_grid(8), 256, 0, st>>>(bm3 + (size_t)r * part_words, part_words / 32);
-        k_probe_part<4><<<list_grid(per_sm), 256, 0, st>>>(pl, m, bm3, list, n_list, (uint32_t)r, 32 - log2p, r == 0,
-                                                          r == parts - 1, h0w, h1w, h2w, single, trio);
+        const unsigned grid = list_grid(per_sm);
+        const uint32_t part = (uint32_t)r;
+        const int shift = 32 - log2p;
+        const bool first = r == 0, last = r == parts - 1;
+        if (lpw == 1) k_probe_part<1><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, shift, first, last, h0w, h1w, h2w, single, trio);
+        else if (lpw == 2) k_probe_part<2><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, shift, first, last, h0w, h1w, h2w, single, trio);
+        else k_probe_part<4><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, shift, first, last, h0w, h1w, h2w, single, trio);
         if (launches) *launches += 2;
     }
     return cudaGetLastError();
