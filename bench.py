@@ -392,11 +392,33 @@ def run_b200(args):
                   "frac_of_hbm": round(design.get(p, 0) / 1e9 / (avg[p] / 1e3) / peak, 3) if avg[p] > 0 else None,
                   "kernels": [n for n, t in PHASE_KERNELS[p] if t], "ncu_dram_bytes": ncu_traffic(p)}
               for p in PHASES}
-    # the dominant KERNEL: the full probe (one launch per step = the whole scan_probe phase).  SURVEY 8(d): 97 B per
-    # reference base = 1 B of text + 3 probes x one 32 B DRAM sector; the units of a launch are the bases it probes.
-    dom = "scan_probe_ms"
-    dom_kernel = "k_probe_full" if args.no_prune else "k_probe_part (8 launches: the table in 8 parts)"
-    alg = BYTES_PER_REF_BASE_FULL * probed_bases
+    # the dominant KERNEL: the largest of the phases that consist of one kernel (the probe: one kernel, 8 launches).
+    # Algorithmic bytes: the probe uses SURVEY 8(d)'s 97 B per reference base (1 B of text + 3 probes x one 32 B DRAM
+    # sector) x the bases it probes; for the other kernels SURVEY gives no per-kernel figure, so the bytes the kernel
+    # must move in this design (the `phases` entry below) are used and the note says so.
+    single_kernel = {"scan_probe_ms": "k_probe_full" if args.no_prune else "k_probe_part (8 launches: the table in 8 parts)",
+                     "scan_sample_ms": "k_probe_sampled", "ref_pack_ms": "k_pack_fasta (+ memsets of the planes)",
+                     "query_count_ms": "k_count_slices_persistent"}
+    dom = max(single_kernel, key=lambda p_: avg[p_])
+    dom_kernel = single_kernel[dom]
+    if dom == "scan_probe_ms":
+        alg, per_unit, units, unit_name = BYTES_PER_REF_BASE_FULL * probed_bases, BYTES_PER_REF_BASE_FULL, probed_bases, \
+            "reference bases probed by the launches (all three streams)"
+        roof_note = ("random 4-byte probes: a 512 MiB bitmap answers 57-58 G/s on this B200 and DRAM moves ~100 B per "
+                     "probe (tools/probe_bench.cu); walking the table in 8 L2-sized parts turns most probes into L2 "
+                     "hits, so ncu's DRAM traffic is below the algorithmic bytes and the rounds are instruction-bound "
+                     "(sm 60-68 %)")
+    else:
+        units = {"scan_sample_ms": info["ref_bases"], "ref_pack_ms": info["ref_bases"], "query_count_ms": codes}[dom]
+        unit_name = {"scan_sample_ms": "reference bases", "ref_pack_ms": "reference bases",
+                     "query_count_ms": "query codes (3 per valid 32-mer)"}[dom]
+        alg = design[dom]
+        per_unit = round(alg / max(units, 1), 3)
+        roof_note = ("SURVEY 8(d) gives no per-kernel figure here: bytes this kernel must move in this design "
+                     "(DESIGN.md section 3); " +
+                     {"scan_sample_ms": "bound by one scattered L2 sector per clock and SM (l1tex 82 %)",
+                      "ref_pack_ms": "instruction-bound (sm 83 %): ~30 integer operations per 4 text bytes",
+                      "query_count_ms": "bound by shared-memory atomics (l1tex 58 %), one CTA per SM"}[dom])
     achieved = alg / 1e9 / (avg[dom] / 1e3) if avg[dom] > 0 else 0.0
     largest = max(avg, key=avg.get)
     scan_ms = sum(avg[p] for p in PHASES if p.startswith("scan_"))
@@ -433,13 +455,10 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "kernel": dom_kernel, "phase": dom,
                      "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "traffic": ncu_traffic(dom), "peak_source": peak_src,
-                     "algorithmic_bytes_per_unit": BYTES_PER_REF_BASE_FULL, "units_per_launch": int(probed_bases),
-                     "unit_name": "reference bases probed by the launch (all three streams)",
+                     "algorithmic_bytes_per_unit": per_unit, "units_per_launch": int(units), "unit_name": unit_name,
                      "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4),
-                     "probes_per_s": round(3.0 * probed_bases / (avg[dom] / 1e3) / 1e9, 1),
-                     "note": "random 4-byte probes of a 512 MiB bitmap: this B200 answers 57-58 G/s whatever the load "
-                             "flavour (tools/probe_bench.cu; 49 G/s when nothing hits L2), and DRAM moves 64-128 B per "
-                             "32 B sector asked for, hence traffic above the algorithmic bytes",
+                     "probes_per_s_G": round(3.0 * probed_bases / (avg["scan_probe_ms"] / 1e3) / 1e9, 1),
+                     "note": roof_note,
                      "largest_phase": largest},
         "phases": phases,
         "survey_8d": {"table_build": {"bytes_per_query_base": BYTES_PER_QUERY_BASE_BUILD,
