@@ -529,3 +529,52 @@ def test_eref_binary_reads_gzip_inputs(golden, tmp_path):
                        capture_output=True, env=dict(os.environ, EREF_GPUS="1"))
     assert r.returncode == 0, r.stderr.decode()
     assert r.stdout.decode() == expect
+
+
+# ---- candidate filter on ragged databases: a property that needs no oracle --------------------------
+
+def _ragged_case(seed, n_records=3000):
+    """records of 33..700 bases (plus a few long ones) packed tightly, so that the 17-word look-back / look-ahead of
+    the candidate filter crosses record boundaries almost everywhere; a third of the records is covered 4x by reads"""
+    rng = np.random.default_rng(seed)
+    lens = rng.integers(33, 700, n_records)
+    lens[rng.integers(0, n_records, 20)] = rng.integers(3000, 20000, 20)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    fa, reads = [], []
+    for i, n in enumerate(lens):
+        seq = acgt[rng.integers(0, 4, int(n))]
+        fa.append(b">r%d\n" % i + seq.tobytes() + b"\n")
+        if i % 3 == 0:
+            for _ in range(4):
+                reads.append(seq.tobytes())
+                if n > 400:                                   # the reference's line buffer holds 400 characters
+                    reads[-1] = None
+                    for s in range(0, int(n) - 32, 150):
+                        reads.append(seq[s:s + 300].tobytes())
+    reads = [r for r in reads if r]
+    order = rng.permutation(len(reads))
+    def fastq(idx):
+        return np.frombuffer(b"".join(b"@q\n" + reads[k] + b"\n+\n" + b"I" * len(reads[k]) + b"\n" for k in idx), np.uint8)
+    return np.frombuffer(b"".join(fa), np.uint8), fastq(order[0::2]), fastq(order[1::2])
+
+
+@pytest.mark.parametrize("seed", [301, 302, 303])
+def test_pruned_scan_equals_full_scan_on_ragged_records(seed):
+    fa, f1, f2 = _ragged_case(seed)
+    coder = eref.random_coder(seed)
+    for ratios in ((0.9, 0.85), (0.99, 0.97), (0.95, 0.9), (0.5, 0.45)):
+        _, full = eref.run_eref(f1, f2, fa, None, *ratios, 1, coder=coder, prune=False, return_results=True)
+        for pipelined in (False, True):
+            _, got = eref.run_eref(f1, f2, fa, None, *ratios, 1, coder=coder, prune=True, pipelined=pipelined,
+                                   chunks=3, return_results=True)
+            assert (got == full).all(), f"seed {seed} ratios {ratios} pipelined={pipelined}"
+        if ratios[0] == 0.9:
+            assert (full["el"] > 0).sum() > 100
+
+
+def test_ragged_records_match_the_oracle(oracle):
+    fa, f1, f2 = _ragged_case(304, n_records=800)
+    coder = eref.random_coder(304)
+    want = oracle.run(f1, f2, fa, coder, 0.9, 0.85, threads=4)
+    _, got = eref.run_eref(f1, f2, fa, None, 0.9, 0.85, 1, coder=coder, return_results=True)
+    assert (got == want).all()
