@@ -12,8 +12,10 @@ The reference loads the whole database into a Biopython dictionary first (:62); 
 Biopython: it finds the header lines with one vectorised pass over the bytes and touches only the selected
 records.  Semantics kept from Biopython's FASTA parser: the record id is the header up to the first white
 space, the sequence is the record's lines joined with trailing white space, blanks and '\\r' removed, and a
-duplicated id is an error.  PARITY UNPINNED: Biopython is not installed in the build image, so this mirror is
-checked against hand-computed cases only (tests/test_host.py).
+duplicated id is an error.  Parity: pinned to the UNMODIFIED reference script's outputs and messages
+(tests/golden/f1.json, made by tests/golden/make_golden_f1.py); Biopython itself is not in the build image, so
+that run used a stand-in for SeqIO.parse/to_dict restating Biopython's FASTA rules — the Biopython half stays
+unpinned, the script's own logic does not.
 """
 import sys
 

@@ -119,3 +119,23 @@ def test_get_ref_by_index_mirror(tmp_path):
     (tmp_path / "dup.fa").write_bytes(b">a x\nAC\n>a y\nGT\n")
     with pytest.raises(ValueError):
         g.fasta_records((tmp_path / "dup.fa").read_bytes())
+
+
+def test_get_ref_by_index_against_the_reference_script(tmp_path, capsys):
+    """f1 pinned: tests/golden/f1.json holds what the UNMODIFIED reference script wrote (files and messages) on these
+    inputs, generated by tests/golden/make_golden_f1.py with a stand-in for the two Bio.SeqIO calls"""
+    import json
+    from palace_b200 import get_ref_by_index as g
+    golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "f1.json")))
+    assert set(golden) >= {"hand", "missing", "edge", "empty_names"}
+    for name, c in golden.items():
+        d = tmp_path / name
+        d.mkdir()
+        (d / "db.fa").write_bytes(c["fasta"].encode("latin-1"))
+        (d / "db.fa.fai").write_text(c["fai"])
+        (d / "names.txt").write_text(c["names"])
+        capsys.readouterr()
+        g.main(["x", str(d / "db.fa"), str(d / "db.fa.fai"), str(d / "names.txt"), str(d / "out.fa"), str(d / "out.txt")])
+        assert capsys.readouterr().out == c["log"], name
+        assert (d / "out.fa").read_text() == c["out_fasta"], name
+        assert (d / "out.txt").read_text() == c["out_percent"], name
