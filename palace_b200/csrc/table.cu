@@ -84,7 +84,8 @@ __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks
 }
 
 // P0: histogram of the codes of one file over the NSLICES table slices (top 13 code bits).  Persistent grid:
-// a CTA accumulates in shared memory over all its tiles and flushes once.
+// a CTA accumulates in shared memory over all its tiles and flushes once.  (Two 1024-thread CTAs per SM — a third
+// of the flush atomics — measured the same 55 us per file: the flush is not what bounds it.)
 __global__ void __launch_bounds__(256)
 k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, CoderMasks m,
              unsigned long long* __restrict__ g_hist)
@@ -203,10 +204,11 @@ k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long 
     });
     __syncthreads();
     const uint32_t total = s_start[nb];
+    if (threadIdx.x < nb) s_base[threadIdx.x] -= s_start[threadIdx.x];     // element i of the sorted tile goes to s_base[b] + i
+    __syncthreads();
     for (uint32_t i = threadIdx.x; i < total; i += CS_THREADS) {
         const uint32_t cd = s_codes[i];
-        const uint32_t b = cd >> shift;
-        codes_out[s_base[b] + (i - s_start[b])] = cd;
+        codes_out[s_base[cd >> shift] + i] = cd;
     }
 }
 
@@ -274,20 +276,29 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
     __shared__ uint32_t s_cnt[MAX_BUCKETS], s_off[MAX_BUCKETS + 1];
     __shared__ uint32_t s_delta[MAX_BUCKETS];
     __shared__ uint32_t s_warp[8];
+    __shared__ int s_bucket;
     constexpr int FINE_PER_THREAD = FINE_CHUNK / FINE_THREADS;
     const int fbits = 32 - SLICE_BITS - cbits, nf = 1 << fbits, ncoarse = 1 << cbits;
     if (blockIdx.x >= chunk_start[ncoarse]) return;                         // the grid is sized from an upper bound
-    // which coarse bucket does this chunk belong to?
-    int lo = 0, hi = ncoarse;
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (chunk_start[mid] <= blockIdx.x) lo = mid; else hi = mid; }
-    const int b = lo;
+    // which coarse bucket does this chunk belong to?  chunk_start is non-decreasing: b = #{i : chunk_start[i] <= chunk} - 1,
+    // counted by the first warp with one load per lane and round and handed over at the barrier that follows the
+    // zeroing of the counters (a binary search here was five dependent loads in every thread before the first code load)
+    if (threadIdx.x < 32) {
+        int below = 0;
+        for (int i0 = 0; i0 < ncoarse; i0 += 32) {
+            const int i = i0 + (int)threadIdx.x;
+            below += __popc(__ballot_sync(0xffffffffu, i < ncoarse && chunk_start[i] <= blockIdx.x));
+        }
+        if (threadIdx.x == 0) s_bucket = below - 1;
+    }
+    if (threadIdx.x < nf) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int b = s_bucket;
     const uint64_t first = (uint64_t)(blockIdx.x - chunk_start[b]) * FINE_CHUNK;
     const uint64_t nb = coarse_n[b];
     if (first >= nb) return;
     const uint32_t cnt = (uint32_t)min((uint64_t)FINE_CHUNK, nb - first);
     const uint32_t* src = in + slice_off[(size_t)b << fbits] + first;       // 16-byte aligned: slice starts and chunks are
-    if (threadIdx.x < nf) s_cnt[threadIdx.x] = 0;
-    __syncthreads();
     uint32_t code[FINE_PER_THREAD];
     uint16_t rank[FINE_PER_THREAD];
 #pragma unroll
@@ -492,28 +503,36 @@ k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t
                 count_unit(__ldcs(src + u), (uint32_t)min((uint64_t)4, n - u * 4), L1, L2, L3);
         }
         __syncthreads();
-        if (POP) for (int i = threadIdx.x; i < SLICE_WORDS; i += COUNT_THREADS) { p1 += __popc(L1[i]); p2 += __popc(L2[i]); p3 += __popc(L3[i]); }
+        if (POP) {
+            for (int i = threadIdx.x; i < SLICE_WORDS; i += COUNT_THREADS) { p1 += __popc(L1[i]); p2 += __popc(L2[i]); p3 += __popc(L3[i]); }
+            __syncthreads();                               // the copy-out below clears words other threads count here
+        }
         // level 3 out, one 16-byte unit per thread and round; summary word j covers table words 16j .. 16j+15 = four
         // consecutive units, i.e. four neighbouring lanes: 8 summary bits each, combined with two shuffles
         uint4* dst = reinterpret_cast<uint4*>(bm3 + (size_t)slice * SLICE_WORDS);
         const uint4* l3 = reinterpret_cast<const uint4*>(L3);
+        uint4* l3w = reinterpret_cast<uint4*>(L3);
+        uint4* l1w = reinterpret_cast<uint4*>(L1);
+        uint4* l2w = reinterpret_cast<uint4*>(L2);
         for (int i = threadIdx.x; i < SLICE_WORDS / 4; i += COUNT_THREADS) {
             const uint4 v = l3[i];
             __stcs(dst + i, v);
+            // the three levels are zeroed for the next slice as they are read out (a thread clears what it alone read)
+            l3w[i] = make_uint4(0, 0, 0, 0); l1w[i] = make_uint4(0, 0, 0, 0); l2w[i] = make_uint4(0, 0, 0, 0);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            uint32_t out = 0;
+            // "half-word != 0" lands in bits 15 and 31 of t (no carry crosses a half), word k's pair goes to bits 2k and 16+2k
+            uint32_t acc = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                out |= (uint32_t)((w[k] & 0x0000FFFFu) != 0) << (k * 2);
-                out |= (uint32_t)((w[k] & 0xFFFF0000u) != 0) << (k * 2 + 1);
+                const uint32_t t = (((w[k] & 0x7FFF7FFFu) + 0x7FFF7FFFu) | w[k]) & 0x80008000u;
+                acc |= t >> (15 - 2 * k);
             }
+            uint32_t out = (acc | (acc >> 15)) & 0xFFu;
             out <<= 8 * (i & 3);
             out |= __shfl_xor_sync(0xffffffffu, out, 1);
             out |= __shfl_xor_sync(0xffffffffu, out, 2);
             if ((i & 3) == 0) summary[(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
         }
-        __syncthreads();
-        for (int i = threadIdx.x; i < 3 * SLICE_WORDS / 4; i += COUNT_THREADS) s_raw[i] = make_uint4(0, 0, 0, 0);
         __syncthreads();
     }
     if (POP) {
