@@ -92,7 +92,7 @@ struct eref_ctx {
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
     int probe_parts = 8;                       // EREF_PROBE_PARTS: rounds of the listed-word probe, 1 = whole table at once
-    int bucket_bits = 5;                       // EREF_BUCKET_BITS: 2^bits coarse buckets, 2^(13-bits) slices per bucket
+    int bucket_bits = 32 - SLICE_BITS - 8;     // EREF_BUCKET_BITS: 2^bits coarse buckets, 256 slices per bucket by default
     // reference side
     DevBuf r_text, tile_sum, tile_pre, rec_hdr_off, rec_first, rec_len, rec_kept, rec_words,
         rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
@@ -651,7 +651,7 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->table_stream, cudaStreamNonBlocking);
     if (const char* v = getenv("EREF_DOWN_SAMPLING_SIZE")) { long long k = atoll(v); if (k > 0) c->down_sampling_size = (uint64_t)k; }
     if (const char* v = getenv("EREF_PROBE_PARTS")) { int k = atoi(v); if (k == 1 || k == 2 || k == 4 || k == 8 || k == 16 || k == 32) c->probe_parts = k; }
-    if (const char* v = getenv("EREF_BUCKET_BITS")) { int k = atoi(v); if (k >= 5 && k <= 8) c->bucket_bits = k; }
+    if (const char* v = getenv("EREF_BUCKET_BITS")) { int k = atoi(v); if (k >= 32 - SLICE_BITS - 8 && k <= 8) c->bucket_bits = k; }
     for (int l = (flags & EREF_FLAG_DIRECT_COUNT) ? 0 : 2; l < 3 && e == cudaSuccess; l++)
         e = cudaMalloc(&c->bm[l], (size_t)TABLE_WORDS * 4);
     if (e == cudaSuccess) e = c->level_pop.ensure(64);

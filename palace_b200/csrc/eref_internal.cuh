@@ -15,7 +15,10 @@ constexpr int      WINDOW       = 500;               // :510
 constexpr int      WIN_WORDS    = 16;                // a 500-position window reaches back 16 words
 constexpr uint32_t SUMMARY_WORDS = 1u << 23;         // level-3 summary: 1 bit per 16 slots = 32 MiB
 constexpr int      MAX_BUCKETS = 256;                // coarse / fine partition fan-out of the table build (table.cu)
-constexpr int      SLICE_BITS  = 19;                 // a table slice = 2^19 slots: its three levels fit one CTA's shared memory
+#ifndef EREF_SLICE_BITS
+#define EREF_SLICE_BITS 19
+#endif
+constexpr int      SLICE_BITS  = EREF_SLICE_BITS;    // a table slice = 2^SLICE_BITS slots: at 19 its three levels (192 KiB) fill one CTA's shared memory; 18 = two CTAs per SM
 constexpr int      NSLICES     = 1 << (32 - SLICE_BITS);
 constexpr int      SLICE_WORDS = 1 << (SLICE_BITS - 5);
 constexpr uint32_t SLICE_MASK  = (1u << SLICE_BITS) - 1u;

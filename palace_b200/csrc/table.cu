@@ -86,11 +86,13 @@ __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks
 // P0: histogram of the codes of one file over the NSLICES table slices (top 13 code bits).  Persistent grid:
 // a CTA accumulates in shared memory over all its tiles and flushes once.  (Two 1024-thread CTAs per SM — a third
 // of the flush atomics — measured the same 55 us per file: the flush is not what bounds it.)
-__global__ void __launch_bounds__(256)
+constexpr int HIST_THREADS = NSLICES * 4 > 48 * 1024 ? 512 : 256;      // 64 KiB of bins: three CTAs of 512 per SM
+
+__global__ void __launch_bounds__(HIST_THREADS)
 k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, CoderMasks m,
              unsigned long long* __restrict__ g_hist)
 {
-    __shared__ uint32_t s_hist[NSLICES];
+    extern __shared__ uint32_t s_hist[];                   // NSLICES
     for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     const uint64_t nwords = (*plane_bits + 31) >> 5;      // the host has not seen the packed size yet
@@ -241,12 +243,17 @@ k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned
 #pragma unroll
     for (int k = 0; k < PER; k++) { off[threadIdx.x * PER + k] = run; run += (v[k] + 3) & ~3ull; }
     if (threadIdx.x == 1023) off[NSLICES] = run;
+    // codes per coarse bucket: a bucket's 2^fbits slices sit in 2^fbits / PER neighbouring threads (at most one warp for
+    // cbits >= 32 - SLICE_BITS - 8), so it is a segmented shuffle sum of what the threads already hold
     const int fbits = 32 - SLICE_BITS - cbits, NC = 1 << cbits;
-    if (threadIdx.x < NC) {
-        unsigned long long nb = 0;
-        for (int f = 0; f < (1 << fbits); f++) nb += hist[((size_t)threadIdx.x << fbits) + f];
-        coarse_n[threadIdx.x] = nb;
-        s_coarse[threadIdx.x] = nb;
+    const int tpb = (1 << fbits) / PER;                    // threads per bucket: a power of two, 1..32
+    unsigned long long raw = 0;
+#pragma unroll
+    for (int k = 0; k < PER; k++) raw += v[k];
+    for (int d = 1; d < tpb; d <<= 1) raw += __shfl_xor_sync(0xffffffffu, raw, d);
+    if ((threadIdx.x & (tpb - 1)) == 0) {
+        coarse_n[threadIdx.x / tpb] = raw;
+        s_coarse[threadIdx.x / tpb] = raw;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -352,7 +359,8 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
 // of the slice from every pending file are counted with shared-memory atomics; the finished level-3 slice
 // and its part of the summary (1 bit per 16 slots) go to HBM with plain, coalesced stores.  Also
 // accumulates the number of codes at each level (eref_query_popcount).
-constexpr int COUNT_THREADS = 1024;
+constexpr int COUNT_THREADS = SLICE_BITS >= 19 ? 1024 : 512;     // 192 KiB of levels: one CTA per SM; 96 KiB: two
+constexpr int COUNT_CTAS = SLICE_BITS >= 19 ? 1 : 2;
 constexpr int COUNT_PRE = 2;                 // 16-byte units per thread and list fetched before the levels are zeroed
 
 __device__ __forceinline__ void count_unit(const uint4& v, uint32_t left, uint32_t* L1, uint32_t* L2, uint32_t* L3)
@@ -449,7 +457,7 @@ k_count_slices(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restric
 // counted and written out, the first codes of the NEXT slice are already on their way into registers, so the HBM
 // round trip and the CTA turn-around of k_count_slices (about a third of its 8.8 us per slice) disappear.
 template <bool POP>
-__global__ void __launch_bounds__(COUNT_THREADS, 1)
+__global__ void __launch_bounds__(COUNT_THREADS, COUNT_CTAS)
 k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary,
                           unsigned long long* __restrict__ level_pop)
 {
@@ -592,7 +600,10 @@ cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t*
 cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, CoderMasks m, unsigned long long* g_hist,
                               cudaStream_t st)
 {
-    k_slice_hist<<<148 * 6, 256, 0, st>>>(pl, plane_bits, m, g_hist);
+    const int smem = NSLICES * 4;
+    cudaError_t e = cudaFuncSetAttribute(k_slice_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    k_slice_hist<<<148 * 1536 / HIST_THREADS, HIST_THREADS, smem, st>>>(pl, plane_bits, m, g_hist);
     return cudaGetLastError();
 }
 
@@ -647,8 +658,8 @@ cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t
         cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                                   : cudaFuncSetAttribute(k_count_slices_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        if (level_pop) k_count_slices_persistent<true><<<sms, COUNT_THREADS, smem, st>>>(lists, bm3, summary, level_pop);
-        else k_count_slices_persistent<false><<<sms, COUNT_THREADS, smem, st>>>(lists, bm3, summary, nullptr);
+        if (level_pop) k_count_slices_persistent<true><<<sms * COUNT_CTAS, COUNT_THREADS, smem, st>>>(lists, bm3, summary, level_pop);
+        else k_count_slices_persistent<false><<<sms * COUNT_CTAS, COUNT_THREADS, smem, st>>>(lists, bm3, summary, nullptr);
         return cudaGetLastError();
     }
     cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
