@@ -96,7 +96,7 @@ struct eref_ctx {
     // reference side
     DevBuf r_text, tile_sum, tile_pre, rec_hdr_off, rec_first, rec_len, rec_kept, rec_words,
         rec_kept_ex, rec_words_ex, g_rec, g_len, g_word, g_first, r_hi, r_lo, r_ok, word_genome,
-        sample_hits, need, need_list, hits0, hits1, hits2, single, trio, good, results, codes_tmp;
+        sample_hits, need, need_list, genome_listed, hits0, hits1, hits2, single, trio, good, results, codes_tmp;
     const uint8_t* ref_text_dev = nullptr;    // where the current reference text lives
     uint64_t ref_text_n = 0;
     bool have_ref = false;
@@ -541,11 +541,13 @@ int scan_impl(eref_ctx* c)
         CUDA_TRY(c->sample_hits.ensure(nw + 64)); CUDA_TRY(c->need.ensure(nw + 64));
         CUDA_TRY(c->need_list.ensure((nw + 64) * 4));
         CUDA_TRY(cudaMemsetAsync(need_count, 0, 8, st));
+        CUDA_TRY(c->genome_listed.ensure(((size_t)G + 1) * 4));
+        CUDA_TRY(cudaMemsetAsync(c->genome_listed.p, 0, ((size_t)G + 1) * 4, st));
         LAUNCH(c, launch_probe_sampled(pl, c->masks, c->bm[2], c->summary, c->sample_stride, c->sample_hits.as<uint8_t>(), st));
         CUDA_TRY(cudaEventRecord(c->ev[S2], st));
         LAUNCH(c, launch_need(c->sample_hits.as<uint8_t>(), c->word_genome.as<uint32_t>(), nw, min_sample_hits,
                               c->need.as<uint8_t>(), c->need_list.as<uint32_t>(), need_count, c->single.as<uint32_t>(),
-                              c->trio.as<uint32_t>(), c->good.as<uint32_t>(), st));
+                              c->trio.as<uint32_t>(), c->good.as<uint32_t>(), c->genome_listed.as<uint32_t>(), st));
         CUDA_TRY(cudaEventRecord(c->ev[S3], st));
         if (c->probe_parts > 1) {
             // the table is walked one L2-sized part at a time (scan.cu, P3')
@@ -577,7 +579,7 @@ int scan_impl(eref_ctx* c)
     }
     CUDA_TRY(cudaEventRecord(c->ev[S5], st));
     LAUNCH(c, launch_intervals(c->good.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), G,
-                               c->results.as<uint32_t>(), st));
+                               prune ? c->genome_listed.as<uint32_t>() : nullptr, c->results.as<uint32_t>(), st));
     CUDA_TRY(cudaEventRecord(c->ev[S6], st));
     return 0;
 }

@@ -178,7 +178,7 @@ cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, c
                                  uint8_t* sample_hits, cudaStream_t st);
 cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, uint64_t nwords, int min_sample_hits,
                         uint8_t* need, uint32_t* list, unsigned long long* need_count, uint32_t* single,
-                        uint32_t* trio, uint32_t* good, cudaStream_t st);
+                        uint32_t* trio, uint32_t* good, uint32_t* genome_listed, cudaStream_t st);
 cudaError_t launch_probe_full(Planes pl, CoderMasks m, const uint32_t* bm3, const uint8_t* need,
                               uint32_t* single, uint32_t* trio, cudaStream_t st);
 cudaError_t launch_probe_list(Planes pl, CoderMasks m, const uint32_t* bm3, const uint32_t* list,
@@ -193,8 +193,9 @@ cudaError_t launch_window_list(const uint32_t* single, const uint32_t* trio, con
                                const unsigned long long* n_list, const uint32_t* word_genome, const uint32_t* g_word,
                                const uint32_t* g_len, uint64_t nwords, int one_min, int three_min, uint32_t* good,
                                cudaStream_t st);
+// genome_listed: null, or one word per record, non-zero iff k_need listed a word of it (others answer {0, 0} unread)
 cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const uint32_t* g_len,
-                             uint32_t n_genomes, uint32_t* results, cudaStream_t st);
+                             uint32_t n_genomes, const uint32_t* genome_listed, uint32_t* results, cudaStream_t st);
 cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,
                                 uint32_t* codes, cudaStream_t st);
 cudaError_t launch_index_body(Planes pl, CoderMasks m, const uint32_t* g_word, const uint32_t* g_len,

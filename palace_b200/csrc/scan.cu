@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256)
 k_need(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ word_genome, uint64_t nwords,
        int min_sample_hits, uint8_t* __restrict__ need, uint32_t* __restrict__ list,
        unsigned long long* __restrict__ need_count, uint32_t* __restrict__ single, uint32_t* __restrict__ trio,
-       uint32_t* __restrict__ good)
+       uint32_t* __restrict__ good, uint32_t* __restrict__ genome_listed)
 {
     const uint64_t w0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * NEED_SPAN;
     uint32_t bits = 0;                                     // bit j: word w0+j is needed
@@ -214,6 +214,9 @@ k_need(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ wor
         const int j = __ffs(bits) - 1;
         bits &= bits - 1;
         *dst++ = (uint32_t)(w0 + j);
+        // records without a listed word keep good == 0 everywhere: k_intervals answers {0, 0} for them without reading it
+        const uint32_t g = word_genome[w0 + j];
+        if (g != 0xFFFFFFFFu) genome_listed[g] = 1u;
     }
 }
 
@@ -465,13 +468,18 @@ constexpr int IV_UNROLL = 8;                          // 128-byte rows of a reco
 
 __global__ void __launch_bounds__(128)
 k_intervals(const uint32_t* __restrict__ good, const uint32_t* __restrict__ g_word,
-            const uint32_t* __restrict__ g_len, uint32_t n_genomes, uint32_t* __restrict__ results)
+            const uint32_t* __restrict__ g_len, uint32_t n_genomes, const uint32_t* __restrict__ genome_listed,
+            uint32_t* __restrict__ results)
 {
     const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (g >= n_genomes) return;
     const uint64_t gs = g_word[g];
     const int len = (int)g_len[g];
+    if (genome_listed && !genome_listed[g]) {             // candidate filter on: no word of this record was listed
+        if (lane == 0) reinterpret_cast<uint4*>(results)[g] = make_uint4(g + 1, 0u, 0u, (uint32_t)len);
+        return;
+    }
     const uint32_t nw = ((uint32_t)len + 31u) >> 5;
     int start = 0, last_end = 0, frag = 0, el = 0;
     bool open = false;
@@ -600,12 +608,12 @@ cudaError_t launch_probe_sampled(Planes pl, CoderMasks m, const uint32_t* bm3, c
 
 cudaError_t launch_need(const uint8_t* sample_hits, const uint32_t* word_genome, uint64_t nwords, int min_sample_hits,
                         uint8_t* need, uint32_t* list, unsigned long long* need_count, uint32_t* single,
-                        uint32_t* trio, uint32_t* good, cudaStream_t st)
+                        uint32_t* trio, uint32_t* good, uint32_t* genome_listed, cudaStream_t st)
 {
     if (!nwords) return cudaSuccess;
     k_need<<<grid_for((nwords + NEED_SPAN - 1) / NEED_SPAN, 256), 256, 0, st>>>(sample_hits, word_genome, nwords,
                                                                               min_sample_hits, need, list, need_count,
-                                                                              single, trio, good);
+                                                                              single, trio, good, genome_listed);
     return cudaGetLastError();
 }
 
@@ -705,10 +713,10 @@ cudaError_t launch_window_list(const uint32_t* single, const uint32_t* trio, con
 }
 
 cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const uint32_t* g_len,
-                             uint32_t n_genomes, uint32_t* results, cudaStream_t st)
+                             uint32_t n_genomes, const uint32_t* genome_listed, uint32_t* results, cudaStream_t st)
 {
     if (!n_genomes) return cudaSuccess;
-    k_intervals<<<grid_for((uint64_t)n_genomes * 32, 128), 128, 0, st>>>(good, g_word, g_len, n_genomes, results);
+    k_intervals<<<grid_for((uint64_t)n_genomes * 32, 128), 128, 0, st>>>(good, g_word, g_len, n_genomes, genome_listed, results);
     return cudaGetLastError();
 }
 
