@@ -464,7 +464,8 @@ k_window_list(const uint32_t* __restrict__ single, const uint32_t* __restrict__ 
 // ---- P5: good runs -> padded, merged intervals -> {ordinal, frag, el, ref_len} (:568-617) ------------
 // One warp per record walks its good words in order; the (rare) rising/falling edges are replayed by
 // every lane in lock step, so the state machine stays warp-uniform.
-constexpr int IV_UNROLL = 8;                          // 128-byte rows of a record in flight per warp
+constexpr int IV_UNROLL = 32;                         // 128-byte rows of a record in flight per warp: the kernel lasts as long as the
+                                                      // longest listed record, i.e. (its words / (32 * IV_UNROLL)) dependent round trips
 
 __global__ void __launch_bounds__(128)
 k_intervals(const uint32_t* __restrict__ good, const uint32_t* __restrict__ g_word,
