@@ -516,16 +516,28 @@ class CpuArm:
                        f"GPU arm, BASELINE configs[0] size), threads={self.cores}")
         self.stdout = None
 
-    def run_once(self):
+    def run_once(self, threads=None):
         env = dict(os.environ, EREF_CODER_SEED="1", EREF_ORACLE_WRITE_INDEX="1")
         t0 = time.perf_counter()
-        r = subprocess.run([self.bin, "r1.fq", "r2.fq", "db.fa", "tmp.txt", "0.9", "0.85", str(self.cores)], cwd=self.dir,
-                           capture_output=True, env=env)
+        r = subprocess.run([self.bin, "r1.fq", "r2.fq", "db.fa", "tmp.txt", "0.9", "0.85", str(threads or self.cores)],
+                           cwd=self.dir, capture_output=True, env=env)
         dt = time.perf_counter() - t0
         if r.returncode != 0:
             raise RuntimeError(f"{self.bin} failed: {r.stderr.decode()[-400:]}")
         self.stdout = r.stdout
         return dt
+
+    def run_product(self):
+        """palace_b200/bin/eref as a process on the very same files (it takes the coder from the index header the
+        CPU run left next to the database): wall time and stdout"""
+        exe = os.path.join(ROOT, "palace_b200", "bin", "eref")
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, "r1.fq", "r2.fq", "db.fa", "tmp_b200.txt", "0.9", "0.85", str(self.cores)], cwd=self.dir,
+                           capture_output=True, env=dict(os.environ, EREF_GPUS="1"))
+        dt = time.perf_counter() - t0
+        if r.returncode != 0:
+            raise RuntimeError(f"{exe} failed: {r.stderr.decode()[-400:]}")
+        return dt, r.stdout
 
     def close(self):
         import shutil
@@ -537,10 +549,25 @@ def cpu_baseline(budget_runs=1):
     try:
         cold = arm.run_once()                          # builds <db>.k32.index.dat serially (:1250)
         warm = min(arm.run_once() for _ in range(budget_runs))
-        return {"value": round(arm.bases / 1e9 / warm, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
-                "sample": arm.sample + "; value = warm run (index on disk)", "warm_s": round(warm, 2),
-                "cold_s": round(cold, 2), "cold_value": round(arm.bases / 1e9 / cold, 6),
-                "selected_refs": arm.stdout.count(b"\n")}
+        out = {"value": round(arm.bases / 1e9 / warm, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
+               "sample": arm.sample + "; value = warm run (index on disk)", "warm_s": round(warm, 2),
+               "cold_s": round(cold, 2), "cold_value": round(arm.bases / 1e9 / cold, 6),
+               "selected_refs": arm.stdout.count(b"\n")}
+        # wall time of the whole eref PROCESS, both executables on the same files of this sample, and
+        # the same-run parity check: the reference at threads=1 (the parity configuration) against the drop-in's stdout
+        try:
+            t1 = arm.run_once(threads=1)
+            ref_t1_stdout = arm.stdout
+            first, _ = arm.run_product()                  # includes a cold CUDA context and module load
+            again, mine = arm.run_product()
+            out["process"] = {"reference_threads1_wall_s": round(t1, 2), "reference_wall_s": round(warm, 2),
+                              "b200_wall_s": round(min(first, again), 3), "b200_first_run_wall_s": round(first, 3),
+                              "stdout_identical_to_reference_threads1": mine == ref_t1_stdout,
+                              "result_lines": mine.count(b"\n"),
+                              "note": "one process per sample as palace runs it: file reads, CUDA context, upload, kernels, output"}
+        except Exception as e:                            # the bench line must not depend on this extra
+            out["process"] = {"error": str(e)[-300:]}
+        return out
     finally:
         arm.close()
 
