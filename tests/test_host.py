@@ -139,3 +139,22 @@ def test_get_ref_by_index_against_the_reference_script(tmp_path, capsys):
         assert capsys.readouterr().out == c["log"], name
         assert (d / "out.fa").read_text() == c["out_fasta"], name
         assert (d / "out.txt").read_text() == c["out_percent"], name
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the driver's CPU arm) end to end without a GPU: forced onto the oracle port and the
+    small sample so that it takes seconds; the line must carry the contract's keys with zero copy bytes"""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, timeout=300, env=dict(os.environ, EREF_BENCH_CPU_SAMPLE="small"))
+    assert r.returncode == 0, r.stderr.decode()[-400:]
+    lines = [l for l in r.stdout.decode().splitlines() if l.strip()]
+    assert len(lines) == 1                                         # stdout carries the one JSON line and nothing else
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "Gbp/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["steps"] == 1 and d["n_gpus"] == 1
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"] == {"value": d["value"], "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
