@@ -50,25 +50,32 @@ def cases():
     yield "empty_names", b">a\nAC\n", "a\t2\n", ""
 
 
+def run_reference(fa: bytes, fai: str, names: str):
+    """(out_fasta, out_percent, messages) of the unmodified reference script on these inputs"""
+    standin = os.path.join(HERE, "bio_standin")
+    if standin not in sys.path:
+        sys.path.insert(0, standin)
+    with tempfile.TemporaryDirectory() as d:
+        p = {k: os.path.join(d, k) for k in ("db.fa", "db.fa.fai", "names.txt", "out.fa", "out.txt")}
+        open(p["db.fa"], "wb").write(fa)
+        open(p["db.fa.fai"], "w").write(fai)
+        open(p["names.txt"], "w").write(names)
+        argv, sys.argv = sys.argv, ["get_ref_by_index.py"] + [p[k] for k in ("db.fa", "db.fa.fai", "names.txt", "out.fa", "out.txt")]
+        log = io.StringIO()
+        try:
+            with contextlib.redirect_stdout(log):
+                runpy.run_path(SCRIPT, run_name="__main__")
+        finally:
+            sys.argv = argv
+        return open(p["out.fa"]).read(), open(p["out.txt"]).read(), log.getvalue()
+
+
 def main():
-    sys.path.insert(0, os.path.join(HERE, "bio_standin"))
     out = {}
     for name, fa, fai, names in cases():
-        with tempfile.TemporaryDirectory() as d:
-            p = {k: os.path.join(d, k) for k in ("db.fa", "db.fa.fai", "names.txt", "out.fa", "out.txt")}
-            open(p["db.fa"], "wb").write(fa)
-            open(p["db.fa.fai"], "w").write(fai)
-            open(p["names.txt"], "w").write(names)
-            argv, sys.argv = sys.argv, ["get_ref_by_index.py"] + [p[k] for k in ("db.fa", "db.fa.fai", "names.txt", "out.fa", "out.txt")]
-            log = io.StringIO()
-            try:
-                with contextlib.redirect_stdout(log):
-                    runpy.run_path(SCRIPT, run_name="__main__")
-            finally:
-                sys.argv = argv
-            out[name] = {"fasta": fa.decode("latin-1"), "fai": fai, "names": names,
-                         "out_fasta": open(p["out.fa"]).read(), "out_percent": open(p["out.txt"]).read(),
-                         "log": log.getvalue()}
+        out_fa, out_txt, log = run_reference(fa, fai, names)
+        out[name] = {"fasta": fa.decode("latin-1"), "fai": fai, "names": names,
+                     "out_fasta": out_fa, "out_percent": out_txt, "log": log}
     json.dump(out, open(os.path.join(HERE, "f1.json"), "w"), indent=1)
     for k, v in out.items():
         print(k, len(v["out_fasta"]), repr(v["out_percent"][:80]))

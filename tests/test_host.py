@@ -158,3 +158,53 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["value"] > 0 and d["steps"] == 1 and d["n_gpus"] == 1
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"] == {"value": d["value"], "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/share/palace/scripts/get_ref_by_index.py"),
+                    reason="needs the reference checkout (build container only)")
+def test_get_ref_by_index_fuzz_against_the_reference_script(tmp_path, capsys):
+    """f1, randomised: the unmodified reference script (Bio.SeqIO resolved to tests/golden/bio_standin) and the mirror on
+    the same seeded inputs — ragged line lengths, blanks and CRs inside sequences, odd header white space, records the
+    .fai does not know, indices past its end, repeated and malformed ref_index lines"""
+    import importlib.util
+    from palace_b200 import get_ref_by_index as g
+    spec = importlib.util.spec_from_file_location("make_golden_f1", os.path.join(os.path.dirname(__file__), "golden", "make_golden_f1.py"))
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    rng = np.random.default_rng(4242)
+    for case in range(40):
+        n = int(rng.integers(1, 12))
+        fa, names_in_fa = b"", []
+        if rng.random() < 0.3:
+            fa += b"junk before the first header\n"
+        for r in range(n):
+            name = f"s{case}_{r}" + ("|x" if rng.random() < 0.3 else "")
+            sep = [b" ", b"\t", b"  ", b""][int(rng.integers(0, 4))]
+            fa += b">" + name.encode() + (sep + b"desc " + str(r).encode() if sep else b"") + [b"\n", b"\r\n", b" \n"][int(rng.integers(0, 3))]
+            names_in_fa.append(name)
+            for _ in range(int(rng.integers(0, 5))):
+                line = bytes(rng.choice(np.frombuffer(b"ACGTNacgt", np.uint8), int(rng.integers(0, 30))))
+                if rng.random() < 0.2:
+                    line = line[:3] + b" " + line[3:]
+                fa += line + [b"\n", b"\r\n", b"  \n", b"\n\n"][int(rng.integers(0, 4))]
+        if rng.random() < 0.5:
+            fa = fa.rstrip(b"\n")
+        fai_names = list(names_in_fa)
+        if rng.random() < 0.4:
+            fai_names.insert(int(rng.integers(0, len(fai_names) + 1)), "ghost")
+        fai = "".join(f"{nm}\t1\t2\t3\t4\n" for nm in fai_names)
+        lines = []
+        for _ in range(int(rng.integers(0, 10))):
+            k = int(rng.integers(0, len(fai_names) + 3))
+            pct = ["0.9", "1", "0.7512", "7.5e-01", "nan", "x"][int(rng.integers(0, 6))]
+            lines.append([f"ref_index\t{k}\t1\t10\t12\t{pct}", f"ref_index {k} {pct}", f"other\t{k}\t{pct}", f" ref_index\t{k}\t{pct} ",
+                          f"ref_index\tx{k}\t{pct}"][int(rng.integers(0, 5))])
+        names = "\n".join(lines) + ("\n" if lines else "")
+        want = ref.run_reference(fa, fai, names)
+        d = tmp_path / f"c{case}"
+        d.mkdir()
+        (d / "db.fa").write_bytes(fa); (d / "db.fa.fai").write_text(fai); (d / "names.txt").write_text(names)
+        capsys.readouterr()
+        g.main(["x", str(d / "db.fa"), str(d / "db.fa.fai"), str(d / "names.txt"), str(d / "out.fa"), str(d / "out.txt")])
+        got = ((d / "out.fa").read_text(), (d / "out.txt").read_text(), capsys.readouterr().out)
+        assert got == want, (case, fa, fai, names)
