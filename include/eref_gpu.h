@@ -34,6 +34,7 @@ extern "C" {
 #define EREF_FLAG_NO_PRUNE 1u          /* probe all three streams at every position (no candidate filter) */
 #define EREF_FLAG_DIRECT_COUNT 2u      /* count k-mers straight into the table (no code-range partitioning) */
 #define EREF_FLAG_KEEP_RAND_STATE 4u   /* eref_run_host: do not srand(1) before the down-sampling draws (:1236-1238) */
+#define EREF_FLAG_LEVEL_POP 8u         /* count the codes at each level during every table build (eref_query_popcount) */
 
 typedef struct eref_ctx eref_ctx;
 
@@ -134,6 +135,33 @@ int  eref_ref_records(eref_ctx* ctx, uint32_t* len_out, uint32_t* hdr_off_out, s
  * A host streams the chunks to disk behind the 400-byte coder header to share a DB directory with the CPU
  * eref. */
 int  eref_index_body(eref_ctx* ctx, uint32_t first, uint32_t* out_host, size_t cap_words, size_t* n_words, uint32_t* next);
+
+/* Sharded table build.  The reference shares ONE table among its scan threads (:1257-1291 build it, :1309-1329 read
+ * it); with the database sharded over GPUs every GPU needs the whole table, but the saturating count of a code does
+ * not depend on any other code (:995-997), so GPU `part` of `parts` counts only the table slices
+ * [8192*part/parts, 8192*(part+1)/parts) and the finished level-3 slices are exchanged instead of every GPU counting
+ * everything.  Two ways to complete the tables:
+ *   peers  eref_table_export on every context, eref_table_set_peer for every other part: the counting kernel stores
+ *          each finished slice into every GPU's table through peer pointers (NVLink) and raises a flag there; the
+ *          scan waits for all flags on the device.  ipc_handles (EREF_TABLE_HANDLE_BYTES, from the peer's
+ *          eref_table_export) for a context in another process, or its raw device pointers + device id in the same one.
+ *   hook   eref_table_set_hook: called on the context's stream once the local part is complete and before the first
+ *          probe; the callee completes the table there (e.g. NCCL all-gather in place over eref_table_part_range).
+ * Every GPU of a build must make the same sequence of calls, and a collective or barrier ordered on the streams must
+ * separate a scan from the NEXT table build (the all-gather of the result records is one): a builder writes into
+ * its peers' tables.  eref_query_popcount then reports this part's codes only. */
+#define EREF_TABLE_HANDLE_BYTES 192
+typedef int (*eref_table_hook)(void* arg, void* cuda_stream);
+int  eref_table_export(eref_ctx* ctx, void* ipc_handles, void** bm3_dev, void** summary_dev, void** flags_dev);
+int  eref_table_set_part(eref_ctx* ctx, int part, int parts);
+int  eref_table_set_peer(eref_ctx* ctx, int peer_part, int peer_device, const void* ipc_handles, void* bm3_dev,
+                         void* summary_dev, void* flags_dev);
+int  eref_table_set_hook(eref_ctx* ctx, eref_table_hook fn, void* arg);
+int  eref_table_part_range(eref_ctx* ctx, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes);
+/* queue the build of the files added so far and make the context's stream wait for the complete table */
+int  eref_table_join(eref_ctx* ctx);
+/* wait for everything queued on the context */
+int  eref_sync(eref_ctx* ctx);
 
 /* table inspection (tests): number of codes with count >= level (1..3) */
 int  eref_query_popcount(eref_ctx* ctx, int level, uint64_t* out);

@@ -91,6 +91,17 @@ struct eref_ctx {
     cudaEvent_t aux_ev[2]{};
     uint32_t* summary = nullptr;               // 1 bit per 16 level-3 slots
     bool summary_stale = true;
+    // Sharded build (eref_table_set_part): this GPU counts the slices [slice0, slice0 + nslices) and stores them into
+    // every peer's table; share_words = 16 flag words (one per part) | done counter | error word
+    int parts = 1, part = 0;
+    uint32_t slice0 = 0, nslices = NSLICES;
+    struct Peer { uint32_t* bm3 = nullptr; uint32_t* summary = nullptr; uint32_t* flags = nullptr; bool ipc = false; };
+    Peer peers[MAX_PARTS];
+    uint32_t* share_words = nullptr;
+    uint32_t table_epoch = 0;
+    bool join_pending = false;                 // a sharded build was queued and the main stream has not joined it yet
+    eref_table_hook hook = nullptr;
+    void* hook_arg = nullptr;
     int probe_parts = 8;                       // EREF_PROBE_PARTS: rounds of the listed-word probe, 1 = whole table at once
     int bucket_bits = 32 - SLICE_BITS - 8;     // EREF_BUCKET_BITS: 2^bits coarse buckets, 256 slices per bucket by default
     // reference side
@@ -125,6 +136,7 @@ namespace {
 
 int start_table_update(eref_ctx* c);
 int wait_table(eref_ctx* c, cudaStream_t st);
+int join_table(eref_ctx* c, cudaStream_t st);
 // layout of part_ctr after the u64 arrays: u32 chunk_start[260], then u64 totals[3]
 inline unsigned long long* chunk_start_end(uint32_t* chunk_start) { return reinterpret_cast<unsigned long long*>(chunk_start + 260); }
 
@@ -310,7 +322,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         unsigned long long* coarse_n = coarse_tail + 256;
         uint32_t* chunk_start = reinterpret_cast<uint32_t*>(coarse_n + 256);
         CUDA_TRY(cudaMemsetAsync(hist, 0, ((size_t)NSLICES * 2 + 256) * 8, st));
-        LAUNCH(c, launch_slice_hist(pl, plane_bits, c->masks, hist, st));
+        LAUNCH(c, launch_slice_hist(pl, plane_bits, c->masks, hist, c->slice0, c->nslices, st));
         unsigned long long* totals = chunk_start_end(chunk_start);     // {codes, padded size, chunks}
         if (c->lists.size() <= c->n_lists) c->lists.resize(c->n_lists + 1);
         eref_ctx::CodeList& L = c->lists[c->n_lists];
@@ -327,7 +339,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         CUDA_TRY(L.codes.ensure((size_t)padded * 4 + 16));
         CUDA_TRY(c->codes_coarse.ensure((size_t)padded * 4 + 16));
         LAUNCH(c, launch_coarse_scatter(pl, c->masks, cbits, L.off.as<unsigned long long>(), coarse_tail,
-                                        c->codes_coarse.as<uint32_t>(), st));
+                                        c->codes_coarse.as<uint32_t>(), c->slice0, c->nslices, st));
         LAUNCH(c, launch_fine_partition(c->codes_coarse.as<uint32_t>(), L.off.as<unsigned long long>(), coarse_n, chunk_start,
                                         nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), st));
         // the partition kernels are queued; nothing below waits for them (times and byte counts: collect_times)
@@ -382,7 +394,25 @@ int start_table_update(eref_ctx* c)
         cl.cnt[k] = c->lists[k].cnt.as<unsigned long long>();
     }
     if (c->want_pop) CUDA_TRY(cudaMemsetAsync(c->level_pop.p, 0, 24, ts));
-    LAUNCH(c, launch_count_slices(cl, c->bm[2], c->summary, c->want_pop ? c->level_pop.as<unsigned long long>() : nullptr, ts));
+    // destinations of the finished slices: this GPU's table, and in a sharded build with peers every other GPU's
+    TableShare sh{};
+    sh.bm3[0] = c->bm[2]; sh.summary[0] = c->summary; sh.flags[0] = c->share_words;
+    sh.n = 1; sh.part = c->part; sh.s0 = c->slice0; sh.ns = c->nslices;
+    sh.done = c->share_words + MAX_PARTS;
+    bool all_peers = c->parts > 1;
+    for (int p = 0; p < c->parts && all_peers; p++) if (p != c->part && !c->peers[p].bm3) all_peers = false;
+    if (c->parts > 1) {
+        if (!all_peers && !c->hook)
+            return eref_fail(EREF_ERR_STATE, "sharded table build: neither every peer (eref_table_set_peer) nor a completion hook "
+                                             "(eref_table_set_hook) is set");
+        c->table_epoch++;
+        sh.epoch = c->table_epoch;
+        if (all_peers)
+            for (int p = 0; p < c->parts; p++)
+                if (p != c->part) { sh.bm3[sh.n] = c->peers[p].bm3; sh.summary[sh.n] = c->peers[p].summary; sh.flags[sh.n] = c->peers[p].flags; sh.n++; }
+        c->join_pending = true;
+    }
+    LAUNCH(c, launch_count_slices(cl, sh, c->want_pop ? c->level_pop.as<unsigned long long>() : nullptr, ts));
     c->have_pop = c->want_pop;
     CUDA_TRY(cudaEventRecord(c->evf[1], ts));
     CUDA_TRY(cudaEventRecord(c->table_ready, ts));
@@ -397,6 +427,26 @@ int start_table_update(eref_ctx* c)
 int wait_table(eref_ctx* c, cudaStream_t st)
 {
     if (c->table_inflight) CUDA_TRY(cudaStreamWaitEvent(st, c->table_ready, 0));
+    return 0;
+}
+
+// Make `st` wait for the table to be complete.  Local build: the update queued last.  Sharded build: also every other
+// GPU's part — with peer pointers the builders stored their slices straight into this table and raised a flag each
+// (k_table_wait acquires them); without, the caller's hook completes the table on `st` (e.g. an in-place all-gather).
+int join_table(eref_ctx* c, cudaStream_t st)
+{
+    int rc = wait_table(c, st);
+    if (rc || !c->join_pending) return rc;
+    c->join_pending = false;
+    bool all_peers = true;
+    for (int p = 0; p < c->parts; p++) if (p != c->part && !c->peers[p].bm3) all_peers = false;
+    if (all_peers) {
+        LAUNCH(c, launch_table_wait(c->share_words, c->parts, c->table_epoch, c->share_words + MAX_PARTS + 1, st));
+        return 0;
+    }
+    if (!c->hook) return eref_fail(EREF_ERR_STATE, "sharded table build without peers or a completion hook");
+    rc = c->hook(c->hook_arg, (void*)st);
+    if (rc) return eref_fail(EREF_ERR_STATE, "the table completion hook failed (%d)", rc);
     return 0;
 }
 
@@ -516,7 +566,7 @@ int scan_impl(eref_ctx* c)
     int frc = start_table_update(c);
     if (frc) return frc;
     cudaStream_t st = c->stream;
-    frc = wait_table(c, st);
+    frc = join_table(c, st);
     if (frc) return frc;
     const uint64_t nw = c->ref_words;
     const uint32_t G = c->n_genomes;
@@ -661,6 +711,9 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = c->counters.ensure(64);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, (8 + MAX_BUCKETS) * 8, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->share_words, (MAX_PARTS + 2) * 4);
+    if (e == cudaSuccess) e = cudaMemset(c->share_words, 0, (MAX_PARTS + 2) * 4);
+    if (flags & EREF_FLAG_LEVEL_POP) c->want_pop = true;
     if (e != cudaSuccess) { eref_destroy(c); return eref_fail_cuda(e, "context allocation", __FILE__, __LINE__); }
     c->stream = c->own_stream;
     *out = c;
@@ -682,8 +735,14 @@ void eref_destroy(eref_ctx* c)
                       &c->sample_hits, &c->need, &c->need_list, &c->hits0, &c->hits1, &c->hits2, &c->single, &c->trio, &c->good, &c->results,
                       &c->codes_tmp, &c->cell_pre};
     for (DevBuf* b : bufs) b->release();
+    for (int p = 0; p < MAX_PARTS; p++)
+        if (c->peers[p].ipc) {
+            cudaIpcCloseMemHandle(c->peers[p].bm3); cudaIpcCloseMemHandle(c->peers[p].summary);
+            cudaIpcCloseMemHandle(c->peers[p].flags);
+        }
     for (int l = 0; l < 3; l++) if (c->bm[l]) cudaFree(c->bm[l]);
     if (c->summary) cudaFree(c->summary);
+    if (c->share_words) cudaFree(c->share_words);
     if (c->h_pin) cudaFreeHost(c->h_pin);
     c->part_ctr.release(); c->codes_coarse.release(); c->level_pop.release();
     for (auto& L : c->lists) { L.codes.release(); L.off.release(); L.cnt.release(); }
@@ -855,11 +914,18 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     size_t n = c->n_genomes < cap ? c->n_genomes : cap;
     if (n) CUDA_TRY(cudaMemcpyAsync(out, c->results.p, n * sizeof(eref_result), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    if (c->parts > 1) CUDA_TRY(cudaMemcpyAsync(c->h_pin + 7, c->share_words + MAX_PARTS, 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev[S7], c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->scan_pending = true; c->scan_pending_d2h = true;
     collect_times(c);
     if (n_out) *n_out = c->n_genomes;
+    if (c->parts > 1 && (c->h_pin[7] >> 32)) {
+        const unsigned who = (unsigned)(c->h_pin[7] >> 32) - 1;
+        cudaMemsetAsync(c->share_words + MAX_PARTS + 1, 0, 4, c->stream);
+        return eref_fail(EREF_ERR_STATE, "sharded table build: part %u never arrived in this GPU's table (is every GPU "
+                                         "of the build running the same sequence of calls?)", who);
+    }
     return 0;
 }
 
@@ -1165,8 +1231,11 @@ int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
 {
     if (!c || !out || level < 1 || level > 3) return eref_fail(EREF_ERR_ARG, "eref_query_popcount: bad argument");
     CUDA_TRY(cudaSetDevice(c->device));
+    if (c->parts > 1 && !c->want_pop)
+        return eref_fail(EREF_ERR_STATE, "level populations of a sharded build need EREF_FLAG_LEVEL_POP at eref_create "
+                                         "(a rebuild for the count would write into the peers' tables)");
     if (!(c->flags & EREF_FLAG_DIRECT_COUNT) && !c->want_pop) { c->want_pop = true; c->table_dirty = true; }
-    if (!(c->flags & EREF_FLAG_DIRECT_COUNT) && !c->have_pop) c->table_dirty = true;
+    if (!(c->flags & EREF_FLAG_DIRECT_COUNT) && !c->have_pop && c->parts == 1) c->table_dirty = true;
     int frc = finalize_table(c);
     if (frc) return frc;
     unsigned long long h = 0;
@@ -1182,6 +1251,112 @@ int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     *out = h;
     return 0;
+}
+
+int eref_sync(eref_ctx* c)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    if (c->table_inflight) { CUDA_TRY(cudaStreamSynchronize(c->table_stream)); table_done(c); }
+    collect_times(c);
+    return 0;
+}
+
+int eref_table_export(eref_ctx* c, void* ipc_handles, void** bm3_dev, void** summary_dev, void** flags_dev)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (c->flags & EREF_FLAG_DIRECT_COUNT) return eref_fail(EREF_ERR_UNSUPPORTED, "the direct build cannot be sharded");
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (ipc_handles) {
+        static_assert(3 * sizeof(cudaIpcMemHandle_t) == EREF_TABLE_HANDLE_BYTES, "handle blob size");
+        cudaIpcMemHandle_t h[3];
+        CUDA_TRY(cudaIpcGetMemHandle(&h[0], c->bm[2]));
+        CUDA_TRY(cudaIpcGetMemHandle(&h[1], c->summary));
+        CUDA_TRY(cudaIpcGetMemHandle(&h[2], c->share_words));
+        memcpy(ipc_handles, h, sizeof h);
+    }
+    if (bm3_dev) *bm3_dev = c->bm[2];
+    if (summary_dev) *summary_dev = c->summary;
+    if (flags_dev) *flags_dev = c->share_words;
+    return 0;
+}
+
+int eref_table_set_part(eref_ctx* c, int part, int parts)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (parts < 1 || parts > MAX_PARTS || part < 0 || part >= parts)
+        return eref_fail(EREF_ERR_ARG, "eref_table_set_part: part %d of %d (at most %d parts)", part, parts, MAX_PARTS);
+    if (parts > 1 && (c->flags & EREF_FLAG_DIRECT_COUNT))
+        return eref_fail(EREF_ERR_UNSUPPORTED, "the direct build cannot be sharded");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = eref_sync(c);
+    if (rc) return rc;
+    c->parts = parts; c->part = part;
+    c->slice0 = (uint32_t)((uint64_t)NSLICES * part / parts);
+    c->nslices = (uint32_t)((uint64_t)NSLICES * (part + 1) / parts) - c->slice0;
+    c->table_dirty = true; c->join_pending = false;
+    c->n_lists = 0;                             // code lists hold only the codes of the part they were made for
+    return 0;
+}
+
+int eref_table_set_peer(eref_ctx* c, int peer_part, int peer_device, const void* ipc_handles, void* bm3_dev,
+                        void* summary_dev, void* flags_dev)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (peer_part < 0 || peer_part >= c->parts || peer_part == c->part)
+        return eref_fail(EREF_ERR_ARG, "eref_table_set_peer: part %d (this context is part %d of %d)", peer_part, c->part, c->parts);
+    CUDA_TRY(cudaSetDevice(c->device));
+    eref_ctx::Peer& P = c->peers[peer_part];
+    if (P.ipc) { cudaIpcCloseMemHandle(P.bm3); cudaIpcCloseMemHandle(P.summary); cudaIpcCloseMemHandle(P.flags); }
+    P = eref_ctx::Peer();
+    if (ipc_handles) {
+        cudaIpcMemHandle_t h[3];
+        memcpy(h, ipc_handles, sizeof h);
+        void *a = nullptr, *b = nullptr, *f = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&a, h[0], cudaIpcMemLazyEnablePeerAccess));
+        CUDA_TRY(cudaIpcOpenMemHandle(&b, h[1], cudaIpcMemLazyEnablePeerAccess));
+        CUDA_TRY(cudaIpcOpenMemHandle(&f, h[2], cudaIpcMemLazyEnablePeerAccess));
+        P.bm3 = (uint32_t*)a; P.summary = (uint32_t*)b; P.flags = (uint32_t*)f; P.ipc = true;
+        return 0;
+    }
+    if (!bm3_dev || !summary_dev || !flags_dev) return eref_fail(EREF_ERR_ARG, "eref_table_set_peer: null table pointer");
+    if (peer_device >= 0 && peer_device != c->device) {
+        int can = 0;
+        CUDA_TRY(cudaDeviceCanAccessPeer(&can, c->device, peer_device));
+        if (!can) return eref_fail(EREF_ERR_UNSUPPORTED, "GPU %d cannot access GPU %d's memory", c->device, peer_device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) return eref_fail_cuda(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+    }
+    P.bm3 = (uint32_t*)bm3_dev; P.summary = (uint32_t*)summary_dev; P.flags = (uint32_t*)flags_dev;
+    return 0;
+}
+
+int eref_table_set_hook(eref_ctx* c, eref_table_hook fn, void* arg)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    c->hook = fn; c->hook_arg = arg;
+    return 0;
+}
+
+int eref_table_part_range(eref_ctx* c, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (table_off) *table_off = (size_t)c->slice0 * SLICE_WORDS * 4;
+    if (table_bytes) *table_bytes = (size_t)c->nslices * SLICE_WORDS * 4;
+    if (summary_off) *summary_off = (size_t)c->slice0 * (SLICE_WORDS / 16) * 4;
+    if (summary_bytes) *summary_bytes = (size_t)c->nslices * (SLICE_WORDS / 16) * 4;
+    return 0;
+}
+
+int eref_table_join(eref_ctx* c)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = start_table_update(c);
+    if (rc) return rc;
+    return join_table(c, c->stream);
 }
 
 int eref_timings(eref_ctx* c, eref_phase_times* out)

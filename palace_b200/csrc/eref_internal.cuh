@@ -152,10 +152,11 @@ cudaError_t launch_pack_fasta(const uint8_t* text, uint64_t n, const TileSum* ti
 // table.cu
 cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t* bm2, uint32_t* bm3,
                                cudaStream_t st);
+// s0/ns: the table slices whose codes are kept (all of them unless the build is sharded over GPUs)
 cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, CoderMasks m, unsigned long long* g_hist,
-                              cudaStream_t st);
+                              uint32_t s0, uint32_t ns, cudaStream_t st);
 cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
-                                  unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st);
+                                  unsigned long long* g_tail, uint32_t* codes_out, uint32_t s0, uint32_t ns, cudaStream_t st);
 cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
                                   const uint32_t* chunk_start, uint32_t nchunks, int cbits, unsigned long long* g_tail,
                                   uint32_t* out, cudaStream_t st);
@@ -169,8 +170,21 @@ struct CountLists {
     const unsigned long long* cnt[MAX_LISTS];
     int n;
 };
-cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t* summary, unsigned long long* level_pop,
+// Sharded table build: one GPU ("part") counts the slices [s0, s0 + ns) and stores them into the table of every GPU
+// of the build through peer pointers (index 0 = its own table; n = 1: a local build).  flags[p] points at GPU p's
+// flag words (one per part): part `part` of build `epoch` has landed there once flags[p][part] >= epoch.
+constexpr int MAX_PARTS = 16;
+struct TableShare {
+    uint32_t* bm3[MAX_PARTS];
+    uint32_t* summary[MAX_PARTS];
+    uint32_t* flags[MAX_PARTS];
+    unsigned int* done;              // CTAs of the current build that have finished (this GPU's own counter)
+    int n, part;
+    uint32_t s0, ns, epoch;
+};
+cudaError_t launch_count_slices(const CountLists& lists, const TableShare& share, unsigned long long* level_pop,
                                 cudaStream_t st);
+cudaError_t launch_table_wait(const uint32_t* flags, int n, uint32_t epoch, uint32_t* err, cudaStream_t st);
 cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, uint32_t summary_words, cudaStream_t st);
 cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);
 // scan.cu

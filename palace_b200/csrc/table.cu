@@ -15,6 +15,7 @@
 // three levels and writes the finished level-3 slice (and its summary) to HBM with plain stores.
 #include "eref_internal.cuh"
 #include <cstdlib>
+#include <algorithm>
 
 namespace {
 
@@ -88,16 +89,20 @@ __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks
 // of the flush atomics — measured the same 55 us per file: the flush is not what bounds it.)
 constexpr int HIST_THREADS = NSLICES * 4 > 48 * 1024 ? 512 : 256;      // 64 KiB of bins: three CTAs of 512 per SM
 
+// s0/ns: the table slices this GPU counts (sharded build, api.cu); codes of other slices are some other GPU's work.
 __global__ void __launch_bounds__(HIST_THREADS)
 k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, CoderMasks m,
-             unsigned long long* __restrict__ g_hist)
+             unsigned long long* __restrict__ g_hist, uint32_t s0, uint32_t ns)
 {
     extern __shared__ uint32_t s_hist[];                   // NSLICES
     for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     const uint64_t nwords = (*plane_bits + 31) >> 5;      // the host has not seen the packed size yet
     for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += (uint64_t)gridDim.x * blockDim.x)
-        for_each_code(pl, m, w, [&](uint32_t code) { atomicAdd(&s_hist[code >> SLICE_BITS], 1u); });
+        for_each_code(pl, m, w, [&](uint32_t code) {
+            const uint32_t s = code >> SLICE_BITS;
+            if (s - s0 < ns) atomicAdd(&s_hist[s], 1u);
+        });
     __syncthreads();
     for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) {
         const uint32_t v = s_hist[i];
@@ -110,7 +115,7 @@ k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, Coder
 // slice offset table: coarse bucket b starts where its first slice starts.
 __global__ void __launch_bounds__(256)
 k_coarse_scatter(Planes pl, CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
-                 unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out)
+                 unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out, uint32_t s0, uint32_t ns)
 {
     __shared__ uint32_t s_hist[8][MAX_BUCKETS];
     __shared__ unsigned long long s_base[MAX_BUCKETS];
@@ -121,7 +126,7 @@ k_coarse_scatter(Planes pl, CoderMasks m, int shift, const unsigned long long* _
     __syncthreads();
     const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = w < pl.nwords;
-    if (live) for_each_code(pl, m, w, [&](uint32_t code) { atomicAdd(&s_hist[warp][code >> shift], 1u); });
+    if (live) for_each_code(pl, m, w, [&](uint32_t code) { if ((code >> SLICE_BITS) - s0 < ns) atomicAdd(&s_hist[warp][code >> shift], 1u); });
     __syncthreads();
     if (threadIdx.x < nb) {
         uint32_t c = 0;
@@ -134,7 +139,7 @@ k_coarse_scatter(Planes pl, CoderMasks m, int shift, const unsigned long long* _
     __syncthreads();
     if (live) for_each_code(pl, m, w, [&](uint32_t code) {
         const uint32_t b = code >> shift;
-        codes_out[s_base[b] + atomicAdd(&s_cursor[b], 1u)] = code;
+        if ((code >> SLICE_BITS) - s0 < ns) codes_out[s_base[b] + atomicAdd(&s_cursor[b], 1u)] = code;
     });
 }
 
@@ -161,7 +166,7 @@ __device__ __forceinline__ void for_each_code_half(const Planes& pl, const Coder
 
 __global__ void __launch_bounds__(CS_THREADS)
 k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
-                        unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out)
+                        unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out, uint32_t s0, uint32_t ns)
 {
     extern __shared__ uint32_t s_codes[];                  // CS_CODES
     __shared__ uint32_t s_cur[CS_THREADS / 32][MAX_BUCKETS];   // per warp: counts, then cursors into s_codes
@@ -175,7 +180,7 @@ k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long 
     const uint64_t w = (uint64_t)blockIdx.x * CS_WORDS + (threadIdx.x >> 1);
     const int half = threadIdx.x & 1;
     const bool live = w < pl.nwords;
-    if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) { atomicAdd(&s_cur[warp][code >> shift], 1u); });
+    if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) { if ((code >> SLICE_BITS) - s0 < ns) atomicAdd(&s_cur[warp][code >> shift], 1u); });
     __syncthreads();
     // bucket totals -> exclusive prefix (nb <= 256: one bucket per thread), global reservation, per-warp cursors
     uint32_t c = 0;
@@ -202,7 +207,7 @@ k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long 
     if (threadIdx.x == CS_THREADS - 1) s_start[nb] = base + inc;
     __syncthreads();
     if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) {
-        s_codes[atomicAdd(&s_cur[warp][code >> shift], 1u)] = code;
+        if ((code >> SLICE_BITS) - s0 < ns) s_codes[atomicAdd(&s_cur[warp][code >> shift], 1u)] = code;
     });
     __syncthreads();
     const uint32_t total = s_start[nb];
@@ -384,13 +389,13 @@ __device__ __forceinline__ void count_unit(const uint4& v, uint32_t left, uint32
 template <bool POP>
 __global__ void __launch_bounds__(COUNT_THREADS, 1)
 k_count_slices(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary,
-               unsigned long long* __restrict__ level_pop)
+               unsigned long long* __restrict__ level_pop, uint32_t s0)
 {
     extern __shared__ uint4 s_raw[];
     uint32_t* L1 = reinterpret_cast<uint32_t*>(s_raw);
     uint32_t* L2 = L1 + SLICE_WORDS;
     uint32_t* L3 = L2 + SLICE_WORDS;
-    const uint32_t slice = blockIdx.x;
+    const uint32_t slice = s0 + blockIdx.x;
     // the first codes of the first two lists are requested before the levels are zeroed, so that the HBM round
     // trip overlaps the shared-memory stores
     uint4 pre[2][COUNT_PRE];
@@ -456,10 +461,15 @@ k_count_slices(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restric
 // P3 (persistent): one CTA per SM walks the slices blockIdx.x, blockIdx.x + gridDim.x, ...  While a slice is being
 // counted and written out, the first codes of the NEXT slice are already on their way into registers, so the HBM
 // round trip and the CTA turn-around of k_count_slices (about a third of its 8.8 us per slice) disappear.
+//
+// Sharded build (TableShare, eref_internal.cuh): the CTAs walk only this GPU's slices [s0, s0 + ns) and store every
+// finished level-3 slice and its summary into the table of EVERY GPU of the build — plain 16-byte stores through
+// peer pointers, i.e. the all-gather of the table rides on the copy-out over NVLink, slice by slice, while the
+// other SMs are still counting.  The last CTA to finish publishes the build's epoch in every GPU's flag word
+// (release at system scope); k_table_wait on the consumer's stream acquires all of them before the first probe.
 template <bool POP>
 __global__ void __launch_bounds__(COUNT_THREADS, COUNT_CTAS)
-k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restrict__ summary,
-                          unsigned long long* __restrict__ level_pop)
+k_count_slices_persistent(CountLists lists, TableShare share, unsigned long long* __restrict__ level_pop)
 {
     extern __shared__ uint4 s_raw[];
     uint32_t* L1 = reinterpret_cast<uint32_t*>(s_raw);
@@ -467,11 +477,12 @@ k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t
     uint32_t* L3 = L2 + SLICE_WORDS;
     uint4 pre[2][COUNT_PRE];
     uint64_t n_pre[2] = {0, 0};
+    const uint32_t slice_end = share.s0 + share.ns;
     auto fetch = [&](uint32_t slice) {
 #pragma unroll
         for (int l = 0; l < 2; l++) {
             n_pre[l] = 0;
-            if (l < lists.n && slice < (uint32_t)NSLICES) {
+            if (l < lists.n && slice < slice_end) {
                 n_pre[l] = lists.cnt[l][slice];
                 const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);
 #pragma unroll
@@ -483,10 +494,10 @@ k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t
         }
     };
     uint32_t p1 = 0, p2 = 0, p3 = 0;
-    fetch(blockIdx.x);
+    fetch(share.s0 + blockIdx.x);
     for (int i = threadIdx.x; i < 3 * SLICE_WORDS / 4; i += COUNT_THREADS) s_raw[i] = make_uint4(0, 0, 0, 0);
     __syncthreads();
-    for (uint32_t slice = blockIdx.x; slice < (uint32_t)NSLICES; slice += gridDim.x) {
+    for (uint32_t slice = share.s0 + blockIdx.x; slice < slice_end; slice += gridDim.x) {
         // the prefetched units of this slice, then whatever the registers could not hold
         uint4 cur[2][COUNT_PRE];
         uint64_t n_cur[2];
@@ -517,14 +528,14 @@ k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t
         }
         // level 3 out, one 16-byte unit per thread and round; summary word j covers table words 16j .. 16j+15 = four
         // consecutive units, i.e. four neighbouring lanes: 8 summary bits each, combined with two shuffles
-        uint4* dst = reinterpret_cast<uint4*>(bm3 + (size_t)slice * SLICE_WORDS);
+        const size_t dst_unit = (size_t)slice * (SLICE_WORDS / 4);
         const uint4* l3 = reinterpret_cast<const uint4*>(L3);
         uint4* l3w = reinterpret_cast<uint4*>(L3);
         uint4* l1w = reinterpret_cast<uint4*>(L1);
         uint4* l2w = reinterpret_cast<uint4*>(L2);
         for (int i = threadIdx.x; i < SLICE_WORDS / 4; i += COUNT_THREADS) {
             const uint4 v = l3[i];
-            __stcs(dst + i, v);
+            for (int p = 0; p < share.n; p++) __stcs(reinterpret_cast<uint4*>(share.bm3[p]) + dst_unit + i, v);
             // the three levels are zeroed for the next slice as they are read out (a thread clears what it alone read)
             l3w[i] = make_uint4(0, 0, 0, 0); l1w[i] = make_uint4(0, 0, 0, 0); l2w[i] = make_uint4(0, 0, 0, 0);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -539,9 +550,24 @@ k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t
             out <<= 8 * (i & 3);
             out |= __shfl_xor_sync(0xffffffffu, out, 1);
             out |= __shfl_xor_sync(0xffffffffu, out, 2);
-            if ((i & 3) == 0) summary[(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
+            if ((i & 3) == 0)
+                for (int p = 0; p < share.n; p++) share.summary[p][(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
         }
         __syncthreads();
+    }
+    if (share.n > 1) {
+        // publish: every thread's peer stores are ordered before the CTA's arrival; the last CTA to arrive raises this
+        // part's flag on every GPU
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            if (atomicAdd(share.done, 1u) == gridDim.x - 1) {
+                __threadfence_system();
+                for (int p = 0; p < share.n; p++)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(share.flags[p] + share.part), "r"(share.epoch) : "memory");
+            }
+        }
     }
     if (POP) {
         p1 = __reduce_add_sync(0xffffffffu, p1); p2 = __reduce_add_sync(0xffffffffu, p2); p3 = __reduce_add_sync(0xffffffffu, p3);
@@ -550,6 +576,25 @@ k_count_slices_persistent(CountLists lists, uint32_t* __restrict__ bm3, uint32_t
             if (p2) atomicAdd(level_pop + 1, (unsigned long long)p2);
             if (p3) atomicAdd(level_pop + 2, (unsigned long long)p3);
         }
+    }
+}
+
+// Consumer side of the sharded build: lane q waits until part q of build `epoch` has landed in this GPU's table
+// (flag >= epoch, acquire at system scope).  Bounded: after ~4 s without progress the error word is set and the
+// kernel returns, so a peer that died cannot hang the stream.
+__global__ void k_table_wait(const uint32_t* __restrict__ flags, int n, uint32_t epoch, uint32_t* __restrict__ err)
+{
+    if ((int)threadIdx.x >= n) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+        if ((int32_t)(v - epoch) >= 0) return;
+        __nanosleep(200);
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 4000000000ull) { atomicExch(err, 1u + threadIdx.x); return; }
     }
 }
 
@@ -598,17 +643,17 @@ cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t*
 }
 
 cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, CoderMasks m, unsigned long long* g_hist,
-                              cudaStream_t st)
+                              uint32_t s0, uint32_t ns, cudaStream_t st)
 {
     const int smem = NSLICES * 4;
     cudaError_t e = cudaFuncSetAttribute(k_slice_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    k_slice_hist<<<148 * 1536 / HIST_THREADS, HIST_THREADS, smem, st>>>(pl, plane_bits, m, g_hist);
+    k_slice_hist<<<148 * 1536 / HIST_THREADS, HIST_THREADS, smem, st>>>(pl, plane_bits, m, g_hist, s0, ns);
     return cudaGetLastError();
 }
 
 cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
-                                  unsigned long long* g_tail, uint32_t* codes_out, cudaStream_t st)
+                                  unsigned long long* g_tail, uint32_t* codes_out, uint32_t s0, uint32_t ns, cudaStream_t st)
 {
     if (!pl.nwords) return cudaSuccess;
     static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 1; }();
@@ -617,9 +662,9 @@ cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsi
         cudaError_t e = cudaFuncSetAttribute(k_coarse_scatter_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         k_coarse_scatter_staged<<<(unsigned)((pl.nwords + CS_WORDS - 1) / CS_WORDS), CS_THREADS, smem, st>>>(
-            pl, m, 32 - cbits, slice_off, g_tail, codes_out);
+            pl, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
     } else {
-        k_coarse_scatter<<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, 32 - cbits, slice_off, g_tail, codes_out);
+        k_coarse_scatter<<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
     }
     return cudaGetLastError();
 }
@@ -643,12 +688,13 @@ cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* 
     return cudaGetLastError();
 }
 
-cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t* summary, unsigned long long* level_pop,
+cudaError_t launch_count_slices(const CountLists& lists, const TableShare& share, unsigned long long* level_pop,
                                 cudaStream_t st)
 {
     const int smem = 3 * SLICE_WORDS * 4;
     static const int persistent = [] { const char* v = getenv("EREF_COUNT_PERSISTENT"); return v ? atoi(v) : 1; }();
-    if (persistent) {
+    if (!share.ns) return cudaSuccess;
+    if (persistent || share.n > 1) {
         static int sms = 0;
         if (!sms) {
             int dev = 0;
@@ -658,15 +704,23 @@ cudaError_t launch_count_slices(const CountLists& lists, uint32_t* bm3, uint32_t
         cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                                   : cudaFuncSetAttribute(k_count_slices_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        if (level_pop) k_count_slices_persistent<true><<<sms * COUNT_CTAS, COUNT_THREADS, smem, st>>>(lists, bm3, summary, level_pop);
-        else k_count_slices_persistent<false><<<sms * COUNT_CTAS, COUNT_THREADS, smem, st>>>(lists, bm3, summary, nullptr);
+        if (share.n > 1) { e = cudaMemsetAsync(share.done, 0, 4, st); if (e != cudaSuccess) return e; }
+        const unsigned grid = (unsigned)std::min<uint32_t>((uint32_t)(sms * COUNT_CTAS), share.ns);
+        if (level_pop) k_count_slices_persistent<true><<<grid, COUNT_THREADS, smem, st>>>(lists, share, level_pop);
+        else k_count_slices_persistent<false><<<grid, COUNT_THREADS, smem, st>>>(lists, share, nullptr);
         return cudaGetLastError();
     }
     cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                               : cudaFuncSetAttribute(k_count_slices<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    if (level_pop) k_count_slices<true><<<NSLICES, COUNT_THREADS, smem, st>>>(lists, bm3, summary, level_pop);
-    else k_count_slices<false><<<NSLICES, COUNT_THREADS, smem, st>>>(lists, bm3, summary, nullptr);
+    if (level_pop) k_count_slices<true><<<share.ns, COUNT_THREADS, smem, st>>>(lists, share.bm3[0], share.summary[0], level_pop, share.s0);
+    else k_count_slices<false><<<share.ns, COUNT_THREADS, smem, st>>>(lists, share.bm3[0], share.summary[0], nullptr, share.s0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_table_wait(const uint32_t* flags, int n, uint32_t epoch, uint32_t* err, cudaStream_t st)
+{
+    k_table_wait<<<1, 32, 0, st>>>(flags, n, epoch, err);
     return cudaGetLastError();
 }
 

@@ -26,6 +26,9 @@ K = 32
 FLAG_NO_PRUNE = 1
 FLAG_DIRECT_COUNT = 2
 FLAG_KEEP_RAND_STATE = 4
+FLAG_LEVEL_POP = 8
+TABLE_HANDLE_BYTES = 192
+TABLE_HOOK = ctypes.CFUNCTYPE(c_int, c_void_p, c_void_p)
 DOWN_SAMPLING_SIZE = 2_000_000_000                       # bin/extract_ref.cpp:1230
 
 RESULT_DTYPE = np.dtype([("ordinal", "<u4"), ("frag", "<u4"), ("el", "<u4"), ("ref_len", "<u4")])
@@ -38,6 +41,8 @@ ABI_SYMBOLS = (
     "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
     "eref_run_host", "eref_ref_records", "eref_index_body", "eref_query_census", "eref_query_census_device",
     "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
+    "eref_table_export", "eref_table_set_part", "eref_table_set_peer", "eref_table_set_hook", "eref_table_part_range",
+    "eref_table_join", "eref_sync",
 )
 
 
@@ -98,6 +103,13 @@ def load_library() -> ctypes.CDLL:
     lib.eref_query_add_masked_device.argtypes = [c_void_p, c_void_p, c_size_t, c_void_p, c_uint64]
     lib.eref_ref_records.argtypes = [c_void_p, c_void_p, c_void_p, c_size_t, POINTER(c_size_t)]
     lib.eref_index_body.argtypes = [c_void_p, c_uint32, c_void_p, c_size_t, POINTER(c_size_t), POINTER(c_uint32)]
+    lib.eref_table_export.argtypes = [c_void_p, c_void_p, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p)]
+    lib.eref_table_set_part.argtypes = [c_void_p, c_int, c_int]
+    lib.eref_table_set_peer.argtypes = [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
+    lib.eref_table_set_hook.argtypes = [c_void_p, TABLE_HOOK, c_void_p]
+    lib.eref_table_part_range.argtypes = [c_void_p, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]
+    lib.eref_table_join.argtypes = [c_void_p]
+    lib.eref_sync.argtypes = [c_void_p]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
     lib.eref_format_line.argtypes = [c_void_p, ctypes.c_char_p, c_size_t]
     _lib = lib
@@ -150,7 +162,7 @@ class ErefGPU:
     """One context = one GPU: the query table, one reference text (whole DB or one shard), the scan."""
 
     def __init__(self, coder, hit_ratio: float = 0.9, perfect_hit_ratio: float = 0.85, device: int = 0,
-                 prune: bool = True, bucketed: bool = True):
+                 prune: bool = True, bucketed: bool = True, level_pop: bool = False):
         self.lib = load_library()
         if self.lib.eref_device_count() <= 0:
             raise ErefError("no CUDA device visible; liberef_gpu.so has no CPU fallback")
@@ -160,8 +172,11 @@ class ErefGPU:
         self._h = c_void_p()
         rc = self.lib.eref_create(byref(self._h), device, c.ctypes.data_as(POINTER(c_int16)),
                                   c_float(hit_ratio), c_float(perfect_hit_ratio),
-                                  (0 if prune else FLAG_NO_PRUNE) | (0 if bucketed else FLAG_DIRECT_COUNT))
+                                  (0 if prune else FLAG_NO_PRUNE) | (0 if bucketed else FLAG_DIRECT_COUNT) |
+                                  (FLAG_LEVEL_POP if level_pop else 0))
         _check(self.lib, rc, "eref_create")
+        self.device = device
+        self._hook = None
 
     def close(self):
         if getattr(self, "_h", None):
@@ -302,6 +317,49 @@ class ErefGPU:
             yield buf[:n.value].copy()
             first = nxt.value
 
+    # ---- sharded table build (include/eref_gpu.h): GPU `part` of `parts` counts its slices of the table and stores them
+    # into every peer's table over NVLink ----
+    def table_export(self, ipc: bool = False):
+        """(handles, bm3, summary, flags): IPC handle blob (bytes) for a context in another process, or the raw device
+        pointers for one in this process"""
+        h = ctypes.create_string_buffer(TABLE_HANDLE_BYTES) if ipc else None
+        a, b, f = c_void_p(), c_void_p(), c_void_p()
+        _check(self.lib, self.lib.eref_table_export(self._h, h, byref(a), byref(b), byref(f)), "eref_table_export")
+        return (h.raw if ipc else None), a.value, b.value, f.value
+
+    def table_set_part(self, part: int, parts: int):
+        _check(self.lib, self.lib.eref_table_set_part(self._h, part, parts), "eref_table_set_part")
+
+    def table_set_peer(self, peer_part: int, exported, peer_device: int = -1):
+        h, a, b, f = exported
+        _check(self.lib, self.lib.eref_table_set_peer(self._h, peer_part, peer_device, h, c_void_p(None if h else a),
+                                                      c_void_p(None if h else b), c_void_p(None if h else f)),
+               "eref_table_set_peer")
+
+    def table_set_hook(self, fn):
+        """fn(cuda_stream: int) -> None completes the table on that stream (e.g. an in-place NCCL all-gather)"""
+        def _cb(_arg, stream):
+            try:
+                fn(stream or 0)
+                return 0
+            except Exception:                              # an exception must not unwind through the C frame
+                import traceback
+                traceback.print_exc()
+                return 1
+        self._hook = TABLE_HOOK(_cb) if fn else TABLE_HOOK()
+        _check(self.lib, self.lib.eref_table_set_hook(self._h, self._hook, None), "eref_table_set_hook")
+
+    def table_part_range(self):
+        v = [c_size_t() for _ in range(4)]
+        _check(self.lib, self.lib.eref_table_part_range(self._h, *[byref(x) for x in v]), "eref_table_part_range")
+        return tuple(x.value for x in v)
+
+    def table_join(self):
+        _check(self.lib, self.lib.eref_table_join(self._h), "eref_table_join")
+
+    def sync(self):
+        _check(self.lib, self.lib.eref_sync(self._h), "eref_sync")
+
     def query_popcount(self, level: int) -> int:
         v = c_uint64()
         _check(self.lib, self.lib.eref_query_popcount(self._h, level, byref(v)), "eref_query_popcount")
@@ -410,13 +468,16 @@ def draw_keep(ratio: int, n_lines: int, reseed: bool = True) -> np.ndarray:
 def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
              perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
              bucketed: bool = True, pipelined: bool = False, chunks: int = 4, return_results: bool = False,
-             down_sampling_size: int = DOWN_SAMPLING_SIZE):
+             down_sampling_size: int = DOWN_SAMPLING_SIZE, shard_table: bool = False):
     """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
 
     `devices`: GPUs to shard the database over (one context each, run one after the other here —
     the concurrent multi-GPU drivers are palace_b200/bin/eref and bench.py under torchrun).
     """
     del threads                                            # a hint in the reference, unused here
+    if shard_table and len(devices) > 1:
+        return _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hit_ratio, coder, devices, prune,
+                                       pipelined, chunks, return_results)
     if interval_out:
         open(interval_out, "w").close()                   # :825
     if coder is None:
@@ -452,6 +513,74 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
             os.environ.pop("EREF_DOWN_SAMPLING_SIZE", None)
         else:
             os.environ["EREF_DOWN_SAMPLING_SIZE"] = old_env
+    base = 0
+    for p in parts:
+        p["ordinal"] += base
+        base += p.size
+    res = np.concatenate(parts) if parts else np.zeros(0, RESULT_DTYPE)
+    text = format_results(res)
+    return (text, res) if return_results else text
+
+
+def wire_table_peers(ctxs):
+    """contexts of ONE process, one per part: every builder gets the raw table pointers of all the others"""
+    exported = [g.table_export() for g in ctxs]
+    for i, g in enumerate(ctxs):
+        g.table_set_part(i, len(ctxs))
+    for i, g in enumerate(ctxs):
+        for j, h in enumerate(ctxs):
+            if i != j:
+                g.table_set_peer(j, exported[j], h.device)
+
+
+def _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hit_ratio, coder, devices, prune, pipelined,
+                            chunks, return_results):
+    """run_eref with the database AND the table build sharded over `devices` (entries may repeat: several contexts on
+    one GPU emulate a multi-GPU box).  Context i counts slices [8192 i/n, 8192 (i+1)/n) of the table and stores them into
+    every context's table; here the contexts run one after the other, so every build is waited for before any scan."""
+    if interval_out:
+        open(interval_out, "w").close()
+    if coder is None:
+        raise ErefError("run_eref needs the coder assignment (read_coder(index) or random_coder(seed))")
+    fq1, fq2, fasta = _as_bytes_array(fq1), _as_bytes_array(fq2), _as_bytes_array(fasta)
+    cuts = shard_offsets(fasta, len(devices))
+    ctxs = [ErefGPU(coder, hit_ratio, perfect_hit_ratio, d, prune) for d in devices]
+    try:
+        wire_table_peers(ctxs)
+        parts = [None] * len(ctxs)
+        if pipelined:
+            # eref_run_host builds, joins and scans in one call, so the contexts must run side by side like the GPUs of
+            # a box do: one host thread each (the calls release the GIL)
+            import threading
+            errs = []
+
+            def work(i, g):
+                try:
+                    shard = fasta[cuts[i]:cuts[i + 1]]
+                    parts[i] = g.run_host(fq1, fq2, shard, chunks, cap=int(np.count_nonzero(shard == 62)) + 1).copy()
+                except Exception as e:                     # noqa: BLE001 - reported below
+                    errs.append(e)
+            ts = [threading.Thread(target=work, args=(i, g)) for i, g in enumerate(ctxs)]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
+            if errs:
+                raise errs[0]
+        else:
+            for g in ctxs:
+                if sample_ratio(g.query_add(fq1)) < 100:
+                    raise ErefError("the sharded-table emulation does not down-sample")
+                g.query_add(fq2)
+            for i, g in enumerate(ctxs):
+                g.ref_set(fasta[cuts[i]:cuts[i + 1]])      # queues this part's build beside the framing
+            for g in ctxs:
+                g.sync()                                   # every part has landed in every table
+            for i, g in enumerate(ctxs):
+                parts[i] = g.scan().copy()
+    finally:
+        for g in ctxs:
+            g.close()
     base = 0
     for p in parts:
         p["ordinal"] += base

@@ -11,6 +11,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+# several contexts on one GPU emulate a multi-GPU box in the sharded-table tests: give their streams hardware queues
+# of their own (more streams than connections can serialise a spinning wait kernel ahead of the work it waits for)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 
 def pytest_configure(config):

@@ -578,3 +578,101 @@ def test_ragged_records_match_the_oracle(oracle):
     want = oracle.run(f1, f2, fa, coder, 0.9, 0.85, threads=4)
     _, got = eref.run_eref(f1, f2, fa, None, 0.9, 0.85, 1, coder=coder, return_results=True)
     assert (got == want).all()
+
+
+# ---- sharded table build (the table counted by N GPUs, exchanged through peer pointers / a hook) --------------
+
+@pytest.mark.parametrize("parts", [2, 4, 3])
+def test_sharded_table_build_equals_replicated(oracle, parts):
+    """N contexts on one GPU emulate an N-GPU box: context i counts slices [8192 i/N, 8192 (i+1)/N) and stores them into
+    every context's table; the records equal the replicated build's and the oracle's, with and without the filter"""
+    db, f1, f2, _ = _case(71 + parts, n_genomes=90, db_bp=2_500_000, q_bp=700_000)
+    coder = eref.random_coder(71)
+    want = oracle.run(f1, f2, db.text, coder, 0.9, 0.85, threads=4)
+    for prune in (True, False):
+        _, rep = eref.run_eref(f1, f2, db.text, coder=coder, devices=(0,) * parts, prune=prune, return_results=True)
+        _, sh = eref.run_eref(f1, f2, db.text, coder=coder, devices=(0,) * parts, prune=prune, shard_table=True,
+                              return_results=True)
+        assert rep.size == sh.size == want.size
+        assert (sh == rep).all() and (sh == want).all()
+    assert (want["el"] > 0).any()
+
+
+def test_sharded_table_levels_sum_to_the_replicated_ones():
+    """every level's population, summed over the parts, equals the replicated build's; every part's table is the same"""
+    db, f1, f2, _ = _case(75, n_genomes=30, db_bp=600_000, q_bp=500_000)
+    coder = eref.random_coder(75)
+    with eref.ErefGPU(coder, level_pop=True) as g:
+        g.query_add(f1); g.query_add(f2)
+        whole = [g.query_popcount(l) for l in (1, 2, 3)]
+    ctxs = [eref.ErefGPU(coder, level_pop=True) for _ in range(4)]
+    try:
+        eref.wire_table_peers(ctxs)
+        for g in ctxs:
+            g.query_add(f1); g.query_add(f2)
+        for g in ctxs:
+            g.ref_set(db.text)                             # queues the build
+        for g in ctxs:
+            g.sync()
+        part_pops = [[g.query_popcount(l) for l in (1, 2, 3)] for g in ctxs]
+        assert [sum(p[l] for p in part_pops) for l in range(3)] == whole
+        assert all(p[0] > 0 for p in part_pops)
+        recs = [g.scan().copy() for g in ctxs]
+        assert all((r == recs[0]).all() for r in recs[1:])
+    finally:
+        for g in ctxs:
+            g.close()
+
+
+def test_sharded_table_pipelined_call_side_by_side(golden):
+    """eref_run_host on two contexts that share the table build, one host thread each (as the executable runs its GPUs)"""
+    name, meta, fa, f1, f2 = golden
+    _, a = eref.run_eref(f1, f2, fa, coder=meta["coder"], devices=(0, 0), return_results=True)
+    for _ in range(2):
+        text, b = eref.run_eref(f1, f2, fa, coder=meta["coder"], devices=(0, 0), shard_table=True, pipelined=True, chunks=2,
+                                return_results=True)
+        assert a.size == b.size and (a == b).all()
+        assert text == meta["stdout"]["0.9,0.85"]
+
+
+def test_sharded_table_completion_hook(golden):
+    """without peer pointers the caller's hook completes the table on the context's stream (here: device copies of the
+    other context's part; in bench.py an in-place NCCL all-gather)"""
+    try:
+        from cuda.bindings import runtime as cudart
+    except ImportError:
+        from cuda import cudart
+    name, meta, fa, f1, f2 = golden
+    ctxs = [eref.ErefGPU(meta["coder"]) for _ in range(2)]
+    try:
+        ptrs = [g.table_export() for g in ctxs]
+        for i, g in enumerate(ctxs):
+            g.table_set_part(i, 2)
+        ranges = [g.table_part_range() for g in ctxs]
+        called = []
+
+        def make_hook(i):
+            def hook(stream):
+                j = 1 - i                                  # fetch part j from context j's table
+                toff, tbytes, soff, sbytes = ranges[j]
+                for k, (off, nb) in ((1, (toff, tbytes)), (2, (soff, sbytes))):
+                    err, = cudart.cudaMemcpyAsync(ptrs[i][k] + off, ptrs[j][k] + off, nb,
+                                                  cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice, stream)
+                    assert err == cudart.cudaError_t.cudaSuccess
+                called.append(i)
+            return hook
+        for i, g in enumerate(ctxs):
+            g.table_set_hook(make_hook(i))
+            g.query_add(f1); g.query_add(f2)
+        for g in ctxs:
+            g.ref_set(fa)
+        for g in ctxs:
+            g.sync()                                       # both local parts are built before either hook copies
+        recs = [g.scan().copy() for g in ctxs]
+        assert sorted(called) == [0, 1]
+        _, want = eref.run_eref(f1, f2, fa, coder=meta["coder"], return_results=True)
+        assert all((r == want).all() for r in recs)
+        assert eref.format_results(recs[0]) == meta["stdout"]["0.9,0.85"]
+    finally:
+        for g in ctxs:
+            g.close()
