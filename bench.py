@@ -1,22 +1,35 @@
 #!/usr/bin/env python
 """bench.py — reference Gbp k-mer-screened per second on B200 (BASELINE.json's metric).
 
-A step = one pass of the whole `eref` hot path over one synthetic sample: zero the 2^32-slot table,
+A step = one pass of the whole `eref` hot path over one synthetic sample: reset the 2^32-slot table,
 frame+pack+count both FASTQ files, frame+pack the FASTA database, scan it (candidate filter, probes,
 500-position window rule, interval merge) down to one {ordinal, frag, el, ref_len} record per
-reference and, at N>1, allgather the records (the path's only collective).
+reference and, at N>1, all-gather the records.
 
   value   inputs already resident in HBM (eref_*_device entry points), CUDA events, max over ranks
-  e2e     the same through the host-buffer C ABI calls (pinned host -> H2D -> ... -> D2H of the records)
+  e2e     the same through the host-buffer C ABI call (pinned host -> H2D -> ... -> D2H of the records)
 
-Workload at N=1: BASELINE.json configs[1] — 50 Mbp reads vs a 10,000-genome ~500 Mbp phage DB.
-At N>1 every rank holds its own 10,000-genome shard (weak scaling); the query is replicated.
-`--impl reference` times the reference's own CPU implementation (oracle/_ref/eref_ref, else the
-oracle port) on a bounded sample of the same generator on the host cores.
+The ONE JSON line carries, besides the contract's keys:
+  headline   BASELINE configs[1] per GPU (weak scaling: every rank its own 10,000-genome ~500 Mbp shard, the
+             50 Mbp query replicated) — `value`, `e2e`, `phases`, `roofline`
+  strong     BASELINE configs[2] (and [3] with --strong c3,c4): ONE 30,000-genome ~1.5 Gbp database sharded over the
+             N GPUs, 50 Mbp (500 Mbp) of reads — the strong-scaling curve north_star's target is written for
+  c5         BASELINE configs[4]: short-read-heavy query (20-150 bp reads) against the headline database
+  scan_unpruned   the scan with the candidate filter off (all 3 probes at every position), the only figure
+             comparable with SURVEY 8(d)'s 97 B per reference base
+  parity     the records of the workloads that were timed, compared with the CPU oracle in this very run
+  cpu_baseline    (N=1) the unmodified reference on the host cores, bounded sample, and the whole-process comparison
+At N>1 the query-table build is sharded over the GPUs (each counts 1/N of the table slices and stores them into
+every peer's table over NVLink, include/eref_gpu.h); the DB is sharded by record; the records are all-gathered.
+
+`--impl reference` times the UNMODIFIED reference (oracle/_ref/eref_ref) on the host cores, on the headline
+workload when the run fits the time budget, else on BASELINE configs[0] — the line says which.
 """
 import argparse
+import hashlib
 import json
 import os
+import shutil
 import subprocess
 import sys
 import tempfile
@@ -31,27 +44,38 @@ sys.path.insert(0, ROOT)
 METRIC = "reference Gbp k-mer-screened/sec"
 UNIT = "Gbp/s"
 WORKLOADS = {
-    # name: (genomes per GPU shard, DB bp per shard, query bp total)
-    "c2": (10000, 500_000_000, 50_000_000),
-    "c1": (1000, 50_000_000, 5_000_000),
-    "small": (400, 20_000_000, 2_000_000),
-    # BASELINE configs[2] and [3] are 8-GPU configurations: a 30,000-genome ~1.5 Gbp database sharded over 8 GPUs
-    "c3": (3750, 187_500_000, 50_000_000),
-    "c4": (3750, 187_500_000, 500_000_000),
+    # name: (genomes per GPU shard, DB bp per shard, query bp total, read length range)
+    "c2": (10000, 500_000_000, 50_000_000, (100, 400)),
+    "c1": (1000, 50_000_000, 5_000_000, (100, 400)),
+    "small": (400, 20_000_000, 2_000_000, (100, 400)),
+    "c5": (10000, 500_000_000, 50_000_000, (20, 150)),
 }
 WORKLOAD_DESC = {
     "c2": "BASELINE configs[1]: 50 Mbp reads vs 10,000-genome ~500 Mbp synthetic phage DB per GPU",
-    "c1": "BASELINE configs[0]: 5 Mbp reads vs 1,000-genome ~50 Mbp synthetic phage DB per GPU",
-    "c3": "BASELINE configs[2] at 8 GPUs: 50 Mbp reads vs 3,750 genomes ~187.5 Mbp of a 30,000-genome ~1.5 Gbp DB per GPU",
-    "c4": "BASELINE configs[3] at 8 GPUs: 500 Mbp reads vs 3,750 genomes ~187.5 Mbp of a 30,000-genome ~1.5 Gbp DB per GPU",
-    "small": "development: 2 Mbp reads vs 400-genome 20 Mbp DB per GPU",
+    "c1": "BASELINE configs[0]: 5 Mbp reads vs 1,000-genome ~50 Mbp synthetic phage DB",
+    "c5": "BASELINE configs[4]: short-read-heavy 50 Mbp query (reads 20-150 bp) vs 10,000-genome ~500 Mbp synthetic phage DB per GPU",
+    "small": "development: 2 Mbp reads vs 400-genome 20 Mbp DB",
+}
+# strong scaling: ONE database of 8 fixed sub-databases (3,750 genomes, ~187.5 Mbp each), whatever N is
+STRONG_SUBS = 8
+STRONG = {
+    "c3": {"sub": (3750, 187_500_000), "query_bp": 50_000_000,
+           "desc": "BASELINE configs[2]: 50 Mbp reads vs ONE 30,000-genome ~1.5 Gbp synthetic phage DB sharded over the GPUs"},
+    "c4": {"sub": (3750, 187_500_000), "query_bp": 500_000_000,
+           "desc": "BASELINE configs[3]: 500 Mbp reads (~1.3 G query codes) vs ONE 30,000-genome ~1.5 Gbp synthetic phage DB "
+                   "sharded over the GPUs"},
 }
 # algorithmic bytes per unit (restated in DESIGN.md §8)
 BYTES_PER_REF_BASE_FULL = 97.0        # 1 B text + 3 probes x 32 B sector
 BYTES_PER_QUERY_BASE_BUILD = 193.0    # 1 B text + 3 codes x (32 B sector fill + 32 B write-back)
-
+PLANE_BYTES_PER_BASE = 0.375          # three one-bit planes
 
 _emit = print
+
+
+def config_for(workload_desc, gpus):
+    """the `config` both arms print for the same workload (the driver compares them)"""
+    return {"workload": workload_desc, "k": 32, "hit_ratio": 0.9, "perfect_hit_ratio": 0.85, "gpus": gpus}
 
 
 def peaks():
@@ -99,12 +123,34 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def gen_inputs(workload, rank, world):
+# ---- synthetic inputs -------------------------------------------------------------------------------
+
+def gen_weak(workload, rank, world, db=None):
+    """every rank its own shard (seed 1000 + rank) and 1/world of the reads (seed 2000 + rank), gathered later"""
     from palace_b200 import synth
-    G, R, Q = WORKLOADS[workload]
-    db = synth.make_db(G, R, 1000 + rank)
-    f1, f2, _ = synth.make_reads(db, Q // world, 2000 + rank)
-    return db.text, f1, f2, int(db.lengths.sum())
+    G, R, Q, (lo, hi) = WORKLOADS[workload]
+    if db is None:
+        db = synth.make_db(G, R, 1000 + rank)
+    f1, f2, _ = synth.make_reads(db, Q // world, (2000 if workload != "c5" else 5000) + rank, min_len=lo, max_len=hi)
+    return db, f1, f2
+
+
+def gen_strong(kind, rank, world, subs=None):
+    """rank r holds sub-databases [8 r/N, 8 (r+1)/N) of the one strong-scaling database and generates the reads drawn
+    from them; returns (shard text, fq1 part, fq2 part, bases of the shard, the sub-databases for reuse)"""
+    from palace_b200 import synth
+    G, R = STRONG[kind]["sub"]
+    Q = STRONG[kind]["query_bp"] // STRONG_SUBS
+    mine = range(STRONG_SUBS * rank // world, STRONG_SUBS * (rank + 1) // world)
+    if subs is None:
+        subs = {k: synth.make_db(G, R, 3000 + k) for k in mine}
+    f1s, f2s = [], []
+    for k in mine:
+        a, b, _ = synth.make_reads(subs[k], Q, (4000 if kind == "c3" else 6000) + k)
+        f1s.append(a); f2s.append(b)
+    text = np.concatenate([subs[k].text for k in mine])
+    bases = int(sum(int(subs[k].lengths.sum()) for k in mine))
+    return text, np.concatenate(f1s), np.concatenate(f2s), bases, subs
 
 
 def gather_bytes(t_local, world, device):
@@ -126,8 +172,9 @@ def gather_bytes(t_local, world, device):
 QUERY_PHASES = ("query_pack_ms", "query_bucket_ms", "query_count_ms")
 PHASES = QUERY_PHASES + ("ref_frame_ms", "ref_pack_ms", "scan_summary_ms", "scan_sample_ms", "scan_cand_ms",
                          "scan_probe_ms", "scan_window_ms", "scan_interval_ms")
-# kernels of each phase (names as ncu prints them) and how often each runs per step
+SCAN_PHASES = tuple(p for p in PHASES if p.startswith("scan_"))
 PHASE_STEPS = 3                                # instrumented steps (phase times), not part of the timed region
+# kernels of each phase (names as ncu prints them) and how often each runs per step
 PHASE_KERNELS = {
     "query_pack_ms": (("k_count_newlines", 2), ("k_fastq_kept", 2), ("k_pack_fastq", 2)),
     "query_bucket_ms": (("k_slice_hist", 2), ("k_slice_offsets", 2), ("k_coarse_scatter_staged", 2), ("k_fine_partition", 2)),
@@ -143,10 +190,18 @@ PHASE_KERNELS = {
 }
 
 
+def ncu_file():
+    for name in ("ncu_kernels_r02.json", "ncu_kernels_r01.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            return p
+    return None
+
+
 def ncu_traffic(phase):
     """DRAM bytes per step of a phase's kernels from the committed `ncu --set full` capture (profiles/), or None"""
-    p = os.path.join(ROOT, "profiles", "ncu_kernels_r01.json")
-    if not os.path.exists(p):
+    p = ncu_file()
+    if not p:
         return None
     try:
         k = json.load(open(p))["kernels"]
@@ -155,324 +210,615 @@ def ncu_traffic(phase):
         return None
 
 
-def run_b200(args):
-    import torch
-    import torch.distributed as dist
-    from palace_b200 import eref
-    from palace_b200.dist import agree_slot, allgather_records
+def records_sha(rec):
+    return hashlib.sha256(np.ascontiguousarray(rec).view(np.uint8).tobytes()).hexdigest()[:16]
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus and world > 1:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the eref path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
 
-    fa_np, f1_np, f2_np, shard_bases = gen_inputs(args.workload, rank, world)
-    stream = torch.cuda.Stream(device=dev)             # the library launches on this stream: its events time the step
-    with torch.cuda.stream(stream):
-        fa_h = torch.from_numpy(fa_np).pin_memory()
-        fa_d = fa_h.to(dev, non_blocking=True)
-        f1_d = torch.from_numpy(f1_np).to(dev)
-        f2_d = torch.from_numpy(f2_np).to(dev)
-        if world > 1:
-            f1_d = gather_bytes(f1_d, world, dev)
-            f2_d = gather_bytes(f2_d, world, dev)
-        f1_h = f1_d.cpu().pin_memory()
-        f2_h = f2_d.cpu().pin_memory()
-    stream.synchronize()
-    query_bases = None
+def prefix_fasta(text, max_records):
+    """the first max_records records of a FASTA text (records are independent and ordinals run in file order, so the
+    oracle's records of a prefix equal the prefix of the records)"""
+    starts = np.flatnonzero(text == 62)
+    starts = starts[(starts == 0) | (text[np.maximum(starts, 1) - 1] == 10)]
+    if starts.size <= max_records:
+        return text
+    return text[: int(starts[max_records])]
 
-    f1_np_h, f2_np_h, fa_np_h = f1_h.numpy(), f2_h.numpy(), fa_h.numpy()
-    host_cap = int(np.count_nonzero(fa_np == 62)) + 16
-    coder = eref.random_coder(1)                       # EREF_CODER_SEED=1 convention for GPU-only runs
-    g = eref.ErefGPU(coder, 0.9, 0.85, device=local, prune=not args.no_prune)
-    g.set_stream(stream.cuda_stream)
-    acc = {p: 0.0 for p in PHASES}
-    info = {}
 
-    def step_device(collect):
-        # no call below waits for its own kernels beyond the sizes the host needs for allocations; the phase times
-        # are read (which does wait) only in the instrumented steps, outside the timed region
-        g.query_reset()
-        g.query_add_device(f1_d.data_ptr(), f1_d.numel(), want_bytes=False)
-        g.query_add_device(f2_d.data_ptr(), f2_d.numel(), want_bytes=False)
-        g.ref_set_device(fa_d.data_ptr(), fa_d.numel())
-        ptr, n = g.scan_device(wait=False)
-        merged = None
-        if world > 1:
-            if "slot" not in info:
-                info["slot"] = agree_slot(n, dev)     # once per sharded database
-            merged = allgather_records(device_records(ptr, n, dev), n, info["slot"])
-        if collect:
-            t = g.timings()                           # query times: sums over both files
-            for p in PHASES:
-                acc[p] += t[p]
-            info.update(ref_bases=t["ref_bases"], ref_words=t["ref_words"], need_words=t["ref_need_words"],
-                        seq_bytes=t["query_seq_bytes"], n_records=n, query_codes=t["query_codes"])
-        return merged
+class Rig:
+    """one rank's view of the run: device, stream, process group, the library contexts"""
 
-    # N > 1: the query is the same on every rank, so each rank uploads 1/N of it and NCCL all-gathers the text
-    # over NVLink; the library takes the gathered (device) text and this rank's database shard (host)
-    share = None
-    if world > 1:
-        share = []
-        for h in (f1_h, f2_h):
-            slot = (h.numel() + world - 1) // world
-            lo, hi = min(rank * slot, h.numel()), min((rank + 1) * slot, h.numel())
-            share.append({"host": h[lo:hi], "mine": torch.zeros(slot, dtype=torch.uint8, device=dev),
-                          "full": torch.empty(world * slot, dtype=torch.uint8, device=dev), "n": h.numel()})
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        from palace_b200 import eref
+        self.torch, self.dist, self.eref = torch, dist, eref
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus and self.world > 1:
+            raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={self.world}")
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the eref path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.stream = torch.cuda.Stream(device=self.dev)   # the library launches on this stream: its events time the step
+        self.coder = eref.random_coder(1)                  # EREF_CODER_SEED=1 convention for GPU-only runs
+        self.g = eref.ErefGPU(self.coder, 0.9, 0.85, device=self.local, prune=not args.no_prune)
+        self.g.set_stream(self.stream.cuda_stream)
+        self.g_full = None                                 # second context, candidate filter off (scan_unpruned)
+        self.table_mode = "one GPU: whole table built locally"
+        if self.world > 1:
+            self.table_mode = self.wire_table()
 
-    def gathered_query():
-        out = []
-        for s_ in share:
-            s_["mine"][: s_["host"].numel()].copy_(s_["host"], non_blocking=True)
-            dist.all_gather_into_tensor(s_["full"], s_["mine"])
-            out.append(eref.DeviceBytes(s_["full"].data_ptr(), s_["n"]))
-        return out
+    # ---- sharded table build across the ranks ----
+    def view(self, ptr, nbytes):
+        class _A:
+            pass
+        a = _A()
+        a.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        return self.torch.as_tensor(a, device=self.dev)
 
-    def step_host():
-        # the public host-buffer call: pinned host -> (overlapped H2D) -> kernels -> D2H of the records
-        if world > 1:
-            q1, q2 = gathered_query()
-            rec = g.run_host(q1, q2, fa_np_h, chunks=args.chunks, cap=host_cap)
-        else:
-            rec = g.run_host(f1_np_h, f2_np_h, fa_np_h, chunks=args.chunks, cap=host_cap)
-        if world > 1:
-            t = torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(dev)
-            merged = allgather_records(t, rec.size, info.get("slot"))
-            return merged.cpu() if rank == 0 else None
-        return rec
+    def all_ok(self, ok):
+        t = self.torch.tensor([1 if ok else 0], dtype=self.torch.int32, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN)
+        return bool(t.item())
 
-    def device_records(ptr, n, dev):
-        # zero-copy view of the library's result buffer (n x 4 uint32) as a torch tensor
+    def wire_table(self):
+        g, world, rank = self.g, self.world, self.rank
+        if self.args.table == "replicated":
+            return "replicated: every GPU counts the whole table"
+        if self.args.table in ("auto", "peer"):
+            ok = True
+            try:
+                blob = g.table_export(ipc=True)[0]
+            except self.eref.ErefError as e:
+                print(f"rank {rank}: no IPC export: {e}", file=sys.stderr)
+                ok, blob = False, b""
+            blobs = [None] * world
+            self.dist.all_gather_object(blobs, blob)
+            g.table_set_part(rank, world)
+            if ok:
+                try:
+                    for p in range(world):
+                        if p != rank:
+                            g.table_set_peer(p, (blobs[p], 0, 0, 0))
+                except self.eref.ErefError as e:
+                    print(f"rank {rank}: cannot open a peer's table: {e}", file=sys.stderr)
+                    ok = False
+            if self.all_ok(ok):
+                return (f"sharded x{world}: each GPU counts 1/{world} of the table slices and stores them into every "
+                        f"GPU's table through CUDA-IPC peer pointers (NVLink), device-side flags")
+            if self.args.table == "peer":
+                raise SystemExit("--table peer: peer pointers unavailable")
+        # hook: in-place NCCL all-gather of the level-3 part and its summary on the library's stream
+        if world & (world - 1):
+            g.table_set_part(0, 1)
+            return "replicated: every GPU counts the whole table (the all-gather fallback needs a power-of-two N)"
+        g.table_set_part(rank, world)                      # (also drops half-wired peers)
+        _, bm3, summ, _ = g.table_export()
+        toff, tbytes, soff, sbytes = g.table_part_range()
+        full_t, full_s = self.view(bm3, tbytes * world), self.view(summ, sbytes * world)
+        part_t, part_s = full_t[toff: toff + tbytes], full_s[soff: soff + sbytes]
+
+        def hook(_stream):
+            self.dist.all_gather_into_tensor(full_t, part_t)
+            self.dist.all_gather_into_tensor(full_s, part_s)
+        g.table_set_hook(hook)
+        return (f"sharded x{world}: each GPU counts 1/{world} of the table slices, two in-place NCCL all-gathers "
+                f"({tbytes >> 20} + {sbytes >> 20} MiB per GPU) complete the tables")
+
+    def full_ctx(self):
+        if self.g_full is None:
+            self.g_full = self.eref.ErefGPU(self.coder, 0.9, 0.85, device=self.local, prune=False)
+            self.g_full.set_stream(self.stream.cuda_stream)
+        return self.g_full
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, x, op):
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op={"max": self.dist.ReduceOp.MAX, "sum": self.dist.ReduceOp.SUM,
+                                    "min": self.dist.ReduceOp.MIN}[op])
+        return float(t.item())
+
+    def device_records(self, ptr, n):
+        """zero-copy view of the library's result buffer (n x 4 uint32) as a torch tensor"""
         if n == 0:
-            return torch.zeros((0, 4), dtype=torch.int32, device=dev)
-        class _Arr:                                    # __cuda_array_interface__ v2
+            return self.torch.zeros((0, 4), dtype=self.torch.int32, device=self.dev)
+
+        class _Arr:                                        # __cuda_array_interface__ v2
             pass
         a = _Arr()
         a.__cuda_array_interface__ = {"shape": (n, 4), "typestr": "<i4", "data": (ptr, False), "version": 2}
-        return torch.as_tensor(a, device=dev)
+        return self.torch.as_tensor(a, device=self.dev)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def close(self):
+        if self.g_full is not None:
+            self.g_full.close()
+        self.g.close()
+        if self.world > 1:
+            self.dist.destroy_process_group()
 
-    def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
 
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+class Job:
+    """one workload on one rank: its texts in HBM and in pinned host memory, and the measurements on it"""
 
-    with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
-            step_device(False)
-        for _ in range(PHASE_STEPS):                   # instrumented steps: per-phase times, outside the timed region
-            step_device(True)
-        barrier()
-        launches0 = g.timings()["kernel_launches"]
-        sampler = ClockSampler(local) if rank == 0 else None
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(args.steps):
-            merged = step_device(False)
-        e1.record(stream)
-        barrier()
-        dev_ms = e0.elapsed_time(e1)
-        launches = g.timings()["kernel_launches"] - launches0
-        clocks = sampler.stop() if sampler else None
-        # ---- the same sample against a database whose planes stay in HBM (eref_ref_set once, many samples) ----
+    def __init__(self, rig, fa_np, f1_np, f2_np, shard_bases, label):
+        torch = rig.torch
+        self.rig, self.label, self.shard_bases = rig, label, shard_bases
+        self.info = {}
+        with torch.cuda.stream(rig.stream):
+            self.fa_h = torch.from_numpy(fa_np).pin_memory()
+            self.fa_d = self.fa_h.to(rig.dev, non_blocking=True)
+            f1_d = torch.from_numpy(f1_np).to(rig.dev)
+            f2_d = torch.from_numpy(f2_np).to(rig.dev)
+            if rig.world > 1:                              # the query is the same on every rank
+                f1_d = gather_bytes(f1_d, rig.world, rig.dev)
+                f2_d = gather_bytes(f2_d, rig.world, rig.dev)
+            self.f1_d, self.f2_d = f1_d, f2_d
+            self.f1_h = f1_d.cpu().pin_memory()
+            self.f2_h = f2_d.cpu().pin_memory()
+        rig.stream.synchronize()
+        self.host_cap = int(np.count_nonzero(fa_np == 62)) + 16
+        # N > 1, e2e: the query is the same on every rank, so each rank uploads 1/N of it and NCCL all-gathers the
+        # text over NVLink; the library takes the gathered (device) text and this rank's database shard (host)
+        self.share = None
+        if rig.world > 1:
+            self.share = []
+            for h in (self.f1_h, self.f2_h):
+                slot = (h.numel() + rig.world - 1) // rig.world
+                lo, hi = min(rig.rank * slot, h.numel()), min((rig.rank + 1) * slot, h.numel())
+                self.share.append({"host": h[lo:hi], "mine": torch.zeros(slot, dtype=torch.uint8, device=rig.dev),
+                                   "full": torch.empty(rig.world * slot, dtype=torch.uint8, device=rig.dev), "n": h.numel()})
+
+    # ---- steps ----
+    def step_device(self, g=None, collect=None):
+        # no call below waits for its own kernels beyond the sizes the host needs for allocations; the phase times
+        # are read (which does wait) only in the instrumented steps, outside the timed region
+        from palace_b200.dist import agree_slot, allgather_records
+        rig = self.rig
+        g = g or rig.g
+        g.query_reset()
+        g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
+        g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
+        g.ref_set_device(self.fa_d.data_ptr(), self.fa_d.numel())
+        ptr, n = g.scan_device(wait=False)
+        merged = None
+        if rig.world > 1:
+            if "slot" not in self.info:
+                self.info["slot"] = agree_slot(n, rig.dev)     # once per sharded database
+            merged = allgather_records(rig.device_records(ptr, n), n, self.info["slot"])
+        if collect is not None:
+            t = g.timings()                                # query times: sums over both files
+            for p in PHASES:
+                collect[p] = collect.get(p, 0.0) + t[p]
+            self.info.update(ref_bases=t["ref_bases"], ref_words=t["ref_words"], need_words=t["ref_need_words"],
+                             seq_bytes=t["query_seq_bytes"], n_records=n, query_codes=t["query_codes"])
+        return merged
+
+    def gathered_query(self):
+        out = []
+        for s_ in self.share:
+            s_["mine"][: s_["host"].numel()].copy_(s_["host"], non_blocking=True)
+            self.rig.dist.all_gather_into_tensor(s_["full"], s_["mine"])
+            out.append(self.rig.eref.DeviceBytes(s_["full"].data_ptr(), s_["n"]))
+        return out
+
+    def step_host(self):
+        """the public host-buffer call: pinned host -> (overlapped H2D) -> kernels -> D2H of the records"""
+        from palace_b200.dist import allgather_records
+        rig = self.rig
+        if rig.world > 1:
+            q1, q2 = self.gathered_query()
+            rec = rig.g.run_host(q1, q2, self.fa_h.numpy(), chunks=rig.args.chunks, cap=self.host_cap)
+            t = rig.torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(rig.dev)
+            merged = allgather_records(t, rec.size, self.info.get("slot"))
+            self.last_host_records = rec
+            return merged.cpu() if rig.rank == 0 else None
+        rec = rig.g.run_host(self.f1_h.numpy(), self.f2_h.numpy(), self.fa_h.numpy(), chunks=rig.args.chunks, cap=self.host_cap)
+        self.last_host_records = rec
+        return rec
+
+    # ---- measurements ----
+    def time_device(self, steps, warmup):
+        rig, torch = self.rig, self.rig.torch
+        acc = {}
+        with torch.cuda.stream(rig.stream):
+            for _ in range(warmup):
+                self.step_device()
+            for _ in range(PHASE_STEPS):                   # instrumented steps: per-phase times, outside the timed region
+                self.step_device(collect=acc)
+            rig.barrier()
+            launches0 = rig.g.timings()["kernel_launches"]
+            sampler = ClockSampler(rig.local) if rig.rank == 0 else None
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(rig.stream)
+            for _ in range(steps):
+                self.step_device()
+            e1.record(rig.stream)
+            rig.barrier()
+            dev_ms = e0.elapsed_time(e1)
+            launches = rig.g.timings()["kernel_launches"] - launches0
+            clocks = sampler.stop() if sampler else None
+        self.avg = {p: acc[p] / PHASE_STEPS for p in PHASES}
+        ms = rig.reduce(dev_ms, "max") / steps
+        self.total_bases = rig.reduce(float(self.info["ref_bases"]), "sum")
+        return {"ms_per_step": ms, "value": self.total_bases / 1e9 / (ms / 1e3),
+                "launches": int(rig.reduce(float(launches), "sum")), "clocks": clocks}
+
+    def time_host(self, steps, warmup):
+        rig, torch = self.rig, self.rig.torch
+        with torch.cuda.stream(rig.stream):
+            for _ in range(min(warmup, 2)):
+                self.step_host()
+            rig.barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                self.step_host()
+            rig.barrier()
+            e2e_s = time.perf_counter() - t0
+            # what the bus alone takes: the same pinned buffers copied to the device, nothing else running
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            srcs = (self.f1_h, self.f2_h, self.fa_h) if rig.world == 1 else (self.share[0]["host"], self.share[1]["host"], self.fa_h)
+            h2d_bytes = sum(int(x.numel()) for x in srcs)
+            scratch = [torch.empty(x.numel(), dtype=torch.uint8, device=rig.dev) for x in srcs]
+            for _ in range(2):
+                c0.record(rig.stream)
+                for dst, src in zip(scratch, srcs):
+                    dst.copy_(src, non_blocking=True)
+                c1.record(rig.stream)
+                rig.stream.synchronize()
+            h2d_ms = c0.elapsed_time(c1)
+            del scratch
+        e2e_s = rig.reduce(e2e_s, "max")
+        return {"value": round(self.total_bases / 1e9 / (e2e_s / steps), 3), "unit": UNIT,
+                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(self.info["n_records"]) * 16 + 24,
+                "ms_per_step": round(e2e_s / steps * 1e3, 3),
+                "api": f"eref_run_host(chunks={rig.args.chunks}): pinned host buffers, H2D overlapped with kernels" +
+                       ("" if rig.world == 1 else "; each rank uploads 1/N of the query text, NCCL all-gathers it over NVLink"),
+                "h2d_alone_ms": round(h2d_ms, 3), "h2d_alone_GBps": round(h2d_bytes / 1e6 / h2d_ms, 1)}
+
+    def time_resident(self, steps):
+        """NOT headline numbers: the same sample against a database whose planes stay in HBM (eref_ref_set once)"""
+        from palace_b200.dist import allgather_records
+        rig, torch = self.rig, self.rig.torch
+        g = rig.g
+
         def step_resident():
             g.query_reset()
-            g.query_add_device(f1_d.data_ptr(), f1_d.numel(), want_bytes=False)
-            g.query_add_device(f2_d.data_ptr(), f2_d.numel(), want_bytes=False)
+            g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
+            g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
             ptr, n = g.scan_device(wait=False)
-            if world > 1:
-                allgather_records(device_records(ptr, n, dev), n, info["slot"])
-        step_resident()
-        barrier()
-        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        r0.record(stream)
-        for _ in range(args.steps):
-            step_resident()
-        r1.record(stream)
-        barrier()
-        res_ms = r0.elapsed_time(r1)
-        # ---- e2e: host buffers through the C ABI ----
-        for _ in range(min(args.warmup, 2)):
-            step_host()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            res = step_host()
-        barrier()
-        e2e_s = time.perf_counter() - t0
+            if rig.world > 1:
+                allgather_records(rig.device_records(ptr, n), n, self.info["slot"])
 
-        # ---- what the bus alone takes: the same three pinned buffers copied to the device, nothing else running ----
-        barrier()
-        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        h2d_srcs = (f1_h, f2_h, fa_h) if world == 1 else (share[0]["host"], share[1]["host"], fa_h)
-        h2d_bytes = sum(int(x.numel()) for x in h2d_srcs)
-        scratch = [torch.empty(x.numel(), dtype=torch.uint8, device=dev) for x in h2d_srcs]
-        for _ in range(2):
-            c0.record(stream)
-            for dst, src in zip(scratch, h2d_srcs):
-                dst.copy_(src, non_blocking=True)
-            c1.record(stream)
-            stream.synchronize()
-        h2d_floor_ms = c0.elapsed_time(c1)
-        del scratch
-        # ---- host-buffer sample against the resident database: what a PALACE batch does per sample ----
         def step_host_resident():
-            if world > 1:
-                q1, q2 = gathered_query()
-                rec = g.run_host(q1, q2, None, cap=host_cap)
+            if rig.world > 1:
+                q1, q2 = self.gathered_query()
+                rec = g.run_host(q1, q2, None, cap=self.host_cap)
+                t = torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(rig.dev)
+                allgather_records(t, rec.size, self.info.get("slot"))
             else:
-                rec = g.run_host(f1_np_h, f2_np_h, None, cap=host_cap)  # FASTQ uploads pipelined with the table build
-            if world > 1:
-                t = torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(dev)
-                allgather_records(t, rec.size, info.get("slot"))
-        g.ref_set_device(fa_d.data_ptr(), fa_d.numel())
-        step_host_resident()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
+                g.run_host(self.f1_h.numpy(), self.f2_h.numpy(), None, cap=self.host_cap)
+        with torch.cuda.stream(rig.stream):
+            g.ref_set_device(self.fa_d.data_ptr(), self.fa_d.numel())
+            step_resident()
+            rig.barrier()
+            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            r0.record(rig.stream)
+            for _ in range(steps):
+                step_resident()
+            r1.record(rig.stream)
+            rig.barrier()
+            res_ms = rig.reduce(r0.elapsed_time(r1), "max") / steps
             step_host_resident()
-        barrier()
-        e2e_res_s = time.perf_counter() - t0
+            rig.barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                step_host_resident()
+            rig.barrier()
+            e2e_res_s = rig.reduce(time.perf_counter() - t0, "max") / steps
+        return ({"ms_per_step": round(res_ms, 4), "value": round(self.total_bases / 1e9 / (res_ms / 1e3), 2), "unit": UNIT,
+                 "note": "not the headline: the same step when the database's bit-planes stay in HBM across samples "
+                         "(eref_ref_set once), i.e. table build + scan + all-gather"},
+                {"ms_per_step": round(e2e_res_s * 1e3, 3), "value": round(self.total_bases / 1e9 / e2e_res_s, 2), "unit": UNIT,
+                 "h2d_bytes_per_step": int(self.f1_h.numel() + self.f2_h.numel()),
+                 "note": "not the headline: eref_run_host(fq1, fq2, NULL) from pinned host buffers against a database set "
+                         "once (one phage DB, many samples)"})
 
-    dev_ms = max_over_ranks(dev_ms)
-    e2e_res_s = max_over_ranks(e2e_res_s)
-    res_ms = max_over_ranks(res_ms)
-    e2e_s = max_over_ranks(e2e_s)
-    total_bases = sum_over_ranks(float(info["ref_bases"]))
-    launches = int(sum_over_ranks(float(launches)))
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    ms_per_step = dev_ms / args.steps
-    value = total_bases / 1e9 / (ms_per_step / 1e3)
-    e2e_value = total_bases / 1e9 / (e2e_s / args.steps)
-    peak, peak_src = peaks()
-    avg = {p: acc[p] / PHASE_STEPS for p in PHASES}
-    qbases = info["seq_bytes"]
-    ntext_q = f1_d.numel() + f2_d.numel()
-    codes = info["query_codes"]
-    stride = int(os.environ.get("EREF_SAMPLE_STRIDE", "6"))
-    probed_bases = info["ref_bases"] if args.no_prune else 32 * info["need_words"]
-    design = {
-        # bytes each phase's kernels must move GIVEN THIS DESIGN, per step
-        "query_pack_ms": 3.0 * ntext_q + 0.375 * qbases,                       # census, kept, pack read the text; planes written
-        "query_bucket_ms": 2 * 0.375 * qbases + 12.0 * codes,                  # planes read twice; codes written, read, written
-        "query_count_ms": 4.0 * codes + 4.0 * (1 << 27) + 4.0 * (1 << 23),     # codes read; level 3 + summary written
-        "ref_frame_ms": 1.0 * fa_d.numel(),
-        "ref_pack_ms": 1.0 * fa_d.numel() + 2 * (0.375 + 0.125) * info["ref_bases"],   # planes zeroed, then written
-        "scan_sample_ms": (0.375 + 32.0 / stride + 1.0 / 32) * info["ref_bases"],
-        "scan_cand_ms": (1 + 4.0 / 8 + 1 + 12) / 32.0 * info["ref_bases"],     # hits, record ids, need, zeroed single/trio/good
-        "scan_probe_ms": (96.0 + 0.625) * probed_bases,
-        "scan_window_ms": (0.25 + 0.125) * probed_bases,
-        "scan_interval_ms": 0.125 * info["ref_bases"],
+    def scan_unpruned(self, steps=3):
+        """The scan with the candidate filter OFF (EREF_FLAG_NO_PRUNE): all three probes at every reference position, timed
+        by the library's CUDA events in this run — the figure comparable with SURVEY 8(d)'s 97 B per reference base
+        (1 B of text + 3 probes x one 32 B DRAM sector).  The table is built locally by this second context."""
+        rig, torch = self.rig, self.rig.torch
+        if rig.args.no_prune:
+            g, own = rig.g, False
+        else:
+            g, own = rig.full_ctx(), True
+        peak, _ = peaks()
+        ms = []
+        with torch.cuda.stream(rig.stream):
+            g.query_reset()
+            g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
+            g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
+            g.ref_set_device(self.fa_d.data_ptr(), self.fa_d.numel())
+            for i in range(steps + 1):
+                ptr, n = g.scan_device(wait=True)
+                t = g.timings()
+                if i:
+                    ms.append(sum(t[p] for p in SCAN_PHASES))
+            rec_full = g.scan().copy() if own else None
+        t_ms = rig.reduce(float(np.mean(ms)), "max")
+        R = rig.reduce(float(t["ref_bases"]), "sum")
+        out = {"ms": round(t_ms, 4), "steps": steps, "value": round(R / 1e9 / (t_ms / 1e3), 2), "unit": UNIT,
+               "bytes_per_ref_base": BYTES_PER_REF_BASE_FULL,
+               "frac": round(BYTES_PER_REF_BASE_FULL * R / 1e9 / (t_ms / 1e3) / (peak * rig.world), 4),
+               "probes_per_s_G": round(3.0 * R / (t_ms / 1e3) / 1e9, 1),
+               "phases_ms": {p: round(t[p], 4) for p in SCAN_PHASES if t[p] > 0},
+               "note": "frac = 97 B x reference bases / scan time / (N x measured HBM peak); above 1 would mean the "
+                       "L2-sized table parts answer probes that the 97 B model charges to DRAM"}
+        return out, rec_full
+
+    def parity(self, rec_gpu, max_records=None):
+        """The records of the timed workload against the CPU oracle on the same texts (test infrastructure, outside every
+        timed region).  max_records: compare a prefix of the shard's records (see prefix_fasta).  At N > 1 rank 0 checks
+        its own shard with all host cores (every rank would have to count the whole query again)."""
+        from tests import oracle_util
+        rig = self.rig
+        if rig.rank != 0:
+            return None
+        orc = oracle_util.load()
+        fa = self.fa_h.numpy()
+        if max_records is not None:
+            fa = prefix_fasta(fa, max_records)
+        threads = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        want = orc.run(self.f1_h.numpy(), self.f2_h.numpy(), fa, rig.coder, 0.9, 0.85, threads=threads)
+        dt = time.perf_counter() - t0
+        got = np.ascontiguousarray(rec_gpu[: want.size])
+        same = bool(got.size == want.size and (got == want).all())
+        sel = int(np.count_nonzero((want["el"] > 0) & (want["el"].astype(np.float32) / want["ref_len"].astype(np.float32) > 0.75)))
+        out = {"checked": True, "records": int(want.size), "selected": sel, "identical": same,
+               "of_records_on_rank0": int(len(rec_gpu)),
+               "against": f"oracle port (oracle/liberef_oracle.so, {threads} threads), {dt:.0f} s"
+                          + ("" if rig.world == 1 else "; rank 0's shard"),
+               "sha256_16": records_sha(got)}
+        if not same:
+            bad = np.flatnonzero(~(got == want[: got.size])) if got.size == want.size else []
+            out["first_mismatch"] = [int(x) for x in bad[:4]]
+        return out
+
+
+def phases_report(job, fa_bytes, ntext_q, stride, no_prune):
+    """per-phase times with (i) SURVEY 8(d)'s algorithmic bytes where it gives a figure, (ii) the bytes this design must
+    move, (iii) ncu's DRAM bytes from the committed capture"""
+    peak, _ = peaks()
+    info, avg = job.info, job.avg
+    qbases, codes, R = info["seq_bytes"], info["query_codes"], info["ref_bases"]
+    probed = R if no_prune else 32 * info["need_words"]
+    bytes_8d = {
+        "query_pack_ms": ntext_q + PLANE_BYTES_PER_BASE * qbases,            # K1: text once, planes once
+        "ref_pack_ms": fa_bytes + PLANE_BYTES_PER_BASE * R,                  # K1: text once, planes once
+        "ref_frame_ms": None,                                                # framing is part of K1's single text read
+        "scan_probe_ms": BYTES_PER_REF_BASE_FULL * probed,                   # 1 B + 3 x 32 B per probed base
     }
-    phases = {p: {"ms": round(avg[p], 4), "design_bytes": int(design.get(p, 0)),
-                  "frac_of_hbm": round(design.get(p, 0) / 1e9 / (avg[p] / 1e3) / peak, 3) if avg[p] > 0 else None,
-                  "kernels": [n for n, t in PHASE_KERNELS[p] if t], "ncu_dram_bytes": ncu_traffic(p)}
-              for p in PHASES}
-    # the dominant KERNEL: the largest of the phases that consist of one kernel (the probe: one kernel, 8 launches).
-    # Algorithmic bytes: the probe uses SURVEY 8(d)'s 97 B per reference base (1 B of text + 3 probes x one 32 B DRAM
-    # sector) x the bases it probes; for the other kernels SURVEY gives no per-kernel figure, so the bytes the kernel
-    # must move in this design (the `phases` entry below) are used and the note says so.
-    single_kernel = {"scan_probe_ms": "k_probe_full" if args.no_prune else "k_probe_part (8 launches: the table in 8 parts)",
-                     "scan_sample_ms": "k_probe_sampled", "ref_pack_ms": "k_pack_fasta (+ memsets of the planes)",
-                     "query_count_ms": "k_count_slices_persistent"}
-    dom = max(single_kernel, key=lambda p_: avg[p_])
-    dom_kernel = single_kernel[dom]
+    design = {
+        "query_pack_ms": 3.0 * ntext_q + PLANE_BYTES_PER_BASE * qbases,      # census, kept, pack read the text; planes written
+        "query_bucket_ms": 2 * PLANE_BYTES_PER_BASE * qbases + 12.0 * codes, # planes read twice; codes written, read, written
+        "query_count_ms": 4.0 * codes + 4.0 * (1 << 27) + 4.0 * (1 << 23),   # codes read; level 3 + summary written
+        "ref_frame_ms": 1.0 * fa_bytes,
+        "ref_pack_ms": 1.0 * fa_bytes + 2 * (PLANE_BYTES_PER_BASE + 0.125) * R,   # planes + record ids zeroed, then written
+        "scan_sample_ms": (PLANE_BYTES_PER_BASE + 1.0 / 32) * R,             # planes read, hit bytes written; probes: L2 + ncu
+        "scan_cand_ms": (1 + 4.0 / 8 + 1 + 12) / 32.0 * R,                   # hits, record ids, need, zeroed single/trio/good
+        "scan_probe_ms": (96.0 + 0.625) * probed,
+        "scan_window_ms": (0.25 + 0.125) * probed,
+        "scan_interval_ms": 0.125 * R,
+    }
+    out = {}
+    for p in PHASES:
+        e = {"ms": round(avg[p], 4), "kernels": [n for n, t in PHASE_KERNELS[p] if t],
+             "design_bytes": int(design.get(p, 0)), "ncu_dram_bytes": ncu_traffic(p)}
+        if avg[p] > 0:
+            if bytes_8d.get(p):
+                e["survey_8d_bytes"] = int(bytes_8d[p])
+                e["frac_of_hbm"] = round(bytes_8d[p] / 1e9 / (avg[p] / 1e3) / peak, 3)
+            e["design_frac_of_hbm"] = round(design.get(p, 0) / 1e9 / (avg[p] / 1e3) / peak, 3)
+        out[p] = e
+    return out, bytes_8d, design, probed
+
+
+def roofline_record(job, phases, bytes_8d, design, probed, no_prune):
+    """the dominant KERNEL = the longest of the phases that consist of one kernel; achieved = SURVEY 8(d) algorithmic
+    bytes / its CUDA-event time where 8(d) gives a figure (pack: text once + planes once; probe: 97 B per probed base),
+    else the bytes the kernel must move (count: codes read + table written; sampled probe: ncu's DRAM bytes)"""
+    peak, peak_src = peaks()
+    avg, info = job.avg, job.info
+    single = {"scan_probe_ms": "k_probe_full" if no_prune else "k_probe_part (8 launches: the table in 8 parts)",
+              "scan_sample_ms": "k_probe_sampled", "ref_pack_ms": "k_pack_fasta", "query_count_ms": "k_count_slices_persistent"}
+    dom = max(single, key=lambda p_: avg[p_])
+    R, codes = info["ref_bases"], info["query_codes"]
     if dom == "scan_probe_ms":
-        alg, per_unit, units, unit_name = BYTES_PER_REF_BASE_FULL * probed_bases, BYTES_PER_REF_BASE_FULL, probed_bases, \
+        alg, src, units, unit_name = bytes_8d[dom], "SURVEY 8(d): 97 B per reference base probed", probed, \
             "reference bases probed by the launches (all three streams)"
-        roof_note = ("random 4-byte probes: a 512 MiB bitmap answers 57-58 G/s on this B200 and DRAM moves ~100 B per "
-                     "probe (tools/probe_bench.cu); walking the table in 8 L2-sized parts turns most probes into L2 "
-                     "hits, so ncu's DRAM traffic is below the algorithmic bytes and the rounds are instruction-bound "
-                     "(sm 60-68 %)")
+        note = ("random 4-byte probes; walking the table in L2-sized parts turns most into L2 hits, so ncu's DRAM traffic "
+                "is below the algorithmic bytes and the rounds are instruction-bound")
+    elif dom == "ref_pack_ms":
+        alg, src, units, unit_name = bytes_8d[dom], "SURVEY 8(d) K1: text read once + planes written once", R, "reference bases"
+        note = "instruction-bound text kernel (integer SIMD-in-register masks); design_frac also counts the plane memsets"
+    elif dom == "query_count_ms":
+        alg, src, units, unit_name = design[dom], "codes read once (4 B) + level-3 table and summary written once", codes, \
+            "query codes (3 per valid 32-mer)"
+        note = "bound by shared-memory atomics, one CTA per SM"
     else:
-        units = {"scan_sample_ms": info["ref_bases"], "ref_pack_ms": info["ref_bases"], "query_count_ms": codes}[dom]
-        unit_name = {"scan_sample_ms": "reference bases", "ref_pack_ms": "reference bases",
-                     "query_count_ms": "query codes (3 per valid 32-mer)"}[dom]
-        alg = design[dom]
-        per_unit = round(alg / max(units, 1), 3)
-        roof_note = ("SURVEY 8(d) gives no per-kernel figure here: bytes this kernel must move in this design "
-                     "(DESIGN.md section 3); " +
-                     {"scan_sample_ms": "bound by one scattered L2 sector per clock and SM (l1tex 82 %)",
-                      "ref_pack_ms": "instruction-bound (sm 83 %): ~30 integer operations per 4 text bytes",
-                      "query_count_ms": "bound by shared-memory atomics (l1tex 58 %), one CTA per SM"}[dom])
+        t = ncu_traffic(dom)
+        alg = t if t else design[dom]
+        src = "bytes actually moved (ncu DRAM bytes of the committed capture)" if t else "design bytes (planes + hit bytes)"
+        units, unit_name = R, "reference bases"
+        note = "bound by one scattered L2 sector per clock and SM (most sampled probes are answered by the 32 MiB summary in L2)"
     achieved = alg / 1e9 / (avg[dom] / 1e3) if avg[dom] > 0 else 0.0
-    largest = max(avg, key=avg.get)
-    scan_ms = sum(avg[p] for p in PHASES if p.startswith("scan_"))
+    traffic = ncu_traffic(dom)
+    return {"bound": "hbm", "kernel": single[dom], "phase": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": traffic,
+            "traffic_source": (os.path.relpath(ncu_file(), ROOT) + " (committed ncu --set full capture of this command, "
+                               "not measured in this run)") if traffic else None,
+            "peak_source": peak_src, "bytes_source": src,
+            "algorithmic_bytes_per_unit": round(alg / max(units, 1), 3), "units_per_launch": int(units), "unit_name": unit_name,
+            "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4),
+            "design_frac": round(design[dom] / 1e9 / (avg[dom] / 1e3) / peak, 4) if avg[dom] > 0 else None,
+            "probes_per_s_G": round(3.0 * probed / (avg["scan_probe_ms"] / 1e3) / 1e9, 1) if avg["scan_probe_ms"] > 0 else None,
+            "note": note, "largest_phase": max(avg, key=avg.get)}
+
+
+def sub_record(rig, job, steps, warmup, parity_records, with_e2e=True, with_unpruned=True):
+    """device-resident time, e2e, unpruned scan and parity of one extra workload (strong / c5)"""
+    t = job.time_device(steps, warmup)
+    out = {"ms_per_step": round(t["ms_per_step"], 4), "value": round(t["value"], 3), "unit": UNIT,
+           "db_bases_total": int(job.total_bases), "db_bases_this_gpu": int(job.info["ref_bases"]),
+           "query_seq_bases": int(job.info["seq_bytes"]), "query_codes": int(job.info["query_codes"]),
+           "phases_ms": {k: round(v, 4) for k, v in job.avg.items()},
+           "need_word_fraction": round(job.info["need_words"] / max(job.info["ref_words"], 1), 4),
+           "gpu_launches": t["launches"]}
+    scan_ms = sum(job.avg[p] for p in SCAN_PHASES)
+    out["scan_only"] = {"ms": round(scan_ms, 4), "value": round(job.info["ref_bases"] * rig.world / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT}
+    if with_e2e:
+        e = job.time_host(max(3, steps // 2), 2)
+        out["e2e"] = {k: e[k] for k in ("value", "unit", "ms_per_step", "h2d_bytes_per_step", "d2h_bytes_per_step")}
+    if with_unpruned:
+        out["scan_unpruned"], _ = job.scan_unpruned()
+    if not rig.args.no_parity:
+        with rig.torch.cuda.stream(rig.stream):
+            job.step_host()                                # (a collective at N > 1: every rank takes part)
+        out["parity"] = job.parity(job.last_host_records.copy(), parity_records)
+    return out
+
+
+def run_b200(args):
+    rig = Rig(args)
+    rank, world = rig.rank, rig.world
+    peak, _ = peaks()
+    strong_kinds = [k for k in args.strong.split(",") if k and k != "none"]
+    for k in strong_kinds:
+        if k not in STRONG:
+            raise SystemExit(f"--strong {k}: not one of {sorted(STRONG)}")
+    if world not in (1, 2, 4, 8):
+        strong_kinds = []
+
+    # ---- headline: weak-scaled BASELINE configs[1] (or --workload) ----
+    db, f1, f2 = gen_weak(args.workload, rank, world)
+    job = Job(rig, db.text, f1, f2, int(db.lengths.sum()), args.workload)
+    head = job.time_device(args.steps, args.warmup)
+    db_res, e2e_res = job.time_resident(args.steps)
+    e2e = job.time_host(args.steps, args.warmup)
+    unpruned, rec_full = None, None
+    if not args.no_unpruned:
+        unpruned, rec_full = job.scan_unpruned()
+    par = None
+    if not args.no_parity:
+        with rig.torch.cuda.stream(rig.stream):
+            job.step_host()
+            rec_host = job.last_host_records.copy()
+            # and the device-resident path that `value` times
+            g = rig.g
+            g.query_reset()
+            g.query_add_device(job.f1_d.data_ptr(), job.f1_d.numel(), want_bytes=False)
+            g.query_add_device(job.f2_d.data_ptr(), job.f2_d.numel(), want_bytes=False)
+            g.ref_set_device(job.fa_d.data_ptr(), job.fa_d.numel())
+            rec_dev = g.scan().copy()
+        par = job.parity(rec_host)
+        same_paths = rig.reduce(1.0 if (rec_dev.size == rec_host.size and (rec_dev == rec_host).all()) else 0.0, "min") > 0.5
+        same_full = rig.reduce(1.0 if (rec_full is None or (rec_full.size == rec_host.size and (rec_full == rec_host).all()))
+                               else 0.0, "min") > 0.5
+        if par is not None:
+            par["device_path_equals_host_path"] = bool(same_paths)
+            if rec_full is not None:
+                par["unpruned_equals_pruned"] = bool(same_full)
+    stride = int(os.environ.get("EREF_SAMPLE_STRIDE", "6"))
+    phases, b8d, design, probed = phases_report(job, job.fa_d.numel(), job.f1_d.numel() + job.f2_d.numel(), stride, args.no_prune)
+    roof = roofline_record(job, phases, b8d, design, probed, args.no_prune)
+    info, avg = dict(job.info), dict(job.avg)
+    qbases = info["seq_bytes"]
+    scan_ms = sum(avg[p] for p in SCAN_PHASES)
+    head_fa_bytes, head_q_bytes = job.fa_d.numel(), job.f1_d.numel() + job.f2_d.numel()
+
+    # ---- c5: short-read-heavy query against the same database ----
+    c5 = None
+    if args.workload == "c2" and not args.no_c5:
+        _, s1, s2 = gen_weak("c5", rank, world, db=db)
+        job5 = Job(rig, db.text, s1, s2, int(db.lengths.sum()), "c5")
+        c5 = sub_record(rig, job5, max(5, args.steps // 2), 3, parity_records=2000, with_e2e=True, with_unpruned=False)
+        c5["workload"] = WORKLOAD_DESC["c5"]
+        c5["reads"] = "20-150 bp (40 % shorter than k = 32 contribute nothing, bin/extract_ref.cpp:964); k sweep = the single point k = 32 (:24)"
+        del job5
+    del job, db, f1, f2
+    rig.torch.cuda.empty_cache()
+
+    # ---- strong scaling: ONE 30,000-genome ~1.5 Gbp database over the N GPUs ----
+    strong = {}
+    subs = None
+    for kind in strong_kinds:
+        text, q1, q2, bases, subs = gen_strong(kind, rank, world, subs)
+        js = Job(rig, text, q1, q2, bases, kind)
+        del text, q1, q2
+        rec = sub_record(rig, js, max(5, args.steps // 2), 3, parity_records=1500 if kind == "c4" else 3750,
+                         with_e2e=True, with_unpruned=True)
+        rec["workload"] = STRONG[kind]["desc"]
+        rec["scaling"] = "strong"
+        rec["n_gpus"] = world
+        strong[kind] = rec
+        del js
+        rig.torch.cuda.empty_cache()
+    del subs
+
+    if rank != 0:
+        rig.close()
+        return
     out = {
-        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+        "metric": METRIC, "value": round(head["value"], 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(head["ms_per_step"], 4), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_DESC[args.workload], "db_bases_per_gpu": int(info["ref_bases"]),
-                   "query_seq_bases": int(qbases), "records_per_gpu": int(info["n_records"]), "k": 32,
-                   "hit_ratio": 0.9, "perfect_hit_ratio": 0.85, "parallelism": f"db-shard x{world}, query replicated",
-                   "candidate_filter": not args.no_prune,
-                   "l2": "inputs larger than L2: per step the 512 MiB level-3 table is rewritten and 0.6 GB of text read"},
-        "e2e": {"value": round(e2e_value, 3), "unit": UNIT,
-                "h2d_bytes_per_step": h2d_bytes,
-                "d2h_bytes_per_step": int(info["n_records"]) * 16 + 24, "ms_per_step": round(e2e_s / args.steps * 1e3, 3),
-                "api": f"eref_run_host(chunks={args.chunks}): pinned host buffers, H2D overlapped with kernels" +
-                       ("" if world == 1 else "; each rank uploads 1/N of the query text, NCCL all-gathers it over NVLink"),
-                "h2d_alone_ms": round(h2d_floor_ms, 3),
-                "h2d_alone_GBps": round(h2d_bytes / 1e6 / h2d_floor_ms, 1)},
-        "gpu_launches": launches,
-        "clocks": clocks,
+        "config": config_for(WORKLOAD_DESC[args.workload], world),
+        "workload_detail": {"db_bases_per_gpu": int(info["ref_bases"]), "query_seq_bases": int(qbases),
+                            "records_per_gpu": int(info["n_records"]),
+                            "parallelism": f"db-shard x{world}, query replicated", "table_build": rig.table_mode,
+                            "candidate_filter": not args.no_prune,
+                            "l2": "inputs larger than L2: per step the 512 MiB level-3 table is rewritten and 0.6 GB of text read"},
+        "e2e": e2e,
+        "gpu_launches": head["launches"],
+        "clocks": head["clocks"],
         "phases_ms": {k: round(v, 4) for k, v in avg.items()},
-        "scan_only": {"ms": round(scan_ms, 4), "value": round(info["ref_bases"] / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT,
-                      "need_word_fraction": round(info["need_words"] / max(info["ref_words"], 1), 4)},
-        "db_resident": {"ms_per_step": round(res_ms / args.steps, 4),
-                        "value": round(total_bases / 1e9 / (res_ms / args.steps / 1e3), 2), "unit": UNIT,
-                        "note": "not the headline: the same step when the database's bit-planes stay in HBM across "
-                                "samples (eref_ref_set once), i.e. table build + scan + all-gather"},
-        "e2e_db_resident": {"ms_per_step": round(e2e_res_s / args.steps * 1e3, 3),
-                            "value": round(total_bases / 1e9 / (e2e_res_s / args.steps), 2), "unit": UNIT,
-                            "h2d_bytes_per_step": int(f1_h.numel() + f2_h.numel()),
-                            "note": "not the headline: eref_run_host(fq1, fq2, NULL) from pinned host buffers against a "
-                                    "database set once (one phage DB, many samples)"},
-        "roofline": {"bound": "hbm", "kernel": dom_kernel, "phase": dom,
-                     "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "traffic": ncu_traffic(dom), "peak_source": peak_src,
-                     "algorithmic_bytes_per_unit": per_unit, "units_per_launch": int(units), "unit_name": unit_name,
-                     "algorithmic_bytes_per_launch": int(alg), "kernel_ms": round(avg[dom], 4),
-                     "probes_per_s_G": round(3.0 * probed_bases / (avg["scan_probe_ms"] / 1e3) / 1e9, 1),
-                     "note": roof_note,
-                     "largest_phase": largest},
+        "scan_only": {"ms": round(scan_ms, 4), "value": round(info["ref_bases"] * world / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT,
+                      "need_word_fraction": round(info["need_words"] / max(info["ref_words"], 1), 4),
+                      "note": "pruned scan: the exact candidate filter skips the probes of words no good window can use, so "
+                              "this is NOT comparable with 97 B/base; scan_unpruned is"},
+        "scan_unpruned": unpruned,
+        "parity": par,
+        "strong": strong or None,
+        "c5": c5,
+        "db_resident": db_res, "e2e_db_resident": e2e_res,
+        "roofline": roof,
         "phases": phases,
         "survey_8d": {"table_build": {"bytes_per_query_base": BYTES_PER_QUERY_BASE_BUILD,
                                       "ms": round(sum(avg[p] for p in QUERY_PHASES), 4),
                                       "frac_of_hbm": round(BYTES_PER_QUERY_BASE_BUILD * qbases / 1e9 /
-                                                           (sum(avg[p] for p in QUERY_PHASES) / 1e3) / peak, 3)},
-                      "scan": {"bytes_per_ref_base": BYTES_PER_REF_BASE_FULL, "ms": round(scan_ms, 4),
-                               "frac_of_hbm": round(BYTES_PER_REF_BASE_FULL * info["ref_bases"] / 1e9 / (scan_ms / 1e3) / peak, 3)}},
+                                                           (sum(avg[p] for p in QUERY_PHASES) / 1e3) / peak, 3),
+                                      "note": "193 B per query base assumes three random DRAM read-modify-writes; the "
+                                              "partitioned shared-memory build replaces them"},
+                      "scan": "see scan_unpruned (same run, candidate filter off)"},
     }
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(budget_runs=1)
+    if world > 1 and not args.no_exe_check:
+        out["exe_multi_gpu"] = exe_multi_gpu(world)
     _emit(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+    rig.close()
 
 
 # ---- the reference's CPU implementation on the host cores -----------------------------------------
@@ -491,29 +837,43 @@ def _host_mem_gb():
     return 0.0
 
 
-class CpuArm:
-    """A bounded sample of the bench workload (same generator, C1-sized by default) on disk, and one
-    timed invocation of the reference per step.  kind = "reference": the UNMODIFIED reference binary
-    built from /root/reference/bin/extract_ref.cpp (needs ~24 GB RAM, ~14 s fixed cost per run);
-    kind = "port": oracle/eref_oracle (the C restatement) when the binary or the memory is missing."""
+def _disk_free_gb(path):
+    try:
+        return shutil.disk_usage(path).free / 1e9
+    except Exception:
+        return 0.0
 
-    def __init__(self, sample="c1", prefer_reference=True):
+
+def have_reference():
+    return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK) and _host_mem_gb() > 30
+
+
+class CpuArm:
+    """One workload of the bench generator on disk, and one timed invocation of the reference's CPU implementation per
+    step.  kind = "reference": the UNMODIFIED reference binary built from /root/reference/bin/extract_ref.cpp (needs
+    ~24 GB RAM, seconds of fixed cost per run, a 12 B/base index next to the database); kind = "port": oracle/eref_oracle
+    (the C restatement) only when the binary is missing or the host has too little memory for it."""
+
+    def __init__(self, sample="c1", kind=None):
         from palace_b200 import synth
-        G, R, Q = WORKLOADS[sample]
+        G, R, Q, (lo, hi) = WORKLOADS[sample]
+        self.sample_name = sample
         self.dir = tempfile.mkdtemp(prefix="eref_cpu_")
         db = synth.make_db(G, R, 1000)
-        f1, f2, _ = synth.make_reads(db, Q, 2000)
+        f1, f2, _ = synth.make_reads(db, Q, 2000, min_len=lo, max_len=hi)
         db.text.tofile(os.path.join(self.dir, "db.fa"))
         f1.tofile(os.path.join(self.dir, "r1.fq")); f2.tofile(os.path.join(self.dir, "r2.fq"))
         self.bases = int(db.lengths.sum())
         self.cores = os.cpu_count() or 1
-        use_ref = prefer_reference and os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK) and _host_mem_gb() > 30
-        self.kind = "reference" if use_ref else "port"
-        self.bin = REF_BIN if use_ref else ORACLE_BIN
-        if not use_ref and not os.path.exists(ORACLE_BIN):
+        if kind is None:
+            kind = "reference" if have_reference() else "port"
+        self.kind = kind
+        self.bin = REF_BIN if kind == "reference" else ORACLE_BIN
+        if kind == "port" and not os.path.exists(ORACLE_BIN):
             subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "eref_oracle"], check=True, capture_output=True)
-        self.sample = (f"{G}-genome {self.bases / 1e6:.0f} Mbp DB + {Q / 1e6:.0f} Mbp reads (same generator and seeds as the "
-                       f"GPU arm, BASELINE configs[0] size), threads={self.cores}")
+        self.sample = (f"{WORKLOAD_DESC[sample]}: {G}-genome {self.bases / 1e6:.0f} Mbp DB + {Q / 1e6:.0f} Mbp reads (same "
+                       f"generator and seeds as the GPU arm's rank 0), threads={self.cores}, "
+                       + ("unmodified reference binary oracle/_ref/eref_ref" if kind == "reference" else "oracle port oracle/eref_oracle"))
         self.stdout = None
 
     def run_once(self, threads=None):
@@ -527,31 +887,32 @@ class CpuArm:
         self.stdout = r.stdout
         return dt
 
-    def run_product(self):
+    def run_product(self, gpus=1):
         """palace_b200/bin/eref as a process on the very same files (it takes the coder from the index header the
         CPU run left next to the database): wall time and stdout"""
         exe = os.path.join(ROOT, "palace_b200", "bin", "eref")
         t0 = time.perf_counter()
         r = subprocess.run([exe, "r1.fq", "r2.fq", "db.fa", "tmp_b200.txt", "0.9", "0.85", str(self.cores)], cwd=self.dir,
-                           capture_output=True, env=dict(os.environ, EREF_GPUS="1"))
+                           capture_output=True, env=dict(os.environ, EREF_GPUS=str(gpus)))
         dt = time.perf_counter() - t0
         if r.returncode != 0:
             raise RuntimeError(f"{exe} failed: {r.stderr.decode()[-400:]}")
         return dt, r.stdout
 
     def close(self):
-        import shutil
         shutil.rmtree(self.dir, ignore_errors=True)
 
 
 def cpu_baseline(budget_runs=1):
+    """N=1 line: the reference on the host cores on a BOUNDED sample (BASELINE configs[0] size), and the whole-process
+    comparison on that sample's files"""
     arm = CpuArm("c1")
     try:
         cold = arm.run_once()                          # builds <db>.k32.index.dat serially (:1250)
         warm = min(arm.run_once() for _ in range(budget_runs))
         out = {"value": round(arm.bases / 1e9 / warm, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
-               "sample": arm.sample + "; value = warm run (index on disk)", "warm_s": round(warm, 2),
-               "cold_s": round(cold, 2), "cold_value": round(arm.bases / 1e9 / cold, 6),
+               "sample": arm.sample + "; value = warm run (index on disk)", "sample_db_bases": arm.bases,
+               "warm_s": round(warm, 2), "cold_s": round(cold, 2), "cold_value": round(arm.bases / 1e9 / cold, 6),
                "selected_refs": arm.stdout.count(b"\n")}
         # SURVEY.md §8(d): wall time of the whole eref PROCESS, both executables on the same files of this sample, and
         # the same-run parity check: the reference at threads=1 (the parity configuration) against the drop-in's stdout
@@ -572,15 +933,76 @@ def cpu_baseline(budget_runs=1):
         arm.close()
 
 
+def exe_multi_gpu(world):
+    """N>1 line, rank 0: the drop-in EXECUTABLE with EREF_GPUS=N (one host thread per GPU, sharded table build, NCCL
+    all-gather of the records) next to the unmodified reference at threads=1 on the configs[0]-sized files"""
+    try:
+        arm = CpuArm("c1")
+    except Exception as e:
+        return {"error": str(e)[-300:]}
+    try:
+        arm.run_once()                                 # writes the index (coder header) the drop-in reads
+        t1 = arm.run_once(threads=1) if arm.kind == "reference" else arm.run_once()
+        ref_stdout = arm.stdout
+        wall, mine = arm.run_product(gpus=world)
+        one, mine1 = arm.run_product(gpus=1)
+        return {"n": world, "stdout_identical": mine == ref_stdout, "stdout_identical_1gpu": mine1 == ref_stdout,
+                "wall_s": round(wall, 3), "wall_s_1gpu": round(one, 3), "reference_threads1_wall_s": round(t1, 2),
+                "result_lines": mine.count(b"\n"), "against": arm.kind,
+                "note": "the other ranks of this bench hold their GPUs meanwhile"}
+    except Exception as e:
+        return {"n": world, "error": str(e)[-300:]}
+    finally:
+        arm.close()
+
+
 def run_reference(args):
+    """The reference's own CPU implementation of the path on the host cores, all threads, on the headline workload when
+    the whole run fits the time budget (EREF_REF_BUDGET_S, default 1000 s), else on BASELINE configs[0]; config.workload
+    and `sample` name what actually ran.  The binary is the UNMODIFIED reference whenever it exists; each step is one
+    whole eref process with the index already on disk (the index build is untimed setup, reported as cold_s)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # the unmodified reference takes ~8 s per process on the C1-sized sample on the GPU box (most of it the fixed cost of
-    # zeroing 20 GiB of tables): up to 20 runs (the default 10 + 3 included) stay within three minutes;
-    # beyond that, the port on a smaller sample
-    real = args.steps + args.warmup <= 20 and os.environ.get("EREF_BENCH_CPU_SAMPLE") != "small"   # (the CPU test suite forces the port)
-    arm = CpuArm("c1" if real else "small", prefer_reference=real)
+    t_begin = time.perf_counter()
+    budget = float(os.environ.get("EREF_REF_BUDGET_S", "1000"))
+    forced = os.environ.get("EREF_BENCH_CPU_SAMPLE")          # the CPU test-suite: "small"
+    kind = os.environ.get("EREF_BENCH_CPU_KIND") or None      # ... and "port"
+    runs = args.steps + args.warmup
+    plan, why = None, ""
+    if forced:
+        plan, why = forced, f"EREF_BENCH_CPU_SAMPLE={forced}"
+    else:
+        want = args.workload if args.workload in ("c2", "c1", "small", "c5") else "c2"
+        plan, why = want, "the headline workload"
+        if want in ("c2", "c5"):
+            # what would a run on the headline workload cost?  fixed cost per process (tables zeroed) from a tiny input,
+            # variable cost scaled x10 from the configs[0]-sized sample
+            if (kind or ("reference" if have_reference() else "port")) == "reference" and \
+                    (_disk_free_gb(tempfile.gettempdir()) < 12 or _host_mem_gb() < 40):
+                plan, why = "c1", "the headline workload needs 12 GB of scratch disk and 40 GB of RAM for the reference"
+            else:
+                probe = CpuArm("c1", kind)
+                try:
+                    c1_cold = probe.run_once()
+                    c1_warm = probe.run_once()
+                finally:
+                    probe.close()
+                tiny = CpuArm("small", kind)
+                try:
+                    tiny.run_once()
+                    fixed = tiny.run_once() * 0.9
+                finally:
+                    tiny.close()
+                est_warm = fixed + 10 * max(c1_warm - fixed, 0.05)
+                est_cold = fixed + 10 * max(c1_cold - fixed, 0.05)
+                spent = time.perf_counter() - t_begin
+                est = spent + 30 + est_cold + runs * est_warm
+                why = (f"estimated {est:.0f} s for {runs} runs on the headline workload (fixed {fixed:.1f} s + 10 x the "
+                       f"configs[0] variable cost) against a budget of {budget:.0f} s")
+                if est > budget:
+                    plan = "c1"
+    arm = CpuArm(plan, kind)
     try:
         cold = arm.run_once()                          # index build, untimed setup
         for _ in range(args.warmup):
@@ -595,10 +1017,11 @@ def run_reference(args):
             "impl": "reference", "metric": METRIC, "value": round(value, 6), "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 2), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_DESC[args.workload], "k": 32, "hit_ratio": 0.9, "perfect_hit_ratio": 0.85},
+            "config": config_for(WORKLOAD_DESC[plan], args.gpus),
             "cpu_baseline": {"value": round(value, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
                              "sample": arm.sample + "; each step = one whole eref process, index already on disk",
-                             "cold_s": round(cold, 2)},
+                             "sample_db_bases": arm.bases, "cold_s": round(cold, 2), "chosen_because": why,
+                             "selected_refs": arm.stdout.count(b"\n") if arm.stdout is not None else None},
             "e2e": {"value": round(value, 6), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
         }
@@ -614,8 +1037,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--strong", default="c3,c4", help="strong-scaling sub-records: comma list of c3, c4, or none")
+    ap.add_argument("--table", default="auto", choices=["auto", "peer", "allgather", "replicated"],
+                    help="N>1: how the query table is built (auto: peer stores over CUDA IPC, else NCCL all-gather)")
     ap.add_argument("--no-prune", action="store_true", help="probe all three streams at every position")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-unpruned", action="store_true")
+    ap.add_argument("--no-c5", action="store_true")
+    ap.add_argument("--no-exe-check", action="store_true")
     ap.add_argument("--chunks", type=int, default=4, help="database pieces of the pipelined host-buffer call (e2e)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

@@ -10,6 +10,7 @@
 #include <string.h>
 #ifdef _OPENMP
 #include <omp.h>
+#include <math.h>
 #endif
 
 /* ---- coders ------------------------------------------------------------------------------ */
@@ -189,6 +190,51 @@ void eo_count_fastq_sampled(uint8_t* table, const int16_t coder[96], const char*
     }
 }
 
+/* The same count with T threads, for the case without draws: the saturating count of a slot depends only on how
+ * often ITS code occurs (:995-997), so thread t walks every sequence line and applies exactly the codes whose top
+ * byte falls in its range — every table byte has one writer and ends up as in the serial loop. */
+static void count_read_range(uint8_t* table, const eo_masks* mk, const unsigned char* s, uint32_t len, uint32_t lo8, uint32_t hi8)
+{
+    uint32_t c[3];
+    ROLL_BEGIN(s, len)
+        (void)j_;
+        if (valid_) {
+            codes_from_windows(mk, hi_, lo_, c);
+            for (int i = 0; i < 3; i++) {
+                const uint32_t top = c[i] >> 24;
+                if (top >= lo8 && top < hi8 && table[c[i]] < 3) table[c[i]]++;
+            }
+        }
+    ROLL_END
+}
+
+void eo_count_fastq_mt(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int threads)
+{
+    if (threads <= 1) { eo_count_fastq_sampled(table, coder, text, n, -1); return; }
+    if (threads > 64) threads = 64;
+    eo_masks mk; make_masks(coder, &mk);
+    /* canonical codes are min(fwd, rc): their density falls linearly with the code, so equal-width ranges would
+     * leave the low threads with most of the work; cut at equal areas under 2(1-x) instead */
+    uint32_t cut[65];
+    for (int t = 0; t <= threads; t++) {
+        double x = 1.0 - sqrt(1.0 - (double)t / threads);
+        cut[t] = t == threads ? 256u : (uint32_t)(x * 256.0);
+    }
+    #pragma omp parallel num_threads(threads)
+    {
+        const int t = omp_get_thread_num();
+        const uint32_t lo8 = cut[t], hi8 = cut[t + 1];
+        size_t pos = 0, line = 0;
+        while (pos < n && hi8 > lo8) {
+            const char* nl = memchr(text + pos, '\n', n - pos);
+            size_t end = nl ? (size_t)(nl - text) : n;
+            if (line % 4 == 1) count_read_range(table, &mk, (const unsigned char*)text + pos, (uint32_t)(end - pos), lo8, hi8);
+            line++;
+            pos = end + 1;
+        }
+    }
+}
+
 long eo_fastq_seq_bytes(const char* text, size_t n)
 {
     size_t pos = 0, line = 0; long sum = 0;
@@ -322,8 +368,13 @@ int eo_run_sampled(const char* fq1, size_t n1, const char* fq2, size_t n2, const
     if (sample_size == 0) { eo_table_free(table); return -3; }   /* the reference divides by zero here (:1145) */
     int ratio = (int)(100 * down_sampling_size / sample_size);   /* :1145 */
     srand(1);                                                    /* :1236-1238 */
-    eo_count_fastq_sampled(table, coder, fq1, n1, ratio < 100 ? ratio : -1);   /* :1269-1279 */
-    eo_count_fastq_sampled(table, coder, fq2, n2, ratio < 100 ? ratio : -1);   /* :1281-1291 */
+    if (ratio < 100 || threads <= 1) {
+        eo_count_fastq_sampled(table, coder, fq1, n1, ratio < 100 ? ratio : -1);   /* :1269-1279 */
+        eo_count_fastq_sampled(table, coder, fq2, n2, ratio < 100 ? ratio : -1);   /* :1281-1291 */
+    } else {                                                     /* no draws: the count parallelises by code range */
+        eo_count_fastq_mt(table, coder, fq1, n1, threads);
+        eo_count_fastq_mt(table, coder, fq2, n2, threads);
+    }
     unsigned char* seq; uint64_t* off; size_t kept;
     if (eo_parse_fasta(fasta, nf, &seq, &off, &kept, NULL)) { eo_table_free(table); return -2; }
     eo_result* res = (eo_result*)calloc(kept ? kept : 1, sizeof *res);

@@ -47,6 +47,8 @@ void eo_table_free(uint8_t* t);
 void eo_count_fastq(uint8_t* table, const int16_t coder[96], const char* text, size_t n);
 /* the same under down-sampling (:955-960): down_sam_ratio < 0 = count every read, no rand() draws */
 void eo_count_fastq_sampled(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int down_sam_ratio);
+/* the count without draws on `threads` threads, each owning a range of the code space (same table, byte for byte) */
+void eo_count_fastq_mt(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int threads);
 /* cal_sam_ratio's sum (:1133-1142): bytes on lines with index%4==1 */
 long eo_fastq_seq_bytes(const char* text, size_t n);
 

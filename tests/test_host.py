@@ -149,7 +149,8 @@ def test_bench_reference_arm_prints_the_contract_line():
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
-                       capture_output=True, timeout=300, env=dict(os.environ, EREF_BENCH_CPU_SAMPLE="small"))
+                       capture_output=True, timeout=300,
+                       env=dict(os.environ, EREF_BENCH_CPU_SAMPLE="small", EREF_BENCH_CPU_KIND="port"))
     assert r.returncode == 0, r.stderr.decode()[-400:]
     lines = [l for l in r.stdout.decode().splitlines() if l.strip()]
     assert len(lines) == 1                                         # stdout carries the one JSON line and nothing else
@@ -157,6 +158,9 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["impl"] == "reference" and d["unit"] == "Gbp/s" and d["higher_is_better"] is True
     assert d["value"] > 0 and d["steps"] == 1 and d["n_gpus"] == 1
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    # the labels say what ran: the development sample, the port — not the headline workload
+    assert "development" in d["config"]["workload"] and "oracle port" in d["cpu_baseline"]["sample"]
+    assert d["cpu_baseline"]["sample_db_bases"] > 0
     assert d["e2e"] == {"value": d["value"], "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 
