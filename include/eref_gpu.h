@@ -119,6 +119,14 @@ int  eref_scan_device_async(eref_ctx* ctx, const uint32_t** results_dev, size_t*
 int  eref_run_host(eref_ctx* ctx, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta,
                    size_t nf, int chunks, eref_result* out, size_t cap, size_t* n_out);
 
+/* the records of the last eref_run_host, still in device memory (n x 4 uint32, file-order ordinals): what a multi-GPU
+ * caller hands to its all-gather.  out/cap of eref_run_host may be NULL/0 when only these are wanted. */
+int  eref_run_results_device(eref_ctx* ctx, const uint32_t** results_dev, size_t* n_out);
+/* Down-sampling masks for the NEXT eref_run_host (one bit per sequence line, LSB first, as eref_draw_keep writes them):
+ * when several GPUs screen the same sample the rand() draws of :955-957 must happen once, not once per GPU.  Used only
+ * if that call's ratio is below 100. */
+int  eref_run_host_keep(eref_ctx* ctx, const uint32_t* keep1, uint64_t lines1, const uint32_t* keep2, uint64_t lines2);
+
 /* the per-record body of <db>.k32.index.dat (:711-738): (len-31)*3 codes, 0 = invalid window.
  * ordinal is 1-based within the current reference text.  Test hook and index writer (f2). */
 int  eref_get_codes(eref_ctx* ctx, uint32_t ordinal, uint32_t* codes_host, size_t cap, size_t* n_out);

@@ -44,6 +44,20 @@ struct DevBuf {
         if (e == cudaSuccess) cap = want;
         return e;
     }
+    // grow keeping the first `keep` bytes (stream-ordered copy; the old block is freed after it)
+    cudaError_t grow(size_t bytes, size_t keep, cudaStream_t st)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        void* q = nullptr;
+        const size_t want = bytes + bytes / 2 + 256;
+        cudaError_t e = cudaMalloc(&q, want);
+        if (e != cudaSuccess) return e;
+        if (p && keep) e = cudaMemcpyAsync(q, p, keep, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess && p) { e = cudaStreamSynchronize(st); if (e == cudaSuccess) e = cudaFree(p); }
+        if (e != cudaSuccess) { cudaFree(q); return e; }
+        p = q; cap = want;
+        return cudaSuccess;
+    }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
@@ -62,6 +76,11 @@ struct eref_ctx {
     bool host_tables_valid = false;            // h_g_* mirrors fetched lazily (test hooks only)
     std::vector<cudaEvent_t> copy_ev;          // eref_run_host: one event per staged H2D copy
     DevBuf q_text2, run_results;
+    size_t run_total = 0;                      // records of the last eref_run_host, in run_results
+    // down-sampling masks handed in by the caller for the next eref_run_host (eref_run_host_keep)
+    std::vector<uint32_t> pend_keep1, pend_keep2;
+    uint64_t pend_lines1 = 0, pend_lines2 = 0;
+    bool pend_keep = false;
     CoderMasks masks{};
     float hit_ratio = 0, perfect_hit_ratio = 0;
     int one_min = 0, three_min = 0, sample_stride = 4;
@@ -905,6 +924,25 @@ int eref_ref_count(eref_ctx* c, size_t* n_kept, size_t* n_records, uint64_t* kep
     return 0;
 }
 
+// tail of a synchronous scan: the filter's word count and the sharded build's error word come back with the records,
+// the stream is waited for and the phase times are read
+static int finish_scan_sync(eref_ctx* c)
+{
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    if (c->parts > 1) CUDA_TRY(cudaMemcpyAsync(c->h_pin + 7, c->share_words + MAX_PARTS, 8, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaEventRecord(c->ev[S7], c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->scan_pending = true; c->scan_pending_d2h = true;
+    collect_times(c);
+    if (c->parts > 1 && (c->h_pin[7] >> 32)) {
+        const unsigned who = (unsigned)(c->h_pin[7] >> 32) - 1;
+        cudaMemsetAsync(c->share_words + MAX_PARTS + 1, 0, 4, c->stream);
+        return eref_fail(EREF_ERR_STATE, "sharded table build: part %u never arrived in this GPU's table (is every GPU "
+                                         "of the build running the same sequence of calls?)", who);
+    }
+    return 0;
+}
+
 int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
 {
     if (!c || (cap && !out)) return eref_fail(EREF_ERR_ARG, "eref_scan: null argument");
@@ -913,20 +951,25 @@ int eref_scan(eref_ctx* c, eref_result* out, size_t cap, size_t* n_out)
     if (rc) return rc;
     size_t n = c->n_genomes < cap ? c->n_genomes : cap;
     if (n) CUDA_TRY(cudaMemcpyAsync(out, c->results.p, n * sizeof(eref_result), cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 6, c->counters.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, c->stream));
-    if (c->parts > 1) CUDA_TRY(cudaMemcpyAsync(c->h_pin + 7, c->share_words + MAX_PARTS, 8, cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaEventRecord(c->ev[S7], c->stream));
-    CUDA_TRY(cudaStreamSynchronize(c->stream));
-    c->scan_pending = true; c->scan_pending_d2h = true;
-    collect_times(c);
     if (n_out) *n_out = c->n_genomes;
-    if (c->parts > 1 && (c->h_pin[7] >> 32)) {
-        const unsigned who = (unsigned)(c->h_pin[7] >> 32) - 1;
-        cudaMemsetAsync(c->share_words + MAX_PARTS + 1, 0, 4, c->stream);
-        return eref_fail(EREF_ERR_STATE, "sharded table build: part %u never arrived in this GPU's table (is every GPU "
-                                         "of the build running the same sequence of calls?)", who);
+    return finish_scan_sync(c);
+}
+
+// eref_run_host: scan the current reference (one database piece) and append its records, ordinals continuing in file
+// order, to the run's list in device memory; waits for the scan (the next piece reuses the buffers)
+static int scan_append(eref_ctx* c, size_t* total)
+{
+    int rc = scan_impl(c);
+    if (rc) return rc;
+    const size_t G = c->n_genomes;
+    CUDA_TRY(c->run_results.grow((*total + G + 1) * sizeof(eref_result), *total * sizeof(eref_result), c->stream));
+    if (G) {
+        uint32_t* dst = c->run_results.as<uint32_t>() + *total * 4;
+        CUDA_TRY(cudaMemcpyAsync(dst, c->results.p, G * sizeof(eref_result), cudaMemcpyDeviceToDevice, c->stream));
+        LAUNCH(c, launch_add_ordinal(dst, (uint32_t)G, (uint32_t)*total, c->stream));
     }
-    return 0;
+    *total += G;
+    return finish_scan_sync(c);
 }
 
 /* The whole path in one call, from HOST buffers, with the H2D copies overlapped with the kernels: both
@@ -982,6 +1025,8 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     CUDA_TRY(cudaStreamWaitEvent(cs, c->ev[E9], 0));
     static const bool trace = getenv("EREF_TRACE_E2E") != nullptr;
     const auto h0 = std::chrono::steady_clock::now();
+    // whatever way this call ends, no copy from the caller's buffers is still in flight when it returns
+    struct CopyGuard { cudaStream_t s; ~CopyGuard() { cudaStreamSynchronize(s); } } copy_guard{cs};
     CUDA_TRY(cudaEventRecord(c->ev[E10], cs));
     // cudaMemcpyDefault: the texts may also be device pointers (e.g. a query all-gathered over NVLink by the caller)
     if (n1) CUDA_TRY(cudaMemcpyAsync(c->q_text.p, fq1, n1, cudaMemcpyDefault, cs));
@@ -1012,7 +1057,7 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     // cal_sam_ratio (:1124-1148): 100 * 2e9 / (2 * sequence bytes of fq1)
     int ratio = 0;
     rc = eref_sample_ratio(seq1, c->down_sampling_size, &ratio);
-    if (rc) { cudaStreamSynchronize(cs); return rc; }
+    if (rc) return rc;
     std::vector<uint32_t> keep1, keep2;
     uint64_t lines1 = 0, lines2 = 0;
     if (ratio < 100) {
@@ -1020,15 +1065,22 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         // draw is below the ratio.  Replay the draws on the host in the reference's order (its main() seeds rand with
         // 1, :1236-1238; EREF_FLAG_KEEP_RAND_STATE: the caller has positioned rand() already, like a cold reference run
         // whose coder draw re-seeded it), then count both files again under the masks.
-        rc = census_impl(c, c->q_text.as<uint8_t>(), n1, nullptr, &lines1);
-        if (rc) return rc;
-        CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[1], 0));
-        rc = census_impl(c, c->q_text2.as<uint8_t>(), n2, nullptr, &lines2);
-        if (rc) return rc;
-        if (!(c->flags & EREF_FLAG_KEEP_RAND_STATE)) srand(1);
-        keep1.resize((lines1 + 31) / 32 + 1); keep2.resize((lines2 + 31) / 32 + 1);
-        eref_draw_keep(ratio, lines1, keep1.data());
-        eref_draw_keep(ratio, lines2, keep2.data());
+        if (c->pend_keep) {
+            // the caller drew the masks (several GPUs screen the same sample: the draws happen once, :955-957)
+            keep1.swap(c->pend_keep1); keep2.swap(c->pend_keep2);
+            lines1 = c->pend_lines1; lines2 = c->pend_lines2;
+            c->pend_keep = false;
+        } else {
+            rc = census_impl(c, c->q_text.as<uint8_t>(), n1, nullptr, &lines1);
+            if (rc) return rc;
+            CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[1], 0));
+            rc = census_impl(c, c->q_text2.as<uint8_t>(), n2, nullptr, &lines2);
+            if (rc) return rc;
+            if (!(c->flags & EREF_FLAG_KEEP_RAND_STATE)) srand(1);
+            keep1.resize((lines1 + 31) / 32 + 1); keep2.resize((lines2 + 31) / 32 + 1);
+            eref_draw_keep(ratio, lines1, keep1.data());
+            eref_draw_keep(ratio, lines2, keep2.data());
+        }
         rc = eref_query_reset(c);
         if (rc) return rc;
         CUDA_TRY(cudaEventRecord(c->ev[E0], st));
@@ -1048,10 +1100,8 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     sum.ref_bases = sum.ref_words = sum.ref_need_words = 0;
     size_t total = 0;
     if (resident) {
-        size_t got = 0;
-        rc = eref_scan(c, out, cap, &got);
+        rc = scan_append(c, &total);
         if (rc) return rc;
-        total = got;
         sum.scan_summary_ms = c->t.scan_summary_ms; sum.scan_sample_ms = c->t.scan_sample_ms;
         sum.scan_cand_ms = c->t.scan_cand_ms; sum.scan_probe_ms = c->t.scan_probe_ms;
         sum.scan_window_ms = c->t.scan_window_ms; sum.scan_interval_ms = c->t.scan_interval_ms;
@@ -1063,13 +1113,8 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         CUDA_TRY(cudaEventRecord(c->ev[E0], st));
         rc = ref_set_impl(c, piece_dev[k], cut[k + 1] - cut[k]);
         if (rc) return rc;
-        size_t got = 0;
-        const size_t room = cap > total ? cap - total : 0;
-        rc = eref_scan(c, room ? out + total : nullptr, room, &got);
+        rc = scan_append(c, &total);
         if (rc) return rc;
-        const size_t wrote = got < room ? got : room;
-        for (size_t i = 0; i < wrote; i++) out[total + i].ordinal += (uint32_t)total;   // file-order ordinals
-        total += got;
         sum.ref_frame_ms += c->t.ref_frame_ms; sum.ref_pack_ms += c->t.ref_pack_ms;
         sum.scan_summary_ms += c->t.scan_summary_ms; sum.scan_sample_ms += c->t.scan_sample_ms;
         sum.scan_cand_ms += c->t.scan_cand_ms; sum.scan_probe_ms += c->t.scan_probe_ms;
@@ -1078,11 +1123,18 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         sum.query_count_ms = c->t.query_count_ms;
         sum.ref_bases += c->t.ref_bases; sum.ref_words += c->t.ref_words; sum.ref_need_words += c->t.ref_need_words;
     }
+    c->run_total = total;
+    // the records of all pieces leave the device in one copy (they also stay there: eref_run_results_device)
+    const size_t wrote = total < cap ? total : cap;
+    if (wrote) {
+        CUDA_TRY(cudaMemcpyAsync(out, c->run_results.p, wrote * sizeof(eref_result), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
     if (trace) {
         const auto h2 = std::chrono::steady_clock::now();
         float copy_ms = 0, tail_ms = 0;
         cudaEventElapsedTime(&copy_ms, c->ev[E10], c->ev[E11]);
-        cudaEventElapsedTime(&tail_ms, c->ev[E11], c->ev[S7]);
+        cudaEventElapsedTime(&tail_ms, c->ev[E11], c->ev[S7]);   // (S7: end of the last piece's scan)
         fprintf(stderr, "eref_run_host: queued copies after %.3f ms, returned after %.3f ms; copies took %.3f ms on the "
                         "device, last copy -> last result %.3f ms\n",
                 std::chrono::duration<double, std::milli>(h1 - h0).count(),
@@ -1095,6 +1147,24 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
     c->t = sum;
     if (!resident) c->have_ref = npieces == 1;   // per-record lookups only make sense for a single piece
     if (n_out) *n_out = total;
+    return 0;
+}
+
+int eref_run_host_keep(eref_ctx* c, const uint32_t* keep1, uint64_t lines1, const uint32_t* keep2, uint64_t lines2)
+{
+    if (!c || (lines1 && !keep1) || (lines2 && !keep2)) return eref_fail(EREF_ERR_ARG, "eref_run_host_keep: null argument");
+    c->pend_keep1.assign(keep1, keep1 + (lines1 + 31) / 32); c->pend_keep1.push_back(0);
+    c->pend_keep2.assign(keep2, keep2 + (lines2 + 31) / 32); c->pend_keep2.push_back(0);
+    c->pend_lines1 = lines1; c->pend_lines2 = lines2;
+    c->pend_keep = true;
+    return 0;
+}
+
+int eref_run_results_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
+{
+    if (!c || !results_dev) return eref_fail(EREF_ERR_ARG, "eref_run_results_device: null argument");
+    *results_dev = c->run_results.as<uint32_t>();
+    if (n_out) *n_out = c->run_total;
     return 0;
 }
 

@@ -210,6 +210,7 @@ cudaError_t launch_window_list(const uint32_t* single, const uint32_t* trio, con
 // genome_listed: null, or one word per record, non-zero iff k_need listed a word of it (others answer {0, 0} unread)
 cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const uint32_t* g_len,
                              uint32_t n_genomes, const uint32_t* genome_listed, uint32_t* results, cudaStream_t st);
+cudaError_t launch_add_ordinal(uint32_t* results, uint32_t n, uint32_t base, cudaStream_t st);
 cudaError_t launch_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,
                                 uint32_t* codes, cudaStream_t st);
 cudaError_t launch_index_body(Planes pl, CoderMasks m, const uint32_t* g_word, const uint32_t* g_len,

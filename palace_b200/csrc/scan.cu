@@ -547,6 +547,13 @@ k_intervals(const uint32_t* __restrict__ good, const uint32_t* __restrict__ g_wo
     }
 }
 
+// records of one database piece appended to the run's list: ordinals continue in file order (:887, :1175)
+__global__ void k_add_ordinal(uint32_t* __restrict__ results, uint32_t n, uint32_t base)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) results[(size_t)i * 4] += base;
+}
+
 // ---- index body of one record (:711-738): 3 codes per window start, 0 = invalid --------------------
 __global__ void k_record_codes(Planes pl, CoderMasks m, uint64_t first_word, uint32_t len,
                                uint32_t* __restrict__ codes)
@@ -718,6 +725,13 @@ cudaError_t launch_intervals(const uint32_t* good, const uint32_t* g_word, const
 {
     if (!n_genomes) return cudaSuccess;
     k_intervals<<<grid_for((uint64_t)n_genomes * 32, 128), 128, 0, st>>>(good, g_word, g_len, n_genomes, genome_listed, results);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_add_ordinal(uint32_t* results, uint32_t n, uint32_t base, cudaStream_t st)
+{
+    if (!n || !base) return cudaSuccess;
+    k_add_ordinal<<<grid_for(n, 256), 256, 0, st>>>(results, n, base);
     return cudaGetLastError();
 }
 

@@ -42,7 +42,7 @@ ABI_SYMBOLS = (
     "eref_run_host", "eref_ref_records", "eref_index_body", "eref_query_census", "eref_query_census_device",
     "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
     "eref_table_export", "eref_table_set_part", "eref_table_set_peer", "eref_table_set_hook", "eref_table_part_range",
-    "eref_table_join", "eref_sync",
+    "eref_table_join", "eref_sync", "eref_run_results_device", "eref_run_host_keep",
 )
 
 
@@ -110,6 +110,8 @@ def load_library() -> ctypes.CDLL:
     lib.eref_table_part_range.argtypes = [c_void_p, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]
     lib.eref_table_join.argtypes = [c_void_p]
     lib.eref_sync.argtypes = [c_void_p]
+    lib.eref_run_results_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
+    lib.eref_run_host_keep.argtypes = [c_void_p, c_void_p, c_uint64, c_void_p, c_uint64]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
     lib.eref_format_line.argtypes = [c_void_p, ctypes.c_char_p, c_size_t]
     _lib = lib
@@ -271,6 +273,18 @@ class ErefGPU:
                                     byref(n))
         _check(self.lib, rc, "eref_run_host")
         return self._run_out[:min(n.value, cap)]
+
+    def run_results_device(self):
+        """the records of the last run_host, still in HBM: (device pointer to n x 4 uint32, n)"""
+        p, n = c_void_p(), c_size_t()
+        _check(self.lib, self.lib.eref_run_results_device(self._h, byref(p), byref(n)), "eref_run_results_device")
+        return p.value, n.value
+
+    def run_host_keep(self, keep1: np.ndarray, lines1: int, keep2: np.ndarray, lines2: int):
+        """down-sampling masks for the next run_host (drawn once for all GPUs that screen the same sample)"""
+        k1, k2 = np.ascontiguousarray(keep1, dtype="<u4"), np.ascontiguousarray(keep2, dtype="<u4")
+        _check(self.lib, self.lib.eref_run_host_keep(self._h, c_void_p(k1.ctypes.data), lines1, c_void_p(k2.ctypes.data),
+                                                     lines2), "eref_run_host_keep")
 
     def scan_device(self, wait: bool = True):
         """Results stay in HBM: (device pointer to n x 4 uint32, n).  wait=False: valid in stream order on the

@@ -70,15 +70,32 @@ def run_reference(fa: bytes, fai: str, names: str):
         return open(p["out.fa"]).read(), open(p["out.txt"]).read(), log.getvalue()
 
 
+def fixture_cases():
+    """the eref fixtures themselves: the REFERENCE eref's stdout (every threshold pair of <fixture>.json) through the
+    reference script, on the fixture's own FASTA — what `EREF_REFS_FASTA/EREF_REFS_PERCENT` of the drop-in must write.
+    The FASTA is not repeated in f1.json (it is tests/golden/<fixture>.fa.gz); the sequence file is pinned by sha256."""
+    for fixture in ("basic", "short_reads", "edge"):
+        fa = gzip.open(os.path.join(HERE, fixture + ".fa.gz"), "rb").read()
+        meta = json.load(open(os.path.join(HERE, fixture + ".json")))
+        for key, stdout in meta["stdout"].items():
+            yield fixture, key, fa, fai_of(fa), stdout
+
+
 def main():
+    import hashlib
     out = {}
     for name, fa, fai, names in cases():
         out_fa, out_txt, log = run_reference(fa, fai, names)
         out[name] = {"fasta": fa.decode("latin-1"), "fai": fai, "names": names,
                      "out_fasta": out_fa, "out_percent": out_txt, "log": log}
+    for fixture, key, fa, fai, names in fixture_cases():
+        out_fa, out_txt, log = run_reference(fa, fai, names)
+        out[f"fixture:{fixture}:{key}"] = {"fixture": fixture, "ratios": key, "names": names, "out_percent": out_txt,
+                                          "out_fasta_sha256": hashlib.sha256(out_fa.encode("latin-1")).hexdigest(),
+                                          "out_fasta_records": out_fa.count(">"), "log": log}
     json.dump(out, open(os.path.join(HERE, "f1.json"), "w"), indent=1)
     for k, v in out.items():
-        print(k, len(v["out_fasta"]), repr(v["out_percent"][:80]))
+        print(k, len(v.get("out_fasta", "")), v.get("out_fasta_records"), repr(v["out_percent"][:80]))
 
 
 if __name__ == "__main__":

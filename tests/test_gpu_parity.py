@@ -676,3 +676,68 @@ def test_sharded_table_completion_hook(golden):
     finally:
         for g in ctxs:
             g.close()
+
+
+# ---- SURVEY.md §8(f) row f1 fused into the executable ---------------------------------------------------------
+
+def _f1_fixture_cases():
+    import json
+    from tests.conftest import GOLDEN
+    golden = json.load(open(os.path.join(GOLDEN, "f1.json")))
+    return [(k, v) for k, v in golden.items() if "fixture" in v]
+
+
+@pytest.mark.parametrize("case", [k for k, _ in _f1_fixture_cases()])
+def test_eref_binary_writes_the_next_steps_outputs(case, tmp_path):
+    """EREF_REFS_FASTA / EREF_REFS_PERCENT: the drop-in writes phage_refs.fasta and {prefix}_ref_percent.txt itself;
+    expected = what the UNMODIFIED get_ref_by_index.py made of the REFERENCE eref's stdout on the same fixture
+    (tests/golden/f1.json, tests/golden/make_golden_f1.py), including the index drift past records of <= 32 bases"""
+    import hashlib
+    c = dict(_f1_fixture_cases())[case]
+    meta, fa, f1, f2 = load_golden(c["fixture"])
+    fa.tofile(tmp_path / "db.fa"); f1.tofile(tmp_path / "r1.fq"); f2.tofile(tmp_path / "r2.fq")
+    hdr = np.zeros(100, "<u4"); hdr[:96] = np.asarray(meta["coder"], np.uint32)
+    hdr.tofile(tmp_path / "db.fa.k32.index.dat")
+    hr, phr = c["ratios"].split(",")
+    env = dict(os.environ, EREF_GPUS="1", EREF_REFS_FASTA=str(tmp_path / "refs.fa"), EREF_REFS_PERCENT=str(tmp_path / "pct.txt"))
+    r = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "4"], cwd=tmp_path,
+                       capture_output=True, env=env)
+    assert r.returncode == 0, r.stderr.decode()
+    assert r.stdout.decode() == c["names"]
+    assert (tmp_path / "pct.txt").read_text() == c["out_percent"]
+    out_fa = (tmp_path / "refs.fa").read_bytes()
+    assert out_fa.count(b">") == c["out_fasta_records"]
+    assert hashlib.sha256(out_fa).hexdigest() == c["out_fasta_sha256"]
+
+
+def test_eref_binary_reads_bgzf_and_multi_member_gzip(golden, tmp_path):
+    """BGZF inputs (blocks inflated by several threads) and concatenated gzip members give the stdout of the plain files"""
+    import gzip
+    import struct
+    import zlib
+    name, meta, fa, f1, f2 = golden
+
+    def bgzf(data: bytes, block=30000) -> bytes:
+        out = []
+        for off in list(range(0, len(data), block)) + [len(data)]:      # the last (empty) block is BGZF's EOF marker
+            chunk = data[off:off + block] if off < len(data) else b""
+            co = zlib.compressobj(6, zlib.DEFLATED, -15)
+            body = co.compress(chunk) + co.flush()
+            bsize = len(body) + 25
+            out.append(b"\x1f\x8b\x08\x04\x00\x00\x00\x00\x00\xff\x06\x00BC\x02\x00" + struct.pack("<H", bsize) + body +
+                       struct.pack("<II", zlib.crc32(chunk), len(chunk)))
+        return b"".join(out)
+
+    raw1 = f1.tobytes()
+    (tmp_path / "db.fa.gz").write_bytes(bgzf(fa.tobytes()))
+    (tmp_path / "r1.fq.gz").write_bytes(gzip.compress(raw1[: len(raw1) // 3]) + gzip.compress(raw1[len(raw1) // 3:]))
+    (tmp_path / "r2.fq.gz").write_bytes(bgzf(f2.tobytes(), block=65000))
+    with open(tmp_path / "db.fa.gz.k32.coder", "w") as f:
+        f.write(" ".join(str(x) for x in meta["coder"]) + "\n")
+    key, expect = next(iter(meta["stdout"].items()))
+    hr, phr = key.split(",")
+    r = subprocess.run([eref.EREF_BIN, "r1.fq.gz", "r2.fq.gz", "db.fa.gz", "tmp_out.txt", hr, phr, "8"], cwd=tmp_path,
+                       capture_output=True, env=dict(os.environ, EREF_GPUS="1", EREF_TIMING="1"))
+    assert r.returncode == 0, r.stderr.decode()
+    assert r.stdout.decode() == expect
+    assert "inflated" in r.stderr.decode()

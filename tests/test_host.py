@@ -128,9 +128,23 @@ def test_get_ref_by_index_against_the_reference_script(tmp_path, capsys):
     from palace_b200 import get_ref_by_index as g
     golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "f1.json")))
     assert set(golden) >= {"hand", "missing", "edge", "empty_names"}
+    import gzip
+    import hashlib
     for name, c in golden.items():
-        d = tmp_path / name
+        d = tmp_path / name.replace(":", "_").replace(",", "_")
         d.mkdir()
+        if "fixture" in c:                                 # the eref fixtures: the reference eref's stdout on their FASTA
+            fa = gzip.open(os.path.join(os.path.dirname(__file__), "golden", c["fixture"] + ".fa.gz"), "rb").read()
+            (d / "db.fa").write_bytes(fa)
+            (d / "db.fa.fai").write_text("".join((l[1:].split()[0].decode() if l[1:].split() else "") + "\t0\t0\t0\t0\n"
+                                                 for l in fa.split(b"\n") if l.startswith(b">")))
+            (d / "names.txt").write_text(c["names"])
+            capsys.readouterr()
+            g.main(["x", str(d / "db.fa"), str(d / "db.fa.fai"), str(d / "names.txt"), str(d / "out.fa"), str(d / "out.txt")])
+            assert capsys.readouterr().out == c["log"], name
+            assert hashlib.sha256((d / "out.fa").read_bytes()).hexdigest() == c["out_fasta_sha256"], name
+            assert (d / "out.txt").read_text() == c["out_percent"], name
+            continue
         (d / "db.fa").write_bytes(c["fasta"].encode("latin-1"))
         (d / "db.fa.fai").write_text(c["fai"])
         (d / "names.txt").write_text(c["names"])
