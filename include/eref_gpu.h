@@ -29,12 +29,18 @@ extern "C" {
 #define EREF_ERR_STATE (-3)
 #define EREF_ERR_LIMIT (-4)            /* input beyond an implementation limit (e.g. FASTA shard >= 4 GiB) */
 #define EREF_ERR_UNSUPPORTED (-5)      /* reference behaviour not implemented yet: fails loudly */
+#define EREF_ERR_RETRY (-6)            /* eref_scan*: a query file outgrew buffers sized from its text length (its sequence
+                                          lines are longer than its quality lines); eref_query_reset, add the files again
+                                          — exact sizes are used from then on.  eref_run_host retries by itself. */
 
 /* eref_create flags */
 #define EREF_FLAG_NO_PRUNE 1u          /* probe all three streams at every position (no candidate filter) */
 #define EREF_FLAG_DIRECT_COUNT 2u      /* count k-mers straight into the table (no code-range partitioning) */
 #define EREF_FLAG_KEEP_RAND_STATE 4u   /* eref_run_host: do not srand(1) before the down-sampling draws (:1236-1238) */
 #define EREF_FLAG_LEVEL_POP 8u         /* count the codes at each level during every table build (eref_query_popcount) */
+#define EREF_FLAG_RESIDENT_TEXT 16u    /* texts handed to eref_ref_set_device are complete in device memory when the call is
+                                          made (not merely ordered on the context's stream): their framing may then start at
+                                          once, beside the query work still queued on the stream */
 
 typedef struct eref_ctx eref_ctx;
 

@@ -63,7 +63,7 @@ struct DevBuf {
 };
 
 enum Ev { E0 = 0, E1, E2, E3, E4, E5, E6, E7, E8, E9, E10, E11,
-          R1, R2, R3,                              // eref_ref_set: text landed, framed, packed (E0 = before the upload)
+          R1, R2, R3, R4,                          // eref_ref_set: text landed, framed (census stream), packed; R4 = packing starts (E0 = before the upload)
           S0, S1, S2, S3, S4, S5, S6, S7,          // scan: start, summary, sampled, need, probed, windows, records, copied out
           EV_COUNT };
 
@@ -96,7 +96,10 @@ struct eref_ctx {
     // Table build (table.cu): every file added since the last reset is kept as a slice-ordered code list (codes
     // radix-partitioned by their top 13 bits); a build counts all lists slice by slice in shared memory and
     // writes level 3 and its summary.  Levels 1/2 exist in HBM only for the direct build (EREF_FLAG_DIRECT_COUNT).
-    struct CodeList { DevBuf codes, off, cnt; unsigned long long total = 0; };
+    struct CodeList { DevBuf codes, off, cnt; unsigned long long total = 0; bool total_pending = false; };
+    bool retry_pending = false;
+    bool force_exact = false;                  // size the code buffers from the real count (one host wait per file)
+    uint32_t* guard = nullptr;                 // device word: a file's codes did not fit buffers sized before they were counted
     std::vector<CodeList> lists;
     size_t n_lists = 0;
     bool table_dirty = true;                   // files added / table reset since the last build
@@ -142,7 +145,13 @@ struct eref_ctx {
     // than they must, so the events of a call are read only after a later synchronisation covers them.
     std::vector<cudaEvent_t> qev;              // 4 events per query file since the last reset: start, packed, partitioned, end
     bool q_pending = false, ref_pending = false, scan_pending = false, scan_pending_d2h = false;
-    cudaEvent_t totals_ev = nullptr;           // eref_ref_set: the packed sizes have reached the host
+    cudaEvent_t totals_ev = nullptr;           // (unused since the framing census has a stream of its own)
+    // framing census of the reference text: own stream, ordered behind the text and behind the previous scan
+    cudaStream_t frame_stream = nullptr;
+    cudaEvent_t ev_scan_done = nullptr, ev_frame_done = nullptr, ev_text_free = nullptr;
+    bool scan_done_valid = false, text_free_valid = false;
+    bool text_is_resident = false;             // EREF_FLAG_RESIDENT_TEXT: device texts are complete when the call is made
+    DevBuf frame_cub_tmp;
 };
 
 namespace {
@@ -154,18 +163,22 @@ namespace {
     } while (0)
 
 int start_table_update(eref_ctx* c);
+int check_guard(eref_ctx* c);
 int wait_table(eref_ctx* c, cudaStream_t st);
 int join_table(eref_ctx* c, cudaStream_t st);
 // layout of part_ctr after the u64 arrays: u32 chunk_start[260], then u64 totals[3]
 inline unsigned long long* chunk_start_end(uint32_t* chunk_start) { return reinterpret_cast<unsigned long long*>(chunk_start + 260); }
 
+// (a scan owns its temporary storage while it runs: scans on different streams need different buffers)
 template <class T>
-int exclusive_scan(eref_ctx* c, const T* in, T* out, size_t n)
+int exclusive_scan(eref_ctx* c, const T* in, T* out, size_t n, cudaStream_t st = nullptr, DevBuf* tmp = nullptr)
 {
+    if (!st) st = c->stream;
+    if (!tmp) tmp = &c->cub_tmp;
     size_t bytes = 0;
-    CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, (int)n, c->stream));
-    CUDA_TRY(c->cub_tmp.ensure(bytes));
-    CUDA_TRY(cub::DeviceScan::ExclusiveSum(c->cub_tmp.p, bytes, in, out, (int)n, c->stream));
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, (int)n, st));
+    CUDA_TRY(tmp->ensure(bytes));
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(tmp->p, bytes, in, out, (int)n, st));
     return 0;
 }
 
@@ -187,6 +200,8 @@ cudaEvent_t* list_events(eref_ctx* c, size_t k)
 }
 
 constexpr int HPIN_SEQ = 32;                   // h_pin[HPIN_SEQ + k]: sequence-line bytes of query file k
+constexpr int HPIN_CODES = 48;                 // h_pin[HPIN_CODES + k]: codes of query file k
+constexpr int HPIN_GUARD = 14;                 // h_pin[HPIN_GUARD]: the capacity guard word, read back with the scan
 
 void table_done(eref_ctx* c);
 
@@ -201,6 +216,7 @@ void collect_times(eref_ctx* c)
         for (size_t k = 0; k < c->n_lists; k++) {
             cudaEvent_t* e = c->qev.data() + 4 * k;
             pack += ms(e[0], e[1]); bucket += ms(e[1], e[2]);
+            if (c->lists[k].total_pending) { c->lists[k].total = c->h_pin[HPIN_CODES + k]; c->lists[k].total_pending = false; }
             seq += c->h_pin[HPIN_SEQ + k]; codes += c->lists[k].total;
         }
         // sums over the files added since the last reset
@@ -210,11 +226,12 @@ void collect_times(eref_ctx* c)
     }
     if (c->ref_pending) {
         c->t.ref_h2d_ms = ms(c->ev[E0], c->ev[R1]);
-        c->t.ref_frame_ms = ms(c->ev[R1], c->ev[R2]);
-        c->t.ref_pack_ms = ms(c->ev[R2], c->ev[R3]);
+        c->t.ref_frame_ms = ms(c->ev[R1], c->ev[R2]);     // on the census stream, beside the query work
+        c->t.ref_pack_ms = ms(c->ev[R4], c->ev[R3]);
         c->ref_pending = false;
     }
     if (c->scan_pending) {
+        if (c->h_pin[HPIN_GUARD] & 0xFFFFFFFFull) c->retry_pending = true;
         table_done(c);
         c->t.scan_summary_ms = ms(c->ev[S0], c->ev[S1]);
         c->t.scan_sample_ms = ms(c->ev[S1], c->ev[S2]);
@@ -227,6 +244,19 @@ void collect_times(eref_ctx* c)
         c->t.ref_need_words = pruned ? c->h_pin[6] : c->ref_words;
         c->scan_pending = false;
     }
+}
+
+// after collect_times: did a query file outgrow buffers that were sized before its codes were counted?
+int check_guard(eref_ctx* c)
+{
+    if (!c->retry_pending) return 0;
+    c->retry_pending = false;
+    cudaMemsetAsync(c->guard, 0, 4, c->stream);
+    c->h_pin[HPIN_GUARD] = 0;
+    c->force_exact = true;
+    return eref_fail(EREF_ERR_RETRY, "a query file holds more sequence than quality bytes: its k-mers did not fit the "
+                                     "buffers sized from the text length; eref_query_reset and add the files again "
+                                     "(exact sizes are used from now on)");
 }
 
 // newline census of a text: tile_prefix[t] = newlines before tile t, tile_prefix[ntiles] = total
@@ -346,19 +376,44 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         if (c->lists.size() <= c->n_lists) c->lists.resize(c->n_lists + 1);
         eref_ctx::CodeList& L = c->lists[c->n_lists];
         CUDA_TRY(L.off.ensure(((size_t)NSLICES + 1) * 8)); CUDA_TRY(L.cnt.ensure((size_t)NSLICES * 8));
+        // Sizes.  The number of codes is known to the device only.  A FASTQ record spends as many bytes on its quality
+        // line as on its sequence line, so a file of n bytes holds fewer than n/2 sequence bytes and 3n/2 codes: when the
+        // buffers already hold that much (they only grow), everything is queued without asking — k_slice_offsets
+        // checks the real size against the capacity, and a file that breaks the rule (quality lines shorter than
+        // sequence lines) is reported at the next synchronisation and re-added with exact sizes.  Otherwise the host
+        // waits for the count once and sizes the buffers for the estimate, so the next file of this size goes through.
+        // (a sharded build keeps the codes of its slice range only; canonical codes thin out linearly towards the top
+        // of the code space, so the first of N parts is the fullest: 1 - (1 - 1/N)^2 of all codes)
+        const double part_frac = c->parts > 1 ? 1.1 * (2.0 * c->parts - 1.0) / ((double)c->parts * c->parts) : 1.0;
+        const unsigned long long est_codes = (unsigned long long)(3.0 * (double)(n / 2 + 1) * part_frac) + 4ull * NSLICES + 64;
+        const unsigned long long cap_codes = std::min(L.codes.cap, c->codes_coarse.cap) / 4 > 4
+                                                 ? std::min(L.codes.cap, c->codes_coarse.cap) / 4 - 4 : 0;
+        const bool optimistic = !c->force_exact && cap_codes >= est_codes;
         LAUNCH(c, launch_slice_offsets(hist, cbits, L.off.as<unsigned long long>(), L.cnt.as<unsigned long long>(), coarse_n,
-                                       chunk_start, totals, st));
-        CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, totals, 24, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaStreamSynchronize(st));
-        total_codes = c->h_pin[8];
-        const unsigned long long padded = c->h_pin[9];
-        const uint32_t nchunks = (uint32_t)c->h_pin[10];
-        pl.nwords = (c->h_pin[11] + 31) >> 5;
-        L.total = total_codes;
-        CUDA_TRY(L.codes.ensure((size_t)padded * 4 + 16));
-        CUDA_TRY(c->codes_coarse.ensure((size_t)padded * 4 + 16));
-        LAUNCH(c, launch_coarse_scatter(pl, c->masks, cbits, L.off.as<unsigned long long>(), coarse_tail,
-                                        c->codes_coarse.as<uint32_t>(), c->slice0, c->nslices, st));
+                                       chunk_start, totals, optimistic ? cap_codes : 0ull, optimistic ? c->guard : nullptr, st));
+        CUDA_TRY(cudaMemcpyAsync(c->h_pin + HPIN_CODES + c->n_lists, totals, 8, cudaMemcpyDeviceToHost, st));
+        uint32_t nchunks;
+        Planes pl_scatter = pl;
+        if (optimistic) {
+            pl_scatter.nwords = words_ub;                  // grid bound; the kernel reads the packed size itself
+            nchunks = (uint32_t)std::min<unsigned long long>(cap_codes / FINE_CHUNK + (1u << cbits) + 1, 0x7FFFFFFFull);
+            L.total = 0; L.total_pending = true;
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, totals, 24, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            total_codes = c->h_pin[8];
+            const unsigned long long padded = c->h_pin[9];
+            nchunks = (uint32_t)c->h_pin[10];
+            pl.nwords = (c->h_pin[11] + 31) >> 5;
+            pl_scatter = pl;
+            L.total = total_codes; L.total_pending = false;
+            const size_t want = (size_t)std::max<unsigned long long>(padded, c->force_exact ? 0ull : est_codes) * 4 + 16;
+            CUDA_TRY(L.codes.ensure(want));
+            CUDA_TRY(c->codes_coarse.ensure(want));
+        }
+        LAUNCH(c, launch_coarse_scatter(pl_scatter, optimistic ? plane_bits : nullptr, optimistic ? c->guard : nullptr, c->masks,
+                                        cbits, L.off.as<unsigned long long>(), coarse_tail, c->codes_coarse.as<uint32_t>(),
+                                        c->slice0, c->nslices, st));
         LAUNCH(c, launch_fine_partition(c->codes_coarse.as<uint32_t>(), L.off.as<unsigned long long>(), coarse_n, chunk_start,
                                         nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), st));
         // the partition kernels are queued; nothing below waits for them (times and byte counts: collect_times)
@@ -494,36 +549,53 @@ int finalize_table(eref_ctx* c)
 
 constexpr uint64_t REF_TEXT_LIMIT = 0xFFFFFF00ull;     // text offsets and plane positions of one shard are 32-bit
 
-int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
+// Framing and packing of one reference text.
+//
+// The framing census (per-tile summaries, their prefix, the record table) needs nothing from the query side, and the
+// host must read its totals to size the planes and the record arrays.  It therefore runs on a stream of its own
+// (frame_stream), ordered only behind (a) the text being there — `text_ready`, an event of whoever produced it, or
+// nothing for a text that is already complete in device memory — and (b) the previous scan, which still reads the
+// record tables this call overwrites.  While the host waits for the totals the main stream keeps working through
+// whatever was queued before (in a screening step: both FASTQ files), so the two host round trips cost no idle GPU
+// time; the main stream joins the census just before the packing kernel.
+int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n, cudaEvent_t text_ready, const void* host_text = nullptr)
 {
-    cudaStream_t st = c->stream;
+    cudaStream_t st = c->stream, fs = c->frame_stream;
     c->have_ref = false;
     if (n >= REF_TEXT_LIMIT)
         return eref_fail(EREF_ERR_LIMIT, "reference text of %llu bytes: one shard must stay below 4 GiB",
                          (unsigned long long)n);
     int trc = start_table_update(c);          // pending query files are counted while this text is framed and packed
     if (trc) return trc;
-    CUDA_TRY(cudaEventRecord(c->ev[R1], st));
+    if (c->scan_done_valid) CUDA_TRY(cudaStreamWaitEvent(fs, c->ev_scan_done, 0));
+    if (text_ready) CUDA_TRY(cudaStreamWaitEvent(fs, text_ready, 0));
+    CUDA_TRY(cudaEventRecord(c->ev[E0], fs));
+    if (host_text) {
+        // eref_ref_set: the upload rides on the census stream too (behind the last reader of the text buffer)
+        if (c->text_free_valid) CUDA_TRY(cudaStreamWaitEvent(fs, c->ev_text_free, 0));
+        if (n) CUDA_TRY(cudaMemcpyAsync(const_cast<uint8_t*>(text), host_text, n, cudaMemcpyHostToDevice, fs));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev[R1], fs));
     // 1. per-tile framing summaries and their prefix: line/header state, records and sequence bytes before each tile
     const uint64_t ntiles = (n + TILE_BYTES - 1) / TILE_BYTES;
     CUDA_TRY(c->tile_sum.ensure((ntiles + 1) * sizeof(TileSum)));
     CUDA_TRY(c->tile_pre.ensure((ntiles + 1) * sizeof(TileSum)));
     TileSum* tiles = c->tile_sum.as<TileSum>();
     TileSum* tile_pre = c->tile_pre.as<TileSum>();
-    CUDA_TRY(cudaMemsetAsync(tiles + ntiles, 0, sizeof(TileSum), st));          // sentinel: its prefix is the total
-    LAUNCH(c, launch_fasta_tiles(text, n, tiles, ntiles, st));
+    CUDA_TRY(cudaMemsetAsync(tiles + ntiles, 0, sizeof(TileSum), fs));          // sentinel: its prefix is the total
+    LAUNCH(c, launch_fasta_tiles(text, n, tiles, ntiles, fs));
     {
         size_t bytes = 0;
         const TileSum zero{0, 0, 0, 0};
-        CUDA_TRY(cub::DeviceScan::ExclusiveScan(nullptr, bytes, tiles, tile_pre, TileOp(), zero, (int)(ntiles + 1), st));
-        CUDA_TRY(c->cub_tmp.ensure(bytes));
-        CUDA_TRY(cub::DeviceScan::ExclusiveScan(c->cub_tmp.p, bytes, tiles, tile_pre, TileOp(), zero, (int)(ntiles + 1), st));
+        CUDA_TRY(cub::DeviceScan::ExclusiveScan(nullptr, bytes, tiles, tile_pre, TileOp(), zero, (int)(ntiles + 1), fs));
+        CUDA_TRY(c->frame_cub_tmp.ensure(bytes));
+        CUDA_TRY(cub::DeviceScan::ExclusiveScan(c->frame_cub_tmp.p, bytes, tiles, tile_pre, TileOp(), zero, (int)(ntiles + 1), fs));
         c->launches += 2;
     }
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 8, tile_pre + ntiles, sizeof(TileSum), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 16, tile_pre + ntiles, sizeof(TileSum), cudaMemcpyDeviceToHost, fs));
+    CUDA_TRY(cudaStreamSynchronize(fs));
     TileSum total;
-    memcpy(&total, c->h_pin + 8, sizeof total);
+    memcpy(&total, c->h_pin + 16, sizeof total);
     const uint32_t n_recs = total.hdrs + 1;               // record 0 = whatever precedes the first header
     const uint64_t total_seq = total.seqA + total.seqB;
     // 2. records: first sequence byte, header offset, length, keep flag, packed size
@@ -537,35 +609,40 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n)
     const size_t words_ub = (size_t)(total_seq / 32) + n_recs + 2;   // every kept record: (len>>5)+1 words
     CUDA_TRY(c->r_hi.ensure(words_ub * 4)); CUDA_TRY(c->r_lo.ensure(words_ub * 4));
     CUDA_TRY(c->r_ok.ensure(words_ub * 4)); CUDA_TRY(c->word_genome.ensure(words_ub * 4));
+    Planes pl;
+    pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
+    pl.nwords = 0;
+    // the planes are zeroed here, beside the query work (tiles OR their border words into them; pad words stay 0)
+    CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, fs));
+    CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, fs));
+    CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, fs));
     LAUNCH(c, launch_fasta_records(text, n, tiles, tile_pre, ntiles, c->rec_first.as<uint32_t>(),
-                                   c->rec_hdr_off.as<uint32_t>(), st));
+                                   c->rec_hdr_off.as<uint32_t>(), fs));
     unsigned long long* totals = c->counters.as<unsigned long long>() + 3;      // bases | genomes | words
-    CUDA_TRY(cudaMemsetAsync(totals, 0, 24, st));
+    CUDA_TRY(cudaMemsetAsync(totals, 0, 24, fs));
     LAUNCH(c, launch_record_info(c->rec_first.as<uint32_t>(), n_recs, total_seq, c->rec_len.as<uint32_t>(),
-                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(), totals, st));
-    int rc = exclusive_scan<uint32_t>(c, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(), rn);
+                                 c->rec_kept.as<uint32_t>(), c->rec_words.as<uint32_t>(), totals, fs));
+    int rc = exclusive_scan<uint32_t>(c, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(), rn, fs, &c->frame_cub_tmp);
     if (rc) return rc;
-    rc = exclusive_scan<uint32_t>(c, c->rec_words.as<uint32_t>(), c->rec_words_ex.as<uint32_t>(), rn);
+    rc = exclusive_scan<uint32_t>(c, c->rec_words.as<uint32_t>(), c->rec_words_ex.as<uint32_t>(), rn, fs, &c->frame_cub_tmp);
     if (rc) return rc;
     LAUNCH(c, launch_genome_table(c->rec_len.as<uint32_t>(), c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(),
                                   c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(), n_recs,
                                   c->g_rec.as<uint32_t>(), c->g_len.as<uint32_t>(), c->g_word.as<uint32_t>(),
-                                  c->g_first.as<uint32_t>(), c->word_genome.as<uint32_t>(), totals + 1, st));
-    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 2, totals, 24, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(c->totals_ev, st));
-    CUDA_TRY(cudaEventRecord(c->ev[R2], st));
-    // 3. text -> planes (OR-ed into zeroed planes: words on tile boundaries are shared by two CTAs)
-    Planes pl;
-    pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
-    pl.nwords = 0;
-    CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, st));
-    CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, st));
-    CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, st));
+                                  c->g_first.as<uint32_t>(), c->word_genome.as<uint32_t>(), totals + 1, fs));
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + 2, totals, 24, cudaMemcpyDeviceToHost, fs));
+    CUDA_TRY(cudaEventRecord(c->ev[R2], fs));
+    CUDA_TRY(cudaEventRecord(c->ev_frame_done, fs));
+    // 3. text -> planes, on the main stream once the census is there
+    CUDA_TRY(cudaStreamWaitEvent(st, c->ev_frame_done, 0));
+    CUDA_TRY(cudaEventRecord(c->ev[R4], st));
     LAUNCH(c, launch_pack_fasta(text, n, tile_pre, ntiles, c->rec_kept.as<uint32_t>(), c->rec_kept_ex.as<uint32_t>(),
                                 c->rec_words_ex.as<uint32_t>(), c->rec_first.as<uint32_t>(), pl,
                                 c->word_genome.as<uint32_t>(), st));
     CUDA_TRY(cudaEventRecord(c->ev[R3], st));
-    CUDA_TRY(cudaEventSynchronize(c->totals_ev));     // the sizes are here; the packing kernel is still running
+    CUDA_TRY(cudaEventRecord(c->ev_text_free, st));
+    c->text_free_valid = true;
+    CUDA_TRY(cudaStreamSynchronize(fs));      // the sizes are here; the main stream is still busy
     const uint64_t bases = c->h_pin[2];
     const uint32_t n_genomes = (uint32_t)c->h_pin[3], n_words = (uint32_t)c->h_pin[4];
     c->host_tables_valid = false;             // ordinal -> length / packed offset / header offset: fetched on demand
@@ -640,6 +717,17 @@ int scan_impl(eref_ctx* c)
     } else {
         CUDA_TRY(cudaEventRecord(c->ev[S2], st));
         CUDA_TRY(cudaEventRecord(c->ev[S3], st));
+        if (c->probe_parts > 1) {
+            // every word, the table walked one L2-sized part at a time like the listed scan
+            CUDA_TRY(c->hits0.ensure((nw + 64) * 4)); CUDA_TRY(c->hits1.ensure((nw + 64) * 4));
+            CUDA_TRY(c->hits2.ensure((nw + 64) * 4));
+            int extra = 0;
+            cudaError_t pe = launch_probe_parts(pl, c->masks, c->bm[2], nullptr, nullptr, c->probe_parts, c->hits0.as<uint32_t>(),
+                                                c->hits1.as<uint32_t>(), c->hits2.as<uint32_t>(), c->single.as<uint32_t>(),
+                                                c->trio.as<uint32_t>(), st, &extra);
+            if (pe != cudaSuccess) return eref_fail(EREF_ERR_CUDA, "probe parts: %s", cudaGetErrorString(pe));
+            c->launches += extra;
+        } else
         LAUNCH(c, launch_probe_full(pl, c->masks, c->bm[2], nullptr, c->single.as<uint32_t>(), c->trio.as<uint32_t>(), st));
         CUDA_TRY(cudaEventRecord(c->ev[S4], st));
         LAUNCH(c, launch_window(c->single.as<uint32_t>(), c->trio.as<uint32_t>(), c->word_genome.as<uint32_t>(),
@@ -650,6 +738,9 @@ int scan_impl(eref_ctx* c)
     LAUNCH(c, launch_intervals(c->good.as<uint32_t>(), c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(), G,
                                prune ? c->genome_listed.as<uint32_t>() : nullptr, c->results.as<uint32_t>(), st));
     CUDA_TRY(cudaEventRecord(c->ev[S6], st));
+    CUDA_TRY(cudaEventRecord(c->ev_scan_done, st));
+    c->scan_done_valid = true;
+    CUDA_TRY(cudaMemcpyAsync(c->h_pin + HPIN_GUARD, c->guard, 4, cudaMemcpyDeviceToHost, st));
     return 0;
 }
 
@@ -720,6 +811,10 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->table_ready, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->totals_ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->table_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->frame_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_scan_done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_frame_done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_text_free, cudaEventDisableTiming);
     if (const char* v = getenv("EREF_DOWN_SAMPLING_SIZE")) { long long k = atoll(v); if (k > 0) c->down_sampling_size = (uint64_t)k; }
     if (const char* v = getenv("EREF_PROBE_PARTS")) { int k = atoi(v); if (k == 1 || k == 2 || k == 4 || k == 8 || k == 16 || k == 32) c->probe_parts = k; }
     if (const char* v = getenv("EREF_BUCKET_BITS")) { int k = atoi(v); if (k >= 32 - SLICE_BITS - 8 && k <= 8) c->bucket_bits = k; }
@@ -730,9 +825,12 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = c->counters.ensure(64);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, (8 + MAX_BUCKETS) * 8, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->share_words, (MAX_PARTS + 2) * 4);
-    if (e == cudaSuccess) e = cudaMemset(c->share_words, 0, (MAX_PARTS + 2) * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->share_words, (MAX_PARTS + 4) * 4);
+    if (e == cudaSuccess) e = cudaMemset(c->share_words, 0, (MAX_PARTS + 4) * 4);
+    if (e == cudaSuccess) c->guard = c->share_words + MAX_PARTS + 2;
+    if (getenv("EREF_EXACT_SIZES")) c->force_exact = true;
     if (flags & EREF_FLAG_LEVEL_POP) c->want_pop = true;
+    if (flags & EREF_FLAG_RESIDENT_TEXT) c->text_is_resident = true;
     if (e != cudaSuccess) { eref_destroy(c); return eref_fail_cuda(e, "context allocation", __FILE__, __LINE__); }
     c->stream = c->own_stream;
     *out = c;
@@ -747,6 +845,9 @@ void eref_destroy(eref_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->table_stream) cudaStreamSynchronize(c->table_stream);
+    if (c->frame_stream) { cudaStreamSynchronize(c->frame_stream); cudaStreamDestroy(c->frame_stream); }
+    for (cudaEvent_t e : {c->ev_scan_done, c->ev_frame_done, c->ev_text_free}) if (e) cudaEventDestroy(e);
+    c->frame_cub_tmp.release();
     DevBuf* bufs[] = {&c->tile_counts, &c->tile_prefix, &c->cub_tmp, &c->counters, &c->tile_kept, &c->tile_kept_pre, &c->q_keep, &c->q_text, &c->q_hi, &c->q_lo,
                       &c->q_ok, &c->r_text, &c->tile_sum, &c->tile_pre, &c->rec_hdr_off, &c->rec_first,
                       &c->rec_len, &c->rec_kept, &c->rec_words, &c->rec_kept_ex, &c->rec_words_ex, &c->g_rec,
@@ -899,9 +1000,7 @@ int eref_ref_set(eref_ctx* c, const char* fasta_host, size_t n)
                          (unsigned long long)n);
     CUDA_TRY(cudaSetDevice(c->device));
     CUDA_TRY(c->r_text.ensure(n + 64));
-    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
-    if (n) CUDA_TRY(cudaMemcpyAsync(c->r_text.p, fasta_host, n, cudaMemcpyHostToDevice, c->stream));
-    return ref_set_impl(c, c->r_text.as<uint8_t>(), n);
+    return ref_set_impl(c, c->r_text.as<uint8_t>(), n, nullptr, fasta_host);
 }
 
 int eref_ref_set_device(eref_ctx* c, const void* fasta_dev, size_t n)
@@ -910,8 +1009,9 @@ int eref_ref_set_device(eref_ctx* c, const void* fasta_dev, size_t n)
     int rc = check_text_ptr(fasta_dev, n);
     if (rc) return rc;
     CUDA_TRY(cudaSetDevice(c->device));
-    CUDA_TRY(cudaEventRecord(c->ev[E0], c->stream));
-    return ref_set_impl(c, static_cast<const uint8_t*>(fasta_dev), n);
+    // whatever was queued on the context's stream before this call may have produced the text
+    CUDA_TRY(cudaEventRecord(c->aux_ev[1], c->stream));
+    return ref_set_impl(c, static_cast<const uint8_t*>(fasta_dev), n, c->text_is_resident ? nullptr : c->aux_ev[1]);
 }
 
 int eref_ref_count(eref_ctx* c, size_t* n_kept, size_t* n_records, uint64_t* kept_bases)
@@ -934,6 +1034,7 @@ static int finish_scan_sync(eref_ctx* c)
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->scan_pending = true; c->scan_pending_d2h = true;
     collect_times(c);
+    if (int grc = check_guard(c)) return grc;
     if (c->parts > 1 && (c->h_pin[7] >> 32)) {
         const unsigned who = (unsigned)(c->h_pin[7] >> 32) - 1;
         cudaMemsetAsync(c->share_words + MAX_PARTS + 1, 0, 4, c->stream);
@@ -978,8 +1079,21 @@ static int scan_append(eref_ctx* c, size_t* total)
  * is still in flight, and frames+scans every database piece as soon as its copy completes.  Pieces are
  * independent shards (a record's result depends only on its own bases, :846-896), so their records are
  * concatenated with ordinals continuing in file order.  Host buffers should be pinned for the overlap. */
+static int run_host_impl(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
+                         int chunks, eref_result* out, size_t cap, size_t* n_out);
+
 int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
                   int chunks, eref_result* out, size_t cap, size_t* n_out)
+{
+    int rc = run_host_impl(c, fq1, n1, fq2, n2, fasta, nf, chunks, out, cap, n_out);
+    // a query file outgrew buffers sized from its text length: once more with exact sizes (a sharded build cannot
+    // repeat on its own, the other GPUs would have to follow)
+    if (rc == EREF_ERR_RETRY && c->parts == 1) rc = run_host_impl(c, fq1, n1, fq2, n2, fasta, nf, chunks, out, cap, n_out);
+    return rc;
+}
+
+static int run_host_impl(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size_t n2, const char* fasta, size_t nf,
+                         int chunks, eref_result* out, size_t cap, size_t* n_out)
 {
     if (!c || (n1 && !fq1) || (n2 && !fq2) || (nf && !fasta) || (cap && !out))
         return eref_fail(EREF_ERR_ARG, "eref_run_host: null argument");
@@ -1109,9 +1223,7 @@ int eref_run_host(eref_ctx* c, const char* fq1, size_t n1, const char* fq2, size
         sum.ref_bases = c->t.ref_bases; sum.ref_words = c->t.ref_words; sum.ref_need_words = c->t.ref_need_words;
     }
     for (size_t k = 0; k < npieces && !resident; k++) {
-        CUDA_TRY(cudaStreamWaitEvent(st, c->copy_ev[2 + k], 0));
-        CUDA_TRY(cudaEventRecord(c->ev[E0], st));
-        rc = ref_set_impl(c, piece_dev[k], cut[k + 1] - cut[k]);
+        rc = ref_set_impl(c, piece_dev[k], cut[k + 1] - cut[k], c->copy_ev[2 + k]);
         if (rc) return rc;
         rc = scan_append(c, &total);
         if (rc) return rc;
@@ -1187,7 +1299,7 @@ int eref_scan_device(eref_ctx* c, const uint32_t** results_dev, size_t* n_out)
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     collect_times(c);
-    return 0;
+    return check_guard(c);
 }
 
 int eref_get_codes(eref_ctx* c, uint32_t ordinal, uint32_t* codes_host, size_t cap, size_t* n_out)
@@ -1330,7 +1442,7 @@ int eref_sync(eref_ctx* c)
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     if (c->table_inflight) { CUDA_TRY(cudaStreamSynchronize(c->table_stream)); table_done(c); }
     collect_times(c);
-    return 0;
+    return check_guard(c);
 }
 
 int eref_table_export(eref_ctx* c, void* ipc_handles, void** bm3_dev, void** summary_dev, void** flags_dev)
@@ -1439,7 +1551,7 @@ int eref_timings(eref_ctx* c, eref_phase_times* out)
     }
     *out = c->t;
     out->kernel_launches = c->launches;
-    return 0;
+    return check_guard(c);
 }
 
 int eref_format_line(const eref_result* r, char* buf, size_t cap)

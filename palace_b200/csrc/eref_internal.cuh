@@ -22,6 +22,7 @@ constexpr int      SLICE_BITS  = EREF_SLICE_BITS;    // a table slice = 2^SLICE_
 constexpr int      NSLICES     = 1 << (32 - SLICE_BITS);
 constexpr int      SLICE_WORDS = 1 << (SLICE_BITS - 5);
 constexpr uint32_t SLICE_MASK  = (1u << SLICE_BITS) - 1u;
+constexpr int      FINE_CHUNK  = 8192;               // codes a CTA of the fine partition sorts in shared memory
 constexpr int      MAX_LISTS   = 16;                 // query files counted by one table build
 constexpr int      SAMPLE_STRIDE_MIN = 4, SAMPLE_STRIDE_MAX = 8;   // candidate filter probes every s-th position
 constexpr int      SAMPLE_MIN_HITS = 6;              // smallest hit threshold worth a sparser sampling stride
@@ -155,13 +156,15 @@ cudaError_t launch_count_kmers(Planes pl, CoderMasks m, uint32_t* bm1, uint32_t*
 // s0/ns: the table slices whose codes are kept (all of them unless the build is sharded over GPUs)
 cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, CoderMasks m, unsigned long long* g_hist,
                               uint32_t s0, uint32_t ns, cudaStream_t st);
-cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
-                                  unsigned long long* g_tail, uint32_t* codes_out, uint32_t s0, uint32_t ns, cudaStream_t st);
+cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bits, const uint32_t* skip, CoderMasks m, int cbits,
+                                  const unsigned long long* slice_off, unsigned long long* g_tail, uint32_t* codes_out,
+                                  uint32_t s0, uint32_t ns, cudaStream_t st);
 cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
                                   const uint32_t* chunk_start, uint32_t nchunks, int cbits, unsigned long long* g_tail,
                                   uint32_t* out, cudaStream_t st);
 cudaError_t launch_slice_offsets(const unsigned long long* hist, int cbits, unsigned long long* off, unsigned long long* cnt,
-                                 unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals, cudaStream_t st);
+                                 unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals,
+                                 unsigned long long cap_codes, uint32_t* overflow, cudaStream_t st);
 // slice-ordered code lists of the files one table build counts: list l holds cnt[l][s] codes of slice s at
 // codes[l] + off[l][s] (16-byte aligned)
 struct CountLists {

@@ -9,6 +9,8 @@
 // (listed) words that can influence a window that still might be.  The selected records and their numbers are
 // unchanged; random-sector probes drop from 3 per base to 1/s per base plus 3 per base on candidate regions.
 #include "eref_internal.cuh"
+#include <algorithm>
+#include <cstdlib>
 
 namespace {
 
@@ -329,63 +331,87 @@ k_table_prefetch(const uint32_t* __restrict__ part, uint32_t lines)
         asm volatile("prefetch.global.L2 [%0];" :: "l"(part + (size_t)i * 32));
 }
 
-template <int LPW>
+// Which part does a code fall into?  The top bits of min(fwd, rc) are min(top bits of fwd, top bits of rc) (the smaller
+// number has the smaller-or-equal prefix), the top bit z of fwd is the alphabet bit of the window's base z, and the
+// top bit z of rc that of its base 31-z (complemented) — so for all 32 window starts of a word at once these are the
+// alphabet planes shifted by z and by 31-z.  part_mask returns the starts (bit 31-s) of stream i whose code's top LOG2P
+// bits equal `part`, at ~10 logic operations per bit instead of a full code per start: a round then forms only the
+// ~1/2^LOG2P of the codes it probes.
+template <int LOG2P>
+__device__ __forceinline__ uint32_t part_mask(const CoderMasks& m, int i, uint32_t hi0, uint32_t hi1, uint32_t lo0, uint32_t lo1,
+                                              uint32_t part)
+{
+    uint32_t f[LOG2P], r[LOG2P];
+#pragma unroll
+    for (int z = 0; z < LOG2P; z++) {
+        const uint32_t s0 = 0u - ((m.sel0[i] >> (31 - z)) & 1u), s2 = 0u - ((m.sel2[i] >> (31 - z)) & 1u);
+        const uint32_t H = window32(hi0, hi1, z), L = window32(lo0, lo1, z);
+        f[z] = bitsel(s2, ~L, bitsel(s0, ~(H ^ L), ~H));
+        const uint32_t Hr = window32(hi0, hi1, 31 - z), Lr = window32(lo0, lo1, 31 - z);
+        r[z] = bitsel(s2, Lr, bitsel(s0, ~(Hr ^ Lr), Hr));
+    }
+    // lt: fwd prefix < rc prefix, decided at the first differing bit from the top
+    uint32_t lt = 0, eq = 0xFFFFFFFFu;
+#pragma unroll
+    for (int z = 0; z < LOG2P; z++) {
+        lt |= eq & ~f[z] & r[z];
+        eq &= ~(f[z] ^ r[z]);
+    }
+    uint32_t in = 0xFFFFFFFFu;
+#pragma unroll
+    for (int z = 0; z < LOG2P; z++) {
+        const uint32_t mz = bitsel(lt, f[z], r[z]);
+        const uint32_t want = 0u - ((part >> (LOG2P - 1 - z)) & 1u);
+        in &= ~(mz ^ want);
+    }
+    return in;
+}
+
+// list == nullptr: every word of the planes (the unpruned scan), else the words k_need listed
+template <int LOG2P>
 __global__ void __launch_bounds__(256)
 k_probe_part(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const uint32_t* __restrict__ list,
-             const unsigned long long* __restrict__ n_list, uint32_t part, int part_shift, bool first, bool last,
+             const unsigned long long* __restrict__ n_list, uint32_t part, bool first, bool last,
              uint32_t* __restrict__ h0w, uint32_t* __restrict__ h1w, uint32_t* __restrict__ h2w,
              uint32_t* __restrict__ single, uint32_t* __restrict__ trio)
 {
-    constexpr int PER = 32 / LPW;
-    constexpr int EPW = 32 / LPW;
-    const unsigned long long n = *n_list;
-    const int lane = threadIdx.x & 31, q = lane & (LPW - 1);
-    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
-    for (unsigned long long base = warp * EPW; base < n; base += nwarps * EPW) {
-        const unsigned long long e = base + (lane / LPW);
-        uint32_t a0 = 0, a1 = 0, a2 = 0, w = 0;
-        if (e < n) {
-            w = list[e];
-            const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
-            const uint32_t mine = PER == 32 ? vm : (vm >> ((32 - PER - PER * q) & 31)) & ((1u << (PER & 31)) - 1u);
-            if (mine) {
-                const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
-                constexpr int BATCH = PER < 8 ? PER : 8;
+    const unsigned long long n = list ? *n_list : pl.nwords;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += stride) {
+        const uint64_t w = list ? list[e] : e;
+        uint32_t acc[3] = {0, 0, 0};
+        const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
+        if (vm) {
+            const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
 #pragma unroll
-                for (int s0 = 0; s0 < PER; s0 += BATCH) {
-                    uint32_t code[BATCH * 3];
+            for (int i = 0; i < 3; i++) {
+                uint32_t todo = vm & part_mask<LOG2P>(m, i, hi0, hi1, lo0, lo1, part);
+                while (todo) {                             // four probes in flight per pass
+                    uint32_t code[4];
+                    int pos[4];
 #pragma unroll
-                    for (int j = 0; j < BATCH; j++) {
-                        const int s = PER * q + s0 + j;
-                        WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
-                        const bool v = (vm >> (31 - s)) & 1u;
-#pragma unroll
-                        for (int i = 0; i < 3; i++) {
-                            const uint32_t c = stream_code(m, b, i);
-                            code[j * 3 + i] = (v && (c >> part_shift) == part) ? c : 0u;
+                    for (int q = 0; q < 4; q++) {
+                        code[q] = 0u; pos[q] = 0;
+                        if (todo) {
+                            const int s = __clz(todo);
+                            todo &= ~(0x80000000u >> s);
+                            const WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                            code[q] = stream_code(m, b, i);
+                            pos[q] = s;
                         }
                     }
+                    uint32_t hit[4];
 #pragma unroll
-                    for (int j = 0; j < BATCH; j++) {
-                        a0 |= probe(bm3, code[j * 3]) << (31 - PER * q - s0 - j);
-                        a1 |= probe(bm3, code[j * 3 + 1]) << (31 - PER * q - s0 - j);
-                        a2 |= probe(bm3, code[j * 3 + 2]) << (31 - PER * q - s0 - j);
-                    }
+                    for (int q = 0; q < 4; q++) hit[q] = probe(bm3, code[q]);
+#pragma unroll
+                    for (int q = 0; q < 4; q++) acc[i] |= hit[q] << (31 - pos[q]);
                 }
             }
         }
-#pragma unroll
-        for (int d = 1; d < LPW; d <<= 1) {
-            a0 |= __shfl_xor_sync(0xffffffffu, a0, d);
-            a1 |= __shfl_xor_sync(0xffffffffu, a1, d);
-            a2 |= __shfl_xor_sync(0xffffffffu, a2, d);
-        }
-        if (e < n && q == 0) {
-            if (!first) { a0 |= h0w[w]; a1 |= h1w[w]; a2 |= h2w[w]; }
-            if (last) { single[w] = a0 | a1 | a2; trio[w] = a0 & a1 & a2; }
-            else { h0w[w] = a0; h1w[w] = a1; h2w[w] = a2; }
-        }
+        uint32_t a0 = acc[0], a1 = acc[1], a2 = acc[2];
+        if (!first) { a0 |= h0w[w]; a1 |= h1w[w]; a2 |= h2w[w]; }
+        if (last) { single[w] = a0 | a1 | a2; trio[w] = a0 & a1 & a2; }
+        else { h0w[w] = a0; h1w[w] = a1; h2w[w] = a2; }
     }
 }
 
@@ -671,7 +697,6 @@ cudaError_t launch_probe_parts(Planes pl, CoderMasks m, const uint32_t* bm3, con
                                uint32_t* single, uint32_t* trio, cudaStream_t st, int* launches)
 {
     if (!pl.nwords) return cudaSuccess;
-    static int lpw = 1;                                  // lanes per word: 1 measured best once the table is walked in parts
     static int per_sm = 0, prefetch = 0;          // measured: the prefetch does not pay (0.52 ms with, 0.50 without)
     if (!per_sm) {
         const char* v = getenv("EREF_PROBE_CTAS");
@@ -679,22 +704,25 @@ cudaError_t launch_probe_parts(Planes pl, CoderMasks m, const uint32_t* bm3, con
         if (per_sm < 1 || per_sm > 64) per_sm = 16;
         v = getenv("EREF_PROBE_PREFETCH");
         if (v) prefetch = atoi(v);
-        v = getenv("EREF_PROBE_LPW");
-        if (v) lpw = atoi(v);
     }
     int log2p = 0;
     while ((1 << log2p) < parts) log2p++;
     const uint32_t part_words = TABLE_WORDS >> log2p;
+    // a listed scan is sized by the SMs (the list length lives on the device), an unpruned one by the words
+    const unsigned grid = list ? list_grid(per_sm) : (unsigned)std::min<uint64_t>((pl.nwords + 255) / 256, (uint64_t)list_grid(64));
     for (int r = 0; r < parts; r++) {
         if (prefetch) k_table_prefetch<<<list_grid(8), 256, 0, st>>>(bm3 + (size_t)r * part_words, part_words / 32);
-        const unsigned grid = list_grid(per_sm);
         const uint32_t part = (uint32_t)r;
-        const int shift = 32 - log2p;
         const bool first = r == 0, last = r == parts - 1;
-        if (lpw == 1) k_probe_part<1><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, shift, first, last, h0w, h1w, h2w, single, trio);
-        else if (lpw == 2) k_probe_part<2><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, shift, first, last, h0w, h1w, h2w, single, trio);
-        else k_probe_part<4><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, shift, first, last, h0w, h1w, h2w, single, trio);
-        if (launches) *launches += 2;
+        switch (log2p) {
+        case 1: k_probe_part<1><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, first, last, h0w, h1w, h2w, single, trio); break;
+        case 2: k_probe_part<2><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, first, last, h0w, h1w, h2w, single, trio); break;
+        case 3: k_probe_part<3><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, first, last, h0w, h1w, h2w, single, trio); break;
+        case 4: k_probe_part<4><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, first, last, h0w, h1w, h2w, single, trio); break;
+        case 5: k_probe_part<5><<<grid, 256, 0, st>>>(pl, m, bm3, list, n_list, part, first, last, h0w, h1w, h2w, single, trio); break;
+        default: return cudaErrorInvalidValue;
+        }
+        if (launches) *launches += 1 + (prefetch ? 1 : 0);
     }
     return cudaGetLastError();
 }

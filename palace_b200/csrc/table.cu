@@ -165,9 +165,14 @@ __device__ __forceinline__ void for_each_code_half(const Planes& pl, const Coder
 }
 
 __global__ void __launch_bounds__(CS_THREADS)
-k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
+k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_bits, const uint32_t* __restrict__ skip,
+                        CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
                         unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out, uint32_t s0, uint32_t ns)
 {
+    // plane_bits: the packed size, when the host has not seen it (the grid then covers an upper bound); skip: set by
+    // k_slice_offsets when the codes would not fit the buffers (api.cu: optimistic sizes)
+    const uint64_t nwords = plane_bits ? (*plane_bits + 31) >> 5 : pl.nwords;
+    if ((uint64_t)blockIdx.x * CS_WORDS >= nwords || (skip && *skip)) return;
     extern __shared__ uint32_t s_codes[];                  // CS_CODES
     __shared__ uint32_t s_cur[CS_THREADS / 32][MAX_BUCKETS];   // per warp: counts, then cursors into s_codes
     __shared__ uint32_t s_start[MAX_BUCKETS + 1];
@@ -179,7 +184,7 @@ k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long 
     __syncthreads();
     const uint64_t w = (uint64_t)blockIdx.x * CS_WORDS + (threadIdx.x >> 1);
     const int half = threadIdx.x & 1;
-    const bool live = w < pl.nwords;
+    const bool live = w < nwords;
     if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) { if ((code >> SLICE_BITS) - s0 < ns) atomicAdd(&s_cur[warp][code >> shift], 1u); });
     __syncthreads();
     // bucket totals -> exclusive prefix (nb <= 256: one bucket per thread), global reservation, per-warp cursors
@@ -223,14 +228,15 @@ k_coarse_scatter_staged(Planes pl, CoderMasks m, int shift, const unsigned long 
 // would queue behind the database upload): off[s] = start of slice s (padded to 4 codes so that every slice
 // starts 16-byte aligned), cnt = copy of the histogram, coarse_n[b] = codes of coarse bucket b,
 // chunk_start[b] = first fine-partition chunk of bucket b, totals = {codes, padded size, chunks}.
-constexpr int FINE_CHUNK = 8192;
 
 __global__ void __launch_bounds__(1024)
 k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned long long* __restrict__ off,
                 unsigned long long* __restrict__ cnt, unsigned long long* __restrict__ coarse_n,
-                uint32_t* __restrict__ chunk_start, unsigned long long* __restrict__ totals)
+                uint32_t* __restrict__ chunk_start, unsigned long long* __restrict__ totals,
+                unsigned long long cap_codes, uint32_t* __restrict__ overflow)
 {
     __shared__ unsigned long long s_warp[32];
+    __shared__ unsigned long long s_padded;
     __shared__ unsigned long long s_coarse[MAX_BUCKETS];
     constexpr int PER = NSLICES / 1024;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -247,7 +253,7 @@ k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned
     unsigned long long run = base + inc - sum;
 #pragma unroll
     for (int k = 0; k < PER; k++) { off[threadIdx.x * PER + k] = run; run += (v[k] + 3) & ~3ull; }
-    if (threadIdx.x == 1023) off[NSLICES] = run;
+    if (threadIdx.x == 1023) { off[NSLICES] = run; s_padded = run; }
     // codes per coarse bucket: a bucket's 2^fbits slices sit in 2^fbits / PER neighbouring threads (at most one warp for
     // cbits >= 32 - SLICE_BITS - 8), so it is a segmented shuffle sum of what the threads already hold
     const int fbits = 32 - SLICE_BITS - cbits, NC = 1 << cbits;
@@ -269,6 +275,10 @@ k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned
             chunks += (uint32_t)((s_coarse[b] + FINE_CHUNK - 1) / FINE_CHUNK);
             total += s_coarse[b];
         }
+        // cap_codes: what the code buffers hold when they were sized before this count was known; a file that needs
+        // more is not partitioned at all (no chunks, the scatter skips) and the host is told
+        const bool over = cap_codes && s_padded > cap_codes;
+        if (over) { chunks = 0; if (overflow) *overflow = 1u; }
         chunk_start[NC] = chunks;
         totals[0] = total; totals[2] = chunks;
     }
@@ -652,9 +662,11 @@ cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, C
     return cudaGetLastError();
 }
 
-cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsigned long long* slice_off,
-                                  unsigned long long* g_tail, uint32_t* codes_out, uint32_t s0, uint32_t ns, cudaStream_t st)
+cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bits, const uint32_t* skip, CoderMasks m, int cbits,
+                                  const unsigned long long* slice_off, unsigned long long* g_tail, uint32_t* codes_out,
+                                  uint32_t s0, uint32_t ns, cudaStream_t st)
 {
+    // pl.nwords: the exact word count, or (plane_bits given) an upper bound that sizes the grid
     if (!pl.nwords) return cudaSuccess;
     static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 1; }();
     if (staged) {
@@ -662,17 +674,19 @@ cudaError_t launch_coarse_scatter(Planes pl, CoderMasks m, int cbits, const unsi
         cudaError_t e = cudaFuncSetAttribute(k_coarse_scatter_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         k_coarse_scatter_staged<<<(unsigned)((pl.nwords + CS_WORDS - 1) / CS_WORDS), CS_THREADS, smem, st>>>(
-            pl, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
+            pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
     } else {
+        if (plane_bits) return cudaErrorNotSupported;     // the unstaged variant needs the exact size
         k_coarse_scatter<<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
     }
     return cudaGetLastError();
 }
 
 cudaError_t launch_slice_offsets(const unsigned long long* hist, int cbits, unsigned long long* off, unsigned long long* cnt,
-                                 unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals, cudaStream_t st)
+                                 unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals,
+                                 unsigned long long cap_codes, uint32_t* overflow, cudaStream_t st)
 {
-    k_slice_offsets<<<1, 1024, 0, st>>>(hist, cbits, off, cnt, coarse_n, chunk_start, totals);
+    k_slice_offsets<<<1, 1024, 0, st>>>(hist, cbits, off, cnt, coarse_n, chunk_start, totals, cap_codes, overflow);
     return cudaGetLastError();
 }
 

@@ -27,6 +27,7 @@ FLAG_NO_PRUNE = 1
 FLAG_DIRECT_COUNT = 2
 FLAG_KEEP_RAND_STATE = 4
 FLAG_LEVEL_POP = 8
+FLAG_RESIDENT_TEXT = 16
 TABLE_HANDLE_BYTES = 192
 TABLE_HOOK = ctypes.CFUNCTYPE(c_int, c_void_p, c_void_p)
 DOWN_SAMPLING_SIZE = 2_000_000_000                       # bin/extract_ref.cpp:1230
@@ -164,7 +165,7 @@ class ErefGPU:
     """One context = one GPU: the query table, one reference text (whole DB or one shard), the scan."""
 
     def __init__(self, coder, hit_ratio: float = 0.9, perfect_hit_ratio: float = 0.85, device: int = 0,
-                 prune: bool = True, bucketed: bool = True, level_pop: bool = False):
+                 prune: bool = True, bucketed: bool = True, level_pop: bool = False, resident_text: bool = False):
         self.lib = load_library()
         if self.lib.eref_device_count() <= 0:
             raise ErefError("no CUDA device visible; liberef_gpu.so has no CPU fallback")
@@ -175,7 +176,7 @@ class ErefGPU:
         rc = self.lib.eref_create(byref(self._h), device, c.ctypes.data_as(POINTER(c_int16)),
                                   c_float(hit_ratio), c_float(perfect_hit_ratio),
                                   (0 if prune else FLAG_NO_PRUNE) | (0 if bucketed else FLAG_DIRECT_COUNT) |
-                                  (FLAG_LEVEL_POP if level_pop else 0))
+                                  (FLAG_LEVEL_POP if level_pop else 0) | (FLAG_RESIDENT_TEXT if resident_text else 0))
         _check(self.lib, rc, "eref_create")
         self.device = device
         self._hook = None

@@ -741,3 +741,40 @@ def test_eref_binary_reads_bgzf_and_multi_member_gzip(golden, tmp_path):
     assert r.returncode == 0, r.stderr.decode()
     assert r.stdout.decode() == expect
     assert "inflated" in r.stderr.decode()
+
+
+def test_a_query_that_outgrows_the_optimistic_buffers_is_retried(oracle):
+    """the code buffers are sized from the text length (a FASTQ spends as many bytes on qualities as on bases) so that
+    nothing waits for the count; a file whose quality lines are shorter than its sequence lines breaks that rule: the
+    phase API reports EREF_ERR_RETRY once, the pipelined call retries by itself, and both then match the oracle"""
+    db, f1, f2, _ = _case(81, n_genomes=40, db_bp=800_000, q_bp=600_000)
+    coder = eref.random_coder(81)
+    # the same reads with one-character quality lines, repeated until the file is as long as the original: nearly
+    # twice the sequence bytes per text byte
+    def squeeze(fq, target):
+        lines = fq.tobytes().split(b"\n")
+        recs = [b"\n".join([lines[k], lines[k + 1], b"+", b"I"]) + b"\n" for k in range(0, len(lines) - 3, 4)]
+        out, size, k = [], 0, 0
+        while size < target:
+            out.append(recs[k % len(recs)]); size += len(out[-1]); k += 1
+        return np.frombuffer(b"".join(out), np.uint8)
+    s1, s2 = squeeze(f1, int(f1.size * 0.98)), squeeze(f2, int(f2.size * 0.98))
+    want = oracle.run(s1, s2, db.text, coder, 0.9, 0.85, threads=4)
+    with eref.ErefGPU(coder) as g:
+        g.query_add(f1); g.query_add(f2); g.ref_set(db.text); g.scan()     # sizes the buffers for files of this size
+        g.query_reset()
+        g.query_add(s1); g.query_add(s2)
+        try:
+            got = g.scan().copy()
+            retried = False
+        except eref.ErefError as e:
+            assert "(-6)" in str(e)
+            retried = True
+            g.query_reset(); g.query_add(s1); g.query_add(s2)
+            got = g.scan().copy()
+        assert (got == want).all()
+    with eref.ErefGPU(coder) as g:
+        g.run_host(f1, f2, db.text)
+        got = g.run_host(s1, s2, db.text).copy()
+        assert (got == want).all()
+    assert retried
