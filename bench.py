@@ -479,14 +479,34 @@ class Job:
                 c1.record(rig.stream)
                 rig.stream.synchronize()
             h2d_ms = c0.elapsed_time(c1)
+            # N > 1: the same copies with the ranks taking turns (every other GPU idle) — against the concurrent figure
+            # above this tells how much of an end-to-end slowdown is the host side of PCIe shared by the ranks
+            solo_ms = None
+            if rig.world > 1:
+                for r in range(rig.world):
+                    rig.barrier()
+                    if r == rig.rank:
+                        c0.record(rig.stream)
+                        for dst, src in zip(scratch, srcs):
+                            dst.copy_(src, non_blocking=True)
+                        c1.record(rig.stream)
+                        rig.stream.synchronize()
+                        solo_ms = c0.elapsed_time(c1)
+                rig.barrier()
             del scratch
         e2e_s = rig.reduce(e2e_s, "max")
+        h2d_ms = rig.reduce(h2d_ms, "max")
+        solo = None
+        if solo_ms is not None:
+            solo = {"h2d_solo_GBps_min": round(h2d_bytes / 1e6 / rig.reduce(solo_ms, "max"), 1),
+                    "h2d_concurrent_GBps_min": round(h2d_bytes / 1e6 / h2d_ms, 1),
+                    "note": "per-GPU host->device rate of this step's buffers: one rank at a time vs all ranks at once"}
         return {"value": round(self.total_bases / 1e9 / (e2e_s / steps), 3), "unit": UNIT,
                 "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(self.info["n_records"]) * 16 + 24,
                 "ms_per_step": round(e2e_s / steps * 1e3, 3),
                 "api": f"eref_run_host(chunks={rig.args.chunks}): pinned host buffers, H2D overlapped with kernels" +
                        ("" if rig.world == 1 else "; each rank uploads 1/N of the query text, NCCL all-gathers it over NVLink"),
-                "h2d_alone_ms": round(h2d_ms, 3), "h2d_alone_GBps": round(h2d_bytes / 1e6 / h2d_ms, 1)}
+                "h2d_alone_ms": round(h2d_ms, 3), "h2d_alone_GBps": round(h2d_bytes / 1e6 / h2d_ms, 1), "h2d_sharing": solo}
 
     def time_resident(self, steps):
         """NOT headline numbers: the same sample against a database whose planes stay in HBM (eref_ref_set once)"""

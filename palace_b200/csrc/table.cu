@@ -267,6 +267,14 @@ k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned
         s_coarse[threadIdx.x / tpb] = raw;
     }
     __syncthreads();
+    // cap_codes: what the code buffers hold when they were sized before this count was known.  A file that needs more
+    // (or follows one that did) is not partitioned at all — no chunks, the scatter skips, its slices count as empty —
+    // and the host is told.
+    const bool over = cap_codes && (s_padded > cap_codes || (overflow && *overflow));
+    if (over) {
+#pragma unroll
+        for (int k = 0; k < PER; k++) cnt[threadIdx.x * PER + k] = 0;
+    }
     if (threadIdx.x == 0) {
         unsigned long long total = 0;
         uint32_t chunks = 0;
@@ -275,9 +283,6 @@ k_slice_offsets(const unsigned long long* __restrict__ hist, int cbits, unsigned
             chunks += (uint32_t)((s_coarse[b] + FINE_CHUNK - 1) / FINE_CHUNK);
             total += s_coarse[b];
         }
-        // cap_codes: what the code buffers hold when they were sized before this count was known; a file that needs
-        // more is not partitioned at all (no chunks, the scatter skips) and the host is told
-        const bool over = cap_codes && s_padded > cap_codes;
         if (over) { chunks = 0; if (overflow) *overflow = 1u; }
         chunk_start[NC] = chunks;
         totals[0] = total; totals[2] = chunks;
