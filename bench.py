@@ -357,6 +357,7 @@ class Job:
         torch = rig.torch
         self.rig, self.label, self.shard_bases = rig, label, shard_bases
         self.info = {}
+        rig.barrier()                                      # no rank starts a job's table builds while another still scans
         with torch.cuda.stream(rig.stream):
             self.fa_h = torch.from_numpy(fa_np).pin_memory()
             self.fa_d = self.fa_h.to(rig.dev, non_blocking=True)
@@ -421,8 +422,8 @@ class Job:
         if rig.world > 1:
             q1, q2 = self.gathered_query()
             rec = rig.g.run_host(q1, q2, self.fa_h.numpy(), chunks=rig.args.chunks, cap=self.host_cap)
-            t = rig.torch.from_numpy(rec.view(np.uint32).reshape(-1, 4).astype(np.int32)).to(rig.dev)
-            merged = allgather_records(t, rec.size, self.info.get("slot"))
+            ptr, n = rig.g.run_results_device()            # the records are still in HBM: all-gather them from there
+            merged = allgather_records(rig.device_records(ptr, n), n, self.info.get("slot"))
             self.last_host_records = rec
             return merged.cpu() if rig.rank == 0 else None
         rec = rig.g.run_host(self.f1_h.numpy(), self.f2_h.numpy(), self.fa_h.numpy(), chunks=rig.args.chunks, cap=self.host_cap)

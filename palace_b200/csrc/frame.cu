@@ -98,7 +98,8 @@ __device__ __forceinline__ uint32_t chunk_newlines(const uint32_t w[8])
 }
 
 // positions [0, k) of a chunk as a mask (k in 0..32)
-__device__ __forceinline__ uint32_t before(int k) { return k >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> k); }
+// (one clamped funnel shift: the low word of (0xFFFFFFFF:0) >> min(k, 32))
+__device__ __forceinline__ uint32_t before(int k) { return __funnelshift_rc(0u, 0xFFFFFFFFu, k); }
 
 __device__ __forceinline__ uint32_t count_nl(const uint32_t w[8])
 {
@@ -286,8 +287,12 @@ __global__ void __launch_bounds__(TILE_THREADS)
 k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __restrict__ tile_prefix,
              const uint32_t* __restrict__ keep, const unsigned long long* __restrict__ tile_kept_pre, Planes pl)
 {
-    __shared__ uint32_t s_hi[RING], s_lo[RING], s_ok[RING];
-    for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; }
+    __shared__ __align__(16) uint32_t s_hi[RING], s_lo[RING], s_ok[RING];
+    {
+        const uint2 z = make_uint2(0u, 0u);
+        reinterpret_cast<uint2*>(s_hi)[threadIdx.x] = z; reinterpret_cast<uint2*>(s_lo)[threadIdx.x] = z;
+        reinterpret_cast<uint2*>(s_ok)[threadIdx.x] = z;
+    }
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     uint32_t w[8];
     load32(text, n, off, w);
@@ -537,8 +542,13 @@ k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __rest
              const uint32_t* __restrict__ rec_words_ex, const uint32_t* __restrict__ rec_first,
              Planes pl, uint32_t* __restrict__ word_genome)
 {
-    __shared__ uint32_t s_hi[RING], s_lo[RING], s_ok[RING], s_g[RING];
-    for (int i = threadIdx.x; i < RING; i += TILE_THREADS) { s_hi[i] = 0; s_lo[i] = 0; s_ok[i] = 0; s_g[i] = 0xFFFFFFFFu; }
+    __shared__ __align__(16) uint32_t s_hi[RING], s_lo[RING], s_ok[RING], s_g[RING];
+    static_assert(RING == 2 * TILE_THREADS, "two words of each ring array per thread");
+    {   // clear the ring with 8-byte stores: one per thread and array
+        const uint2 z = make_uint2(0u, 0u), f = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+        reinterpret_cast<uint2*>(s_hi)[threadIdx.x] = z; reinterpret_cast<uint2*>(s_lo)[threadIdx.x] = z;
+        reinterpret_cast<uint2*>(s_ok)[threadIdx.x] = z; reinterpret_cast<uint2*>(s_g)[threadIdx.x] = f;
+    }
     const uint64_t off = (uint64_t)blockIdx.x * TILE_BYTES + (uint64_t)threadIdx.x * 32;
     const FastaChunk c = fasta_chunk<true>(text, n, off);
     const Incoming in = incoming(c, tile_pre[blockIdx.x]);         // (syncs: the ring is zeroed)

@@ -49,6 +49,9 @@ def run(log, title, cmd, cwd, env=None, expect=None, timeout=900):
     log.write(f"## {title}\n$ {' '.join(cmd)}\nrc={rc} wall={dt:.1f}s" + ("" if same is None else f" stdout_identical_to_golden={same}") + "\n")
     for l in tail:
         log.write("  " + l.strip() + "\n")
+    if rc != 0 and not tail:
+        for l in (se + so).splitlines()[-8:]:
+            log.write("  | " + l.rstrip() + "\n")
     log.write("\n")
     log.flush()
     print(title, "rc", rc, f"{dt:.0f}s", tail[-1] if tail else "")
