@@ -295,22 +295,23 @@ class Rig:
                         f"GPU's table through CUDA-IPC peer pointers (NVLink), device-side flags")
             if self.args.table == "peer":
                 raise SystemExit("--table peer: peer pointers unavailable")
-        # hook: in-place NCCL all-gather of the level-3 part and its summary on the library's stream
-        if world & (world - 1):
-            g.table_set_part(0, 1)
-            return "replicated: every GPU counts the whole table (the all-gather fallback needs a power-of-two N)"
+        # hook: one NCCL broadcast per part of the level-3 table and its summary on the library's stream (the parts
+        # are not of equal size, so this is not an all-gather in place)
         g.table_set_part(rank, world)                      # (also drops half-wired peers)
         _, bm3, summ, _ = g.table_export()
-        toff, tbytes, soff, sbytes = g.table_part_range()
-        full_t, full_s = self.view(bm3, tbytes * world), self.view(summ, sbytes * world)
-        part_t, part_s = full_t[toff: toff + tbytes], full_s[soff: soff + sbytes]
+        ranges = [g.table_part_range(p) for p in range(world)]
+        full_t = self.view(bm3, 1 << 29)
+        full_s = self.view(summ, 1 << 25)
+        parts_t = [full_t[o: o + nb] for o, nb, _, _ in ranges]
+        parts_s = [full_s[o: o + nb] for _, _, o, nb in ranges]
 
         def hook(_stream):
-            self.dist.all_gather_into_tensor(full_t, part_t)
-            self.dist.all_gather_into_tensor(full_s, part_s)
+            for p in range(world):
+                self.dist.broadcast(parts_t[p], src=p)
+                self.dist.broadcast(parts_s[p], src=p)
         g.table_set_hook(hook)
-        return (f"sharded x{world}: each GPU counts 1/{world} of the table slices, two in-place NCCL all-gathers "
-                f"({tbytes >> 20} + {sbytes >> 20} MiB per GPU) complete the tables")
+        return (f"sharded x{world}: each GPU counts its part of the table slices, one NCCL broadcast per part "
+                f"(512 + 32 MiB in all) completes the tables")
 
     def full_ctx(self):
         if self.g_full is None:

@@ -153,14 +153,14 @@ int  eref_index_body(eref_ctx* ctx, uint32_t first, uint32_t* out_host, size_t c
 /* Sharded table build.  The reference shares ONE table among its scan threads (:1257-1291 build it, :1309-1329 read
  * it); with the database sharded over GPUs every GPU needs the whole table, but the saturating count of a code does
  * not depend on any other code (:995-997), so GPU `part` of `parts` counts only the table slices
- * [8192*part/parts, 8192*(part+1)/parts) and the finished level-3 slices are exchanged instead of every GPU counting
- * everything.  Two ways to complete the tables:
+ * of its part (a contiguous range; the cut points balance code mass against the per-slice cost, eref_table_part_range)
+ * and the finished level-3 slices are exchanged instead of every GPU counting everything.  Two ways to complete the tables:
  *   peers  eref_table_export on every context, eref_table_set_peer for every other part: the counting kernel stores
  *          each finished slice into every GPU's table through peer pointers (NVLink) and raises a flag there; the
  *          scan waits for all flags on the device.  ipc_handles (EREF_TABLE_HANDLE_BYTES, from the peer's
  *          eref_table_export) for a context in another process, or its raw device pointers + device id in the same one.
  *   hook   eref_table_set_hook: called on the context's stream once the local part is complete and before the first
- *          probe; the callee completes the table there (e.g. NCCL all-gather in place over eref_table_part_range).
+ *          probe; the callee completes the table there (e.g. one NCCL broadcast per part over eref_table_part_range).
  * Every GPU of a build must make the same sequence of calls, and a collective or barrier ordered on the streams must
  * separate a scan from the NEXT table build (the all-gather of the result records is one): a builder writes into
  * its peers' tables.  eref_query_popcount then reports this part's codes only. */
@@ -171,7 +171,9 @@ int  eref_table_set_part(eref_ctx* ctx, int part, int parts);
 int  eref_table_set_peer(eref_ctx* ctx, int peer_part, int peer_device, const void* ipc_handles, void* bm3_dev,
                          void* summary_dev, void* flags_dev);
 int  eref_table_set_hook(eref_ctx* ctx, eref_table_hook fn, void* arg);
-int  eref_table_part_range(eref_ctx* ctx, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes);
+/* byte ranges of part `part` (-1: this context's own) inside the level-3 table and its summary.  The parts are NOT of
+ * equal size: canonical codes thin out towards the top of the code space, so the cut points balance the GPUs' work. */
+int  eref_table_part_range(eref_ctx* ctx, int part, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes);
 /* queue the build of the files added so far and make the context's stream wait for the complete table */
 int  eref_table_join(eref_ctx* ctx);
 /* wait for everything queued on the context */

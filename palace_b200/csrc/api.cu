@@ -3,6 +3,7 @@
 // touches sequence data is hand-written in frame.cu / table.cu / scan.cu.
 #include "eref_internal.cuh"
 #include <cub/device/device_scan.cuh>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -346,7 +347,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     const uint64_t words_ub = (n + 31) / 32 + 2;
     CUDA_TRY(c->q_hi.ensure(words_ub * 4)); CUDA_TRY(c->q_lo.ensure(words_ub * 4)); CUDA_TRY(c->q_ok.ensure(words_ub * 4));
     pl.hi = c->q_hi.as<uint32_t>(); pl.lo = c->q_lo.as<uint32_t>(); pl.ok = c->q_ok.as<uint32_t>();
-    pl.nwords = 0;
+    pl.nwords = 0; pl.cap = words_ub;
     CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, st));           // tiles OR their boundary words in; pad words stay 0
     CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, st));
     CUDA_TRY(cudaMemsetAsync(pl.ok, 0, words_ub * 4, st));
@@ -383,8 +384,9 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         // sequence lines) is reported at the next synchronisation and re-added with exact sizes.  Otherwise the host
         // waits for the count once and sizes the buffers for the estimate, so the next file of this size goes through.
         // (a sharded build keeps the codes of its slice range only; canonical codes thin out linearly towards the top
-        // of the code space, so the first of N parts is the fullest: 1 - (1 - 1/N)^2 of all codes)
-        const double part_frac = c->parts > 1 ? 1.1 * (2.0 * c->parts - 1.0) / ((double)c->parts * c->parts) : 1.0;
+        // of the code space: the range [x0, x1) of it holds (1 - x0)^2 - (1 - x1)^2 of all codes)
+        const double x0 = (double)c->slice0 / NSLICES, x1 = (double)(c->slice0 + c->nslices) / NSLICES;
+        const double part_frac = c->parts > 1 ? std::min(1.0, 1.15 * ((1 - x0) * (1 - x0) - (1 - x1) * (1 - x1))) : 1.0;
         const unsigned long long est_codes = (unsigned long long)(3.0 * (double)(n / 2 + 1) * part_frac) + 4ull * NSLICES + 64;
         const unsigned long long cap_codes = std::min(L.codes.cap, c->codes_coarse.cap) / 4 > 4
                                                  ? std::min(L.codes.cap, c->codes_coarse.cap) / 4 - 4 : 0;
@@ -413,9 +415,9 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         }
         LAUNCH(c, launch_coarse_scatter(pl_scatter, optimistic ? plane_bits : nullptr, optimistic ? c->guard : nullptr, c->masks,
                                         cbits, L.off.as<unsigned long long>(), coarse_tail, c->codes_coarse.as<uint32_t>(),
-                                        c->slice0, c->nslices, st));
+                                        c->codes_coarse.cap / 4, c->slice0, c->nslices, st));
         LAUNCH(c, launch_fine_partition(c->codes_coarse.as<uint32_t>(), L.off.as<unsigned long long>(), coarse_n, chunk_start,
-                                        nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), st));
+                                        nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), L.codes.cap / 4, st));
         // the partition kernels are queued; nothing below waits for them (times and byte counts: collect_times)
         CUDA_TRY(cudaEventRecord(qe[2], st));
         CUDA_TRY(cudaMemcpyAsync(c->h_pin + HPIN_SEQ + c->n_lists, seq_bytes, 8, cudaMemcpyDeviceToHost, st));
@@ -466,6 +468,7 @@ int start_table_update(eref_ctx* c)
         cl.codes[k] = c->lists[k].codes.as<uint32_t>();
         cl.off[k] = c->lists[k].off.as<unsigned long long>();
         cl.cnt[k] = c->lists[k].cnt.as<unsigned long long>();
+        cl.cap[k] = c->lists[k].codes.cap / 4;
     }
     if (c->want_pop) CUDA_TRY(cudaMemsetAsync(c->level_pop.p, 0, 24, ts));
     // destinations of the finished slices: this GPU's table, and in a sharded build with peers every other GPU's
@@ -611,7 +614,7 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n, cudaEvent_t text_
     CUDA_TRY(c->r_ok.ensure(words_ub * 4)); CUDA_TRY(c->word_genome.ensure(words_ub * 4));
     Planes pl;
     pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
-    pl.nwords = 0;
+    pl.nwords = 0; pl.cap = words_ub;
     // the planes are zeroed here, beside the query work (tiles OR their border words into them; pad words stay 0)
     CUDA_TRY(cudaMemsetAsync(pl.hi, 0, words_ub * 4, fs));
     CUDA_TRY(cudaMemsetAsync(pl.lo, 0, words_ub * 4, fs));
@@ -668,7 +671,7 @@ int scan_impl(eref_ctx* c)
     const uint32_t G = c->n_genomes;
     Planes pl;
     pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
-    pl.nwords = nw;
+    pl.nwords = nw; pl.cap = c->r_hi.cap / 4;
     CUDA_TRY(c->single.ensure((nw + 64) * 4)); CUDA_TRY(c->trio.ensure((nw + 64) * 4));
     CUDA_TRY(c->good.ensure((nw + 64) * 4));
     CUDA_TRY(c->results.ensure(((size_t)G + 1) * 16));
@@ -1317,7 +1320,7 @@ int eref_get_codes(eref_ctx* c, uint32_t ordinal, uint32_t* codes_host, size_t c
     CUDA_TRY(c->codes_tmp.ensure(n * 4));
     Planes pl;
     pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
-    pl.nwords = c->ref_words;
+    pl.nwords = c->ref_words; pl.cap = c->r_hi.cap / 4;
     LAUNCH(c, launch_record_codes(pl, c->masks, c->h_g_word[ordinal - 1], len, c->codes_tmp.as<uint32_t>(), c->stream));
     CUDA_TRY(cudaMemcpyAsync(codes_host, c->codes_tmp.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -1397,7 +1400,7 @@ int eref_index_body(eref_ctx* c, uint32_t first, uint32_t* out_host, size_t cap_
         CUDA_TRY(c->codes_tmp.ensure(words * 4));
         Planes pl;
         pl.hi = c->r_hi.as<uint32_t>(); pl.lo = c->r_lo.as<uint32_t>(); pl.ok = c->r_ok.as<uint32_t>();
-        pl.nwords = c->ref_words;
+        pl.nwords = c->ref_words; pl.cap = c->r_hi.cap / 4;
         LAUNCH(c, launch_index_body(pl, c->masks, c->g_word.as<uint32_t>(), c->g_len.as<uint32_t>(),
                                     c->cell_pre.as<unsigned long long>(), g0, g1, c->h_cell_pre[g1] - c->h_cell_pre[g0],
                                     c->codes_tmp.as<uint32_t>(), c->stream));
@@ -1464,6 +1467,23 @@ int eref_table_export(eref_ctx* c, void* ipc_handles, void** bm3_dev, void** sum
     return 0;
 }
 
+// First table slice of part p of `parts`.  Canonical codes are min(fwd, rc): their density falls linearly, 2(1 - x), over
+// the code space, so equal slice ranges would give the first GPU of two 75 % of the codes.  A part's cost is its codes
+// (partition + atomics) plus a fixed cost per slice (clearing and writing out 2^19 slots): the cut points equalise
+// w * mass + (1 - w) * width, w = 0.7 (EREF_PART_WEIGHT; 0 = equal widths).
+static uint32_t part_first_slice(int p, int parts)
+{
+    if (p <= 0) return 0;
+    if (p >= parts) return NSLICES;
+    static const double w = [] { const char* v = getenv("EREF_PART_WEIGHT"); double k = v ? atof(v) : 0.7; return k < 0 ? 0.0 : (k > 0.95 ? 0.95 : k); }();
+    const double t = (double)p / parts;
+    const double x = w > 1e-6 ? ((1 + w) - sqrt((1 + w) * (1 + w) - 4 * w * t)) / (2 * w) : t;
+    long long sl = llround(x * NSLICES);
+    if (sl < p) sl = p;
+    if (sl > NSLICES - (parts - p)) sl = NSLICES - (parts - p);
+    return (uint32_t)sl;
+}
+
 int eref_table_set_part(eref_ctx* c, int part, int parts)
 {
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
@@ -1475,8 +1495,12 @@ int eref_table_set_part(eref_ctx* c, int part, int parts)
     int rc = eref_sync(c);
     if (rc) return rc;
     c->parts = parts; c->part = part;
-    c->slice0 = (uint32_t)((uint64_t)NSLICES * part / parts);
-    c->nslices = (uint32_t)((uint64_t)NSLICES * (part + 1) / parts) - c->slice0;
+    c->slice0 = part_first_slice(part, parts);
+    c->nslices = part_first_slice(part + 1, parts) - c->slice0;
+    for (int p = 0; p < MAX_PARTS; p++) {           // peers are set after the part (a new layout drops the old wiring)
+        if (c->peers[p].ipc) { cudaIpcCloseMemHandle(c->peers[p].bm3); cudaIpcCloseMemHandle(c->peers[p].summary); cudaIpcCloseMemHandle(c->peers[p].flags); }
+        c->peers[p] = eref_ctx::Peer();
+    }
     c->table_dirty = true; c->join_pending = false;
     c->n_lists = 0;                             // code lists hold only the codes of the part they were made for
     return 0;
@@ -1522,13 +1546,16 @@ int eref_table_set_hook(eref_ctx* c, eref_table_hook fn, void* arg)
     return 0;
 }
 
-int eref_table_part_range(eref_ctx* c, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes)
+int eref_table_part_range(eref_ctx* c, int part, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes)
 {
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
-    if (table_off) *table_off = (size_t)c->slice0 * SLICE_WORDS * 4;
-    if (table_bytes) *table_bytes = (size_t)c->nslices * SLICE_WORDS * 4;
-    if (summary_off) *summary_off = (size_t)c->slice0 * (SLICE_WORDS / 16) * 4;
-    if (summary_bytes) *summary_bytes = (size_t)c->nslices * (SLICE_WORDS / 16) * 4;
+    if (part >= c->parts) return eref_fail(EREF_ERR_ARG, "part %d of %d", part, c->parts);
+    const uint32_t s0 = part < 0 ? c->slice0 : part_first_slice(part, c->parts);
+    const uint32_t ns = part < 0 ? c->nslices : part_first_slice(part + 1, c->parts) - s0;
+    if (table_off) *table_off = (size_t)s0 * SLICE_WORDS * 4;
+    if (table_bytes) *table_bytes = (size_t)ns * SLICE_WORDS * 4;
+    if (summary_off) *summary_off = (size_t)s0 * (SLICE_WORDS / 16) * 4;
+    if (summary_bytes) *summary_bytes = (size_t)ns * (SLICE_WORDS / 16) * 4;
     return 0;
 }
 

@@ -5,6 +5,18 @@
 #include <stddef.h>
 #include "../../include/eref_gpu.h"
 
+// ---- bounds-checked build (make -C palace_b200/csrc bounds -> ../liberef_gpu_bounds.so) ----------------------------------
+// compute-sanitizer is not available on every pool, so the kernels carry their own checks: every index whose bound is
+// a capacity (ring words per tile, staging slots, code-list slots, list entries, plane words) is asserted under
+// -DEREF_BOUNDS; a failed assert aborts the kernel and the next API call reports cudaErrorAssert.  The checks compile
+// to nothing in the product build.
+#ifdef EREF_BOUNDS
+#include <cassert>
+#define EREF_ASSERT(x) assert(x)
+#else
+#define EREF_ASSERT(x) ((void)0)
+#endif
+
 // ---- layout constants ---------------------------------------------------------------------------
 // Text tiles: one CTA of 256 threads frames 8 KiB of text, 32 bytes per thread, so one thread owns
 // exactly one 32-position word of the bit-planes.
@@ -42,6 +54,7 @@ struct Planes {
     uint32_t* lo;
     uint32_t* ok;
     uint64_t  nwords;        // without the pad word
+    uint64_t  cap;           // words allocated per plane (bounds-checked build)
 };
 
 // FASTA framing state of a text tile (frame.cu), combined left to right by TileOp: flags bit 0 = a line
@@ -158,10 +171,10 @@ cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, C
                               uint32_t s0, uint32_t ns, cudaStream_t st);
 cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bits, const uint32_t* skip, CoderMasks m, int cbits,
                                   const unsigned long long* slice_off, unsigned long long* g_tail, uint32_t* codes_out,
-                                  uint32_t s0, uint32_t ns, cudaStream_t st);
+                                  unsigned long long out_cap, uint32_t s0, uint32_t ns, cudaStream_t st);
 cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
                                   const uint32_t* chunk_start, uint32_t nchunks, int cbits, unsigned long long* g_tail,
-                                  uint32_t* out, cudaStream_t st);
+                                  uint32_t* out, unsigned long long out_cap, cudaStream_t st);
 cudaError_t launch_slice_offsets(const unsigned long long* hist, int cbits, unsigned long long* off, unsigned long long* cnt,
                                  unsigned long long* coarse_n, uint32_t* chunk_start, unsigned long long* totals,
                                  unsigned long long cap_codes, uint32_t* overflow, cudaStream_t st);
@@ -171,6 +184,7 @@ struct CountLists {
     const uint32_t* codes[MAX_LISTS];
     const unsigned long long* off[MAX_LISTS];
     const unsigned long long* cnt[MAX_LISTS];
+    unsigned long long cap[MAX_LISTS];      // codes allocated per list (bounds-checked build)
     int n;
 };
 // Sharded table build: one GPU ("part") counts the slices [s0, s0 + ns) and stores them into the table of every GPU

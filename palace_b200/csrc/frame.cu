@@ -280,6 +280,7 @@ __device__ __forceinline__ bool ring_range(uint32_t& wmin, uint32_t& wmax)
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < TILE_THREADS / 32; k++) { wmin = min(wmin, s_min[k]); wmax = max(wmax, s_max[k]); }
+    EREF_ASSERT(wmin == 0xFFFFFFFFu || wmax - wmin < (uint32_t)RING);      // a tile's plane words fit the ring
     return wmin != 0xFFFFFFFFu;
 }
 
@@ -316,6 +317,7 @@ k_pack_fastq(const uint8_t* __restrict__ text, uint64_t n, const uint32_t* __res
     }
     if (!ring_range(wmin, wmax)) return;
     for (uint32_t wd = wmin + threadIdx.x; wd <= wmax; wd += TILE_THREADS) {
+        EREF_ASSERT(wd < pl.cap);
         const uint32_t i = wd & (RING - 1);
         const uint32_t vh = s_hi[i], vl = s_lo[i], vo = s_ok[i];
         if (wd == wmin || wd == wmax) {                   // shared with the neighbouring tiles: OR into the zeroed planes
@@ -586,6 +588,7 @@ k_pack_fasta(const uint8_t* __restrict__ text, uint64_t n, const TileSum* __rest
     }
     if (!ring_range(wmin, wmax)) return;                  // no sequence byte of a kept record in this tile
     for (uint32_t w = wmin + threadIdx.x; w <= wmax; w += TILE_THREADS) {
+        EREF_ASSERT(w < pl.cap);
         const uint32_t i = w & (RING - 1);
         const uint32_t vh = s_hi[i], vl = s_lo[i], vo = s_ok[i], g = s_g[i];
         if (w == wmin || w == wmax) {

@@ -211,6 +211,7 @@ k_need(const uint8_t* __restrict__ sample_hits, const uint32_t* __restrict__ wor
     unsigned long long base = 0;
     if (lane == 0) base = atomicAdd(need_count, (unsigned long long)total);
     base = __shfl_sync(0xffffffffu, base, 0);
+    EREF_ASSERT(base + total <= nwords);                  // the list holds at most every word once
     uint32_t* dst = list + base + (inc - cnt);
     while (bits) {
         const int j = __ffs(bits) - 1;
@@ -379,6 +380,7 @@ k_probe_part(Planes pl, CoderMasks m, const uint32_t* __restrict__ bm3, const ui
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += stride) {
         const uint64_t w = list ? list[e] : e;
+        EREF_ASSERT(w < pl.nwords);
         uint32_t acc[3] = {0, 0, 0};
         const uint32_t vm = valid_windows(pl.ok[w], pl.ok[w + 1]);
         if (vm) {

@@ -167,7 +167,8 @@ __device__ __forceinline__ void for_each_code_half(const Planes& pl, const Coder
 __global__ void __launch_bounds__(CS_THREADS)
 k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_bits, const uint32_t* __restrict__ skip,
                         CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
-                        unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out, uint32_t s0, uint32_t ns)
+                        unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out, uint32_t s0, uint32_t ns,
+                        unsigned long long out_cap)
 {
     // plane_bits: the packed size, when the host has not seen it (the grid then covers an upper bound); skip: set by
     // k_slice_offsets when the codes would not fit the buffers (api.cu: optimistic sizes)
@@ -216,10 +217,12 @@ k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_
     });
     __syncthreads();
     const uint32_t total = s_start[nb];
+    EREF_ASSERT(total <= (uint32_t)CS_CODES);
     if (threadIdx.x < nb) s_base[threadIdx.x] -= s_start[threadIdx.x];     // element i of the sorted tile goes to s_base[b] + i
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < total; i += CS_THREADS) {
         const uint32_t cd = s_codes[i];
+        EREF_ASSERT(s_base[cd >> shift] + i < out_cap);
         codes_out[s_base[cd >> shift] + i] = cd;
     }
 }
@@ -297,7 +300,7 @@ template <int FINE_THREADS>
 __global__ void __launch_bounds__(FINE_THREADS, 2048 / FINE_THREADS >= 3 ? 3 : 2)
 k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __restrict__ slice_off,
                  const unsigned long long* __restrict__ coarse_n, const uint32_t* __restrict__ chunk_start,
-                 int cbits, unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ out)
+                 int cbits, unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ out, unsigned long long out_cap)
 {
     __shared__ uint32_t s_stage[FINE_CHUNK];
     __shared__ uint32_t s_cnt[MAX_BUCKETS], s_off[MAX_BUCKETS + 1];
@@ -365,12 +368,16 @@ k_fine_partition(const uint32_t* __restrict__ in, const unsigned long long* __re
         const uint32_t u = (uint32_t)(j * FINE_THREADS + threadIdx.x);
 #pragma unroll
         for (int k = 0; k < 4; k++)
-            if (u * 4 + k < cnt) s_stage[s_off[(code[4 * j + k] >> SLICE_BITS) & (nf - 1)] + rank[4 * j + k]] = code[4 * j + k];
+            if (u * 4 + k < cnt) {
+                EREF_ASSERT(s_off[(code[4 * j + k] >> SLICE_BITS) & (nf - 1)] + rank[4 * j + k] < (uint32_t)FINE_CHUNK);
+                s_stage[s_off[(code[4 * j + k] >> SLICE_BITS) & (nf - 1)] + rank[4 * j + k]] = code[4 * j + k];
+            }
     }
     __syncthreads();
     uint32_t* out_b = out + slice_off[(size_t)b << fbits];
     for (uint32_t i = threadIdx.x; i < cnt; i += FINE_THREADS) {
         const uint32_t c = s_stage[i];
+        EREF_ASSERT(slice_off[(size_t)b << fbits] + s_delta[(c >> SLICE_BITS) & (nf - 1)] + i < out_cap);
         out_b[s_delta[(c >> SLICE_BITS) & (nf - 1)] + i] = c;
     }
 }
@@ -499,6 +506,7 @@ k_count_slices_persistent(CountLists lists, TableShare share, unsigned long long
             n_pre[l] = 0;
             if (l < lists.n && slice < slice_end) {
                 n_pre[l] = lists.cnt[l][slice];
+                EREF_ASSERT(lists.off[l][slice] + n_pre[l] <= lists.cap[l]);
                 const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);
 #pragma unroll
                 for (int j = 0; j < COUNT_PRE; j++) {
@@ -669,7 +677,7 @@ cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, C
 
 cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bits, const uint32_t* skip, CoderMasks m, int cbits,
                                   const unsigned long long* slice_off, unsigned long long* g_tail, uint32_t* codes_out,
-                                  uint32_t s0, uint32_t ns, cudaStream_t st)
+                                  unsigned long long out_cap, uint32_t s0, uint32_t ns, cudaStream_t st)
 {
     // pl.nwords: the exact word count, or (plane_bits given) an upper bound that sizes the grid
     if (!pl.nwords) return cudaSuccess;
@@ -679,7 +687,7 @@ cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bit
         cudaError_t e = cudaFuncSetAttribute(k_coarse_scatter_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         k_coarse_scatter_staged<<<(unsigned)((pl.nwords + CS_WORDS - 1) / CS_WORDS), CS_THREADS, smem, st>>>(
-            pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
+            pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns, out_cap);
     } else {
         if (plane_bits) return cudaErrorNotSupported;     // the unstaged variant needs the exact size
         k_coarse_scatter<<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
@@ -697,13 +705,13 @@ cudaError_t launch_slice_offsets(const unsigned long long* hist, int cbits, unsi
 
 cudaError_t launch_fine_partition(const uint32_t* in, const unsigned long long* slice_off, const unsigned long long* coarse_n,
                                   const uint32_t* chunk_start, uint32_t nchunks, int cbits, unsigned long long* g_tail,
-                                  uint32_t* out, cudaStream_t st)
+                                  uint32_t* out, unsigned long long out_cap, cudaStream_t st)
 {
     if (!nchunks) return cudaSuccess;
     static const int threads = [] { const char* v = getenv("EREF_FINE_THREADS"); return v ? atoi(v) : 1024; }();
-    if (threads == 512) k_fine_partition<512><<<nchunks, 512, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
-    else if (threads == 256) k_fine_partition<256><<<nchunks, 256, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
-    else k_fine_partition<1024><<<nchunks, 1024, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out);
+    if (threads == 512) k_fine_partition<512><<<nchunks, 512, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out, out_cap);
+    else if (threads == 256) k_fine_partition<256><<<nchunks, 256, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out, out_cap);
+    else k_fine_partition<1024><<<nchunks, 1024, 0, st>>>(in, slice_off, coarse_n, chunk_start, cbits, g_tail, out, out_cap);
     return cudaGetLastError();
 }
 

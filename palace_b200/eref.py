@@ -19,7 +19,8 @@ from ctypes import (POINTER, Structure, byref, c_char_p, c_float, c_int, c_int16
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liberef_gpu.so")
+# EREF_GPU_LIB: another build of the same library (the bounds-checked one, `make -C palace_b200/csrc bounds`)
+LIB_PATH = os.environ.get("EREF_GPU_LIB") or os.path.join(_HERE, "liberef_gpu.so")
 EREF_BIN = os.path.join(_HERE, "bin", "eref")
 
 K = 32
@@ -108,7 +109,7 @@ def load_library() -> ctypes.CDLL:
     lib.eref_table_set_part.argtypes = [c_void_p, c_int, c_int]
     lib.eref_table_set_peer.argtypes = [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
     lib.eref_table_set_hook.argtypes = [c_void_p, TABLE_HOOK, c_void_p]
-    lib.eref_table_part_range.argtypes = [c_void_p, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]
+    lib.eref_table_part_range.argtypes = [c_void_p, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]
     lib.eref_table_join.argtypes = [c_void_p]
     lib.eref_sync.argtypes = [c_void_p]
     lib.eref_run_results_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
@@ -364,9 +365,10 @@ class ErefGPU:
         self._hook = TABLE_HOOK(_cb) if fn else TABLE_HOOK()
         _check(self.lib, self.lib.eref_table_set_hook(self._h, self._hook, None), "eref_table_set_hook")
 
-    def table_part_range(self):
+    def table_part_range(self, part: int = -1):
+        """(table offset, table bytes, summary offset, summary bytes) of a part (-1: this context's own)"""
         v = [c_size_t() for _ in range(4)]
-        _check(self.lib, self.lib.eref_table_part_range(self._h, *[byref(x) for x in v]), "eref_table_part_range")
+        _check(self.lib, self.lib.eref_table_part_range(self._h, part, *[byref(x) for x in v]), "eref_table_part_range")
         return tuple(x.value for x in v)
 
     def table_join(self):
@@ -551,7 +553,7 @@ def wire_table_peers(ctxs):
 def _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hit_ratio, coder, devices, prune, pipelined,
                             chunks, return_results):
     """run_eref with the database AND the table build sharded over `devices` (entries may repeat: several contexts on
-    one GPU emulate a multi-GPU box).  Context i counts slices [8192 i/n, 8192 (i+1)/n) of the table and stores them into
+    one GPU emulate a multi-GPU box).  Context i counts its range of the 8192 table slices and stores them into
     every context's table; here the contexts run one after the other, so every build is waited for before any scan."""
     if interval_out:
         open(interval_out, "w").close()
