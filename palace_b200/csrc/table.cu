@@ -506,7 +506,7 @@ k_count_slices_persistent(CountLists lists, TableShare share, unsigned long long
             n_pre[l] = 0;
             if (l < lists.n && slice < slice_end) {
                 n_pre[l] = lists.cnt[l][slice];
-                EREF_ASSERT(lists.off[l][slice] + n_pre[l] <= lists.cap[l]);
+                EREF_ASSERT(n_pre[l] == 0 || lists.off[l][slice] + n_pre[l] <= lists.cap[l]);
                 const uint4* src = reinterpret_cast<const uint4*>(lists.codes[l] + lists.off[l][slice]);
 #pragma unroll
                 for (int j = 0; j < COUNT_PRE; j++) {
