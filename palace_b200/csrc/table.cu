@@ -90,6 +90,7 @@ __device__ __forceinline__ void for_each_code(const Planes& pl, const CoderMasks
 constexpr int HIST_THREADS = NSLICES * 4 > 48 * 1024 ? 512 : 256;      // 64 KiB of bins: three CTAs of 512 per SM
 
 // s0/ns: the table slices this GPU counts (sharded build, api.cu); codes of other slices are some other GPU's work.
+template <bool FILTER>
 __global__ void __launch_bounds__(HIST_THREADS)
 k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, CoderMasks m,
              unsigned long long* __restrict__ g_hist, uint32_t s0, uint32_t ns)
@@ -101,7 +102,7 @@ k_slice_hist(Planes pl, const unsigned long long* __restrict__ plane_bits, Coder
     for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += (uint64_t)gridDim.x * blockDim.x)
         for_each_code(pl, m, w, [&](uint32_t code) {
             const uint32_t s = code >> SLICE_BITS;
-            if (s - s0 < ns) atomicAdd(&s_hist[s], 1u);
+            if (!FILTER || s - s0 < ns) atomicAdd(&s_hist[s], 1u);
         });
     __syncthreads();
     for (int i = threadIdx.x; i < NSLICES; i += blockDim.x) {
@@ -164,6 +165,7 @@ __device__ __forceinline__ void for_each_code_half(const Planes& pl, const Coder
     }
 }
 
+template <bool FILTER>
 __global__ void __launch_bounds__(CS_THREADS)
 k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_bits, const uint32_t* __restrict__ skip,
                         CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
@@ -186,7 +188,7 @@ k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_
     const uint64_t w = (uint64_t)blockIdx.x * CS_WORDS + (threadIdx.x >> 1);
     const int half = threadIdx.x & 1;
     const bool live = w < nwords;
-    if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) { if ((code >> SLICE_BITS) - s0 < ns) atomicAdd(&s_cur[warp][code >> shift], 1u); });
+    if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) { if (!FILTER || (code >> SLICE_BITS) - s0 < ns) atomicAdd(&s_cur[warp][code >> shift], 1u); });
     __syncthreads();
     // bucket totals -> exclusive prefix (nb <= 256: one bucket per thread), global reservation, per-warp cursors
     uint32_t c = 0;
@@ -213,7 +215,7 @@ k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_
     if (threadIdx.x == CS_THREADS - 1) s_start[nb] = base + inc;
     __syncthreads();
     if (live) for_each_code_half(pl, m, w, half, [&](uint32_t code) {
-        if ((code >> SLICE_BITS) - s0 < ns) s_codes[atomicAdd(&s_cur[warp][code >> shift], 1u)] = code;
+        if (!FILTER || (code >> SLICE_BITS) - s0 < ns) s_codes[atomicAdd(&s_cur[warp][code >> shift], 1u)] = code;
     });
     __syncthreads();
     const uint32_t total = s_start[nb];
@@ -489,7 +491,7 @@ k_count_slices(CountLists lists, uint32_t* __restrict__ bm3, uint32_t* __restric
 // peer pointers, i.e. the all-gather of the table rides on the copy-out over NVLink, slice by slice, while the
 // other SMs are still counting.  The last CTA to finish publishes the build's epoch in every GPU's flag word
 // (release at system scope); k_table_wait on the consumer's stream acquires all of them before the first probe.
-template <bool POP>
+template <bool POP, bool SHARED>
 __global__ void __launch_bounds__(COUNT_THREADS, COUNT_CTAS)
 k_count_slices_persistent(CountLists lists, TableShare share, unsigned long long* __restrict__ level_pop)
 {
@@ -558,7 +560,8 @@ k_count_slices_persistent(CountLists lists, TableShare share, unsigned long long
         uint4* l2w = reinterpret_cast<uint4*>(L2);
         for (int i = threadIdx.x; i < SLICE_WORDS / 4; i += COUNT_THREADS) {
             const uint4 v = l3[i];
-            for (int p = 0; p < share.n; p++) __stcs(reinterpret_cast<uint4*>(share.bm3[p]) + dst_unit + i, v);
+            __stcs(reinterpret_cast<uint4*>(share.bm3[0]) + dst_unit + i, v);
+            if (SHARED) for (int p = 1; p < share.n; p++) __stcs(reinterpret_cast<uint4*>(share.bm3[p]) + dst_unit + i, v);
             // the three levels are zeroed for the next slice as they are read out (a thread clears what it alone read)
             l3w[i] = make_uint4(0, 0, 0, 0); l1w[i] = make_uint4(0, 0, 0, 0); l2w[i] = make_uint4(0, 0, 0, 0);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -573,12 +576,14 @@ k_count_slices_persistent(CountLists lists, TableShare share, unsigned long long
             out <<= 8 * (i & 3);
             out |= __shfl_xor_sync(0xffffffffu, out, 1);
             out |= __shfl_xor_sync(0xffffffffu, out, 2);
-            if ((i & 3) == 0)
-                for (int p = 0; p < share.n; p++) share.summary[p][(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
+            if ((i & 3) == 0) {
+                share.summary[0][(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
+                if (SHARED) for (int p = 1; p < share.n; p++) share.summary[p][(size_t)slice * (SLICE_WORDS / 16) + (i >> 2)] = out;
+            }
         }
         __syncthreads();
     }
-    if (share.n > 1) {
+    if (SHARED && share.n > 1) {
         // publish: every thread's peer stores are ordered before the CTA's arrival; the last CTA to arrive raises this
         // part's flag on every GPU
         __threadfence_system();
@@ -669,9 +674,13 @@ cudaError_t launch_slice_hist(Planes pl, const unsigned long long* plane_bits, C
                               uint32_t s0, uint32_t ns, cudaStream_t st)
 {
     const int smem = NSLICES * 4;
-    cudaError_t e = cudaFuncSetAttribute(k_slice_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(k_slice_hist<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    k_slice_hist<<<148 * 1536 / HIST_THREADS, HIST_THREADS, smem, st>>>(pl, plane_bits, m, g_hist, s0, ns);
+    const bool filter = !(s0 == 0 && ns >= (uint32_t)NSLICES);
+    cudaError_t e2 = filter ? cudaFuncSetAttribute(k_slice_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) : cudaSuccess;
+    if (e2 != cudaSuccess) return e2;
+    if (filter) k_slice_hist<true><<<148 * 1536 / HIST_THREADS, HIST_THREADS, smem, st>>>(pl, plane_bits, m, g_hist, s0, ns);
+    else k_slice_hist<false><<<148 * 1536 / HIST_THREADS, HIST_THREADS, smem, st>>>(pl, plane_bits, m, g_hist, s0, ns);
     return cudaGetLastError();
 }
 
@@ -684,10 +693,13 @@ cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bit
     static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 1; }();
     if (staged) {
         const int smem = CS_CODES * 4;
-        cudaError_t e = cudaFuncSetAttribute(k_coarse_scatter_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        const bool filter = !(s0 == 0 && ns >= (uint32_t)NSLICES);
+        cudaError_t e = filter ? cudaFuncSetAttribute(k_coarse_scatter_staged<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                               : cudaFuncSetAttribute(k_coarse_scatter_staged<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        k_coarse_scatter_staged<<<(unsigned)((pl.nwords + CS_WORDS - 1) / CS_WORDS), CS_THREADS, smem, st>>>(
-            pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns, out_cap);
+        const unsigned grid = (unsigned)((pl.nwords + CS_WORDS - 1) / CS_WORDS);
+        if (filter) k_coarse_scatter_staged<true><<<grid, CS_THREADS, smem, st>>>(pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns, out_cap);
+        else k_coarse_scatter_staged<false><<<grid, CS_THREADS, smem, st>>>(pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns, out_cap);
     } else {
         if (plane_bits) return cudaErrorNotSupported;     // the unstaged variant needs the exact size
         k_coarse_scatter<<<(unsigned)((pl.nwords + 255) / 256), 256, 0, st>>>(pl, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns);
@@ -728,13 +740,15 @@ cudaError_t launch_count_slices(const CountLists& lists, const TableShare& share
             sms = 148;
             if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         }
-        cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                  : cudaFuncSetAttribute(k_count_slices_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        const bool shared = share.n > 1;
+        void (*kern)(CountLists, TableShare, unsigned long long*) =
+            level_pop ? (shared ? k_count_slices_persistent<true, true> : k_count_slices_persistent<true, false>)
+                      : (shared ? k_count_slices_persistent<false, true> : k_count_slices_persistent<false, false>);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        if (share.n > 1) { e = cudaMemsetAsync(share.done, 0, 4, st); if (e != cudaSuccess) return e; }
+        if (shared) { e = cudaMemsetAsync(share.done, 0, 4, st); if (e != cudaSuccess) return e; }
         const unsigned grid = (unsigned)std::min<uint32_t>((uint32_t)(sms * COUNT_CTAS), share.ns);
-        if (level_pop) k_count_slices_persistent<true><<<grid, COUNT_THREADS, smem, st>>>(lists, share, level_pop);
-        else k_count_slices_persistent<false><<<grid, COUNT_THREADS, smem, st>>>(lists, share, nullptr);
+        kern<<<grid, COUNT_THREADS, smem, st>>>(lists, share, level_pop);
         return cudaGetLastError();
     }
     cudaError_t e = level_pop ? cudaFuncSetAttribute(k_count_slices<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
