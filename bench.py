@@ -438,8 +438,13 @@ class Job:
         with torch.cuda.stream(rig.stream):
             for _ in range(warmup):
                 self.step_device()
-            for _ in range(PHASE_STEPS):                   # instrumented steps: per-phase times, outside the timed region
+            # instrumented steps, outside the timed region: the library's streams serialised (eref_set_serial) so that every
+            # phase time is the duration of its own kernels; the timed steps overlap them and are shorter than the sum
+            rig.g.set_serial(True)
+            for _ in range(PHASE_STEPS):
                 self.step_device(collect=acc)
+            rig.g.set_serial(False)
+            self.step_device()
             rig.barrier()
             launches0 = rig.g.timings()["kernel_launches"]
             sampler = ClockSampler(rig.local) if rig.rank == 0 else None

@@ -176,6 +176,9 @@ int  eref_table_set_hook(eref_ctx* ctx, eref_table_hook fn, void* arg);
 int  eref_table_part_range(eref_ctx* ctx, int part, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes);
 /* queue the build of the files added so far and make the context's stream wait for the complete table */
 int  eref_table_join(eref_ctx* ctx);
+/* on: the table build and the framing census no longer run beside the main stream's kernels, so the phase times of
+ * eref_timings are per-kernel durations (profiling); off (default): they overlap and a step is shorter than their sum */
+int  eref_set_serial(eref_ctx* ctx, int on);
 /* wait for everything queued on the context */
 int  eref_sync(eref_ctx* ctx);
 

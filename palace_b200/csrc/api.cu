@@ -151,6 +151,7 @@ struct eref_ctx {
     cudaStream_t frame_stream = nullptr;
     cudaEvent_t ev_scan_done = nullptr, ev_frame_done = nullptr, ev_text_free = nullptr;
     bool scan_done_valid = false, text_free_valid = false;
+    bool serial = false;                       // eref_set_serial: no overlap between the streams (per-kernel timing)
     bool text_is_resident = false;             // EREF_FLAG_RESIDENT_TEXT: device texts are complete when the call is made
     DevBuf frame_cub_tmp;
 };
@@ -497,6 +498,7 @@ int start_table_update(eref_ctx* c)
     c->summary_stale = false;
     c->table_inflight = true;
     c->count_time_pending = true;
+    if (c->serial) CUDA_TRY(cudaStreamWaitEvent(st, c->table_ready, 0));   // nothing runs beside the count
     return 0;
 }
 
@@ -572,6 +574,10 @@ int ref_set_impl(eref_ctx* c, const uint8_t* text, uint64_t n, cudaEvent_t text_
     if (trc) return trc;
     if (c->scan_done_valid) CUDA_TRY(cudaStreamWaitEvent(fs, c->ev_scan_done, 0));
     if (text_ready) CUDA_TRY(cudaStreamWaitEvent(fs, text_ready, 0));
+    if (c->serial) {                          // the census starts only when the main stream has drained
+        CUDA_TRY(cudaEventRecord(c->aux_ev[1], st));
+        CUDA_TRY(cudaStreamWaitEvent(fs, c->aux_ev[1], 0));
+    }
     CUDA_TRY(cudaEventRecord(c->ev[E0], fs));
     if (host_text) {
         // eref_ref_set: the upload rides on the census stream too (behind the last reader of the text buffer)
@@ -1435,6 +1441,13 @@ int eref_query_popcount(eref_ctx* c, int level, uint64_t* out)
     CUDA_TRY(cudaMemcpyAsync(&h, ctr, 8, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     *out = h;
+    return 0;
+}
+
+int eref_set_serial(eref_ctx* c, int on)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    c->serial = on != 0;
     return 0;
 }
 

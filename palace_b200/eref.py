@@ -44,7 +44,7 @@ ABI_SYMBOLS = (
     "eref_run_host", "eref_ref_records", "eref_index_body", "eref_query_census", "eref_query_census_device",
     "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
     "eref_table_export", "eref_table_set_part", "eref_table_set_peer", "eref_table_set_hook", "eref_table_part_range",
-    "eref_table_join", "eref_sync", "eref_run_results_device", "eref_run_host_keep",
+    "eref_table_join", "eref_sync", "eref_run_results_device", "eref_run_host_keep", "eref_set_serial",
 )
 
 
@@ -112,6 +112,7 @@ def load_library() -> ctypes.CDLL:
     lib.eref_table_part_range.argtypes = [c_void_p, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]
     lib.eref_table_join.argtypes = [c_void_p]
     lib.eref_sync.argtypes = [c_void_p]
+    lib.eref_set_serial.argtypes = [c_void_p, c_int]
     lib.eref_run_results_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
     lib.eref_run_host_keep.argtypes = [c_void_p, c_void_p, c_uint64, c_void_p, c_uint64]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
@@ -373,6 +374,10 @@ class ErefGPU:
 
     def table_join(self):
         _check(self.lib, self.lib.eref_table_join(self._h), "eref_table_join")
+
+    def set_serial(self, on: bool):
+        """profiling: no overlap between the context's streams, so phase times are per-kernel durations"""
+        _check(self.lib, self.lib.eref_set_serial(self._h, 1 if on else 0), "eref_set_serial")
 
     def sync(self):
         _check(self.lib, self.lib.eref_sync(self._h), "eref_sync")
