@@ -399,7 +399,9 @@ class Job:
         if rig.world > 1:
             if "slot" not in self.info:
                 self.info["slot"] = agree_slot(n, rig.dev)     # once per sharded database
-            merged = allgather_records(rig.device_records(ptr, n), n, self.info["slot"])
+            # (compact=False: the merged records stay on the device with their padding; squeezing it out would read a
+            # count back and make the host wait for every step)
+            merged = allgather_records(rig.device_records(ptr, n), n, self.info["slot"], compact=False)
         if collect is not None:
             t = g.timings()                                # query times: sums over both files
             for p in PHASES:
@@ -527,7 +529,7 @@ class Job:
             g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
             ptr, n = g.scan_device(wait=False)
             if rig.world > 1:
-                allgather_records(rig.device_records(ptr, n), n, self.info["slot"])
+                allgather_records(rig.device_records(ptr, n), n, self.info["slot"], compact=False)
 
         def step_host_resident():
             if rig.world > 1:

@@ -40,11 +40,14 @@ def agree_slot(n_local: int, device) -> int:
     return int(t.item())
 
 
-def allgather_records(local, n_local: int, slot: int | None = None):
+def allgather_records(local, n_local: int, slot: int | None = None, compact: bool = True):
     """local: (n_local, 4) int32 tensor on this rank's device (cuda under NCCL, cpu under gloo).
     Returns the merged (sum n, 4) int64 tensor on every rank, ordinals offset into file order.
     The count of each shard travels in the same collective (one extra header row per block) and the merge is
-    done on the device without reading the counts back, so the step has ONE collective and one host sync."""
+    done on the device without reading the counts back, so the step has ONE collective.
+    compact=False: return (body, valid) — the (world, slot, 4) records with global ordinals and the mask of the real
+    ones — without squeezing the padding out: boolean indexing must read the number of survivors back, i.e. it makes
+    the host wait for the whole step, which a caller that keeps the records on the device does not need."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size()
@@ -64,4 +67,6 @@ def allgather_records(local, n_local: int, slot: int | None = None):
     body = out[:, 1:, :].clone()
     body[:, :, 0] += base[:, None]
     valid = torch.arange(slot, device=local.device)[None, :] < counts[:, None]
+    if not compact:
+        return body, valid
     return body[valid]

@@ -77,7 +77,10 @@ def _worker(rank, world, port, q):
         n = 4 if rank == 0 else 2                                  # ragged shards
         rec = np.zeros(n, eref.RESULT_DTYPE)
         rec["ordinal"] = np.arange(1, n + 1); rec["el"] = 100 * (rank + 1) + np.arange(n); rec["ref_len"] = 1000
-        merged = allgather_records(torch.from_numpy(rec.view(np.uint32).reshape(n, 4).astype(np.int32)), n)
+        local = torch.from_numpy(rec.view(np.uint32).reshape(n, 4).astype(np.int32))
+        merged = allgather_records(local, n)
+        body, valid = allgather_records(local, n, compact=False)   # padded form: no count is read back
+        assert body.shape == (world, 4, 4) and body[valid].tolist() == merged.tolist()
         q.put((rank, merged.tolist()))
     finally:
         dist.destroy_process_group()
