@@ -299,16 +299,14 @@ class Rig:
         # are not of equal size, so this is not an all-gather in place)
         g.table_set_part(rank, world)                      # (also drops half-wired peers)
         _, bm3, summ, _ = g.table_export()
-        ranges = [g.table_part_range(p) for p in range(world)]
         full_t = self.view(bm3, 1 << 29)
         full_s = self.view(summ, 1 << 25)
-        parts_t = [full_t[o: o + nb] for o, nb, _, _ in ranges]
-        parts_s = [full_s[o: o + nb] for _, _, o, nb in ranges]
 
         def hook(_stream):
-            for p in range(world):
-                self.dist.broadcast(parts_t[p], src=p)
-                self.dist.broadcast(parts_s[p], src=p)
+            for p in range(world):                         # (the parts are re-cut for every query: ask now)
+                to, tb, so, sb = g.table_part_range(p)
+                self.dist.broadcast(full_t[to: to + tb], src=p)
+                self.dist.broadcast(full_s[so: so + sb], src=p)
         g.table_set_hook(hook)
         return (f"sharded x{world}: each GPU counts its part of the table slices, one NCCL broadcast per part "
                 f"(512 + 32 MiB in all) completes the tables")
@@ -449,21 +447,25 @@ class Job:
             self.step_device()
             rig.barrier()
             launches0 = rig.g.timings()["kernel_launches"]
-            sampler = ClockSampler(rig.local) if rig.rank == 0 else None
+            sampler = ClockSampler(rig.local) if rig.rank == 0 and not os.environ.get("EREF_BENCH_NO_SAMPLER") else None
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]      # step-by-step spread (diagnostic)
             e0.record(rig.stream)
-            for _ in range(steps):
+            for k in range(steps):
                 self.step_device()
+                marks[k].record(rig.stream)
             e1.record(rig.stream)
             rig.barrier()
             dev_ms = e0.elapsed_time(e1)
+            per = [([e0] + marks)[k].elapsed_time(marks[k]) for k in range(steps)]
+            self.step_spread = {"min": round(min(per), 4), "median": round(float(np.median(per)), 4), "max": round(max(per), 4)}
             launches = rig.g.timings()["kernel_launches"] - launches0
             clocks = sampler.stop() if sampler else None
         self.avg = {p: acc[p] / PHASE_STEPS for p in PHASES}
         ms = rig.reduce(dev_ms, "max") / steps
         self.total_bases = rig.reduce(float(self.info["ref_bases"]), "sum")
         return {"ms_per_step": ms, "value": self.total_bases / 1e9 / (ms / 1e3),
-                "launches": int(rig.reduce(float(launches), "sum")), "clocks": clocks}
+                "launches": int(rig.reduce(float(launches), "sum")), "clocks": clocks, "step_spread_rank0": self.step_spread}
 
     def time_host(self, steps, warmup):
         rig, torch = self.rig, self.rig.torch
@@ -824,6 +826,7 @@ def run_b200(args):
         "e2e": e2e,
         "gpu_launches": head["launches"],
         "clocks": head["clocks"],
+        "step_spread_ms_rank0": head["step_spread_rank0"],
         "phases_ms": {k: round(v, 4) for k, v in avg.items()},
         "scan_only": {"ms": round(scan_ms, 4), "value": round(info["ref_bases"] * world / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT,
                       "need_word_fraction": round(info["need_words"] / max(info["ref_words"], 1), 4),

@@ -172,7 +172,9 @@ int  eref_table_set_peer(eref_ctx* ctx, int peer_part, int peer_device, const vo
                          void* summary_dev, void* flags_dev);
 int  eref_table_set_hook(eref_ctx* ctx, eref_table_hook fn, void* arg);
 /* byte ranges of part `part` (-1: this context's own) inside the level-3 table and its summary.  The parts are NOT of
- * equal size: canonical codes thin out towards the top of the code space, so the cut points balance the GPUs' work. */
+ * equal size and are re-cut for every query (at the first file added after a reset, from its size): canonical codes
+ * thin out towards the top of the code space, so the cut points balance code mass against the per-slice cost of the
+ * exchange.  A completion hook must therefore ask for the ranges when it runs, not when it is installed. */
 int  eref_table_part_range(eref_ctx* ctx, int part, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes);
 /* queue the build of the files added so far and make the context's stream wait for the complete table */
 int  eref_table_join(eref_ctx* ctx);

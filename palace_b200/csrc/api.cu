@@ -117,6 +117,7 @@ struct eref_ctx {
     // Sharded build (eref_table_set_part): this GPU counts the slices [slice0, slice0 + nslices) and stores them into
     // every peer's table; share_words = 16 flag words (one per part) | done counter | error word
     int parts = 1, part = 0;
+    double part_w = 0.0;                       // balance of the parts: weight of code mass against width
     uint32_t slice0 = 0, nslices = NSLICES;
     struct Peer { uint32_t* bm3 = nullptr; uint32_t* summary = nullptr; uint32_t* flags = nullptr; bool ipc = false; };
     Peer peers[MAX_PARTS];
@@ -166,6 +167,7 @@ namespace {
 
 int start_table_update(eref_ctx* c);
 int check_guard(eref_ctx* c);
+void rebalance_parts(eref_ctx* c, uint64_t first_file_bytes);
 int wait_table(eref_ctx* c, cudaStream_t st);
 int join_table(eref_ctx* c, cudaStream_t st);
 // layout of part_ctr after the u64 arrays: u32 chunk_start[260], then u64 totals[3]
@@ -314,6 +316,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     int wrc = wait_table(c, st);              // an update still in flight reads the code lists this call rewrites
     if (wrc) return wrc;
     const bool direct = (c->flags & EREF_FLAG_DIRECT_COUNT) != 0;
+    if (c->parts > 1 && c->n_lists == 0) rebalance_parts(c, n);
     if (!direct && c->n_lists >= (size_t)MAX_LISTS)
         return eref_fail(EREF_ERR_LIMIT, "more than %d query files since the last eref_query_reset", MAX_LISTS);
     // events of this file: E1..E4 for the direct build (read at the end of this call), a set of its own otherwise
@@ -527,6 +530,49 @@ int join_table(eref_ctx* c, cudaStream_t st)
     rc = c->hook(c->hook_arg, (void*)st);
     if (rc) return eref_fail(EREF_ERR_STATE, "the table completion hook failed (%d)", rc);
     return 0;
+}
+
+// First table slice of part p of `parts`.  Canonical codes are min(fwd, rc): their density falls linearly, 2(1 - x), over
+// the code space, so equal slice ranges would give the first GPU of two 75 % of the codes; but a part also costs per
+// slice — clearing and writing out 2^19 slots and, above all, storing them into N - 1 peers over NVLink (egress is
+// balanced only for equal widths).  The cut points equalise w * mass + (1 - w) * width.
+uint32_t part_first_slice(int p, int parts, double w)
+{
+    if (p <= 0) return 0;
+    if (p >= parts) return NSLICES;
+    const double t = (double)p / parts;
+    const double x = w > 1e-6 ? ((1 + w) - sqrt((1 + w) * (1 + w) - 4 * w * t)) / (2 * w) : t;
+    long long sl = llround(x * NSLICES);
+    if (sl < p) sl = p;
+    if (sl > NSLICES - (parts - p)) sl = NSLICES - (parts - p);
+    return (uint32_t)sl;
+}
+
+// The weight for a query of `query_bytes` of FASTQ text on `parts` GPUs, from the measured costs (B200):
+// partitioning + counting ~0.5 ms per 100 MB of FASTQ text, spread by code mass; per unit of width 0.3 ms of local
+// clearing/copy-out plus 0.6 ms for every peer the 544 MiB table goes to.  Small queries on many GPUs end up with
+// nearly equal widths (the exchange dominates), large queries with nearly equal code mass.  EREF_PART_WEIGHT overrides.
+double part_weight(int parts, uint64_t query_bytes)
+{
+    static const double forced = [] { const char* v = getenv("EREF_PART_WEIGHT"); return v ? atof(v) : -1.0; }();
+    if (forced >= 0) return forced > 0.95 ? 0.95 : forced;
+    const double a = 0.5 * (double)query_bytes / 1.04e8, b = 0.3 + 0.6 * (parts - 1);
+    const double w = a / (a + b);
+    return w > 0.95 ? 0.95 : w;
+}
+
+void set_part_range(eref_ctx* c)
+{
+    c->slice0 = part_first_slice(c->part, c->parts, c->part_w);
+    c->nslices = part_first_slice(c->part + 1, c->parts, c->part_w) - c->slice0;
+}
+
+// Sharded build, first file after a reset: the parts are cut for the size of this query (every GPU sees the same file
+// sizes in the same order, so every GPU cuts alike; a sample is two files of about this size)
+void rebalance_parts(eref_ctx* c, uint64_t first_file_bytes)
+{
+    c->part_w = part_weight(c->parts, 2 * first_file_bytes);
+    set_part_range(c);
 }
 
 // after a host synchronisation that covers the table stream: collect the update's duration
@@ -1480,23 +1526,6 @@ int eref_table_export(eref_ctx* c, void* ipc_handles, void** bm3_dev, void** sum
     return 0;
 }
 
-// First table slice of part p of `parts`.  Canonical codes are min(fwd, rc): their density falls linearly, 2(1 - x), over
-// the code space, so equal slice ranges would give the first GPU of two 75 % of the codes.  A part's cost is its codes
-// (partition + atomics) plus a fixed cost per slice (clearing and writing out 2^19 slots): the cut points equalise
-// w * mass + (1 - w) * width, w = 0.7 (EREF_PART_WEIGHT; 0 = equal widths).
-static uint32_t part_first_slice(int p, int parts)
-{
-    if (p <= 0) return 0;
-    if (p >= parts) return NSLICES;
-    static const double w = [] { const char* v = getenv("EREF_PART_WEIGHT"); double k = v ? atof(v) : 0.7; return k < 0 ? 0.0 : (k > 0.95 ? 0.95 : k); }();
-    const double t = (double)p / parts;
-    const double x = w > 1e-6 ? ((1 + w) - sqrt((1 + w) * (1 + w) - 4 * w * t)) / (2 * w) : t;
-    long long sl = llround(x * NSLICES);
-    if (sl < p) sl = p;
-    if (sl > NSLICES - (parts - p)) sl = NSLICES - (parts - p);
-    return (uint32_t)sl;
-}
-
 int eref_table_set_part(eref_ctx* c, int part, int parts)
 {
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
@@ -1508,8 +1537,8 @@ int eref_table_set_part(eref_ctx* c, int part, int parts)
     int rc = eref_sync(c);
     if (rc) return rc;
     c->parts = parts; c->part = part;
-    c->slice0 = part_first_slice(part, parts);
-    c->nslices = part_first_slice(part + 1, parts) - c->slice0;
+    c->part_w = part_weight(parts, 0);
+    set_part_range(c);
     for (int p = 0; p < MAX_PARTS; p++) {           // peers are set after the part (a new layout drops the old wiring)
         if (c->peers[p].ipc) { cudaIpcCloseMemHandle(c->peers[p].bm3); cudaIpcCloseMemHandle(c->peers[p].summary); cudaIpcCloseMemHandle(c->peers[p].flags); }
         c->peers[p] = eref_ctx::Peer();
@@ -1563,8 +1592,8 @@ int eref_table_part_range(eref_ctx* c, int part, size_t* table_off, size_t* tabl
 {
     if (!c) return eref_fail(EREF_ERR_ARG, "null context");
     if (part >= c->parts) return eref_fail(EREF_ERR_ARG, "part %d of %d", part, c->parts);
-    const uint32_t s0 = part < 0 ? c->slice0 : part_first_slice(part, c->parts);
-    const uint32_t ns = part < 0 ? c->nslices : part_first_slice(part + 1, c->parts) - s0;
+    const uint32_t s0 = part < 0 ? c->slice0 : part_first_slice(part, c->parts, c->part_w);
+    const uint32_t ns = part < 0 ? c->nslices : part_first_slice(part + 1, c->parts, c->part_w) - s0;
     if (table_off) *table_off = (size_t)s0 * SLICE_WORDS * 4;
     if (table_bytes) *table_bytes = (size_t)ns * SLICE_WORDS * 4;
     if (summary_off) *summary_off = (size_t)s0 * (SLICE_WORDS / 16) * 4;

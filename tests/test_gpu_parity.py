@@ -648,13 +648,13 @@ def test_sharded_table_completion_hook(golden):
         ptrs = [g.table_export() for g in ctxs]
         for i, g in enumerate(ctxs):
             g.table_set_part(i, 2)
-        ranges = [g.table_part_range() for g in ctxs]
         called = []
 
         def make_hook(i):
             def hook(stream):
                 j = 1 - i                                  # fetch part j from context j's table
-                toff, tbytes, soff, sbytes = ranges[j]
+                toff, tbytes, soff, sbytes = ctxs[i].table_part_range(j)    # (the parts are re-cut for every query)
+                assert (toff, tbytes, soff, sbytes) == ctxs[j].table_part_range()
                 for k, (off, nb) in ((1, (toff, tbytes)), (2, (soff, sbytes))):
                     err, = cudart.cudaMemcpyAsync(ptrs[i][k] + off, ptrs[j][k] + off, nb,
                                                   cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice, stream)
