@@ -291,8 +291,9 @@ class Rig:
                     print(f"rank {rank}: cannot open a peer's table: {e}", file=sys.stderr)
                     ok = False
             if self.all_ok(ok):
-                return (f"sharded x{world}: each GPU counts 1/{world} of the table slices and stores them into every "
-                        f"GPU's table through CUDA-IPC peer pointers (NVLink), device-side flags")
+                return (f"shared out over {world} GPUs when the query is large enough (EREF_SHARD_MIN_BYTES, default 160 MB of "
+                        f"FASTQ text): each GPU counts its part of the table slices and stores them into every GPU's table "
+                        f"through CUDA-IPC peer pointers (NVLink), device-side flags; smaller queries: every GPU counts all")
             if self.args.table == "peer":
                 raise SystemExit("--table peer: peer pointers unavailable")
         # hook: one NCCL broadcast per part of the level-3 table and its summary on the library's stream (the parts
@@ -308,8 +309,8 @@ class Rig:
                 self.dist.broadcast(full_t[to: to + tb], src=p)
                 self.dist.broadcast(full_s[so: so + sb], src=p)
         g.table_set_hook(hook)
-        return (f"sharded x{world}: each GPU counts its part of the table slices, one NCCL broadcast per part "
-                f"(512 + 32 MiB in all) completes the tables")
+        return (f"shared out over {world} GPUs when the query is large enough (EREF_SHARD_MIN_BYTES): each GPU counts its "
+                f"part of the table slices, one NCCL broadcast per part (512 + 32 MiB in all) completes the tables")
 
     def full_ctx(self):
         if self.g_full is None:
@@ -462,6 +463,10 @@ class Job:
             launches = rig.g.timings()["kernel_launches"] - launches0
             clocks = sampler.stop() if sampler else None
         self.avg = {p: acc[p] / PHASE_STEPS for p in PHASES}
+        if rig.world > 1:
+            to, tb, _, _ = rig.g.table_part_range()
+            self.info["table_build"] = ("every GPU counts the whole table (query below EREF_SHARD_MIN_BYTES)" if tb == 1 << 29 else
+                                        f"shared out: rank 0 counts table bytes [{to}, {to + tb}) of 2^29 and receives the rest")
         ms = rig.reduce(dev_ms, "max") / steps
         self.total_bases = rig.reduce(float(self.info["ref_bases"]), "sum")
         return {"ms_per_step": ms, "value": self.total_bases / 1e9 / (ms / 1e3),
@@ -718,7 +723,9 @@ def sub_record(rig, job, steps, warmup, parity_records, with_e2e=True, with_unpr
            "query_seq_bases": int(job.info["seq_bytes"]), "query_codes": int(job.info["query_codes"]),
            "phases_ms": {k: round(v, 4) for k, v in job.avg.items()},
            "need_word_fraction": round(job.info["need_words"] / max(job.info["ref_words"], 1), 4),
-           "gpu_launches": t["launches"]}
+           "gpu_launches": t["launches"], "step_spread_ms_rank0": t["step_spread_rank0"]}
+    if "table_build" in job.info:
+        out["table_build"] = job.info["table_build"]
     scan_ms = sum(job.avg[p] for p in SCAN_PHASES)
     out["scan_only"] = {"ms": round(scan_ms, 4), "value": round(job.info["ref_bases"] * rig.world / 1e9 / (scan_ms / 1e3), 2), "unit": UNIT}
     if with_e2e:
@@ -821,6 +828,7 @@ def run_b200(args):
         "workload_detail": {"db_bases_per_gpu": int(info["ref_bases"]), "query_seq_bases": int(qbases),
                             "records_per_gpu": int(info["n_records"]),
                             "parallelism": f"db-shard x{world}, query replicated", "table_build": rig.table_mode,
+                            "table_build_this_query": info.get("table_build"),
                             "candidate_filter": not args.no_prune,
                             "l2": "inputs larger than L2: per step the 512 MiB level-3 table is rewritten and 0.6 GB of text read"},
         "e2e": e2e,

@@ -118,6 +118,7 @@ struct eref_ctx {
     // every peer's table; share_words = 16 flag words (one per part) | done counter | error word
     int parts = 1, part = 0;
     double part_w = 0.0;                       // balance of the parts: weight of code mass against width
+    bool build_sharded = true;                 // this query's build is shared out (false: small query, every GPU counts all)
     uint32_t slice0 = 0, nslices = NSLICES;
     struct Peer { uint32_t* bm3 = nullptr; uint32_t* summary = nullptr; uint32_t* flags = nullptr; bool ipc = false; };
     Peer peers[MAX_PARTS];
@@ -480,9 +481,10 @@ int start_table_update(eref_ctx* c)
     sh.bm3[0] = c->bm[2]; sh.summary[0] = c->summary; sh.flags[0] = c->share_words;
     sh.n = 1; sh.part = c->part; sh.s0 = c->slice0; sh.ns = c->nslices;
     sh.done = c->share_words + MAX_PARTS;
-    bool all_peers = c->parts > 1;
+    const bool sharded = c->parts > 1 && c->build_sharded;
+    bool all_peers = sharded;
     for (int p = 0; p < c->parts && all_peers; p++) if (p != c->part && !c->peers[p].bm3) all_peers = false;
-    if (c->parts > 1) {
+    if (sharded) {
         if (!all_peers && !c->hook)
             return eref_fail(EREF_ERR_STATE, "sharded table build: neither every peer (eref_table_set_peer) nor a completion hook "
                                              "(eref_table_set_hook) is set");
@@ -569,8 +571,16 @@ void set_part_range(eref_ctx* c)
 
 // Sharded build, first file after a reset: the parts are cut for the size of this query (every GPU sees the same file
 // sizes in the same order, so every GPU cuts alike; a sample is two files of about this size)
+// Sharing the build out costs an exchange of the 544 MiB table (measured on 8 B200s: 0.74 ms per build, NVLink-bound
+// at ~640 GB/s of peer stores per GPU; 0.35 ms on 2) and saves (1 - 1/N) of partitioning and counting (~0.8 ms per
+// 100 MB of FASTQ text): below EREF_SHARD_MIN_BYTES of query text (default 160 MB; 0 = always share) every GPU counts
+// the whole table for itself, as the reference's threads share one table built once (:1257-1291).
 void rebalance_parts(eref_ctx* c, uint64_t first_file_bytes)
 {
+    const char* mv = getenv("EREF_SHARD_MIN_BYTES");
+    const double min_bytes = mv ? atof(mv) : 1.6e8;
+    c->build_sharded = 2.0 * (double)first_file_bytes >= min_bytes;
+    if (!c->build_sharded) { c->slice0 = 0; c->nslices = NSLICES; return; }
     c->part_w = part_weight(c->parts, 2 * first_file_bytes);
     set_part_range(c);
 }
@@ -1538,6 +1548,7 @@ int eref_table_set_part(eref_ctx* c, int part, int parts)
     if (rc) return rc;
     c->parts = parts; c->part = part;
     c->part_w = part_weight(parts, 0);
+    c->build_sharded = true;
     set_part_range(c);
     for (int p = 0; p < MAX_PARTS; p++) {           // peers are set after the part (a new layout drops the old wiring)
         if (c->peers[p].ipc) { cudaIpcCloseMemHandle(c->peers[p].bm3); cudaIpcCloseMemHandle(c->peers[p].summary); cudaIpcCloseMemHandle(c->peers[p].flags); }

@@ -14,6 +14,9 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 # several contexts on one GPU emulate a multi-GPU box in the sharded-table tests: give their streams hardware queues
 # of their own (more streams than connections can serialise a spinning wait kernel ahead of the work it waits for)
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# the test queries are megabytes: share every table build out, however small (the library would count a small query on
+# every GPU for itself); test_small_queries_are_not_shared_out turns the default back on
+os.environ.setdefault("EREF_SHARD_MIN_BYTES", "0")
 
 
 def pytest_configure(config):

@@ -778,3 +778,29 @@ def test_a_query_that_outgrows_the_optimistic_buffers_is_retried(oracle):
         got = g.run_host(s1, s2, db.text).copy()
         assert (got == want).all()
     assert retried
+
+
+def test_small_queries_are_not_shared_out(golden, monkeypatch):
+    """below EREF_SHARD_MIN_BYTES of query text the exchange of the table would cost more than counting it everywhere:
+    every context of a sharded setup then builds the whole table for itself (same decision on every GPU: it depends
+    only on the file sizes) and the records are the same"""
+    name, meta, fa, f1, f2 = golden
+    monkeypatch.delenv("EREF_SHARD_MIN_BYTES", raising=False)      # the library's default: 160 MB of FASTQ text
+    _, want = eref.run_eref(f1, f2, fa, coder=meta["coder"], return_results=True)
+    ctxs = [eref.ErefGPU(meta["coder"], level_pop=True) for _ in range(2)]
+    try:
+        eref.wire_table_peers(ctxs)
+        with eref.ErefGPU(meta["coder"], level_pop=True) as one:
+            one.query_add(f1); one.query_add(f2)
+            whole = [one.query_popcount(l) for l in (1, 2, 3)]
+        for g in ctxs:
+            g.query_add(f1); g.query_add(f2); g.ref_set(fa)
+        for g in ctxs:
+            g.sync()
+        for g in ctxs:
+            assert [g.query_popcount(l) for l in (1, 2, 3)] == whole      # not a part: the whole table
+            assert (g.scan() == want).all()
+        assert ctxs[0].table_part_range() == (0, 1 << 29, 0, 1 << 25)
+    finally:
+        for g in ctxs:
+            g.close()
