@@ -229,6 +229,97 @@ k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_
     }
 }
 
+// P1 (staged, codes kept in registers): the staged scatter above forms every code twice — once to count the CTA's
+// codes per bucket, once to place them.  Here a thread owns a quarter word (8 window starts, 24 codes), forms its codes
+// once into registers (fully unrolled, invalid starts predicated off) and uses them in both passes: a third fewer
+// instructions for the same stores.  512 threads per CTA over the same 128 plane words, two CTAs per SM.
+constexpr int CR_THREADS = 512, CR_STARTS = 8;
+
+template <bool FILTER>
+__global__ void __launch_bounds__(CR_THREADS, 2)
+k_coarse_scatter_reg(Planes pl, const unsigned long long* __restrict__ plane_bits, const uint32_t* __restrict__ skip,
+                     CoderMasks m, int shift, const unsigned long long* __restrict__ slice_off,
+                     unsigned long long* __restrict__ g_tail, uint32_t* __restrict__ codes_out, uint32_t s0, uint32_t ns,
+                     unsigned long long out_cap)
+{
+    extern __shared__ uint32_t s_codes[];                  // CS_CODES
+    __shared__ uint32_t s_cur[CR_THREADS / 32][MAX_BUCKETS];   // per warp: counts, then cursors into s_codes
+    __shared__ uint32_t s_start[MAX_BUCKETS + 1];
+    __shared__ unsigned long long s_base[MAX_BUCKETS];
+    __shared__ uint32_t s_wsum[CR_THREADS / 32];
+    const uint64_t nwords = plane_bits ? (*plane_bits + 31) >> 5 : pl.nwords;
+    if ((uint64_t)blockIdx.x * CS_WORDS >= nwords || (skip && *skip)) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nb = 1 << (32 - shift);
+    for (int i = threadIdx.x; i < (CR_THREADS / 32) * MAX_BUCKETS; i += CR_THREADS) (&s_cur[0][0])[i] = 0;
+    __syncthreads();
+    const uint64_t w = (uint64_t)blockIdx.x * CS_WORDS + (threadIdx.x >> 2);
+    const int first = (threadIdx.x & 3) * CR_STARTS;
+    // this thread's codes: code[3 j + i] for start first + j, stream i; bit j of vm = that start is a valid window
+    uint32_t code[3 * CR_STARTS];
+    uint32_t keep = 0;                                     // bit 3 j + i: the code is counted (valid, and in this GPU's slices)
+    if (w < nwords) {
+        const uint32_t vm = (valid_windows(pl.ok[w], pl.ok[w + 1]) >> (32 - CR_STARTS - first)) & ((1u << CR_STARTS) - 1u);
+        if (vm) {
+            const uint32_t hi0 = pl.hi[w], hi1 = pl.hi[w + 1], lo0 = pl.lo[w], lo1 = pl.lo[w + 1];
+#pragma unroll
+            for (int j = 0; j < CR_STARTS; j++) {
+                const int s = first + j;
+                const WindowBits b = window_bits(window32(hi0, hi1, s), window32(lo0, lo1, s));
+                const bool v = (vm >> (CR_STARTS - 1 - j)) & 1u;
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    const uint32_t c = stream_code(m, b, i);
+                    code[3 * j + i] = c;
+                    if (v && (!FILTER || (c >> SLICE_BITS) - s0 < ns)) keep |= 1u << (3 * j + i);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 3 * CR_STARTS; q++)
+        if ((keep >> q) & 1u) atomicAdd(&s_cur[warp][code[q] >> shift], 1u);
+    __syncthreads();
+    // bucket totals -> exclusive prefix (nb <= 256: one bucket per thread), global reservation, per-warp cursors
+    uint32_t c = 0;
+    if (threadIdx.x < nb) {
+#pragma unroll
+        for (int k = 0; k < CR_THREADS / 32; k++) c += s_cur[k][threadIdx.x];
+    }
+    uint32_t inc = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) s_wsum[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+#pragma unroll
+    for (int k = 0; k < CR_THREADS / 32; k++) if (k < warp) base += s_wsum[k];
+    if (threadIdx.x < nb) {
+        uint32_t run = base + inc - c;
+        s_start[threadIdx.x] = run;
+        s_base[threadIdx.x] = slice_off[(size_t)threadIdx.x << (shift - SLICE_BITS)] +
+                              (c ? atomicAdd(g_tail + threadIdx.x, (unsigned long long)c) : 0ull);
+#pragma unroll
+        for (int k = 0; k < CR_THREADS / 32; k++) { const uint32_t v = s_cur[k][threadIdx.x]; s_cur[k][threadIdx.x] = run; run += v; }
+    }
+    // (threads nb .. 255 of the first 8 warps hold c = 0: the running sum of the last of them is the CTA's total)
+    if (threadIdx.x == MAX_BUCKETS - 1) s_start[nb] = base + inc;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 3 * CR_STARTS; q++)
+        if ((keep >> q) & 1u) s_codes[atomicAdd(&s_cur[warp][code[q] >> shift], 1u)] = code[q];
+    __syncthreads();
+    const uint32_t total = s_start[nb];
+    EREF_ASSERT(total <= (uint32_t)CS_CODES);
+    if (threadIdx.x < nb) s_base[threadIdx.x] -= s_start[threadIdx.x];     // element i of the sorted tile goes to s_base[b] + i
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < total; i += CR_THREADS) {
+        const uint32_t cd = s_codes[i];
+        EREF_ASSERT(s_base[cd >> shift] + i < out_cap);
+        codes_out[s_base[cd >> shift] + i] = cd;
+    }
+}
+
 // Slice offsets of one file from its slice histogram, on the device (no host round trip, no H2D copy that
 // would queue behind the database upload): off[s] = start of slice s (padded to 4 codes so that every slice
 // starts 16-byte aligned), cnt = copy of the histogram, coarse_n[b] = codes of coarse bucket b,
@@ -690,7 +781,18 @@ cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bit
 {
     // pl.nwords: the exact word count, or (plane_bits given) an upper bound that sizes the grid
     if (!pl.nwords) return cudaSuccess;
-    static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 1; }();
+    static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 2; }();
+    if (staged == 2) {                                    // codes formed once, kept in registers between the two passes
+        const int smem = CS_CODES * 4;
+        const bool filter = !(s0 == 0 && ns >= (uint32_t)NSLICES);
+        cudaError_t e = filter ? cudaFuncSetAttribute(k_coarse_scatter_reg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                               : cudaFuncSetAttribute(k_coarse_scatter_reg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        const unsigned grid = (unsigned)((pl.nwords + CS_WORDS - 1) / CS_WORDS);
+        if (filter) k_coarse_scatter_reg<true><<<grid, CR_THREADS, smem, st>>>(pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns, out_cap);
+        else k_coarse_scatter_reg<false><<<grid, CR_THREADS, smem, st>>>(pl, plane_bits, skip, m, 32 - cbits, slice_off, g_tail, codes_out, s0, ns, out_cap);
+        return cudaGetLastError();
+    }
     if (staged) {
         const int smem = CS_CODES * 4;
         const bool filter = !(s0 == 0 && ns >= (uint32_t)NSLICES);
