@@ -229,10 +229,10 @@ k_coarse_scatter_staged(Planes pl, const unsigned long long* __restrict__ plane_
     }
 }
 
-// P1 (staged, codes kept in registers): the staged scatter above forms every code twice — once to count the CTA's
-// codes per bucket, once to place them.  Here a thread owns a quarter word (8 window starts, 24 codes), forms its codes
-// once into registers (fully unrolled, invalid starts predicated off) and uses them in both passes: a third fewer
-// instructions for the same stores.  512 threads per CTA over the same 128 plane words, two CTAs per SM.
+// P1 (staged, codes kept in registers; EREF_COARSE_STAGED=2, a measured variant that LOST): the staged scatter above
+// forms every code twice — once to count the CTA's codes per bucket, once to place them.  Here a thread owns a quarter
+// word (8 window starts, 24 codes), forms its codes once into registers (fully unrolled, invalid starts predicated off)
+// and uses them in both passes.  512 threads per CTA over the same 128 plane words, two CTAs per SM: 9 % slower.
 constexpr int CR_THREADS = 512, CR_STARTS = 8;
 
 template <bool FILTER>
@@ -781,7 +781,10 @@ cudaError_t launch_coarse_scatter(Planes pl, const unsigned long long* plane_bit
 {
     // pl.nwords: the exact word count, or (plane_bits given) an upper bound that sizes the grid
     if (!pl.nwords) return cudaSuccess;
-    static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 2; }();
+    // 1 (default): staged scatter; 2: the register-cached variant — measured SLOWER (B200, bench workload: bucket phases
+    // 0.896 ms against 0.823 ms; configs[3]: 8.05 against 7.31 ms): 64 registers and two 512-thread CTAs per SM lose more
+    // than forming each code once saves; 0: unstaged
+    static const int staged = [] { const char* v = getenv("EREF_COARSE_STAGED"); return v ? atoi(v) : 1; }();
     if (staged == 2) {                                    // codes formed once, kept in registers between the two passes
         const int smem = CS_CODES * 4;
         const bool filter = !(s0 == 0 && ns >= (uint32_t)NSLICES);
