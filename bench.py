@@ -635,7 +635,7 @@ class Job:
         return out
 
 
-def phases_report(job, fa_bytes, ntext_q, stride, no_prune):
+def phases_report(job, fa_bytes, ntext_q, no_prune):
     """per-phase times with (i) SURVEY 8(d)'s algorithmic bytes where it gives a figure, (ii) the bytes this design must
     move, (iii) ncu's DRAM bytes from the committed capture"""
     peak, _ = peaks()
@@ -780,8 +780,7 @@ def run_b200(args):
             par["device_path_equals_host_path"] = bool(same_paths)
             if rec_full is not None:
                 par["unpruned_equals_pruned"] = bool(same_full)
-    stride = int(os.environ.get("EREF_SAMPLE_STRIDE", "6"))
-    phases, b8d, design, probed = phases_report(job, job.fa_d.numel(), job.f1_d.numel() + job.f2_d.numel(), stride, args.no_prune)
+    phases, b8d, design, probed = phases_report(job, job.fa_d.numel(), job.f1_d.numel() + job.f2_d.numel(), args.no_prune)
     roof = roofline_record(job, phases, b8d, design, probed, args.no_prune)
     info, avg = dict(job.info), dict(job.avg)
     qbases = info["seq_bytes"]
