@@ -176,6 +176,22 @@ int  eref_table_set_hook(eref_ctx* ctx, eref_table_hook fn, void* arg);
  * thin out towards the top of the code space, so the cut points balance code mass against the per-slice cost of the
  * exchange.  A completion hook must therefore ask for the ranges when it runs, not when it is installed. */
 int  eref_table_part_range(eref_ctx* ctx, int part, size_t* table_off, size_t* table_bytes, size_t* summary_off, size_t* summary_bytes);
+/* Shared reads — the whole query side divided by N.  With the table build shared out every GPU still packs the whole
+ * query and forms all its codes, keeping those of its part.  With shared reads the CALLER gives every GPU 1/N of each
+ * query file (any cut at a 4-line record boundary is a valid FASTQ text; every GPU adds the same number of files in the
+ * same order); a GPU partitions the codes of its share over ALL table slices into lists that live in one exported arena,
+ * and a build first waits (device flags) until every GPU's lists are complete, pulls the codes of ITS table slices out
+ * of each peer's lists — one contiguous range per list, over NVLink — and counts them with its own.  Everything else is
+ * the sharded build above (peer stores of the finished slices, flags, the barrier contract).
+ *   eref_query_reserve   fixed-address arena for max_files lists of files up to max_file_bytes (same arguments on every GPU)
+ *   eref_lists_export / eref_lists_set_peer   like eref_table_export / eref_table_set_peer (which must come first)
+ *   eref_query_set_share on/off; while on, eref_query_add* take this GPU's share, the byte count of cal_sam_ratio is this
+ *                        share's only (down-sampling decisions are the caller's), and eref_run_host is refused. */
+#define EREF_LISTS_HANDLE_BYTES 64
+int  eref_query_reserve(eref_ctx* ctx, size_t max_file_bytes, int max_files);
+int  eref_lists_export(eref_ctx* ctx, void* ipc_handle, void** arena_dev);
+int  eref_lists_set_peer(eref_ctx* ctx, int peer_part, const void* ipc_handle, void* arena_dev);
+int  eref_query_set_share(eref_ctx* ctx, int on);
 /* queue the build of the files added so far and make the context's stream wait for the complete table */
 int  eref_table_join(eref_ctx* ctx);
 /* on: the table build and the framing census no longer run beside the main stream's kernels, so the phase times of

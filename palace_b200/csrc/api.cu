@@ -36,9 +36,12 @@ namespace {
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
+    bool view = false;                         // a window into memory someone else owns (fixed size, never freed here)
+    void attach(void* q, size_t bytes) { release(); p = q; cap = bytes; view = true; }
     cudaError_t ensure(size_t bytes)
     {
         if (bytes <= cap) return cudaSuccess;
+        if (view) return cudaErrorMemoryAllocation;
         if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }
         size_t want = bytes + bytes / 8 + 256;
         cudaError_t e = cudaMalloc(&p, want);
@@ -59,7 +62,7 @@ struct DevBuf {
         p = q; cap = want;
         return cudaSuccess;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release() { if (p && !view) cudaFree(p); p = nullptr; cap = 0; view = false; }
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
@@ -127,6 +130,17 @@ struct eref_ctx {
     bool join_pending = false;                 // a sharded build was queued and the main stream has not joined it yet
     eref_table_hook hook = nullptr;
     void* hook_arg = nullptr;
+    // Shared reads (eref_query_set_share): this GPU partitions only ITS share of every query file, into lists that live
+    // in one exported arena; a build pulls the codes of this GPU's table slices out of every peer's lists.
+    // arena layout per list: off[NSLICES + 1] u64 | cnt[NSLICES] u64 | codes[arena_cap_codes] u32, list_stride bytes apart
+    DevBuf list_arena, pulled;
+    size_t list_stride = 0;
+    unsigned long long arena_cap_codes = 0;
+    int arena_lists = 0;
+    bool share_reads = false;
+    struct ListPeer { uint8_t* arena = nullptr; bool ipc = false; };
+    ListPeer list_peers[MAX_PARTS];
+    uint32_t lists_epoch = 0;
     int probe_parts = 8;                       // EREF_PROBE_PARTS: rounds of the listed-word probe, 1 = whole table at once
     int bucket_bits = 32 - SLICE_BITS - 8;     // EREF_BUCKET_BITS: 2^bits coarse buckets, 256 slices per bucket by default
     // reference side
@@ -204,6 +218,8 @@ cudaEvent_t* list_events(eref_ctx* c, size_t k)
     return c->qev.data() + 4 * k;
 }
 
+// share_words: [0, 16) table-part flags | 16 done counter | 17 error word | 18 capacity guard | [32, 48) lists-ready flags
+constexpr int SHARE_WORDS = 64, LISTS_FLAG0 = 32;
 constexpr int HPIN_SEQ = 32;                   // h_pin[HPIN_SEQ + k]: sequence-line bytes of query file k
 constexpr int HPIN_CODES = 48;                 // h_pin[HPIN_CODES + k]: codes of query file k
 constexpr int HPIN_GUARD = 14;                 // h_pin[HPIN_GUARD]: the capacity guard word, read back with the scan
@@ -317,7 +333,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     int wrc = wait_table(c, st);              // an update still in flight reads the code lists this call rewrites
     if (wrc) return wrc;
     const bool direct = (c->flags & EREF_FLAG_DIRECT_COUNT) != 0;
-    if (c->parts > 1 && c->n_lists == 0) rebalance_parts(c, n);
+    if (c->parts > 1 && c->n_lists == 0) rebalance_parts(c, c->share_reads ? n * (uint64_t)c->parts : n);
     if (!direct && c->n_lists >= (size_t)MAX_LISTS)
         return eref_fail(EREF_ERR_LIMIT, "more than %d query files since the last eref_query_reset", MAX_LISTS);
     // events of this file: E1..E4 for the direct build (read at the end of this call), a set of its own otherwise
@@ -370,6 +386,8 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         // codes -> slice-ordered list: histogram over the 8192 table slices, exact offsets, coarse scatter from the
         // planes, fine partition through shared memory; counted by the next table build
         const int cbits = c->bucket_bits;
+        // shared reads: every GPU keeps ALL slices of its share of the reads; else only the slices of its table part
+        const uint32_t f_s0 = c->share_reads ? 0u : c->slice0, f_ns = c->share_reads ? (uint32_t)NSLICES : c->nslices;
         CUDA_TRY(c->part_ctr.ensure(((size_t)NSLICES * 2 + 512 + 4) * 8 + 260 * 4));
         unsigned long long* hist = c->part_ctr.as<unsigned long long>();
         unsigned long long* slice_tail = hist + NSLICES;
@@ -377,11 +395,20 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         unsigned long long* coarse_n = coarse_tail + 256;
         uint32_t* chunk_start = reinterpret_cast<uint32_t*>(coarse_n + 256);
         CUDA_TRY(cudaMemsetAsync(hist, 0, ((size_t)NSLICES * 2 + 256) * 8, st));
-        LAUNCH(c, launch_slice_hist(pl, plane_bits, c->masks, hist, c->slice0, c->nslices, st));
+        LAUNCH(c, launch_slice_hist(pl, plane_bits, c->masks, hist, f_s0, f_ns, st));
         unsigned long long* totals = chunk_start_end(chunk_start);     // {codes, padded size, chunks}
         if (c->lists.size() <= c->n_lists) c->lists.resize(c->n_lists + 1);
         eref_ctx::CodeList& L = c->lists[c->n_lists];
+        if (c->share_reads) {
+            if ((int)c->n_lists >= c->arena_lists)
+                return eref_fail(EREF_ERR_LIMIT, "shared reads: eref_query_reserve made room for %d files per build", c->arena_lists);
+            uint8_t* base = c->list_arena.as<uint8_t>() + c->n_lists * c->list_stride;     // the exported arena: fixed addresses
+            L.off.attach(base, ((size_t)NSLICES + 1) * 8);
+            L.cnt.attach(base + ((size_t)NSLICES + 1) * 8, (size_t)NSLICES * 8);
+            L.codes.attach(base + ((size_t)2 * NSLICES + 2) * 8, (size_t)c->arena_cap_codes * 4);
+        } else if (L.codes.view) { L.codes.release(); L.off.release(); L.cnt.release(); }
         CUDA_TRY(L.off.ensure(((size_t)NSLICES + 1) * 8)); CUDA_TRY(L.cnt.ensure((size_t)NSLICES * 8));
+
         // Sizes.  The number of codes is known to the device only.  A FASTQ record spends as many bytes on its quality
         // line as on its sequence line, so a file of n bytes holds fewer than n/2 sequence bytes and 3n/2 codes: when the
         // buffers already hold that much (they only grow), everything is queued without asking — k_slice_offsets
@@ -391,7 +418,7 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
         // (a sharded build keeps the codes of its slice range only; canonical codes thin out linearly towards the top
         // of the code space: the range [x0, x1) of it holds (1 - x0)^2 - (1 - x1)^2 of all codes)
         const double x0 = (double)c->slice0 / NSLICES, x1 = (double)(c->slice0 + c->nslices) / NSLICES;
-        const double part_frac = c->parts > 1 ? std::min(1.0, 1.15 * ((1 - x0) * (1 - x0) - (1 - x1) * (1 - x1))) : 1.0;
+        const double part_frac = c->parts > 1 && !c->share_reads ? std::min(1.0, 1.15 * ((1 - x0) * (1 - x0) - (1 - x1) * (1 - x1))) : 1.0;
         const unsigned long long est_codes = (unsigned long long)(3.0 * (double)(n / 2 + 1) * part_frac) + 4ull * NSLICES + 64;
         const unsigned long long cap_codes = std::min(L.codes.cap, c->codes_coarse.cap) / 4 > 4
                                                  ? std::min(L.codes.cap, c->codes_coarse.cap) / 4 - 4 : 0;
@@ -414,13 +441,16 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
             pl.nwords = (c->h_pin[11] + 31) >> 5;
             pl_scatter = pl;
             L.total = total_codes; L.total_pending = false;
-            const size_t want = (size_t)std::max<unsigned long long>(padded, c->force_exact ? 0ull : est_codes) * 4 + 16;
+            const size_t want = (size_t)std::max<unsigned long long>(padded, c->force_exact || L.codes.view ? 0ull : est_codes) * 4 + 16;
+            if (L.codes.view && want > L.codes.cap)
+                return eref_fail(EREF_ERR_LIMIT, "shared reads: a file of %llu bytes needs %zu bytes of code list, eref_query_reserve "
+                                                 "made room for %zu", (unsigned long long)n, want, L.codes.cap);
             CUDA_TRY(L.codes.ensure(want));
             CUDA_TRY(c->codes_coarse.ensure(want));
         }
         LAUNCH(c, launch_coarse_scatter(pl_scatter, optimistic ? plane_bits : nullptr, optimistic ? c->guard : nullptr, c->masks,
                                         cbits, L.off.as<unsigned long long>(), coarse_tail, c->codes_coarse.as<uint32_t>(),
-                                        c->codes_coarse.cap / 4, c->slice0, c->nslices, st));
+                                        c->codes_coarse.cap / 4, f_s0, f_ns, st));
         LAUNCH(c, launch_fine_partition(c->codes_coarse.as<uint32_t>(), L.off.as<unsigned long long>(), coarse_n, chunk_start,
                                         nchunks, cbits, slice_tail, L.codes.as<uint32_t>(), L.codes.cap / 4, st));
         // the partition kernels are queued; nothing below waits for them (times and byte counts: collect_times)
@@ -474,6 +504,44 @@ int start_table_update(eref_ctx* c)
         cl.off[k] = c->lists[k].off.as<unsigned long long>();
         cl.cnt[k] = c->lists[k].cnt.as<unsigned long long>();
         cl.cap[k] = c->lists[k].codes.cap / 4;
+    }
+    if (c->share_reads && c->parts > 1) {
+        // Shared reads: this GPU's lists hold all slices of ITS share of the reads.  Tell every peer they are complete,
+        // wait for theirs, pull the codes of this GPU's table slices out of each peer list (one contiguous range per list)
+        // into local staging, and count own lists + staged copies.
+        const int files = (int)c->n_lists;
+        if (files * c->parts > MAX_LISTS)
+            return eref_fail(EREF_ERR_LIMIT, "shared reads: %d files x %d GPUs exceed %d lists per build", files, c->parts, MAX_LISTS);
+        TableShare sig{};
+        sig.part = c->part;
+        sig.flags[0] = c->share_words; sig.n = 1;
+        for (int p = 0; p < c->parts; p++)
+            if (p != c->part) {
+                if (!c->peers[p].flags || !c->list_peers[p].arena)
+                    return eref_fail(EREF_ERR_STATE, "shared reads: peer %d is not wired (eref_table_set_peer, eref_lists_set_peer)", p);
+                sig.flags[sig.n++] = c->peers[p].flags;
+            }
+        c->lists_epoch++;
+        LAUNCH(c, launch_lists_signal(sig, LISTS_FLAG0, c->lists_epoch, st));      // behind this GPU's partition kernels
+        CUDA_TRY(cudaEventRecord(c->aux_ev[0], st));
+        CUDA_TRY(cudaStreamWaitEvent(ts, c->aux_ev[0], 0));
+        LAUNCH(c, launch_table_wait(c->share_words + LISTS_FLAG0, c->parts, c->lists_epoch, c->share_words + MAX_PARTS + 1, ts));
+        PullLists pull{};
+        CUDA_TRY(c->pulled.ensure((size_t)(c->parts - 1) * files * c->list_stride));
+        pull.dst = c->pulled.as<uint8_t>(); pull.list_stride = c->list_stride; pull.cap_codes = c->arena_cap_codes;
+        pull.s0 = c->slice0; pull.ns = c->nslices;
+        for (int p = 0; p < c->parts; p++)
+            if (p != c->part)
+                for (int f = 0; f < files; f++) {
+                    pull.src[pull.n] = c->list_peers[p].arena + (size_t)f * c->list_stride;
+                    uint8_t* d = pull.dst + (size_t)pull.n * c->list_stride;
+                    cl.off[cl.n] = reinterpret_cast<const unsigned long long*>(d);
+                    cl.cnt[cl.n] = cl.off[cl.n] + NSLICES + 1;
+                    cl.codes[cl.n] = reinterpret_cast<const uint32_t*>(d + ((size_t)2 * NSLICES + 2) * 8);
+                    cl.cap[cl.n] = c->arena_cap_codes;
+                    cl.n++; pull.n++;
+                }
+        LAUNCH(c, launch_pull_lists(pull, ts));
     }
     if (c->want_pop) CUDA_TRY(cudaMemsetAsync(c->level_pop.p, 0, 24, ts));
     // destinations of the finished slices: this GPU's table, and in a sharded build with peers every other GPU's
@@ -579,7 +647,7 @@ void rebalance_parts(eref_ctx* c, uint64_t first_file_bytes)
 {
     const char* mv = getenv("EREF_SHARD_MIN_BYTES");
     const double min_bytes = mv ? atof(mv) : 1.6e8;
-    c->build_sharded = 2.0 * (double)first_file_bytes >= min_bytes;
+    c->build_sharded = c->share_reads || 2.0 * (double)first_file_bytes >= min_bytes;   // (shared reads divide ALL query work)
     if (!c->build_sharded) { c->slice0 = 0; c->nslices = NSLICES; return; }
     c->part_w = part_weight(c->parts, 2 * first_file_bytes);
     set_part_range(c);
@@ -890,8 +958,8 @@ int eref_create(eref_ctx** out, int device, const int16_t coder[96], float hit_r
     if (e == cudaSuccess) e = c->counters.ensure(64);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->h_pin, (8 + MAX_BUCKETS) * 8, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc(&c->summary, (size_t)SUMMARY_WORDS * 4);
-    if (e == cudaSuccess) e = cudaMalloc((void**)&c->share_words, (MAX_PARTS + 4) * 4);
-    if (e == cudaSuccess) e = cudaMemset(c->share_words, 0, (MAX_PARTS + 4) * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->share_words, SHARE_WORDS * 4);
+    if (e == cudaSuccess) e = cudaMemset(c->share_words, 0, SHARE_WORDS * 4);
     if (e == cudaSuccess) c->guard = c->share_words + MAX_PARTS + 2;
     if (getenv("EREF_EXACT_SIZES")) c->force_exact = true;
     if (flags & EREF_FLAG_LEVEL_POP) c->want_pop = true;
@@ -920,6 +988,9 @@ void eref_destroy(eref_ctx* c)
                       &c->sample_hits, &c->need, &c->need_list, &c->hits0, &c->hits1, &c->hits2, &c->single, &c->trio, &c->good, &c->results,
                       &c->codes_tmp, &c->cell_pre};
     for (DevBuf* b : bufs) b->release();
+    for (int p = 0; p < MAX_PARTS; p++) if (c->list_peers[p].ipc) cudaIpcCloseMemHandle(c->list_peers[p].arena);
+    for (auto& L : c->lists) { L.codes.release(); L.off.release(); L.cnt.release(); }
+    c->list_arena.release(); c->pulled.release();
     for (int p = 0; p < MAX_PARTS; p++)
         if (c->peers[p].ipc) {
             cudaIpcCloseMemHandle(c->peers[p].bm3); cudaIpcCloseMemHandle(c->peers[p].summary);
@@ -1162,6 +1233,9 @@ static int run_host_impl(eref_ctx* c, const char* fq1, size_t n1, const char* fq
 {
     if (!c || (n1 && !fq1) || (n2 && !fq2) || (nf && !fasta) || (cap && !out))
         return eref_fail(EREF_ERR_ARG, "eref_run_host: null argument");
+    if (c->share_reads)
+        return eref_fail(EREF_ERR_STATE, "eref_run_host takes whole query files (cal_sam_ratio needs all of fq1): turn shared "
+                                         "reads off (eref_query_set_share) or use the phase calls");
     CUDA_TRY(cudaSetDevice(c->device));
     // fasta == NULL: screen this sample against the reference that is already set (one database, many samples)
     const bool resident = !fasta && nf == 0;
@@ -1550,6 +1624,11 @@ int eref_table_set_part(eref_ctx* c, int part, int parts)
     c->part_w = part_weight(parts, 0);
     c->build_sharded = true;
     set_part_range(c);
+    for (int p = 0; p < MAX_PARTS; p++) {
+        if (c->list_peers[p].ipc) cudaIpcCloseMemHandle(c->list_peers[p].arena);
+        c->list_peers[p] = eref_ctx::ListPeer();
+    }
+    c->share_reads = false;
     for (int p = 0; p < MAX_PARTS; p++) {           // peers are set after the part (a new layout drops the old wiring)
         if (c->peers[p].ipc) { cudaIpcCloseMemHandle(c->peers[p].bm3); cudaIpcCloseMemHandle(c->peers[p].summary); cudaIpcCloseMemHandle(c->peers[p].flags); }
         c->peers[p] = eref_ctx::Peer();
@@ -1589,6 +1668,77 @@ int eref_table_set_peer(eref_ctx* c, int peer_part, int peer_device, const void*
         else if (e != cudaSuccess) return eref_fail_cuda(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
     }
     P.bm3 = (uint32_t*)bm3_dev; P.summary = (uint32_t*)summary_dev; P.flags = (uint32_t*)flags_dev;
+    return 0;
+}
+
+int eref_query_reserve(eref_ctx* c, size_t max_file_bytes, int max_files)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (max_files < 1 || max_files > MAX_LISTS) return eref_fail(EREF_ERR_ARG, "eref_query_reserve: %d files (1..%d)", max_files, MAX_LISTS);
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = eref_sync(c);
+    if (rc) return rc;
+    // room for the codes of a well-formed FASTQ file of that size (3 per sequence byte, fewer than half the bytes are
+    // sequence), every slice padded to 4 codes
+    const unsigned long long cap = ((3ull * (max_file_bytes / 2 + 1) + 4ull * NSLICES + 64 + 3) & ~3ull) + 4;
+    const size_t stride = ((((size_t)2 * NSLICES + 2) * 8 + (size_t)cap * 4) + 255) & ~(size_t)255;
+    for (auto& L : c->lists) if (L.codes.view) { L.codes.release(); L.off.release(); L.cnt.release(); }
+    c->n_lists = 0; c->table_dirty = true;
+    c->list_arena.release();                   // (a new arena has a new address: peers must be wired again)
+    CUDA_TRY(c->list_arena.ensure(stride * max_files));
+    c->list_stride = stride; c->arena_cap_codes = cap; c->arena_lists = max_files;
+    CUDA_TRY(c->codes_coarse.ensure((size_t)cap * 4 + 16));
+    return 0;
+}
+
+int eref_lists_export(eref_ctx* c, void* ipc_handle, void** arena_dev)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (!c->list_arena.p) return eref_fail(EREF_ERR_STATE, "eref_lists_export before eref_query_reserve");
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (ipc_handle) {
+        static_assert(sizeof(cudaIpcMemHandle_t) == EREF_LISTS_HANDLE_BYTES, "handle blob size");
+        cudaIpcMemHandle_t h;
+        CUDA_TRY(cudaIpcGetMemHandle(&h, c->list_arena.p));
+        memcpy(ipc_handle, &h, sizeof h);
+    }
+    if (arena_dev) *arena_dev = c->list_arena.p;
+    return 0;
+}
+
+int eref_lists_set_peer(eref_ctx* c, int peer_part, const void* ipc_handle, void* arena_dev)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (peer_part < 0 || peer_part >= c->parts || peer_part == c->part)
+        return eref_fail(EREF_ERR_ARG, "eref_lists_set_peer: part %d (this context is part %d of %d)", peer_part, c->part, c->parts);
+    CUDA_TRY(cudaSetDevice(c->device));
+    eref_ctx::ListPeer& P = c->list_peers[peer_part];
+    if (P.ipc) cudaIpcCloseMemHandle(P.arena);
+    P = eref_ctx::ListPeer();
+    if (ipc_handle) {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, ipc_handle, sizeof h);
+        void* a = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&a, h, cudaIpcMemLazyEnablePeerAccess));
+        P.arena = (uint8_t*)a; P.ipc = true;
+        return 0;
+    }
+    if (!arena_dev) return eref_fail(EREF_ERR_ARG, "eref_lists_set_peer: null arena pointer");
+    P.arena = (uint8_t*)arena_dev;             // (peer access was enabled by eref_table_set_peer)
+    return 0;
+}
+
+int eref_query_set_share(eref_ctx* c, int on)
+{
+    if (!c) return eref_fail(EREF_ERR_ARG, "null context");
+    if (on && (c->parts < 2 || !c->list_arena.p))
+        return eref_fail(EREF_ERR_STATE, "shared reads need eref_table_set_part (parts > 1) and eref_query_reserve first");
+    if (on && (c->flags & EREF_FLAG_DIRECT_COUNT)) return eref_fail(EREF_ERR_UNSUPPORTED, "the direct build cannot share reads");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = eref_sync(c);
+    if (rc) return rc;
+    c->share_reads = on != 0;
+    c->n_lists = 0; c->table_dirty = true;
     return 0;
 }
 

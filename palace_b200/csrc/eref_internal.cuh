@@ -202,6 +202,17 @@ struct TableShare {
 cudaError_t launch_count_slices(const CountLists& lists, const TableShare& share, unsigned long long* level_pop,
                                 cudaStream_t st);
 cudaError_t launch_table_wait(const uint32_t* flags, int n, uint32_t epoch, uint32_t* err, cudaStream_t st);
+// shared reads: peer lists (arena layout) whose slices [s0, s0 + ns) are pulled into local staging, one slot per list
+struct PullLists {
+    const uint8_t* src[MAX_LISTS];
+    uint8_t* dst;
+    size_t list_stride;
+    unsigned long long cap_codes;
+    uint32_t s0, ns;
+    int n;
+};
+cudaError_t launch_lists_signal(const TableShare& share, uint32_t flag0, uint32_t epoch, cudaStream_t st);
+cudaError_t launch_pull_lists(const PullLists& pl, cudaStream_t st);
 cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, uint32_t summary_words, cudaStream_t st);
 cudaError_t launch_popcount(const uint32_t* bm, uint64_t nwords, unsigned long long* out, cudaStream_t st);
 // scan.cu

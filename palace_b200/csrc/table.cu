@@ -717,6 +717,41 @@ __global__ void k_table_wait(const uint32_t* __restrict__ flags, int n, uint32_t
     }
 }
 
+// ---- shared reads: every GPU partitions its share of the reads; a build pulls its slices out of every peer's lists ----
+// "My lists of build `epoch` are complete": raise this GPU's word in every GPU's lists-ready flags (release, system scope).
+__global__ void k_lists_signal(TableShare share, uint32_t flag0, uint32_t epoch)
+{
+    if (threadIdx.x >= (unsigned)share.n) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(share.flags[threadIdx.x] + flag0 + share.part), "r"(epoch) : "memory");
+}
+
+// One peer list (blockIdx.y) -> local staging: the codes of the slices [s0, s0 + ns) are ONE contiguous range of a
+// slice-ordered list (every slice starts 16-byte aligned), copied with 16-byte loads over NVLink; the offsets are rebased
+// onto the staging copy, the counts copied.  Lists use the arena layout off[NSLICES + 1] | cnt[NSLICES] | codes[cap].
+__global__ void __launch_bounds__(256)
+k_pull_lists(PullLists pl)
+{
+    const int slot = blockIdx.y;
+    const uint8_t* src = pl.src[slot];
+    uint8_t* dst = pl.dst + (size_t)slot * pl.list_stride;
+    const unsigned long long* soff = reinterpret_cast<const unsigned long long*>(src);
+    const unsigned long long* scnt = soff + NSLICES + 1;
+    const uint4* scodes = reinterpret_cast<const uint4*>(src + ((size_t)2 * NSLICES + 2) * 8);
+    unsigned long long* doff = reinterpret_cast<unsigned long long*>(dst);
+    unsigned long long* dcnt = doff + NSLICES + 1;
+    uint4* dcodes = reinterpret_cast<uint4*>(dst + ((size_t)2 * NSLICES + 2) * 8);
+    const unsigned long long lo = soff[pl.s0], hi = soff[pl.s0 + pl.ns];
+    EREF_ASSERT((lo & 3) == 0 && hi >= lo && hi - lo <= pl.cap_codes);
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long s = tid; s <= pl.ns; s += nthreads) {
+        doff[pl.s0 + s] = soff[pl.s0 + s] - lo;
+        if (s < pl.ns) dcnt[pl.s0 + s] = scnt[pl.s0 + s];
+    }
+    const unsigned long long units = (hi - lo + 3) >> 2;
+    for (unsigned long long u = tid; u < units; u += nthreads) dcodes[u] = scodes[(lo >> 2) + u];
+}
+
 // summary bit = OR of 16 consecutive level-3 bits: a 32 MiB filter that stays in L2 during the scan
 // (direct build only; the partitioned build writes the summary from shared memory)
 __global__ void __launch_bounds__(256)
@@ -861,6 +896,19 @@ cudaError_t launch_count_slices(const CountLists& lists, const TableShare& share
     if (e != cudaSuccess) return e;
     if (level_pop) k_count_slices<true><<<share.ns, COUNT_THREADS, smem, st>>>(lists, share.bm3[0], share.summary[0], level_pop, share.s0);
     else k_count_slices<false><<<share.ns, COUNT_THREADS, smem, st>>>(lists, share.bm3[0], share.summary[0], nullptr, share.s0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lists_signal(const TableShare& share, uint32_t flag0, uint32_t epoch, cudaStream_t st)
+{
+    k_lists_signal<<<1, 32, 0, st>>>(share, flag0, epoch);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pull_lists(const PullLists& pl, cudaStream_t st)
+{
+    if (!pl.n || !pl.ns) return cudaSuccess;
+    k_pull_lists<<<dim3(148 * 2, (unsigned)pl.n), 256, 0, st>>>(pl);
     return cudaGetLastError();
 }
 

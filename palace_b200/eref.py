@@ -45,6 +45,7 @@ ABI_SYMBOLS = (
     "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
     "eref_table_export", "eref_table_set_part", "eref_table_set_peer", "eref_table_set_hook", "eref_table_part_range",
     "eref_table_join", "eref_sync", "eref_run_results_device", "eref_run_host_keep", "eref_set_serial",
+    "eref_query_reserve", "eref_lists_export", "eref_lists_set_peer", "eref_query_set_share",
 )
 
 
@@ -113,6 +114,10 @@ def load_library() -> ctypes.CDLL:
     lib.eref_table_join.argtypes = [c_void_p]
     lib.eref_sync.argtypes = [c_void_p]
     lib.eref_set_serial.argtypes = [c_void_p, c_int]
+    lib.eref_query_reserve.argtypes = [c_void_p, c_size_t, c_int]
+    lib.eref_lists_export.argtypes = [c_void_p, c_void_p, POINTER(c_void_p)]
+    lib.eref_lists_set_peer.argtypes = [c_void_p, c_int, c_void_p, c_void_p]
+    lib.eref_query_set_share.argtypes = [c_void_p, c_int]
     lib.eref_run_results_device.argtypes = [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]
     lib.eref_run_host_keep.argtypes = [c_void_p, c_void_p, c_uint64, c_void_p, c_uint64]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
@@ -353,6 +358,23 @@ class ErefGPU:
                                                       c_void_p(None if h else b), c_void_p(None if h else f)),
                "eref_table_set_peer")
 
+    # ---- shared reads: every GPU adds 1/N of each query file; a build pulls its table slices out of the peers' lists ----
+    def query_reserve(self, max_file_bytes: int, max_files: int = 2):
+        _check(self.lib, self.lib.eref_query_reserve(self._h, max_file_bytes, max_files), "eref_query_reserve")
+
+    def lists_export(self, ipc: bool = False):
+        h = ctypes.create_string_buffer(64) if ipc else None
+        a = c_void_p()
+        _check(self.lib, self.lib.eref_lists_export(self._h, h, byref(a)), "eref_lists_export")
+        return (h.raw if ipc else None), a.value
+
+    def lists_set_peer(self, peer_part: int, exported):
+        h, a = exported
+        _check(self.lib, self.lib.eref_lists_set_peer(self._h, peer_part, h, c_void_p(None if h else a)), "eref_lists_set_peer")
+
+    def query_set_share(self, on: bool):
+        _check(self.lib, self.lib.eref_query_set_share(self._h, 1 if on else 0), "eref_query_set_share")
+
     def table_set_hook(self, fn):
         """fn(cuda_stream: int) -> None completes the table on that stream (e.g. an in-place NCCL all-gather)"""
         def _cb(_arg, stream):
@@ -490,7 +512,7 @@ def draw_keep(ratio: int, n_lines: int, reseed: bool = True) -> np.ndarray:
 def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float = 0.9,
              perfect_hit_ratio: float = 0.85, threads: int = 1, *, coder=None, devices=(0,), prune: bool = True,
              bucketed: bool = True, pipelined: bool = False, chunks: int = 4, return_results: bool = False,
-             down_sampling_size: int = DOWN_SAMPLING_SIZE, shard_table: bool = False):
+             down_sampling_size: int = DOWN_SAMPLING_SIZE, shard_table: bool = False, share_reads: bool = False):
     """The whole `eref` path on in-memory texts; returns the stdout text (and the raw records).
 
     `devices`: GPUs to shard the database over (one context each, run one after the other here —
@@ -499,7 +521,7 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
     del threads                                            # a hint in the reference, unused here
     if shard_table and len(devices) > 1:
         return _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hit_ratio, coder, devices, prune,
-                                       pipelined, chunks, return_results)
+                                       pipelined, chunks, return_results, share_reads)
     if interval_out:
         open(interval_out, "w").close()                   # :825
     if coder is None:
@@ -544,8 +566,9 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
     return (text, res) if return_results else text
 
 
-def wire_table_peers(ctxs):
-    """contexts of ONE process, one per part: every builder gets the raw table pointers of all the others"""
+def wire_table_peers(ctxs, share_file_bytes: int = 0, files: int = 2):
+    """contexts of ONE process, one per part: every builder gets the raw table pointers of all the others; with
+    share_file_bytes also the list arenas (shared reads: every context then adds 1/N of each query file)"""
     exported = [g.table_export() for g in ctxs]
     for i, g in enumerate(ctxs):
         g.table_set_part(i, len(ctxs))
@@ -553,10 +576,32 @@ def wire_table_peers(ctxs):
         for j, h in enumerate(ctxs):
             if i != j:
                 g.table_set_peer(j, exported[j], h.device)
+    if share_file_bytes:
+        for g in ctxs:
+            g.query_reserve(share_file_bytes, files)
+        arenas = [g.lists_export() for g in ctxs]
+        for i, g in enumerate(ctxs):
+            for j in range(len(ctxs)):
+                if i != j:
+                    g.lists_set_peer(j, arenas[j])
+            g.query_set_share(True)
+
+
+def split_fastq(fq, shares: int):
+    """a FASTQ text cut into `shares` pieces at 4-line record boundaries (each piece is a valid FASTQ text)"""
+    a = _as_bytes_array(fq)
+    nl = np.flatnonzero(a == 10)
+    n_rec = (nl.size + (1 if a.size and a[-1] != 10 else 0)) // 4
+    cuts = [0]
+    for k in range(1, shares):
+        r = n_rec * k // shares
+        cuts.append(int(nl[4 * r - 1]) + 1 if r > 0 else 0)
+    cuts.append(a.size)
+    return [a[cuts[k]:cuts[k + 1]] for k in range(shares)]
 
 
 def _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hit_ratio, coder, devices, prune, pipelined,
-                            chunks, return_results):
+                            chunks, return_results, share_reads=False):
     """run_eref with the database AND the table build sharded over `devices` (entries may repeat: several contexts on
     one GPU emulate a multi-GPU box).  Context i counts its range of the 8192 table slices and stores them into
     every context's table; here the contexts run one after the other, so every build is waited for before any scan."""
@@ -568,6 +613,28 @@ def _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hi
     cuts = shard_offsets(fasta, len(devices))
     ctxs = [ErefGPU(coder, hit_ratio, perfect_hit_ratio, d, prune) for d in devices]
     try:
+        if share_reads:
+            # shared reads: context i adds the i-th of N pieces of each query file (cut at record boundaries)
+            if pipelined:
+                raise ErefError("eref_run_host takes whole query files: shared reads go through the phase calls")
+            s1, s2 = split_fastq(fq1, len(ctxs)), split_fastq(fq2, len(ctxs))
+            wire_table_peers(ctxs, share_file_bytes=max(max(x.size for x in s1), max(x.size for x in s2), 1))
+            parts = [None] * len(ctxs)
+            for i, g in enumerate(ctxs):
+                g.query_add(s1[i]); g.query_add(s2[i])
+            for i, g in enumerate(ctxs):
+                g.ref_set(fasta[cuts[i]:cuts[i + 1]])      # queues this part's build: signal, wait, pull, count
+            for g in ctxs:
+                g.sync()
+            for i, g in enumerate(ctxs):
+                parts[i] = g.scan().copy()
+            base = 0
+            for p in parts:
+                p["ordinal"] += base
+                base += p.size
+            res = np.concatenate(parts) if parts else np.zeros(0, RESULT_DTYPE)
+            text = format_results(res)
+            return (text, res) if return_results else text
         wire_table_peers(ctxs)
         parts = [None] * len(ctxs)
         if pipelined:

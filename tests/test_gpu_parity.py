@@ -804,3 +804,60 @@ def test_small_queries_are_not_shared_out(golden, monkeypatch):
     finally:
         for g in ctxs:
             g.close()
+
+
+# ---- shared reads: every GPU partitions 1/N of each query file; a build pulls its table slices out of the peers' lists ----
+
+def test_split_fastq_cuts_at_record_boundaries():
+    db, f1, f2, _ = _case(90, n_genomes=10, db_bp=100_000, q_bp=60_000)
+    for shares in (1, 2, 3, 8):
+        parts = eref.split_fastq(f1, shares)
+        assert np.concatenate(parts).tobytes() == f1.tobytes()
+        for p in parts:
+            assert p.size == 0 or (p[0] == ord("@") and p[-1] == 10 and np.count_nonzero(p == 10) % 4 == 0)
+
+
+@pytest.mark.parametrize("parts", [2, 3, 4, 8])
+def test_shared_reads_equal_the_replicated_build(oracle, parts):
+    """N contexts on one GPU, each adding 1/N of the reads: the tables every context ends up with, hence the records, equal
+    those of one context that adds everything, and the oracle's"""
+    db, f1, f2, _ = _case(91 + parts, n_genomes=90, db_bp=2_500_000, q_bp=700_000)
+    coder = eref.random_coder(91)
+    want = oracle.run(f1, f2, db.text, coder, 0.9, 0.85, threads=4)
+    for prune in (True, False):
+        _, sh = eref.run_eref(f1, f2, db.text, coder=coder, devices=(0,) * parts, prune=prune, shard_table=True, share_reads=True,
+                              return_results=True)
+        assert sh.size == want.size and (sh == want).all()
+    assert (want["el"] > 0).any()
+
+
+def test_shared_reads_levels_and_repeated_builds(golden):
+    """level populations summed over the parts equal one context's; a second sample through the same wiring (new epoch,
+    other files, ragged shares: one context gets an empty piece) is right too; run_host is refused while sharing"""
+    name, meta, fa, f1, f2 = golden
+    with eref.ErefGPU(meta["coder"], level_pop=True) as one:
+        one.query_add(f1); one.query_add(f2)
+        whole = [one.query_popcount(l) for l in (1, 2, 3)]
+    _, want = eref.run_eref(f1, f2, fa, coder=meta["coder"], return_results=True)
+    _, want_swapped = eref.run_eref(f2, f2, fa, coder=meta["coder"], return_results=True)
+    ctxs = [eref.ErefGPU(meta["coder"], level_pop=True) for _ in range(3)]
+    try:
+        eref.wire_table_peers(ctxs, share_file_bytes=max(f1.size, f2.size))
+        for sample, expect in (((f1, f2), want), ((f2, f2), want_swapped)):
+            a, b = eref.split_fastq(sample[0], 3), eref.split_fastq(sample[1], 2) + [np.zeros(0, np.uint8)]
+            for i, g in enumerate(ctxs):
+                g.query_reset(); g.query_add(a[i]); g.query_add(b[i])
+            for g in ctxs:
+                g.ref_set(fa)
+            for g in ctxs:
+                g.sync()
+            if sample[0] is f1:
+                pops = [[g.query_popcount(l) for l in (1, 2, 3)] for g in ctxs]
+                assert [sum(p[l] for p in pops) for l in range(3)] == whole
+            for g in ctxs:
+                assert (g.scan() == expect).all()
+        with pytest.raises(eref.ErefError):
+            ctxs[0].run_host(f1, f2, fa)
+    finally:
+        for g in ctxs:
+            g.close()
