@@ -252,6 +252,8 @@ class Rig:
         self.g.set_stream(self.stream.cuda_stream)
         self.g_full = None                                 # second context, candidate filter off (scan_unpruned)
         self.table_mode = "one GPU: whole table built locally"
+        self.can_share = False                             # shared reads need the peer pointers
+        self.sharing = False
         if self.world > 1:
             self.table_mode = self.wire_table()
 
@@ -291,6 +293,11 @@ class Rig:
                     print(f"rank {rank}: cannot open a peer's table: {e}", file=sys.stderr)
                     ok = False
             if self.all_ok(ok):
+                self.can_share = self.args.reads == "shared"
+                if self.can_share:
+                    return (f"shared reads: each of the {world} GPUs packs and partitions 1/{world} of every query file; a build waits "
+                            f"for the peers' lists (device flags), pulls the codes of its table slices out of them over NVLink "
+                            f"(CUDA-IPC peer pointers), counts them and stores the finished slices into every GPU's table")
                 return (f"shared out over {world} GPUs when the query is large enough (EREF_SHARD_MIN_BYTES, default 160 MB of "
                         f"FASTQ text): each GPU counts its part of the table slices and stores them into every GPU's table "
                         f"through CUDA-IPC peer pointers (NVLink), device-side flags; smaller queries: every GPU counts all")
@@ -311,6 +318,28 @@ class Rig:
         g.table_set_hook(hook)
         return (f"shared out over {world} GPUs when the query is large enough (EREF_SHARD_MIN_BYTES): each GPU counts its "
                 f"part of the table slices, one NCCL broadcast per part (512 + 32 MiB in all) completes the tables")
+
+    def wire_lists(self, share_bytes):
+        """shared reads: a fixed-address arena for this job's lists on every rank, handles exchanged (setup, untimed)"""
+        g = self.g
+        g.query_set_share(False)
+        self.sharing = False
+        t = self.torch.tensor([int(share_bytes)], dtype=self.torch.int64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        g.query_reserve(int(t.item()) + 4096, 2)
+        blobs = [None] * self.world
+        self.dist.all_gather_object(blobs, g.lists_export(ipc=True)[0])
+        for p in range(self.world):
+            if p != self.rank:
+                g.lists_set_peer(p, (blobs[p], 0))
+        self.barrier()
+
+    def set_sharing(self, on):
+        if self.can_share and on != self.sharing:
+            self.barrier()
+            self.g.query_set_share(on)
+            self.sharing = on
+            self.barrier()
 
     def full_ctx(self):
         if self.g_full is None:
@@ -363,6 +392,7 @@ class Job:
             self.fa_d = self.fa_h.to(rig.dev, non_blocking=True)
             f1_d = torch.from_numpy(f1_np).to(rig.dev)
             f2_d = torch.from_numpy(f2_np).to(rig.dev)
+            self.s1_d, self.s2_d = f1_d, f2_d             # this rank's share of the reads (what it generated)
             if rig.world > 1:                              # the query is the same on every rank
                 f1_d = gather_bytes(f1_d, rig.world, rig.dev)
                 f2_d = gather_bytes(f2_d, rig.world, rig.dev)
@@ -370,6 +400,8 @@ class Job:
             self.f1_h = f1_d.cpu().pin_memory()
             self.f2_h = f2_d.cpu().pin_memory()
         rig.stream.synchronize()
+        if rig.can_share:
+            rig.wire_lists(max(f1_np.size, f2_np.size))
         self.host_cap = int(np.count_nonzero(fa_np == 62)) + 16
         # N > 1, e2e: the query is the same on every rank, so each rank uploads 1/N of it and NCCL all-gathers the
         # text over NVLink; the library takes the gathered (device) text and this rank's database shard (host)
@@ -383,6 +415,15 @@ class Job:
                                    "full": torch.empty(rig.world * slot, dtype=torch.uint8, device=rig.dev), "n": h.numel()})
 
     # ---- steps ----
+    def add_query(self, g):
+        """both query files: whole (replicated on every rank), or — shared reads — this rank's 1/N of each"""
+        if g is self.rig.g and self.rig.sharing:
+            g.query_add_device(self.s1_d.data_ptr(), self.s1_d.numel(), want_bytes=False)
+            g.query_add_device(self.s2_d.data_ptr(), self.s2_d.numel(), want_bytes=False)
+        else:
+            g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
+            g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
+
     def step_device(self, g=None, collect=None):
         # no call below waits for its own kernels beyond the sizes the host needs for allocations; the phase times
         # are read (which does wait) only in the instrumented steps, outside the timed region
@@ -390,8 +431,7 @@ class Job:
         rig = self.rig
         g = g or rig.g
         g.query_reset()
-        g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
-        g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
+        self.add_query(g)
         g.ref_set_device(self.fa_d.data_ptr(), self.fa_d.numel())
         ptr, n = g.scan_device(wait=False)
         merged = None
@@ -435,6 +475,7 @@ class Job:
     # ---- measurements ----
     def time_device(self, steps, warmup):
         rig, torch = self.rig, self.rig.torch
+        rig.set_sharing(True)
         acc = {}
         with torch.cuda.stream(rig.stream):
             for _ in range(warmup):
@@ -463,6 +504,9 @@ class Job:
             launches = rig.g.timings()["kernel_launches"] - launches0
             clocks = sampler.stop() if sampler else None
         self.avg = {p: acc[p] / PHASE_STEPS for p in PHASES}
+        if rig.sharing:                                    # every rank saw its share of the reads only
+            self.info["seq_bytes"] = int(rig.reduce(float(self.info["seq_bytes"]), "sum"))
+            self.info["query_codes"] = int(rig.reduce(float(self.info["query_codes"]), "sum"))
         if rig.world > 1:
             to, tb, _, _ = rig.g.table_part_range()
             self.info["table_build"] = ("every GPU counts the whole table (query below EREF_SHARD_MIN_BYTES)" if tb == 1 << 29 else
@@ -474,6 +518,7 @@ class Job:
 
     def time_host(self, steps, warmup):
         rig, torch = self.rig, self.rig.torch
+        rig.set_sharing(False)                             # eref_run_host takes whole files
         with torch.cuda.stream(rig.stream):
             for _ in range(min(warmup, 2)):
                 self.step_host()
@@ -532,8 +577,7 @@ class Job:
 
         def step_resident():
             g.query_reset()
-            g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
-            g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
+            self.add_query(g)
             ptr, n = g.scan_device(wait=False)
             if rig.world > 1:
                 allgather_records(rig.device_records(ptr, n), n, self.info["slot"], compact=False)
@@ -546,6 +590,7 @@ class Job:
                 allgather_records(t, rec.size, self.info.get("slot"))
             else:
                 g.run_host(self.f1_h.numpy(), self.f2_h.numpy(), None, cap=self.host_cap)
+        rig.set_sharing(True)
         with torch.cuda.stream(rig.stream):
             g.ref_set_device(self.fa_d.data_ptr(), self.fa_d.numel())
             step_resident()
@@ -557,6 +602,8 @@ class Job:
             r1.record(rig.stream)
             rig.barrier()
             res_ms = rig.reduce(r0.elapsed_time(r1), "max") / steps
+        rig.set_sharing(False)
+        with torch.cuda.stream(rig.stream):
             step_host_resident()
             rig.barrier()
             t0 = time.perf_counter()
@@ -585,8 +632,9 @@ class Job:
         ms = []
         with torch.cuda.stream(rig.stream):
             g.query_reset()
-            g.query_add_device(self.f1_d.data_ptr(), self.f1_d.numel(), want_bytes=False)
-            g.query_add_device(self.f2_d.data_ptr(), self.f2_d.numel(), want_bytes=False)
+            if g is rig.g:
+                rig.set_sharing(False)
+            self.add_query(g)
             g.ref_set_device(self.fa_d.data_ptr(), self.fa_d.numel())
             for i in range(steps + 1):
                 ptr, n = g.scan_device(wait=True)
@@ -734,6 +782,7 @@ def sub_record(rig, job, steps, warmup, parity_records, with_e2e=True, with_unpr
     if with_unpruned:
         out["scan_unpruned"], _ = job.scan_unpruned()
     if not rig.args.no_parity:
+        rig.set_sharing(False)
         with rig.torch.cuda.stream(rig.stream):
             job.step_host()                                # (a collective at N > 1: every rank takes part)
         out["parity"] = job.parity(job.last_host_records.copy(), parity_records)
@@ -762,16 +811,19 @@ def run_b200(args):
         unpruned, rec_full = job.scan_unpruned()
     par = None
     if not args.no_parity:
+        rig.set_sharing(False)
         with rig.torch.cuda.stream(rig.stream):
             job.step_host()
             rec_host = job.last_host_records.copy()
-            # and the device-resident path that `value` times
+        # and the device-resident path that `value` times (at N > 1: shared reads), against the host-buffer call's records
+        rig.set_sharing(True)
+        with rig.torch.cuda.stream(rig.stream):
             g = rig.g
             g.query_reset()
-            g.query_add_device(job.f1_d.data_ptr(), job.f1_d.numel(), want_bytes=False)
-            g.query_add_device(job.f2_d.data_ptr(), job.f2_d.numel(), want_bytes=False)
+            job.add_query(g)
             g.ref_set_device(job.fa_d.data_ptr(), job.fa_d.numel())
             rec_dev = g.scan().copy()
+        rig.set_sharing(False)
         par = job.parity(rec_host)
         same_paths = rig.reduce(1.0 if (rec_dev.size == rec_host.size and (rec_dev == rec_host).all()) else 0.0, "min") > 0.5
         same_full = rig.reduce(1.0 if (rec_full is None or (rec_full.size == rec_host.size and (rec_full == rec_host).all()))
@@ -1079,6 +1131,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--strong", default="c3,c4", help="strong-scaling sub-records: comma list of c3, c4, or none")
+    ap.add_argument("--reads", default="shared", choices=["shared", "replicated"],
+                    help="N>1, device-resident steps: every GPU packs 1/N of the reads (needs peer pointers) or all of them")
     ap.add_argument("--table", default="auto", choices=["auto", "peer", "allgather", "replicated"],
                     help="N>1: how the query table is built (auto: peer stores over CUDA IPC, else NCCL all-gather)")
     ap.add_argument("--no-prune", action="store_true", help="probe all three streams at every position")
