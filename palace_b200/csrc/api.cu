@@ -333,7 +333,9 @@ int query_add_impl(eref_ctx* c, const uint8_t* text, uint64_t n, const uint32_t*
     int wrc = wait_table(c, st);              // an update still in flight reads the code lists this call rewrites
     if (wrc) return wrc;
     const bool direct = (c->flags & EREF_FLAG_DIRECT_COUNT) != 0;
-    if (c->parts > 1 && c->n_lists == 0) rebalance_parts(c, c->share_reads ? n * (uint64_t)c->parts : n);
+    // (shared reads: the shares differ in size from GPU to GPU, the cut points must not — take the reserved file size)
+    if (c->parts > 1 && c->n_lists == 0)
+        rebalance_parts(c, c->share_reads ? (uint64_t)((c->arena_cap_codes - 4ull * NSLICES) / 3 * 2) * (uint64_t)c->parts : n);
     if (!direct && c->n_lists >= (size_t)MAX_LISTS)
         return eref_fail(EREF_ERR_LIMIT, "more than %d query files since the last eref_query_reset", MAX_LISTS);
     // events of this file: E1..E4 for the direct build (read at the end of this call), a set of its own otherwise
@@ -1621,6 +1623,7 @@ int eref_table_set_part(eref_ctx* c, int part, int parts)
     int rc = eref_sync(c);
     if (rc) return rc;
     c->parts = parts; c->part = part;
+    if (parts > 1) CUDA_TRY(preload_share_kernels());
     c->part_w = part_weight(parts, 0);
     c->build_sharded = true;
     set_part_range(c);

@@ -211,6 +211,7 @@ struct PullLists {
     uint32_t s0, ns;
     int n;
 };
+cudaError_t preload_share_kernels();
 cudaError_t launch_lists_signal(const TableShare& share, uint32_t flag0, uint32_t epoch, cudaStream_t st);
 cudaError_t launch_pull_lists(const PullLists& pl, cudaStream_t st);
 cudaError_t launch_build_summary(const uint32_t* bm3, uint32_t* summary, uint32_t summary_words, cudaStream_t st);

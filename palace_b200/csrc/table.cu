@@ -899,6 +899,22 @@ cudaError_t launch_count_slices(const CountLists& lists, const TableShare& share
     return cudaGetLastError();
 }
 
+// With lazy module loading (the CUDA 12 default) a kernel is loaded at its first launch, which may synchronise the
+// context: a first launch issued while k_table_wait is already spinning on this GPU would wait for the spin, and the
+// spin for a peer.  Loading the kernels of the shared build up front keeps the host out of that wait.
+cudaError_t preload_share_kernels()
+{
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, k_table_wait);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, k_lists_signal);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, k_pull_lists);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, k_count_slices_persistent<false, true>);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, k_count_slices_persistent<true, true>);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, k_count_slices_persistent<false, false>);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, k_count_slices_persistent<true, false>);
+    return e;
+}
+
 cudaError_t launch_lists_signal(const TableShare& share, uint32_t flag0, uint32_t epoch, cudaStream_t st)
 {
     k_lists_signal<<<1, 32, 0, st>>>(share, flag0, epoch);

@@ -17,6 +17,9 @@ os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 # the test queries are megabytes: share every table build out, however small (the library would count a small query on
 # every GPU for itself); test_small_queries_are_not_shared_out turns the default back on
 os.environ.setdefault("EREF_SHARD_MIN_BYTES", "0")
+# ... and load every kernel when the library is loaded: a kernel's first launch may synchronise the context, which would
+# wait for a wait kernel of ANOTHER emulated GPU spinning on this same device (on a real box each GPU has its own context)
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
 
 
 def pytest_configure(config):
