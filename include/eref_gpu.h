@@ -210,6 +210,19 @@ int  eref_timings(eref_ctx* ctx, eref_phase_times* out);
 /* the stdout line of :615-617; returns bytes written, 0 if the record is not selected */
 int  eref_format_line(const eref_result* r, char* buf, size_t cap);
 
+/* eref_query_census_device without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Needs no context: it works on the CURRENT device, queues everything on cuda_stream (0 = default stream)
+ * and returns without waiting.  fastq_dev: n bytes of FASTQ text in device memory, 16-byte aligned;
+ * out_dev: two uint64 in device memory, [0] = bytes on sequence lines, [1] = sequence lines — the two numbers
+ * eref_query_census[_device] return.  The per-tile scratch of the pass lives in one file-scope __device__ array of
+ * 512 KiB (csrc/noalloc.cu) that every GPU using the library holds until the process exits, which bounds the text:
+ * n > EREF_NOALLOC_MAX_BYTES is refused with EREF_ERR_LIMIT.  Every call shares that array: calls ordered on one stream
+ * are safe, calls that overlap on the GPU (different streams or threads) race and give wrong counts.
+ * Calls no cudaMalloc / cudaFree / allocating library routine. */
+#define EREF_NOALLOC_MAX_BYTES (256ull << 20)
+int  eref_census_noalloc(const void* fastq_dev, size_t n, uint64_t* out_dev, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

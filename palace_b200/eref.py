@@ -46,7 +46,9 @@ ABI_SYMBOLS = (
     "eref_table_export", "eref_table_set_part", "eref_table_set_peer", "eref_table_set_hook", "eref_table_part_range",
     "eref_table_join", "eref_sync", "eref_run_results_device", "eref_run_host_keep", "eref_set_serial",
     "eref_query_reserve", "eref_lists_export", "eref_lists_set_peer", "eref_query_set_share",
+    "eref_census_noalloc",
 )
+NOALLOC_MAX_BYTES = 256 << 20          # EREF_NOALLOC_MAX_BYTES
 
 
 class PhaseTimes(Structure):
@@ -122,6 +124,7 @@ def load_library() -> ctypes.CDLL:
     lib.eref_run_host_keep.argtypes = [c_void_p, c_void_p, c_uint64, c_void_p, c_uint64]
     lib.eref_timings.argtypes = [c_void_p, POINTER(PhaseTimes)]
     lib.eref_format_line.argtypes = [c_void_p, ctypes.c_char_p, c_size_t]
+    lib.eref_census_noalloc.argtypes = [c_void_p, c_size_t, c_void_p, c_void_p]
     _lib = lib
     return lib
 
@@ -129,6 +132,15 @@ def load_library() -> ctypes.CDLL:
 def _check(lib, rc, what):
     if rc != 0:
         raise ErefError(f"{what} failed ({rc}): {lib.eref_last_error().decode(errors='replace')}")
+
+
+def census_noalloc(fastq_dev_ptr: int, n: int, out_dev_ptr: int, stream: int = 0):
+    """eref_census_noalloc (no counterpart in the reference): the census of a FASTQ text in DEVICE memory on the current
+    device, queued on `stream`, results (sequence-line bytes, sequence lines) written to two uint64 at out_dev_ptr.
+    Allocates nothing; texts above NOALLOC_MAX_BYTES are refused."""
+    lib = load_library()
+    _check(lib, lib.eref_census_noalloc(c_void_p(fastq_dev_ptr), n, c_void_p(out_dev_ptr), c_void_p(stream)),
+           "eref_census_noalloc")
 
 
 # ---- coder assignment (bin/extract_ref.cpp:1082-1122) -------------------------------------------
