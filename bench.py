@@ -1051,7 +1051,8 @@ def exe_multi_gpu(world):
 
 def run_reference(args):
     """The reference's own CPU implementation of the path on the host cores, all threads, on the headline workload when
-    the whole run fits the time budget (EREF_REF_BUDGET_S, default 1000 s), else on BASELINE configs[0]; config.workload
+    the whole run fits the time budget (EREF_REF_BUDGET_S, default 1000 s, estimated; EREF_REF_HARD_S, default 1500 s,
+    projected from the first real process), else on BASELINE configs[0]; config.workload
     and `sample` name what actually ran.  The binary is the UNMODIFIED reference whenever it exists; each step is one
     whole eref process with the index already on disk (the index build is untimed setup, reported as cold_s)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -1095,10 +1096,24 @@ def run_reference(args):
                        f"configs[0] variable cost) against a budget of {budget:.0f} s")
                 if est > budget:
                     plan = "c1"
+    # the estimate above extrapolates from a tenth of the headline size: once the headline workload has REALLY run
+    # (index build + one warm process) project the whole run again, and fall back to configs[0] rather than let the
+    # driver's per-command limit (1800 s) cut the arm short and leave no reference line at all
+    hard = float(os.environ.get("EREF_REF_HARD_S", "1500"))
     arm = CpuArm(plan, kind)
     try:
         cold = arm.run_once()                          # index build, untimed setup
-        for _ in range(args.warmup):
+        first = arm.run_once()                         # first warm-up run (an extra untimed one when --warmup 0)
+        projected = time.perf_counter() - t_begin + (runs - 1) * first
+        if plan in ("c2", "c5") and not forced and projected > hard:
+            arm.close()
+            why += (f"; measured {first:.1f} s per process on the headline workload -> {projected:.0f} s for the run, over "
+                    f"the hard limit of {hard:.0f} s")
+            plan = "c1"
+            arm = CpuArm(plan, kind)
+            cold = arm.run_once()
+            arm.run_once()
+        for _ in range(args.warmup - 1):
             arm.run_once()
         t0 = time.perf_counter()
         for _ in range(args.steps):

@@ -127,13 +127,18 @@ bool inflate_bgzf(const unsigned char* z, const std::vector<BgzfBlock>& blocks, 
             const int r = inflate(&zs, Z_FINISH);
             if (r != Z_STREAM_END || zs.total_out != b.out_len) bad.store(1);
             inflateEnd(&zs);
+            // raw deflate checks nothing: compare the block's CRC-32 (the four bytes behind the deflate stream) like
+            // gzip -d does for the stream it inflates
+            const unsigned char* c = z + b.in_off + b.in_len;
+            const uLong stored = (uLong)c[0] | ((uLong)c[1] << 8) | ((uLong)c[2] << 16) | ((uLong)c[3] << 24);
+            if (!bad.load() && crc32(crc32(0L, Z_NULL, 0), (const unsigned char*)out + b.out_off, (uInt)b.out_len) != stored) bad.store(2);
         }
     };
     std::vector<std::thread> pool;
     for (int t = 1; t < threads; t++) pool.emplace_back(work);
     work();
     for (auto& t : pool) t.join();
-    if (bad.load()) { err = "corrupt BGZF block"; return false; }
+    if (bad.load()) { err = bad.load() == 2 ? "corrupt BGZF block (CRC mismatch)" : "corrupt BGZF block"; return false; }
     return true;
 }
 
