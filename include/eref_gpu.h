@@ -96,6 +96,14 @@ int  eref_sample_ratio(uint64_t seq_bytes_fq1, uint64_t down_sampling_size, int*
 void eref_draw_keep(int ratio, uint64_t n_lines, uint32_t* keep_bits);
 int  eref_query_add_masked(eref_ctx* ctx, const char* fastq_host, size_t n, const uint32_t* keep_bits, uint64_t n_keep);
 int  eref_query_add_masked_device(eref_ctx* ctx, const void* fastq_dev, size_t n, const uint32_t* keep_bits, uint64_t n_keep);
+/* read_fastq's byte budget (:942-945 `if (add_size >= end) break; add_size += reads_seq.length();`): the prefix of a
+ * FASTQ text the reference reads when main hands it the range [0, end) — every line in front of which fewer than `end`
+ * characters (newlines not counted) were read.  main passes end = file_size(fq1) for fq1 AND fq2 (:1265-1291), so fq2
+ * loses its tail when it is the longer file by more than its number of lines.  Returns the prefix length (n when
+ * nothing is cut).  Host arithmetic, no GPU.  eref_run_host applies it to a host fq2 itself; callers of the phase
+ * functions (eref_query_add* = read_fastq over the whole text) and callers that hand eref_run_host a DEVICE fq2 pass
+ * eref_fastq_limit(fq2, n2, n1) as fq2's size. */
+size_t eref_fastq_limit(const char* fastq_host, size_t n, uint64_t end);
 /* cal_sam_ratio's sum (:1133-1142) for the file of the last eref_query_add* call */
 int  eref_query_seq_bytes(eref_ctx* ctx, uint64_t* out);
 

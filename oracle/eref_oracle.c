@@ -235,6 +235,24 @@ void eo_count_fastq_mt(uint8_t* table, const int16_t coder[96], const char* text
     }
 }
 
+/* The part of a FASTQ text that read_fastq processes when it is handed the byte range [0, end) (:940-946): the
+ * getline loop stops in front of the first line whose PRECEDING lines add up to >= end characters, newlines not
+ * counted (`if (add_size >= end) break; add_size += reads_seq.length();`).  main computes `size = file_size(fq1)` once
+ * (:1265) and passes it as `end` for fq1 AND for fq2 (:1269-1291), so at one thread fq1 is always read whole and fq2
+ * loses its tail whenever it is the longer file by more than its number of lines. */
+size_t eo_fastq_limit(const char* text, size_t n, long end)
+{
+    size_t pos = 0; long add_size = 0;
+    while (pos < n) {
+        if (add_size >= end) return pos;                        /* :942-944 */
+        const char* nl = memchr(text + pos, '\n', n - pos);
+        size_t e = nl ? (size_t)(nl - text) : n;
+        add_size += (long)(e - pos);                            /* :945 */
+        pos = e + 1;
+    }
+    return n;
+}
+
 long eo_fastq_seq_bytes(const char* text, size_t n)
 {
     size_t pos = 0, line = 0; long sum = 0;
@@ -368,6 +386,9 @@ int eo_run_sampled(const char* fq1, size_t n1, const char* fq2, size_t n2, const
     if (sample_size == 0) { eo_table_free(table); return -3; }   /* the reference divides by zero here (:1145) */
     int ratio = (int)(100 * down_sampling_size / sample_size);   /* :1145 */
     srand(1);                                                    /* :1236-1238 */
+    const long size = (long)n1;                                  /* :1265 file_size(fq1), the `end` of BOTH files */
+    n1 = eo_fastq_limit(fq1, n1, size);                          /* (never shortens fq1) */
+    n2 = eo_fastq_limit(fq2, n2, size);                          /* :1281-1288: fq2 read up to fq1's size */
     if (ratio < 100 || threads <= 1) {
         eo_count_fastq_sampled(table, coder, fq1, n1, ratio < 100 ? ratio : -1);   /* :1269-1279 */
         eo_count_fastq_sampled(table, coder, fq2, n2, ratio < 100 ? ratio : -1);   /* :1281-1291 */

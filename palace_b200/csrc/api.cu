@@ -1103,6 +1103,41 @@ int eref_query_census_device(eref_ctx* c, const void* fastq_dev, size_t n, uint6
     return census_impl(c, static_cast<const uint8_t*>(fastq_dev), n, seq_bytes, seq_lines);
 }
 
+// read_fastq's byte budget (:942-945): the getline loop stops in front of the first line whose PRECEDING lines add up
+// to >= end characters, newlines not counted.  main hands file_size(fq1) to both files (:1265-1291), so fq2 is cut short
+// when it is the longer one.  A line that starts at byte c behind nl(c) newlines is read iff c - nl(c) < end; returns the
+// first line start that is not (the length of the prefix that is read), or n.  Host code, no CUDA.
+// Cost: nothing when n <= end; else newlines are counted block-wise from the start (no line start below `end` can be
+// cut) and the walk stops as soon as n - end of them were seen — behind that many newlines no line start can reach
+// the budget — which for two mates of similar size is after a small part of the text.
+size_t eref_fastq_limit(const char* text, size_t n, uint64_t end)
+{
+    if (!text || n <= end) return n;
+    if (end == 0) return 0;                              // the very first line already meets an empty budget
+    const uint64_t d = n - end;
+    size_t pos = 0;
+    uint64_t cnt = 0;
+    while (pos < end) {
+        const size_t len = std::min<size_t>((size_t)1 << 16, (size_t)end - pos);
+        const char* p = text + pos;
+        uint32_t k = 0;
+        for (size_t i = 0; i < len; i++) k += p[i] == '\n';
+        cnt += k;
+        pos += len;
+        if (cnt >= d) return n;
+    }
+    while (pos < n) {
+        const char* q = (const char*)memchr(text + pos, '\n', n - pos);
+        if (!q) return n;
+        cnt++;
+        const size_t c = (size_t)(q - text) + 1;
+        if (c < n && c - cnt >= end) return c;
+        if (cnt >= d) return n;
+        pos = c;
+    }
+    return n;
+}
+
 int eref_sample_ratio(uint64_t seq_bytes_fq1, uint64_t down_sampling_size, int* ratio)
 {
     if (!ratio) return eref_fail(EREF_ERR_ARG, "null argument");
@@ -1298,6 +1333,15 @@ static int run_host_impl(eref_ctx* c, const char* fq1, size_t n1, const char* fq
         doff += (len + 255) & ~(size_t)255;
     }
     CUDA_TRY(cudaEventRecord(c->ev[E11], cs));
+    // main reads fq2 only up to fq1's size (:1265-1291, eref_fastq_limit): whatever lies behind that was uploaded but
+    // is not counted.  Looked up here, while the first copy is still in flight.  A query in DEVICE memory cannot be
+    // walked by the host: its caller passes the limited size (the executable does).
+    {
+        cudaPointerAttributes at{};
+        const bool on_device = n2 && cudaPointerGetAttributes(&at, fq2) == cudaSuccess && at.type == cudaMemoryTypeDevice;
+        cudaGetLastError();
+        if (n2 && !on_device) n2 = eref_fastq_limit(fq2, n2, n1);
+    }
     const auto h1 = std::chrono::steady_clock::now();
     int rc = eref_query_reset(c);
     if (rc) return rc;

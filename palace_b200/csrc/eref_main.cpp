@@ -586,6 +586,9 @@ int main(int argc, char** argv)
         cleanup();
         return 3;
     }
+    // main hands file_size(fq1) to read_fastq as the byte budget of BOTH files (:1265-1291, :942-945): whatever of fq2
+    // lies behind it is never read.  Cut it here, once, so that every path below (upload slices, census, masks) agrees.
+    f2.n = eref_fastq_limit(f2.p, f2.n, f1.n);
     if (!getenv("EREF_PIN") || atoi(getenv("EREF_PIN")) != 0) {
         cudaSetDevice(0);
         std::thread p1([&] { cudaSetDevice(0); f1.pin(); }), p2([&] { cudaSetDevice(0); f2.pin(); });

@@ -42,7 +42,7 @@ ABI_SYMBOLS = (
     "eref_ref_set", "eref_ref_set_device", "eref_ref_count", "eref_scan", "eref_scan_device", "eref_scan_device_async",
     "eref_get_codes", "eref_ref_record", "eref_query_popcount", "eref_timings", "eref_format_line",
     "eref_run_host", "eref_ref_records", "eref_index_body", "eref_query_census", "eref_query_census_device",
-    "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
+    "eref_fastq_limit", "eref_sample_ratio", "eref_draw_keep", "eref_query_add_masked", "eref_query_add_masked_device",
     "eref_table_export", "eref_table_set_part", "eref_table_set_peer", "eref_table_set_hook", "eref_table_part_range",
     "eref_table_join", "eref_sync", "eref_run_results_device", "eref_run_host_keep", "eref_set_serial",
     "eref_query_reserve", "eref_lists_export", "eref_lists_set_peer", "eref_query_set_share",
@@ -101,6 +101,8 @@ def load_library() -> ctypes.CDLL:
     lib.eref_query_popcount.argtypes = [c_void_p, c_int, POINTER(c_uint64)]
     lib.eref_query_census.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_uint64), POINTER(c_uint64)]
     lib.eref_query_census_device.argtypes = [c_void_p, c_void_p, c_size_t, POINTER(c_uint64), POINTER(c_uint64)]
+    lib.eref_fastq_limit.argtypes = [c_void_p, c_size_t, c_uint64]
+    lib.eref_fastq_limit.restype = c_size_t
     lib.eref_sample_ratio.argtypes = [c_uint64, c_uint64, POINTER(c_int)]
     lib.eref_draw_keep.argtypes = [c_int, c_uint64, c_void_p]
     lib.eref_draw_keep.restype = None
@@ -501,6 +503,14 @@ def shard_offsets(fasta: np.ndarray, shards: int):
     return cuts
 
 
+def fastq_limit(fastq, end: int) -> int:
+    """read_fastq's byte budget (:942-945): the length of the prefix of a FASTQ text the reference reads when main hands
+    it the range [0, end).  main passes end = file_size(fq1) for BOTH files (:1265-1291): callers of the phase functions
+    add fq2[:fastq_limit(fq2, fq1.size)] (run_eref and eref_run_host do it themselves).  Host arithmetic, no GPU."""
+    a = _as_bytes_array(fastq)
+    return int(load_library().eref_fastq_limit(c_void_p(a.ctypes.data), a.size, int(end)))
+
+
 def sample_ratio(seq_bytes_fq1: int, down_sampling_size: int = DOWN_SAMPLING_SIZE) -> int:
     """cal_sam_ratio (:1124-1148): 100 * down_sampling_size / (2 * sequence bytes of fq1); below 100 the
     reference down-samples.  Raises where the reference divides by zero (empty fq1)."""
@@ -531,6 +541,8 @@ def run_eref(fq1, fq2, fasta, interval_out: str | None = None, hit_ratio: float 
     the concurrent multi-GPU drivers are palace_b200/bin/eref and bench.py under torchrun).
     """
     del threads                                            # a hint in the reference, unused here
+    fq1, fq2 = _as_bytes_array(fq1), _as_bytes_array(fq2)
+    fq2 = fq2[:fastq_limit(fq2, fq1.size)]                 # main reads fq2 only up to fq1's size (:1265-1291)
     if shard_table and len(devices) > 1:
         return _run_eref_sharded_table(fq1, fq2, fasta, interval_out, hit_ratio, perfect_hit_ratio, coder, devices, prune,
                                        pipelined, chunks, return_results, share_reads)

@@ -67,3 +67,16 @@ GOLDEN_CASES = ("basic", "short_reads", "edge")
 @pytest.fixture(scope="session", params=GOLDEN_CASES)
 def golden(request):
     return (request.param,) + load_golden(request.param)
+
+
+def fq2_limit_inputs():
+    """Inputs on which the reference's byte budget for fq2 bites (bin/extract_ref.cpp:1265-1291 hand file_size(fq1)
+    to read_fastq for BOTH files, :942-945): derived from the committed "basic" fixture — fq1 keeps the first two thirds
+    of its records, the rest is appended to fq2, so fq2 is twice as long as fq1 and the reference reads only its head.
+    Expected outputs: tests/golden/fq2_limit.json (tests/golden/make_golden_fq2_limit.py, the unmodified reference)."""
+    _, fa, f1, f2 = load_golden("basic")
+    nl = np.flatnonzero(f1 == 10)
+    cut = int(nl[4 * (nl.size // 4 * 2 // 3) - 1]) + 1      # a record boundary two thirds of the way through fq1
+    with open(os.path.join(GOLDEN, "fq2_limit.json")) as f:
+        meta = json.load(f)
+    return meta, fa, f1[:cut].copy(), np.concatenate([f2, f1[cut:]])

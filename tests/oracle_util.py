@@ -53,6 +53,13 @@ class Oracle:
         ok = fn(cp, buf, out.ctypes.data_as(POINTER(c_uint32)))
         return ok, out
 
+    def fastq_limit(self, text, end):
+        """the prefix of a FASTQ text read_fastq processes for the byte range [0, end) (:942-945), literal getline loop"""
+        a = np.ascontiguousarray(text)
+        self.lib.eo_fastq_limit.restype = c_size_t
+        self.lib.eo_fastq_limit.argtypes = [c_void_p, c_size_t, ctypes.c_long]
+        return int(self.lib.eo_fastq_limit(c_void_p(a.ctypes.data), a.size, int(end)))
+
     def fastq_seq_bytes(self, text):
         a = np.ascontiguousarray(text)
         return self.lib.eo_fastq_seq_bytes(c_void_p(a.ctypes.data), a.size)

@@ -167,6 +167,7 @@ def test_edge_inputs(oracle):
 def test_shard_invariance_and_idempotence(oracle):
     """splitting the DB at record boundaries and merging ordinals gives the same records; a second scan too"""
     db, f1, f2, _ = _case(31, n_genomes=120, db_bp=3_000_000, q_bp=600_000)
+    f2 = f2[:eref.fastq_limit(f2, f1.size)]                # what main reads of fq2 (:1265-1291): the phase calls below take it as it is
     coder = eref.random_coder(31)
     _, whole = eref.run_eref(f1, f2, db.text, coder=coder, return_results=True)
     _, three = eref.run_eref(f1, f2, db.text, coder=coder, devices=(0, 0, 0), return_results=True)
@@ -198,11 +199,14 @@ def test_run_host_against_a_resident_database(golden):
         with pytest.raises(eref.ErefError):
             g.run_host(f1, f2, None)                       # nothing set yet
         g.ref_set(fa)
-        g.query_add(f1); g.query_add(f2)
-        want = g.scan().copy()
         for a, b in ((f1, f2), (f2, f1), (f1, f2)):
+            # the table depends on the order of the files only through main's byte budget: the second file is read up to
+            # the first one's size (:1265-1291); the phase calls count exactly the text they are given
+            g.query_reset()
+            g.query_add(a); g.query_add(b[:eref.fastq_limit(b, a.size)])
+            want = g.scan().copy()
             got = g.run_host(a, b, None).copy()
-            assert (got == want).all(), name               # the table does not depend on the order of the files
+            assert (got == want).all(), name
         with pytest.raises(eref.ErefError):
             g.run_host(f1[:0], f2, None)                   # empty fq1: the reference divides by zero (:1145)
         assert (g.run_host(f1, f2, None) == want).all()    # and the database is still set
@@ -227,6 +231,43 @@ def test_run_host_refuses_empty_fq1():
         with pytest.raises(eref.ErefError):
             g.run_host(np.zeros(0, np.uint8), fq, fa, cap=4)
         assert g.run_host(fq, fq, fa, cap=4).size == 1           # and the context is still usable
+
+
+def test_fq2_is_read_only_up_to_fq1s_size(tmp_path):
+    """main hands file_size(fq1) to read_fastq as the byte budget of BOTH files (:1265-1291, :942-945): with fq2 twice
+    as long as fq1 the reference reads only its head.  Expected stdout: the unmodified reference on the same inputs
+    (tests/golden/fq2_limit.json) — through run_eref by phases and pipelined, eref_run_host with the query in device
+    memory (the caller passes the limited size), and the executable."""
+    import torch
+    from tests.conftest import fq2_limit_inputs
+    meta, fa, f1, f2 = fq2_limit_inputs()
+    lim = eref.fastq_limit(f2, f1.size)
+    assert lim == meta["fq2_bytes_read"] < f2.size
+    for key, expect in meta["stdout"].items():
+        hr, phr = (float(x) for x in key.split(","))
+        for pipelined in (False, True):
+            assert eref.run_eref(f1, f2, fa, None, hr, phr, 1, coder=meta["coder"], pipelined=pipelined) == expect, (key, pipelined)
+    assert eref.run_eref(f1, f2, fa, None, 0.5, 0.3, 1, coder=meta["coder"], devices=(0, 0), shard_table=True,
+                         share_reads=True) == meta["stdout"]["0.5,0.3"]
+    d1, d2 = torch.from_numpy(np.array(f1)).cuda(), torch.from_numpy(np.array(f2)).cuda()
+    with eref.ErefGPU(meta["coder"], 0.5, 0.3) as g:
+        host = g.run_host(f1, f2, fa).copy()                      # host fq2: the call applies the budget itself
+        dev = g.run_host(eref.DeviceBytes(d1.data_ptr(), d1.numel()), eref.DeviceBytes(d2.data_ptr(), lim), fa).copy()
+        assert (host == dev).all() and eref.format_results(host) == meta["stdout"]["0.5,0.3"]
+        whole = g.run_host(eref.DeviceBytes(d1.data_ptr(), d1.numel()), eref.DeviceBytes(d2.data_ptr(), d2.numel()), fa)
+        assert eref.format_results(whole) != meta["stdout"]["0.5,0.3"]      # (and the budget is what makes the difference)
+    fa.tofile(tmp_path / "db.fa"); f1.tofile(tmp_path / "r1.fq"); f2.tofile(tmp_path / "r2.fq")
+    hdr = np.zeros(100, "<u4"); hdr[:96] = np.asarray(meta["coder"], np.uint32)
+    hdr.tofile(tmp_path / "db.fa.k32.index.dat")
+    for gpus in ("1", "2"):
+        if gpus == "2" and eref.load_library().eref_device_count() < 2:
+            continue
+        for key, expect in meta["stdout"].items():
+            hr, phr = key.split(",")
+            r = subprocess.run([eref.EREF_BIN, "r1.fq", "r2.fq", "db.fa", "tmp_out.txt", hr, phr, "4"], cwd=tmp_path,
+                               capture_output=True, env=dict(os.environ, EREF_GPUS=gpus))
+            assert r.returncode == 0, r.stderr.decode()
+            assert r.stdout.decode() == expect, (key, gpus)
 
 
 def test_strand_and_order_invariance():

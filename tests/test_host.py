@@ -229,3 +229,24 @@ def test_get_ref_by_index_fuzz_against_the_reference_script(tmp_path, capsys):
         g.main(["x", str(d / "db.fa"), str(d / "db.fa.fai"), str(d / "names.txt"), str(d / "out.fa"), str(d / "out.txt")])
         got = ((d / "out.fa").read_text(), (d / "out.txt").read_text(), capsys.readouterr().out)
         assert got == want, (case, fa, fai, names)
+
+
+def test_fastq_limit_is_the_references_getline_budget(oracle):
+    """eref_fastq_limit (host arithmetic of the library: block-wise newline counts with an early exit) against the
+    oracle's literal getline loop (:942-945) on random texts with every line-length mix, and every kind of budget"""
+    rng = np.random.default_rng(1)
+    cut = 0
+    for _ in range(1500):
+        n = int(rng.integers(0, 400))
+        a = np.where(rng.random(n) < rng.choice([0.02, 0.1, 0.3, 0.9]), 10, 65).astype(np.uint8)
+        for end in [0, 1, 2, n // 2, max(n - 3, 0), max(n - 1, 0), n, n + 1] + [int(x) for x in rng.integers(0, n + 2, 4)]:
+            want = oracle.fastq_limit(a, end)
+            assert eref.fastq_limit(a, end) == want, (bytes(a), end)
+            cut += want < n
+    assert cut > 5000
+    # blocks of 64 KiB, a budget deep inside a long text, both outcomes
+    db = synth.make_db(20, 400_000, 5)
+    f1, f2, _ = synth.make_reads(db, 900_000, 6)
+    for end in (f2.size - 100, f2.size - 3000, f2.size - 20_000, f2.size // 2, 70_000, f1.size):
+        assert eref.fastq_limit(f2, end) == oracle.fastq_limit(f2, end), end
+    assert eref.fastq_limit(f2, f2.size - 20_000) < f2.size and eref.fastq_limit(f2, f2.size - 100) == f2.size

@@ -119,3 +119,23 @@ def test_oracle_downsampling_matches_reference(oracle):
     # and it really is a different answer from the unsampled run
     full = oracle.run(f1, f2, fa, ds["coder"], 0.9, 0.85, threads=2)
     assert oracle.format(full) != ds["stdout"]["0.9,0.85"]
+
+
+def test_oracle_reads_fq2_only_up_to_fq1s_size(oracle):
+    """main hands file_size(fq1) to read_fastq as the byte budget of BOTH files (:1265-1291) and the getline loop stops
+    once the lines read add up to it (:942-945): with fq2 twice as long as fq1 the reference reads only its head.
+    Expected stdout: the unmodified reference on the same inputs (tests/golden/make_golden_fq2_limit.py)."""
+    import hashlib
+    from tests.conftest import fq2_limit_inputs
+    meta, fa, f1, f2 = fq2_limit_inputs()
+    assert hashlib.sha256(f1.tobytes()).hexdigest() == meta["sha256"]["r1"]
+    assert hashlib.sha256(f2.tobytes()).hexdigest() == meta["sha256"]["r2"]
+    assert (f1.size, f2.size) == (meta["fq1_bytes"], meta["fq2_bytes"])
+    assert oracle.fastq_limit(f2, f1.size) == meta["fq2_bytes_read"] < f2.size
+    assert oracle.fastq_limit(f1, f1.size) == f1.size              # fq1 itself is never cut
+    for key, expect in meta["stdout"].items():
+        hr, phr = (float(x) for x in key.split(","))
+        assert oracle.format(oracle.run(f1, f2, fa, meta["coder"], hr, phr, threads=2)) == expect, key
+    # the budget is what makes the difference: the same reads with the longer file first are all counted
+    swapped = oracle.format(oracle.run(f2, f1, fa, meta["coder"], 0.5, 0.3, threads=2))
+    assert swapped.count("\n") > meta["stdout"]["0.5,0.3"].count("\n") > 0
