@@ -980,10 +980,10 @@ class CpuArm:
                        + ("unmodified reference binary oracle/_ref/eref_ref" if kind == "reference" else "oracle port oracle/eref_oracle"))
         self.stdout = None
 
-    def run_once(self, threads=None):
+    def run_once(self, threads=None, fq2="r2.fq"):
         env = dict(os.environ, EREF_CODER_SEED="1", EREF_ORACLE_WRITE_INDEX="1")
         t0 = time.perf_counter()
-        r = subprocess.run([self.bin, "r1.fq", "r2.fq", "db.fa", "tmp.txt", "0.9", "0.85", str(threads or self.cores)],
+        r = subprocess.run([self.bin, "r1.fq", fq2, "db.fa", "tmp.txt", "0.9", "0.85", str(threads or self.cores)],
                            cwd=self.dir, capture_output=True, env=env)
         dt = time.perf_counter() - t0
         if r.returncode != 0:
@@ -991,12 +991,12 @@ class CpuArm:
         self.stdout = r.stdout
         return dt
 
-    def run_product(self, gpus=1):
+    def run_product(self, gpus=1, fq2="r2.fq"):
         """palace_b200/bin/eref as a process on the very same files (it takes the coder from the index header the
         CPU run left next to the database): wall time and stdout"""
         exe = os.path.join(ROOT, "palace_b200", "bin", "eref")
         t0 = time.perf_counter()
-        r = subprocess.run([exe, "r1.fq", "r2.fq", "db.fa", "tmp_b200.txt", "0.9", "0.85", str(self.cores)], cwd=self.dir,
+        r = subprocess.run([exe, "r1.fq", fq2, "db.fa", "tmp_b200.txt", "0.9", "0.85", str(self.cores)], cwd=self.dir,
                            capture_output=True, env=dict(os.environ, EREF_GPUS=str(gpus)))
         dt = time.perf_counter() - t0
         if r.returncode != 0:
@@ -1032,6 +1032,27 @@ def cpu_baseline(budget_runs=1):
                               "note": "one process per sample as palace runs it: file reads, CUDA context, upload, kernels, output"}
         except Exception as e:                            # the bench line must not depend on this extra
             out["process"] = {"error": str(e)[-300:]}
+        # ... and once more with fq2 the LONGER file (its own text followed by the first third of fq1's): main hands
+        # file_size(fq1) to read_fastq as the byte budget of both files (bin/extract_ref.cpp:1265-1291, :942-945), so the
+        # reference never reads the tail; the drop-in must print the same lines
+        try:
+            if "error" not in out["process"]:
+                with open(os.path.join(arm.dir, "r1.fq"), "rb") as f:
+                    r1 = f.read()
+                with open(os.path.join(arm.dir, "r2.fq"), "rb") as f:
+                    r2 = f.read()
+                with open(os.path.join(arm.dir, "r2_longer.fq"), "wb") as f:
+                    f.write(r2 + r1[: len(r1) // 3])
+                arm.run_once(threads=1, fq2="r2_longer.fq")
+                ref_longer = arm.stdout
+                _, mine_longer = arm.run_product(fq2="r2_longer.fq")
+                out["process"]["fq2_longer_than_fq1"] = {
+                    "stdout_identical_to_reference_threads1": mine_longer == ref_longer,
+                    "result_lines": mine_longer.count(b"\n"),
+                    "reference_stdout_equals_the_plain_files": ref_longer == ref_t1_stdout,
+                    "note": "the reference reads fq2 only up to fq1's size: all but the first ~1 % of the appended reads are never counted"}
+        except Exception as e:
+            out["process"]["fq2_longer_than_fq1"] = {"error": str(e)[-300:]}
         return out
     finally:
         arm.close()
