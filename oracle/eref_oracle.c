@@ -348,11 +348,20 @@ static void window_rule(const uint8_t* nhit /* per position: number of coders th
     out->frag = (uint32_t)frag; out->el = (uint32_t)el; out->ref_len = len;
 }
 
+/* The reference never writes the hit flags of a record's last 31 positions (:846-870 fills (ref_len-31)*3 of the
+ * ref_len*3 bytes it allocates, :856) but slide_window reads them (:527-531): whatever the heap held counts.  The
+ * canonical value here is "no hit" (0).  eo_set_tail_hits(3) makes them all count as hit by three coders instead — the
+ * other end of what the reference can print — so that a fuzzer can tell a difference that this undefined read explains
+ * (the reference's lines lie between the two) from a real one. */
+static int g_tail_hits = 0;
+void eo_set_tail_hits(int v) { g_tail_hits = v; }
+
 void eo_scan_record(const uint8_t* table, const int16_t coder[96], const unsigned char* seq,
                     uint32_t len, float hit_ratio, float perfect_hit_ratio, eo_result* out)
 {
     eo_masks mk; make_masks(coder, &mk);
     uint8_t* nhit = (uint8_t*)calloc(len, 1);                    /* tail positions stay 0 */
+    if (g_tail_hits) for (uint32_t j = len >= 31 ? len - 31 : 0; j < len; j++) nhit[j] = (uint8_t)g_tail_hits;
     uint32_t c[3];
     ROLL_BEGIN(seq, len)
         if (valid_) {

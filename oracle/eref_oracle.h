@@ -49,6 +49,9 @@ void eo_count_fastq(uint8_t* table, const int16_t coder[96], const char* text, s
 void eo_count_fastq_sampled(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int down_sam_ratio);
 /* the count without draws on `threads` threads, each owning a range of the code space (same table, byte for byte) */
 void eo_count_fastq_mt(uint8_t* table, const int16_t coder[96], const char* text, size_t n, int threads);
+/* diagnostic: what the last 31 positions of every record count as (0 = canonical "no hit"; 3 = hit by all coders):
+ * the reference reads them uninitialised (:856 vs :527-531) */
+void eo_set_tail_hits(int v);
 /* the prefix of a FASTQ text read_fastq processes for the byte range [0, end) (:942-945); main passes
  * end = file_size(fq1) for both files (:1265-1291), eo_run* apply it */
 size_t eo_fastq_limit(const char* text, size_t n, long end);

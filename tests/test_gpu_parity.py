@@ -623,6 +623,19 @@ def test_ragged_records_match_the_oracle(oracle):
 
 # ---- sharded table build (the table counted by N GPUs, exchanged through peer pointers / a hook) --------------
 
+def test_thresholds_at_the_ends_of_their_range(oracle):
+    """int(500 * ratio) of :513-514 at 0, 1, 500 and with the perfect threshold above the plain one, on records from 33
+    bases up (shorter than a window, clamped paddings): every record equals the oracle's (which the live fuzz compares
+    with the reference binary at the same pairs, oracle/fuzz_vs_reference.py ... extremes)"""
+    fa, f1, f2 = _ragged_case(305, n_records=600)
+    coder = eref.random_coder(305)
+    for ratios in ((0.0, 0.0), (1.0, 1.0), (0.002, 0.002), (0.1, 0.9)):
+        want = oracle.run(f1, f2, fa, coder, *ratios, threads=4)
+        text, got = eref.run_eref(f1, f2, fa, None, *ratios, 1, coder=coder, return_results=True)
+        assert got.size == want.size and (got == want).all(), ratios
+        assert text == oracle.format(want), ratios
+
+
 @pytest.mark.parametrize("parts", [2, 4, 3])
 def test_sharded_table_build_equals_replicated(oracle, parts):
     """N contexts on one GPU emulate an N-GPU box: context i counts slices [8192 i/N, 8192 (i+1)/N) and stores them into
