@@ -3,7 +3,8 @@
 seeded inputs whose FORMAT is mangled — the things real files do and a clean generator does not: CRLF line ends, blank
 lines, a missing final newline, a truncated last record, sequence in front of the first header, header-only records,
 '>' and white space inside sequence lines, lower case, fq2 longer than fq1.  Each case applies a random subset of the
-manglings to a clean synthetic sample and compares stdout under two threshold pairs.  Stays clear of the reference's
+manglings to a clean synthetic sample and compares the index body (every code of every position) and stdout under two
+threshold pairs.  Stays clear of the reference's
 undefined behaviour: FASTQ lines <= 400 characters, no records of 450..499 bases.
 usage: python oracle/fuzz_formats.py [first_seed n_cases]   (each reference run: 15-30 s, ~20 GiB of host memory)"""
 import os
@@ -111,6 +112,15 @@ def main():
                     break
                 ref = r.stdout.decode()
                 coder = eref.read_coder(os.path.join(d, "db.fa.k32.index.dat"))
+                if hr == "0.9":
+                    # the reference's own index of the mangled FASTA (:652-811): record lengths and every code of every
+                    # position, byte for byte
+                    oracle.write_index(os.path.join(d, "mine.dat"), coder, fa)
+                    a = np.fromfile(os.path.join(d, "db.fa.k32.index.dat"), "<u4")[100:]
+                    b = np.fromfile(os.path.join(d, "mine.dat"), "<u4")[100:]
+                    same = a.size == b.size and bool((a == b).all())
+                    bad += not same
+                    print(f"seed {seed}: index body of {a.size} words {'identical' if same else 'DIFFERENT'}", flush=True)
                 mine = oracle.format(oracle.run(f1, f2, fa, coder, hit_ratio=float(hr), perfect_hit_ratio=float(phr)))
                 bad += mine != ref
                 lines += ref.count("\n")

@@ -29,7 +29,7 @@ OUT = os.path.dirname(os.path.abspath(__file__))
 DOWN_SAMPLING_SIZE = 400_000
 
 
-def build_variant():
+def build_variant(DOWN_SAMPLING_SIZE=DOWN_SAMPLING_SIZE):
     text = open(SRC).read()
     pat = r"long down_sampling_size = 2000000000;"
     assert len(re.findall(pat, text)) == 1, "line 1230 not found"
