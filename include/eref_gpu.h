@@ -78,8 +78,9 @@ int  eref_set_stream(eref_ctx* ctx, void* cuda_stream);
 
 /* memset(kmer_count_table) at :1257 */
 int  eref_query_reset(eref_ctx* ctx);
-/* read_fastq at one thread (:905-1008) over one whole FASTQ file: frames lines (index%4==1),
- * forms the three canonical codes of every valid 32-mer and counts them, saturating at 3. */
+/* read_fastq at one thread (:905-1008) over the text it is given: frames lines (index%4==1),
+ * forms the three canonical codes of every valid 32-mer and counts them, saturating at 3.
+ * (main gives read_fastq a byte budget, :1265-1291: for the second file pass eref_fastq_limit's size, below.) */
 int  eref_query_add(eref_ctx* ctx, const char* fastq_host, size_t n);
 int  eref_query_add_device(eref_ctx* ctx, const void* fastq_dev, size_t n);
 /* Down-sampling (:955-960, :1124-1148, :1239-1242).  When fq1 holds more than
