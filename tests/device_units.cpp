@@ -4,10 +4,12 @@
 //   * 32-mer codes from bit-planes (eref_internal.cuh: window32, window_bits, stream_code, valid_windows)
 //   * which table part a code falls into, without forming it (scan.cu: part_mask)
 //   * the associative FASTA framing summary (eref_internal.cuh: TileSum / TileOp)
+//   * the cut points of a sharded table build (api.cu: part_first_slice, part_weight; host arithmetic)
 // The function bodies are NOT copied here: eref_internal.cuh is included as it is, and the test cuts the two source
-// regions out of frame.cu / scan.cu into tests/_build/device_snippets.inc at build time, so what runs is the product's
+// regions out of frame.cu / scan.cu / api.cu into tests/_build/device_snippets.inc at build time, so what runs is the product's
 // own source text with the handful of CUDA integer intrinsics below supplied for the host.
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -238,6 +240,45 @@ int check_tileop(uint64_t seed, int rounds)
     return bad != 0;
 }
 
+// ---- table parts of a sharded build (api.cu: part_first_slice, part_weight): the cut points of `parts` GPUs at weight
+// w partition the NSLICES slices, every part gets at least one, and they equalise w * code mass + (1 - w) * width, the
+// mass of canonical codes min(fwd, rc) falling as 2(1 - x) over the code space
+int check_cuts()
+{
+    long bad = 0;
+    for (int parts = 1; parts <= 16; parts++)
+        for (int wi = 0; wi <= 19; wi++) {
+            const double w = wi * 0.05;
+            bad += part_first_slice(0, parts, w) != 0 || part_first_slice(parts, parts, w) != (uint32_t)NSLICES;
+            double cost_lo = 1e9, cost_hi = 0;
+            for (int p = 0; p < parts; p++) {
+                const uint32_t a = part_first_slice(p, parts, w), b = part_first_slice(p + 1, parts, w);
+                bad += b <= a;
+                const double x0 = (double)a / NSLICES, x1 = (double)b / NSLICES;
+                const double mass = (1 - x0) * (1 - x0) - (1 - x1) * (1 - x1), cost = w * mass + (1 - w) * (x1 - x0);
+                cost_lo = std::min(cost_lo, cost); cost_hi = std::max(cost_hi, cost);
+            }
+            bad += cost_hi - cost_lo > 4.0 / NSLICES;          // equal up to the rounding to whole slices
+        }
+    printf("cuts mismatches %ld\n", bad);
+    for (int parts : {2, 8}) {                                 // the numbers DESIGN.md section 6 quotes (w = 0.7)
+        for (int p = 0; p < parts; p++) printf("%u ", part_first_slice(p, parts, 0.7));
+        printf("\n");
+    }
+    // the weight rises with the query and falls with the number of GPUs, within [0, 0.95]
+    long wbad = 0;
+    for (int parts = 2; parts <= 16; parts++) {
+        double last = -1;
+        for (uint64_t q = 1u << 20; q < (1ull << 36); q <<= 1) {
+            const double w = part_weight(parts, q);
+            wbad += w < last || w < 0 || w > 0.95 || (parts > 2 && w > part_weight(parts - 1, q));
+            last = w;
+        }
+    }
+    printf("weight mismatches %ld\n", wbad);
+    return bad != 0 || wbad != 0;
+}
+
 } // namespace
 
 int main(int argc, char** argv)
@@ -249,6 +290,7 @@ int main(int argc, char** argv)
     if (cmd == "codes") return print_codes();
     if (cmd == "parts") return check_parts(seed, rounds);
     if (cmd == "tileop") return check_tileop(seed, rounds);
+    if (cmd == "cuts") return check_cuts();
     fprintf(stderr, "usage: device_units masks|parts|tileop <seed> <rounds>  |  codes < coder+sequences\n");
     return 2;
 }

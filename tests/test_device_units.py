@@ -1,7 +1,7 @@
 """CPU suite, part 5: the pure-arithmetic device functions of the CUDA path, compiled for the host.
 
 The kernels cannot run here, but the integer arithmetic they are built on can: tests/device_units.cpp includes
-palace_b200/csrc/eref_internal.cuh as it is and the two source regions this file cuts out of frame.cu (text -> masks)
+palace_b200/csrc/eref_internal.cuh as it is and the source regions this file cuts out of frame.cu (text -> masks), api.cu (table parts)
 and scan.cu (part_mask) — the product's own source text, with host versions of five CUDA integer intrinsics — and
 checks them against naive restatements and, for the 32-mer codes, against the oracle's literal z-loop
 (oracle/eref_oracle.c: eo_code3_naive, pinned to the reference's own index file by tests/test_oracle.py):
@@ -10,6 +10,8 @@ checks them against naive restatements and, for the 32-mer codes, against the or
   codes    window_bits + stream_code on bit-planes == the three canonical codes of :971-994, valid_windows == :978-982
   parts    part_mask<1..5>: the table part of min(fwd, rc) decided from shifted alphabet planes == top bits of the code
   tileop   TileSum/TileOp: folding per-tile FASTA framing summaries in any association == framing the text in one go
+  cuts     part_first_slice / part_weight (api.cu, host arithmetic): the table parts of a sharded build partition the
+           8192 slices and equalise w * code mass + (1 - w) * width; the numbers DESIGN.md quotes
 """
 import os
 import re
@@ -38,11 +40,12 @@ def snippets():
     frame = _cut(os.path.join(CSRC, "frame.cu"), "constexpr uint32_t H7", "// exclusive prefix sum over the 256 threads")
     scan = _cut(os.path.join(CSRC, "scan.cu"), "template <int LOG2P>\n__device__ __forceinline__ uint32_t part_mask",
                 "// list == nullptr: every word of the planes")
+    api = _cut(os.path.join(CSRC, "api.cu"), "uint32_t part_first_slice(", "void set_part_range(")
     for name in ("eq7", "gather2", "masks_word", "chunk_masks", "chunk_newlines", "count_nl", "before"):
         assert re.search(r"\b%s\b" % name, frame), name
-    assert "__global__" not in frame + scan and "threadIdx" not in frame + scan
+    assert "__global__" not in frame + scan + api and "threadIdx" not in frame + scan + api
     return ("// cut out of palace_b200/csrc/frame.cu and scan.cu by tests/test_device_units.py — do not edit\n"
-            "namespace {\n" + frame + scan + "}\n")
+            "namespace {\n" + frame + scan + api + "}\n")
 
 
 @pytest.fixture(scope="session")
@@ -77,6 +80,14 @@ def test_part_masks_equal_the_top_bits_of_the_codes(units):
 
 def test_tile_summaries_compose(units):
     assert units("tileop", 5, 3000).strip() == "tileop mismatches 0"
+
+
+def test_table_parts_partition_the_slices_and_balance_their_cost(units):
+    out = units("cuts").splitlines()
+    assert out[0] == "cuts mismatches 0" and out[3] == "weight mismatches 0"
+    # the cut points DESIGN.md section 6 quotes for a weight of 0.7
+    assert out[1].split() == ["0", "2805"]
+    assert out[2].split() == ["0", "622", "1288", "2010", "2805", "3700", "4747", "6066"]
 
 
 def test_bitplane_codes_equal_the_oracles_literal_loop(units, oracle):
