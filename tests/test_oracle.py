@@ -139,3 +139,34 @@ def test_oracle_reads_fq2_only_up_to_fq1s_size(oracle):
     # the budget is what makes the difference: the same reads with the longer file first are all counted
     swapped = oracle.format(oracle.run(f2, f1, fa, meta["coder"], 0.5, 0.3, threads=2))
     assert swapped.count("\n") > meta["stdout"]["0.5,0.3"].count("\n") > 0
+
+
+def test_tail_hits_diagnostic_only_adds_coverage(oracle):
+    """eo_set_tail_hits: what the reference's uninitialised read of a record's last 31 hit flags (:856 vs :527-531) can
+    add at most.  Counting them as hits never lowers a record's covered length, leaves records untouched whose last
+    window is far from good, and does change short, well-covered records — the ones the extremes fuzz classifies."""
+    rng = np.random.default_rng(8)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    fa, reads = [], []
+    for i in range(120):
+        L = int(rng.integers(260, 420)) if i % 2 else int(rng.integers(2000, 6000))
+        seq = acgt[rng.integers(0, 4, L)].tobytes()
+        fa.append(b">t%d\n" % i + seq + b"\n")
+        if i % 4 < 2:                                              # half of the records tiled 6x by error-free reads
+            for _ in range(6 * L // 120):
+                st = int(rng.integers(0, max(L - 150, 1)))
+                reads.append(seq[st:st + 150])
+    fq = np.frombuffer(b"".join(b"@q\n" + r + b"\n+\n" + b"I" * len(r) + b"\n" for r in reads), np.uint8)
+    fa = np.frombuffer(b"".join(fa), np.uint8)
+    coder = oracle.random_coder(8)
+    canonical = oracle.run(fq, fq, fa, coder, 0.5, 0.3, threads=2)
+    try:
+        oracle.lib.eo_set_tail_hits(3)
+        upper = oracle.run(fq, fq, fa, coder, 0.5, 0.3, threads=2)
+    finally:
+        oracle.lib.eo_set_tail_hits(0)
+    assert (upper["el"] >= canonical["el"]).all()
+    uncovered = np.arange(120) % 4 >= 2
+    assert (upper["el"][uncovered] == 0).all() and (canonical["el"][uncovered] == 0).all()
+    assert (upper["el"] > canonical["el"]).any()
+    assert (oracle.run(fq, fq, fa, coder, 0.5, 0.3, threads=2) == canonical).all()      # the knob is back at "no hit"
