@@ -980,11 +980,11 @@ class CpuArm:
                        + ("unmodified reference binary oracle/_ref/eref_ref" if kind == "reference" else "oracle port oracle/eref_oracle"))
         self.stdout = None
 
-    def run_once(self, threads=None, fq2="r2.fq"):
+    def run_once(self, threads=None, fq2="r2.fq", timeout=None):
         env = dict(os.environ, EREF_CODER_SEED="1", EREF_ORACLE_WRITE_INDEX="1")
         t0 = time.perf_counter()
         r = subprocess.run([self.bin, "r1.fq", fq2, "db.fa", "tmp.txt", "0.9", "0.85", str(threads or self.cores)],
-                           cwd=self.dir, capture_output=True, env=env)
+                           cwd=self.dir, capture_output=True, env=env, timeout=timeout)
         dt = time.perf_counter() - t0
         if r.returncode != 0:
             raise RuntimeError(f"{self.bin} failed: {r.stderr.decode()[-400:]}")
@@ -1082,69 +1082,73 @@ def exe_multi_gpu(world):
 
 
 def run_reference(args):
-    """The reference's own CPU implementation of the path on the host cores, all threads, on the headline workload when
-    the whole run fits the time budget (EREF_REF_BUDGET_S, default 1000 s, estimated; EREF_REF_HARD_S, default 1500 s,
-    projected from the first real process), else on BASELINE configs[0]; config.workload
-    and `sample` name what actually ran.  The binary is the UNMODIFIED reference whenever it exists; each step is one
-    whole eref process with the index already on disk (the index build is untimed setup, reported as cold_s)."""
+    """The reference's own CPU implementation of the path on the host cores, all threads: the UNMODIFIED reference binary
+    whenever it exists, each step one whole eref process with the index already on disk (the index build is untimed
+    setup, reported as cold_s).  It runs the headline workload when the whole arm can end within EREF_REF_LIMIT_S
+    (default 780 s: the driver cuts a command of its scaling run at 870 s), else BASELINE configs[0]; config.workload,
+    `sample` and `chosen_because` name what actually ran and why.  configs[0] runs first (with its index on disk it is the
+    fallback, and its time per process says how much the fallback needs); then the headline workload is tried: its index
+    build is abandoned if going on would leave the fallback no time, and after its first warm process the whole arm is
+    projected once more."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     t_begin = time.perf_counter()
-    budget = float(os.environ.get("EREF_REF_BUDGET_S", "1000"))
+    limit = float(os.environ.get("EREF_REF_LIMIT_S", "780"))
     forced = os.environ.get("EREF_BENCH_CPU_SAMPLE")          # the CPU test-suite: "small"
     kind = os.environ.get("EREF_BENCH_CPU_KIND") or None      # ... and "port"
     runs = args.steps + args.warmup
-    plan, why = None, ""
-    if forced:
-        plan, why = forced, f"EREF_BENCH_CPU_SAMPLE={forced}"
-    else:
-        want = args.workload if args.workload in ("c2", "c1", "small", "c5") else "c2"
-        plan, why = want, "the headline workload"
-        if want in ("c2", "c5"):
-            # what would a run on the headline workload cost?  fixed cost per process (tables zeroed) from a tiny input,
-            # variable cost scaled x10 from the configs[0]-sized sample
-            if (kind or ("reference" if have_reference() else "port")) == "reference" and \
-                    (_disk_free_gb(tempfile.gettempdir()) < 12 or _host_mem_gb() < 40):
-                plan, why = "c1", "the headline workload needs 12 GB of scratch disk and 40 GB of RAM for the reference"
-            else:
-                probe = CpuArm("c1", kind)
-                try:
-                    c1_cold = probe.run_once()
-                    c1_warm = probe.run_once()
-                finally:
-                    probe.close()
-                tiny = CpuArm("small", kind)
-                try:
-                    tiny.run_once()
-                    fixed = tiny.run_once() * 0.9
-                finally:
-                    tiny.close()
-                est_warm = fixed + 10 * max(c1_warm - fixed, 0.05)
-                est_cold = fixed + 10 * max(c1_cold - fixed, 0.05)
-                spent = time.perf_counter() - t_begin
-                est = spent + 30 + est_cold + runs * est_warm
-                why = (f"estimated {est:.0f} s for {runs} runs on the headline workload (fixed {fixed:.1f} s + 10 x the "
-                       f"configs[0] variable cost) against a budget of {budget:.0f} s")
-                if est > budget:
-                    plan = "c1"
-    # the estimate above extrapolates from a tenth of the headline size: once the headline workload has REALLY run
-    # (index build + one warm process) project the whole run again, and fall back to configs[0] rather than let the
-    # driver's per-command limit (1800 s) cut the arm short and leave no reference line at all
-    hard = float(os.environ.get("EREF_REF_HARD_S", "1500"))
-    arm = CpuArm(plan, kind)
+    elapsed = lambda: time.perf_counter() - t_begin
+    arm, cold, why = None, None, ""
+    want = args.workload if args.workload in ("c2", "c1", "small", "c5") else "c2"
     try:
-        cold = arm.run_once()                          # index build, untimed setup
-        first = arm.run_once()                         # first warm-up run (an extra untimed one when --warmup 0)
-        projected = time.perf_counter() - t_begin + (runs - 1) * first
-        if plan in ("c2", "c5") and not forced and projected > hard:
-            arm.close()
-            why += (f"; measured {first:.1f} s per process on the headline workload -> {projected:.0f} s for the run, over "
-                    f"the hard limit of {hard:.0f} s")
-            plan = "c1"
-            arm = CpuArm(plan, kind)
+        if forced:
+            arm, why = CpuArm(forced, kind), f"EREF_BENCH_CPU_SAMPLE={forced}"
+            cold = arm.run_once()                          # index build, untimed setup
+            arm.run_once()                                 # first warm-up run (an extra untimed one when --warmup 0)
+        elif want in ("c1", "small"):
+            arm, why = CpuArm(want, kind), "asked for (--workload)"
             cold = arm.run_once()
             arm.run_once()
+        else:
+            # configs[0] first: its times give the estimate, and with its index on disk it is the fallback
+            fallback = CpuArm("c1", kind)
+            arm = fallback
+            c1_cold = fallback.run_once()
+            c1_warm = fallback.run_once()
+            cold = c1_cold
+            reserve = (runs - 1) * c1_warm * 1.1 + 15      # what the fallback still needs from any later moment
+            if (kind or ("reference" if have_reference() else "port")) == "reference" and \
+                    (_disk_free_gb(tempfile.gettempdir()) < 12 or _host_mem_gb() < 40):
+                why = "the headline workload needs 12 GB of scratch disk and 40 GB of RAM for the reference"
+            else:
+                head = None
+                try:
+                    head = CpuArm(want, kind)
+                    allow = limit - elapsed() - reserve
+                    if allow < 30:
+                        raise subprocess.TimeoutExpired("eref", allow)
+                    head_cold = head.run_once(timeout=allow)                 # index build, untimed setup
+                    first = head.run_once(timeout=max(limit - elapsed() - reserve, 1))
+                    projected = elapsed() + (runs - 1) * first
+                    if projected > limit:
+                        why = (f"headline workload: index built in {head_cold:.0f} s, {first:.1f} s per process -> {projected:.0f} s "
+                               f"for the whole arm, over the limit of {limit:.0f} s; configs[0] instead")
+                        head.close()
+                    else:
+                        why = (f"the headline workload: index built in {head_cold:.0f} s, {first:.1f} s per process -> {projected:.0f} s "
+                               f"for the whole arm, within the limit of {limit:.0f} s")
+                        arm, cold = head, head_cold
+                        fallback.close()
+                except subprocess.TimeoutExpired:
+                    why = (f"headline workload: its setup (index build + first process) was abandoned {elapsed():.0f} s into the "
+                           f"arm — going on would have left less than the {reserve:.0f} s the configs[0] fallback needs within "
+                           f"the limit of {limit:.0f} s; configs[0] instead")
+                    head.close()
+                except Exception as e:                      # (no scratch space, a reference crash ...): the fallback stands
+                    why = f"headline workload failed ({str(e)[-200:]}); configs[0] instead"
+                    if head is not None:
+                        head.close()
         for _ in range(args.warmup - 1):
             arm.run_once()
         t0 = time.perf_counter()
@@ -1157,17 +1161,19 @@ def run_reference(args):
             "impl": "reference", "metric": METRIC, "value": round(value, 6), "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 2), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": config_for(WORKLOAD_DESC[plan], args.gpus),
+            "config": config_for(WORKLOAD_DESC[arm.sample_name], args.gpus),
             "cpu_baseline": {"value": round(value, 6), "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
                              "sample": arm.sample + "; each step = one whole eref process, index already on disk",
                              "sample_db_bases": arm.bases, "cold_s": round(cold, 2), "chosen_because": why,
+                             "arm_wall_s": round(elapsed(), 1),
                              "selected_refs": arm.stdout.count(b"\n") if arm.stdout is not None else None},
             "e2e": {"value": round(value, 6), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
         }
         _emit(json.dumps(out))
     finally:
-        arm.close()
+        if arm is not None:
+            arm.close()
 
 
 def main():
