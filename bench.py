@@ -801,6 +801,7 @@ def sub_record(rig, job, steps, warmup, parity_records, with_e2e=True, with_unpr
 
 
 def run_b200(args):
+    t_begin = time.perf_counter()
     rig = Rig(args)
     rank, world = rig.rank, rig.world
     peak, _ = peaks()
@@ -921,6 +922,7 @@ def run_b200(args):
         out["cpu_baseline"] = cpu_baseline(budget_runs=1)
     if world > 1 and not args.no_exe_check:
         out["exe_multi_gpu"] = exe_multi_gpu(world)
+    out["bench_wall_s"] = round(time.perf_counter() - t_begin, 1)     # everything this command did, setup and checks included
     _emit(json.dumps(out))
     rig.close()
 
