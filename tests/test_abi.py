@@ -81,3 +81,13 @@ def test_product_does_not_reach_into_the_oracle():
                     if re.search(r"oracle/|eref_oracle|liberef_oracle|eo_[a-z]+\(", txt):
                         bad.append(os.path.join(dp, fn))
     assert not bad, bad
+
+
+def test_library_exports_nothing_the_header_does_not_declare():
+    """the other direction: every eref_* symbol liberef_gpu.so exports is declared (and documented) in include/eref_gpu.h"""
+    assert os.path.exists(eref.LIB_PATH)
+    r = subprocess.run(["nm", "-D", "--defined-only", eref.LIB_PATH], capture_output=True, text=True)
+    if r.returncode != 0:
+        pytest.skip("nm is not available")
+    exported = {ln.split()[-1] for ln in r.stdout.splitlines() if ln.split() and ln.split()[-1].startswith("eref_")}
+    assert exported == set(_header_symbols())
