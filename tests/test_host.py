@@ -250,3 +250,50 @@ def test_fastq_limit_is_the_references_getline_budget(oracle):
     for end in (f2.size - 100, f2.size - 3000, f2.size - 20_000, f2.size // 2, 70_000, f1.size):
         assert eref.fastq_limit(f2, end) == oracle.fastq_limit(f2, end), end
     assert eref.fastq_limit(f2, f2.size - 20_000) < f2.size and eref.fastq_limit(f2, f2.size - 100) == f2.size
+
+
+def test_candidate_filter_bound_holds_for_every_stride():
+    """DESIGN.md §4.2 as arithmetic, without a GPU: a window is good only if >= three_min of its positions are hit by all
+    three streams (:556-561), hence by stream 0; sampling stream 0 at the plane positions that are multiples of s leaves at
+    most 500 - floor(500/s) positions of any window unsampled, so a window with fewer than three_min - (500 - 500 // s)
+    sampled hits cannot be good.  cand[w] sums the sampled hits of words w-16..w of the record, need[w] = a candidate in
+    w..w+16: every position of every good window must lie in a needed word, whatever the record's offset in the planes."""
+    rng = np.random.default_rng(42)
+    checked = good_total = 0
+    for trial in range(60):
+        length = int(rng.integers(40, 6000))
+        p0 = int(rng.integers(0, 64)) + 32 * int(rng.integers(0, 3))         # the record's first plane position
+        phr = float(rng.choice([0.85, 0.6, 0.97, 0.3]))
+        hr = float(rng.choice([0.9, 0.5, 0.99]))
+        one_min, three_min = int(np.float32(500) * np.float32(hr)), int(np.float32(500) * np.float32(phr))
+        # hit patterns with long dense stretches (so that good windows exist) and noisy borders
+        dense = np.zeros(length, bool)
+        for _ in range(int(rng.integers(0, 4))):
+            a = int(rng.integers(0, length)); dense[a: a + int(rng.integers(100, 2500))] = True
+        h = [(rng.random(length) < np.where(dense, rng.uniform(0.8, 1.0), rng.uniform(0.0, 0.3))) for _ in range(3)]
+        for hi in h:
+            hi[max(length - 31, 0):] = False                                   # no 32-mer starts in the last 31 positions
+        trio, single = h[0] & h[1] & h[2], h[0] | h[1] | h[2]
+        ct, cs = np.concatenate([[0], np.cumsum(trio)]), np.concatenate([[0], np.cumsum(single)])
+        j = np.arange(length)
+        lo = np.maximum(j - 499, 0)
+        good = (cs[j + 1] - cs[lo] >= one_min) & (ct[j + 1] - ct[lo] >= three_min)    # :548-561
+        good_total += int(good.sum())
+        pos = p0 + j                                                           # plane positions, word = pos >> 5
+        w0, w1 = p0 >> 5, (p0 + length - 1) >> 5
+        for s in range(4, 9):
+            min_hits = three_min - (500 - 500 // s)
+            if min_hits <= 0:
+                continue                                                       # the filter is vacuous: everything is probed
+            sampled_hit = h[0] & (pos % s == 0)
+            per_word = np.bincount((pos >> 5) - w0, weights=sampled_hit, minlength=w1 - w0 + 1)
+            cw = np.concatenate([[0], np.cumsum(per_word)])
+            w = np.arange(w1 - w0 + 1)
+            cand = cw[w + 1] - cw[np.maximum(w - 16, 0)] >= min_hits
+            cc = np.concatenate([[0], np.cumsum(cand)])
+            need = cc[np.minimum(w + 17, w.size)] - cc[w] > 0
+            for jj in np.flatnonzero(good):
+                words = np.arange((p0 + lo[jj]) >> 5, ((p0 + jj) >> 5) + 1) - w0
+                assert need[words].all(), (trial, s, int(jj))
+            checked += 1
+    assert checked > 100 and good_total > 1000
