@@ -297,3 +297,35 @@ def test_candidate_filter_bound_holds_for_every_stride():
                 assert need[words].all(), (trial, s, int(jj))
             checked += 1
     assert checked > 100 and good_total > 1000
+    # the worst case for the bound: ONE window that is just good, its three_min trio hits placed on the unsampled
+    # positions first, nothing else in the record; every word under the window must still be needed
+    tight = 0
+    for trial in range(200):
+        length = int(rng.integers(600, 3000))
+        p0 = int(rng.integers(0, 96))
+        phr = float(rng.choice([0.85, 0.6, 0.97]))
+        three_min = int(np.float32(500) * np.float32(phr))
+        jj = int(rng.integers(499, length - 31))
+        window = np.arange(jj - 499, jj + 1)
+        for s in range(4, 9):
+            min_hits = three_min - (500 - 500 // s)
+            if min_hits <= 0:
+                continue
+            on_sample = (p0 + window) % s == 0
+            order = np.concatenate([rng.permutation(window[~on_sample]), rng.permutation(window[on_sample])])
+            h0 = np.zeros(length, bool)
+            h0[order[:three_min]] = True                                      # stream 0 = the trio hits, and nothing more
+            assert int(h0[window].sum()) == three_min                         # the window is good, by exactly one hit
+            pos = p0 + np.arange(length)
+            w0, w1 = p0 >> 5, (p0 + length - 1) >> 5
+            per_word = np.bincount((pos >> 5) - w0, weights=h0 & (pos % s == 0), minlength=w1 - w0 + 1)
+            cw = np.concatenate([[0], np.cumsum(per_word)])
+            w = np.arange(w1 - w0 + 1)
+            cand = cw[w + 1] - cw[np.maximum(w - 16, 0)] >= min_hits
+            cc = np.concatenate([[0], np.cumsum(cand)])
+            need = cc[np.minimum(w + 17, w.size)] - cc[w] > 0
+            words = np.arange((p0 + jj - 499) >> 5, ((p0 + jj) >> 5) + 1) - w0
+            assert need[words].all(), (trial, s, jj)
+            assert min_hits <= int(per_word[words].sum()) <= min_hits + 1      # (the bound is tight: nothing to spare)
+            tight += 1
+    assert tight > 500
